@@ -1,0 +1,177 @@
+/* somar_b200.h -- C ABI of libsomar_b200.so: SOMAR's mapped-Poisson multigrid hot path on B200 (sm_100a).
+ *
+ * The reference (UNC-CFD/somar) has no FFI for this path; its boundary is the C++ virtual-class contract
+ *   LinearOp<T> -> MappedMGLevelOp<T> -> MappedAMRLevelOp<T> -> MappedAMRPoissonOp        (T = LevelData<FArrayBox>)
+ * plus the Chombo-Fortran kernel calling convention (double* + lo/hi + ncomp, x fastest, ghosts inside the box;
+ * SURVEY.md 8(b)).  Every entry point below names the reference interface it replaces (paths relative to the
+ * reference tree).  A maintainer binds these from the adapter classes in include/somar_b200/ (C++ headers).
+ *
+ * Conventions
+ *   - All functions return SOMAR_OK (0) or a negative error code; somar_last_error() gives the text.
+ *     (The reference aborts through MayDay::Error; a C ABI cannot, so the adapter turns codes into MayDay calls.)
+ *   - One caller thread per level; work is stream-ordered on the level's CUDA stream.  Functions that return a
+ *     scalar to the host (norm, dot, solve) synchronise that stream.
+ *   - Fields are opaque device-resident objects created per multigrid depth.  Host data crosses the boundary in the
+ *     CHF_FRA convention: `const double* fab, lo[3], hi[3]` = a Fortran-ordered array over the box [lo,hi]
+ *     (ghost cells included), absolute (global) cell indices.  2-D problems use n[2] == 1.
+ *   - There is no CPU fallback: every call fails with SOMAR_ERR_CUDA when no sm_100 device is usable.
+ */
+#ifndef SOMAR_B200_H
+#define SOMAR_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SOMAR_OK 0
+#define SOMAR_ERR_ARG (-1)
+#define SOMAR_ERR_CUDA (-2)
+#define SOMAR_ERR_LAYOUT (-3)
+#define SOMAR_ERR_COMM (-4)
+#define SOMAR_ERR_DIVERGED (-5) /* residual grew 10x: MappedAMRMultiGrid.H:1134-1145 "kaboom" */
+
+/* BCType codes: src/calculus/BCInterface/BCDescriptor.H:33-38 */
+#define SOMAR_BC_NONE (-1)
+#define SOMAR_BC_NEUM 0
+#define SOMAR_BC_DIRI 1
+#define SOMAR_BC_PERIODIC 2
+
+/* AMRMG.relax_mode: src/utils/ProblemContext.H:324-338 */
+#define SOMAR_RELAX_NONE (-1)
+#define SOMAR_RELAX_JACOBI 0
+#define SOMAR_RELAX_LEVEL_GSRB 1
+#define SOMAR_RELAX_LOOSE_GSRB 2
+#define SOMAR_RELAX_LINE_GSRB 3
+
+typedef struct SomarLevel SomarLevel; /* one AMR level: all multigrid depths, metrics, scratch, halo plans */
+typedef struct SomarField SomarField; /* one cell-centred scalar field (1 component) at one depth           */
+
+/* What MappedAMRPoissonOpFactory::define + MGnewOp receive
+ * (src/calculus/AMRElliptic/MappedAMRPoissonOpFactory.cpp:60-200,362-702) flattened into plain C. */
+typedef struct SomarLevelDesc {
+    int dim;           /* 2 or 3 (CH_SPACEDIM) */
+    int n[3];          /* domain cells; domain box is [0, n-1] */
+    int periodic[3];   /* ProblemDomain::isPeriodic */
+    int nboxes;        /* DisjointBoxLayout of this level: ALL boxes of the level (they fix the MG schedule) */
+    const int* box_lo; /* nboxes x 3 */
+    const int* box_hi; /* nboxes x 3, inclusive */
+    const int* box_rank; /* nboxes owner ranks, or NULL = all on rank 0.  The boxes a rank owns must tile one
+                            rectangular region that spans the whole domain in x and z (columns stay whole:
+                            GSRB.H:90, ProblemContext.cpp:249-255). */
+    double dx[3];      /* computational cell size (LevelGeometry::getDx) */
+    double alpha, beta;/* (alpha I + beta L): MappedAMRPoissonOp::setAlphaAndBeta */
+    int is_diagonal;   /* LevelGeometry::isDiagonal(): J g^{ij} = 0 for i != j */
+    int bc_type[6];    /* [dir*2+side]: BCMethodHolder / BCDescriptor codes for non-periodic sides */
+    double bc_value[6];/* constant Neumann flux / Dirichlet value (EllipticConstNeumBC*, EllipticConstDiriBC*) */
+    int rank, nranks;  /* this process and the job size (1 = single GPU) */
+} SomarLevelDesc;
+
+/* AMRMG.* and bottom.* parameters: src/utils/ProblemContext.cpp:1147-1216, AMRPressureSolver.cpp:46-81 */
+typedef struct SomarSolverParams {
+    double eps;
+    int num_smooth_down, num_smooth_up, num_smooth_bottom, num_smooth_precond;
+    int numMG, imin, imax;
+    double hang, normThresh;
+    int maxDepth, relaxMode, precondMode;
+    double bottom_eps, bottom_reps, bottom_hang, bottom_small;
+    int bottom_imax, bottom_numRestarts, bottom_normType;
+    int verbosity;
+} SomarSolverParams;
+
+/* MappedAMRMultiGrid<T>::m_exitStatus, m_iterations and the per-iteration residual trace
+ * (MappedAMRMultiGrid.H:1050-1055,1105-1117,1148). */
+typedef struct SomarSolveStats {
+    int iters, exitStatus;
+    double initial_rnorm, final_rnorm;
+    int bottom_iters_total;
+    int history_len;
+    double history[128];
+    double solve_ms;       /* device time of the solve (CUDA events on the level stream) */
+    long long launches;    /* kernels of this library launched during the solve */
+} SomarSolveStats;
+
+/* ---- library ------------------------------------------------------------------------------------------- */
+const char* somar_last_error(void);
+const char* somar_version(void);
+int somar_default_params(SomarSolverParams* p);       /* ProblemContext.cpp:1147-1216 defaults */
+int somar_device_count(int* count);
+
+/* ---- communicator (replaces Chombo_MPI::comm for LevelData::exchange and the scalar MPI_Allreduce calls) --
+ * 128-byte NCCL unique id made on rank 0 and sent to the other ranks by the caller (MPI_Bcast / torch.distributed). */
+int somar_comm_unique_id(unsigned char id[128]);
+
+/* ---- level ---------------------------------------------------------------------------------------------
+ * somar_level_create replaces MappedAMRPoissonOpFactory::define + MappedMultiGrid::define
+ * (MappedAMRPoissonOpFactory.cpp:60-200; MappedMultiGrid.H:328-404): builds every multigrid depth
+ * (semicoarsening schedule, Factory.cpp:466-553), allocates device metrics and scratch.  `device` is the CUDA
+ * ordinal; `comm_id` is NULL when nranks == 1.  Metrics are supplied afterwards with somar_level_set_metric_fab
+ * and frozen by somar_level_finalize, which builds the coarse metrics (fill_MGfields, Factory.cpp:1069-1236),
+ * lapDiag (FILLMAPPEDLAPDIAG*, MappedAMRPoissonOpF.ChF:91-274) and runs the null-space probe (:659-693). */
+int somar_level_create(const SomarLevelDesc* desc, const SomarSolverParams* params, int device,
+                       const unsigned char* comm_id, SomarLevel** out);
+int somar_level_destroy(SomarLevel* lev);
+/* Host metric FABs of one box: jgup[d] is the FluxBox component d (face-centred in d, `jgup_ncomp` comps outermost,
+ * comp c = J g^{dc}; ncomp==1 means only J g^{dd}), box [lo,hi] with hi[d]+1 faces in d; jinv is cell-centred.
+ * Replaces LevelGeometry::getFCJgup()/getCCJinv() reads (LevelGeometry.H:130-286). Either pointer set may be NULL. */
+int somar_level_set_metric_fab(SomarLevel* lev, const int lo[3], const int hi[3], int jgup_ncomp,
+                               const double* jgup0, const double* jgup1, const double* jgup2, const double* jinv);
+/* Same, from DEVICE arrays covering the rank-local region without ghosts (x fastest), for device-resident callers. */
+int somar_level_set_metric_device(SomarLevel* lev, int jgup_ncomp, const double* d_jgup0, const double* d_jgup1,
+                                  const double* d_jgup2, const double* d_jinv);
+int somar_level_finalize(SomarLevel* lev);
+int somar_level_set_alpha_beta(SomarLevel* lev, double alpha, double beta); /* MappedAMRPoissonOp::setAlphaAndBeta */
+int somar_level_num_depths(const SomarLevel* lev, int* ndepths);
+/* n = domain cells at that depth, ratio = mgCrseRefRatio to the next coarser depth, local_lo/hi = this rank's region */
+int somar_level_depth_info(const SomarLevel* lev, int depth, int n[3], int ratio[3], double dx[3], int* zero_avg,
+                           int local_lo[3], int local_hi[3]);
+int somar_level_sync(SomarLevel* lev);                 /* cudaStreamSynchronize on the level stream */
+int somar_level_stream(SomarLevel* lev, void** cuda_stream);
+int somar_level_launch_count(const SomarLevel* lev, long long* launches);
+/* Reads back a depth's metric into rank-local arrays without ghosts (tests): comp-outermost for jg. */
+int somar_level_get_metric(SomarLevel* lev, int depth, double* jg0, double* jg1, double* jg2, double* jinv,
+                           double* lapdiag);
+
+/* ---- fields: LinearOp<T>::create / clear (MappedAMRPoissonOp.H:566-575) ---------------------------------- */
+int somar_field_create(SomarLevel* lev, int depth, SomarField** out);
+int somar_field_destroy(SomarField* f);
+/* host FAB [lo,hi] (ghosts included) -> device, only cells inside `valid` (the DisjointBoxLayout box) are taken */
+int somar_field_set_fab(SomarField* f, const double* fab, const int lo[3], const int hi[3], const int vlo[3],
+                        const int vhi[3]);
+int somar_field_get_fab(const SomarField* f, double* fab, const int lo[3], const int hi[3], const int vlo[3],
+                        const int vhi[3]);
+/* rank-local region, no ghosts, x fastest; `on_device` != 0 means the pointer is a device pointer */
+int somar_field_set(SomarField* f, const double* data, int on_device);
+int somar_field_get(const SomarField* f, double* data, int on_device);
+
+/* ---- LinearOp<T> (MappedAMRPoissonOp.H:187-266, .cpp:628-898) -------------------------------------------- */
+int somar_apply_op(SomarLevel* lev, int depth, SomarField* lhs, SomarField* phi, int homogeneous);   /* applyOpI :772 */
+int somar_residual(SomarLevel* lev, int depth, SomarField* res, SomarField* phi, const SomarField* rhs,
+                   int homogeneous);                                                                /* residualI :646 */
+int somar_precond(SomarLevel* lev, int depth, SomarField* cor, const SomarField* res);              /* preCond :684 */
+int somar_set_to_zero(SomarLevel* lev, SomarField* x);
+int somar_assign(SomarLevel* lev, SomarField* y, const SomarField* x);
+int somar_incr(SomarLevel* lev, SomarField* y, const SomarField* x, double scale);
+int somar_axby(SomarLevel* lev, SomarField* lhs, const SomarField* x, const SomarField* y, double a, double b);
+int somar_scale(SomarLevel* lev, SomarField* x, double scale);
+int somar_norm(SomarLevel* lev, const SomarField* x, int ord, double* out);       /* CH_XD::norm, all ranks */
+int somar_local_max_norm(SomarLevel* lev, const SomarField* x, double* out);      /* localMaxNorm */
+int somar_dot(SomarLevel* lev, const SomarField* a, const SomarField* b, double* out);
+
+/* ---- MappedMGLevelOp<T> (MappedMultiGrid.H:43-114) -------------------------------------------------------- */
+int somar_relax(SomarLevel* lev, int depth, SomarField* phi, const SomarField* rhs, int iters);     /* relax :1733 */
+int somar_restrict_residual(SomarLevel* lev, int depth, SomarField* res_coarse, SomarField* phi_fine,
+                            const SomarField* rhs_fine);                                  /* restrictResidual :1281 */
+int somar_prolong_increment(SomarLevel* lev, int depth, SomarField* phi_fine, const SomarField* cor_coarse);
+
+/* ---- drivers --------------------------------------------------------------------------------------------
+ * somar_mg_cycle: MappedMultiGrid<T>::cycle (MappedMultiGrid.H:555-653) from `depth` down.
+ * somar_solve: AMRPressureSolver::solve -> MappedAMRMultiGrid<T>::solveNoInitResid, single level
+ * (AMRPressureSolver.cpp:494-560; MappedAMRMultiGrid.H:979-1186). */
+int somar_mg_cycle(SomarLevel* lev, int depth, SomarField* e, const SomarField* r);
+int somar_solve(SomarLevel* lev, SomarField* phi, const SomarField* rhs, int zero_phi, int force_homogeneous,
+                SomarSolveStats* stats);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SOMAR_B200_H */

@@ -1,0 +1,99 @@
+// capi_ops.cu -- extern "C" operator / driver entry points (LinearOp, MappedMGLevelOp, solver).
+#include "level.hpp"
+#include <cmath>
+
+using namespace somar;
+
+#define CHECK_FINAL(L) do { if (!(L)) { set_error("null level"); return SOMAR_ERR_ARG; } \
+                            if (!(L)->finalized) { set_error("level not finalized (call somar_level_finalize)"); return SOMAR_ERR_ARG; } \
+                            cudaSetDevice((L)->device); } while (0)
+#define CHECK_F(f, L, dpt) do { if (!(f) || (f)->lev != (L) || (f)->depth != (dpt)) { set_error("field does not belong to this level/depth"); return SOMAR_ERR_ARG; } } while (0)
+
+extern "C" {
+
+int somar_apply_op(SomarLevel* L, int depth, SomarField* lhs, SomarField* phi, int homogeneous) {
+    CHECK_FINAL(L); CHECK_F(lhs, L, depth); CHECK_F(phi, L, depth);
+    return op_apply(L, depth, lhs->p, phi, nullptr, 0, homogeneous != 0);
+}
+int somar_residual(SomarLevel* L, int depth, SomarField* res, SomarField* phi, const SomarField* rhs, int homogeneous) {
+    CHECK_FINAL(L); CHECK_F(res, L, depth); CHECK_F(phi, L, depth); CHECK_F(rhs, L, depth);
+    if (res == rhs) { set_error("residual: lhs must not alias rhs"); return SOMAR_ERR_ARG; }
+    return op_apply(L, depth, res->p, phi, rhs->p, 1, homogeneous != 0);
+}
+int somar_precond(SomarLevel* L, int depth, SomarField* cor, const SomarField* res) {
+    CHECK_FINAL(L); CHECK_F(cor, L, depth); CHECK_F(res, L, depth);
+    return op_precond(L, depth, cor, res);
+}
+int somar_set_to_zero(SomarLevel* L, SomarField* x) {
+    CHECK_FINAL(L); CHECK_F(x, L, x ? x->depth : 0);
+    launch_fill(L->cx, L->depths[x->depth].g, x->p, 0.0);
+    return SOMAR_OK;
+}
+int somar_assign(SomarLevel* L, SomarField* y, const SomarField* x) {
+    CHECK_FINAL(L); CHECK_F(x, L, x ? x->depth : 0); CHECK_F(y, L, x->depth);
+    launch_copy(L->cx, L->depths[x->depth].g, y->p, x->p);
+    return SOMAR_OK;
+}
+int somar_incr(SomarLevel* L, SomarField* y, const SomarField* x, double scale) {
+    CHECK_FINAL(L); CHECK_F(x, L, x ? x->depth : 0); CHECK_F(y, L, x->depth);
+    launch_axpy(L->cx, L->depths[x->depth].g, y->p, x->p, scale);
+    return SOMAR_OK;
+}
+int somar_axby(SomarLevel* L, SomarField* lhs, const SomarField* x, const SomarField* y, double a, double b) {
+    CHECK_FINAL(L); CHECK_F(x, L, x ? x->depth : 0); CHECK_F(y, L, x->depth); CHECK_F(lhs, L, x->depth);
+    launch_axby(L->cx, L->depths[x->depth].g, lhs->p, x->p, y->p, a, b);
+    return SOMAR_OK;
+}
+int somar_scale(SomarLevel* L, SomarField* x, double scale) {
+    CHECK_FINAL(L); CHECK_F(x, L, x ? x->depth : 0);
+    launch_scale(L->cx, L->depths[x->depth].g, x->p, scale);
+    return SOMAR_OK;
+}
+// CH_XD::norm semantics (MappedAMRPoissonOp.H:698-702): ord 0 = max |x|, 1 = sum |x|, 2 = sqrt(sum x^2)
+int somar_norm(SomarLevel* L, const SomarField* x, int ord, double* out) {
+    CHECK_FINAL(L); CHECK_F(x, L, x ? x->depth : 0);
+    if (!out || ord < 0 || ord > 2) { set_error("norm: bad argument"); return SOMAR_ERR_ARG; }
+    int rc = reduce_global(L, x->depth, x->p, nullptr, ord, out);
+    if (rc) return rc;
+    if (ord == 2) *out = std::sqrt(*out);
+    return SOMAR_OK;
+}
+int somar_local_max_norm(SomarLevel* L, const SomarField* x, double* out) {
+    CHECK_FINAL(L); CHECK_F(x, L, x ? x->depth : 0);
+    launch_reduce(L->cx, L->depths[x->depth].g, x->p, nullptr, 0, L->d_scal);
+    SOMAR_CUDA(cudaMemcpyAsync(L->h_scal, L->d_scal, sizeof(double), cudaMemcpyDeviceToHost, L->cx.stream));
+    SOMAR_CUDA(cudaStreamSynchronize(L->cx.stream));
+    *out = L->h_scal[0];
+    return SOMAR_OK;
+}
+int somar_dot(SomarLevel* L, const SomarField* a, const SomarField* b, double* out) {
+    CHECK_FINAL(L); CHECK_F(a, L, a ? a->depth : 0); CHECK_F(b, L, a->depth);
+    return reduce_global(L, a->depth, a->p, b->p, 3, out);
+}
+
+int somar_relax(SomarLevel* L, int depth, SomarField* phi, const SomarField* rhs, int iters) {
+    CHECK_FINAL(L); CHECK_F(phi, L, depth); CHECK_F(rhs, L, depth);
+    return op_relax(L, depth, phi, rhs, iters);
+}
+int somar_restrict_residual(SomarLevel* L, int depth, SomarField* res_coarse, SomarField* phi_fine,
+                            const SomarField* rhs_fine) {
+    CHECK_FINAL(L); CHECK_F(res_coarse, L, depth + 1); CHECK_F(phi_fine, L, depth); CHECK_F(rhs_fine, L, depth);
+    return op_restrict(L, depth, res_coarse, phi_fine, rhs_fine);
+}
+int somar_prolong_increment(SomarLevel* L, int depth, SomarField* phi_fine, const SomarField* cor_coarse) {
+    CHECK_FINAL(L); CHECK_F(phi_fine, L, depth); CHECK_F(cor_coarse, L, depth + 1);
+    return op_prolong(L, depth, phi_fine, cor_coarse);
+}
+
+int somar_mg_cycle(SomarLevel* L, int depth, SomarField* e, const SomarField* r) {
+    CHECK_FINAL(L); CHECK_F(e, L, depth); CHECK_F(r, L, depth);
+    return mg_cycle(L, depth, e, r);
+}
+int somar_solve(SomarLevel* L, SomarField* phi, const SomarField* rhs, int zero_phi, int force_homogeneous,
+                SomarSolveStats* stats) {
+    CHECK_FINAL(L); CHECK_F(phi, L, 0); CHECK_F(rhs, L, 0);
+    if (!stats) { set_error("null stats"); return SOMAR_ERR_ARG; }
+    return mg_solve(L, phi, rhs, zero_phi != 0, force_homogeneous != 0, stats);
+}
+
+}  // extern "C"

@@ -1,0 +1,108 @@
+// level.hpp -- host-side objects behind the C ABI: one AMR level with all its multigrid depths resident in HBM.
+// Mirrors, in role only, MappedAMRPoissonOp (one per depth) + MappedMultiGrid (depth stack, scratch) +
+// MappedAMRMultiGrid (outer iteration) of the reference; see each member function for file:line.
+#pragma once
+#include "../../include/somar_b200.h"
+#include "kernels.hpp"
+#include <nccl.h>
+#include <string>
+#include <vector>
+
+struct SomarField {
+    SomarLevel* lev;
+    int depth;
+    double* p;       // brick of lev->depths[depth].g.total doubles
+};
+
+namespace somar {
+
+struct Depth {
+    Geom g;
+    Metric m;
+    int ratio[3] = {1, 1, 1};          // mgCrseRefRatio to the next coarser depth
+    int coarsening[3] = {1, 1, 1};     // total coarsening from depth 0
+    double* jg[3][3] = {{nullptr}};
+    double* jinv = nullptr;
+    double* lapdiag = nullptr;
+    double* line_fact = nullptr;       // lazily built by line relaxation
+    double* line_dmod = nullptr;
+    bool line_valid = false;
+    double* tmp = nullptr;             // ping-pong partner for out-of-place passes / Jacobi residual
+    bool zeroAvg = false;
+    double dxProduct = 1.0;
+    SomarField* res = nullptr;         // MappedMultiGrid::m_residual[depth], m_correction[depth]
+    SomarField* cor = nullptr;
+    double* sendbuf[2] = {nullptr, nullptr};
+    double* recvbuf[2] = {nullptr, nullptr};
+};
+
+}  // namespace somar
+
+struct SomarLevel {
+    SomarLevelDesc desc;
+    std::vector<int> box_lo, box_hi, box_rank;
+    SomarSolverParams prm;
+    int device = 0;
+    somar::Ctx cx;
+    std::vector<somar::Depth> depths;
+    bool finalized = false;
+    bool metric_diag_only = true;
+    int local_lo[3], local_hi[3];      // this rank's region at depth 0 (global indices)
+    int box_size[3];                   // uniform tiling size at depth 0 (0 = not uniform)
+    // communication
+    ncclComm_t comm = nullptr;
+    // scalars
+    double* d_scal = nullptr;          // 8 doubles on device
+    double* h_scal = nullptr;          // pinned mirror
+    // staging for host FAB transfers
+    double* stage = nullptr;
+    size_t stage_bytes = 0;
+    // bottom solver work fields (bottom depth)
+    std::vector<SomarField*> bwork;
+    // outer-solve work fields (depth 0)
+    std::vector<SomarField*> swork;
+    double bottomMetric = 0.0, bottomEps = 1e-6;
+    int bottom_iters_total = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+
+    int ndepths() const { return (int)depths.size(); }
+};
+
+namespace somar {
+
+void set_error(const std::string& s);
+#define SOMAR_CUDA(call)                                                                                   \
+    do {                                                                                                    \
+        cudaError_t e_ = (call);                                                                            \
+        if (e_ != cudaSuccess) {                                                                            \
+            somar::set_error(std::string(#call) + ": " + cudaGetErrorString(e_));                           \
+            return SOMAR_ERR_CUDA;                                                                          \
+        }                                                                                                   \
+    } while (0)
+#define SOMAR_NCCL(call)                                                                                   \
+    do {                                                                                                    \
+        ncclResult_t e_ = (call);                                                                           \
+        if (e_ != ncclSuccess) {                                                                            \
+            somar::set_error(std::string(#call) + ": " + ncclGetErrorString(e_));                           \
+            return SOMAR_ERR_COMM;                                                                          \
+        }                                                                                                   \
+    } while (0)
+
+// level.cu
+int level_build(SomarLevel* L);                      // schedule + allocation
+int level_finalize(SomarLevel* L);                   // coarse metrics, lapDiag, null-space probe
+int field_alloc(SomarLevel* L, int depth, SomarField** out);
+int exchange(SomarLevel* L, int depth, double* x, int width);
+int op_apply(SomarLevel* L, int depth, double* out, SomarField* phi, const double* rhs, int mode, bool homog);
+int op_relax(SomarLevel* L, int depth, SomarField* phi, const SomarField* rhs, int iters, int modeOverride = -100);
+int op_precond(SomarLevel* L, int depth, SomarField* cor, const SomarField* res);
+int op_restrict(SomarLevel* L, int depth, SomarField* crse, SomarField* phi, const SomarField* rhs);
+int op_prolong(SomarLevel* L, int depth, SomarField* phi, const SomarField* crse);
+int reduce_global(SomarLevel* L, int depth, const double* x, const double* y, int kind, double* out);
+// solver.cu
+int mg_cycle(SomarLevel* L, int depth, SomarField* e, const SomarField* r);
+int bottom_solve(SomarLevel* L, SomarField* e, const SomarField* r, int* iters);
+int mg_solve(SomarLevel* L, SomarField* phi, const SomarField* rhs, bool zeroPhi, bool forceHomog,
+             SomarSolveStats* st);
+
+}  // namespace somar

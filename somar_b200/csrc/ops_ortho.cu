@@ -1,0 +1,199 @@
+// ops_ortho.cu -- diagonal-metric operator kernels: apply / residual, red-black point relaxation, Jacobi,
+// diagonal preconditioner, fused residual+restriction.  HBM-bound fp64 streaming kernels (DESIGN.md "Kernels").
+#include "kernels.hpp"
+#include "stencil_ortho.cuh"
+#include "stencil_full.cuh"
+
+namespace somar {
+
+#define BX 64
+#define BY 4
+
+// ---------------------------------------------------------------------------------------------------------
+// apply / residual: one thread per cell of an (BX x BY) tile, marching KZ planes in z.
+// ---------------------------------------------------------------------------------------------------------
+template <int ND, bool FULL>
+__global__ void __launch_bounds__(BX* BY) k_apply(const Geom g, const Metric m, double* __restrict__ out,
+                                                   const double* __restrict__ phi, const double* __restrict__ rhs,
+                                                   int mode, bool homog, int kz) {
+    const int i = blockIdx.x * BX + threadIdx.x;
+    const int j = blockIdx.y * BY + threadIdx.y;
+    if (i >= g.n[0] || j >= g.n[1]) return;
+    const int k0 = blockIdx.z * kz;
+    const int k1 = min(k0 + kz, g.n[2]);
+    for (int k = k0; k < k1; ++k) {
+        const long long c = g.idx(i, j, k);
+        double v;
+        if (FULL) v = apply_cell_full<ND>(g, m, phi, i, j, k, c, homog);
+        else v = apply_cell_ortho<ND>(g, m, phi, i, j, k, c, homog);
+        out[c] = mode ? (rhs[c] - v) : v;
+    }
+}
+
+void launch_apply(Ctx& cx, const Geom& g, const Metric& m, double* out, const double* phi, const double* rhs,
+                  int mode, bool homog) {
+    const int kz = (g.n[2] >= 64) ? 8 : 1;
+    dim3 grid((g.n[0] + BX - 1) / BX, (g.n[1] + BY - 1) / BY, (g.n[2] + kz - 1) / kz), block(BX, BY);
+    if (m.diagonal) {
+        if (g.nd == 3) k_apply<3, false><<<grid, block, 0, cx.stream>>>(g, m, out, phi, rhs, mode, homog, kz);
+        else k_apply<2, false><<<grid, block, 0, cx.stream>>>(g, m, out, phi, rhs, mode, homog, kz);
+    } else {
+        if (g.nd == 3) k_apply<3, true><<<grid, block, 0, cx.stream>>>(g, m, out, phi, rhs, mode, homog, kz);
+        else k_apply<2, true><<<grid, block, 0, cx.stream>>>(g, m, out, phi, rhs, mode, homog, kz);
+    }
+    cx.launches++;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// GSRB colour pass, in place (diagonal metric: a cell only reads the other colour).
+// Thread tx of a row handles cell i = 2*tx + parity.
+// ---------------------------------------------------------------------------------------------------------
+template <int ND>
+__global__ void __launch_bounds__(BX* BY) k_gsrb_ortho(const Geom g, const Metric m, double* __restrict__ phi,
+                                                        const double* __restrict__ rhs, int pass, int kz) {
+    const int t = blockIdx.x * BX + threadIdx.x;
+    const int j = blockIdx.y * BY + threadIdx.y;
+    if (j >= g.n[1]) return;
+    const int k0 = blockIdx.z * kz;
+    const int k1 = min(k0 + kz, g.n[2]);
+    for (int k = k0; k < k1; ++k) {
+        const int par = (g.g0[0] + g.g0[1] + j + ((ND > 2) ? (g.g0[2] + k) : 0) + pass) & 1;
+        const int i = 2 * t + par;
+        if (i < g.n[0]) {
+            const long long c = g.idx(i, j, k);
+            phi[c] = gsrb_cell_ortho<ND>(g, m, phi, rhs, i, j, k, c);
+        }
+    }
+}
+
+void launch_gsrb(Ctx& cx, const Geom& g, const Metric& m, double* phi, const double* rhs, int pass) {
+    const int kz = (g.n[2] >= 64) ? 8 : 1;
+    const int half = (g.n[0] + 1) / 2;
+    dim3 grid((half + BX - 1) / BX, (g.n[1] + BY - 1) / BY, (g.n[2] + kz - 1) / kz), block(BX, BY);
+    if (g.nd == 3) k_gsrb_ortho<3><<<grid, block, 0, cx.stream>>>(g, m, phi, rhs, pass, kz);
+    else k_gsrb_ortho<2><<<grid, block, 0, cx.stream>>>(g, m, phi, rhs, pass, kz);
+    cx.launches++;
+}
+
+// full metric: out of place (cross terms read same-colour cells of the pre-pass state = the `extrap` snapshot,
+// RelaxationMethod.cpp:411).  Every cell is written: updated colour gets the new value, the other a copy.
+template <int ND>
+__global__ void __launch_bounds__(BX* BY) k_gsrb_full(const Geom g, const Metric m, double* __restrict__ phiOut,
+                                                       const double* __restrict__ phiIn,
+                                                       const double* __restrict__ rhs, int pass, int kz) {
+    const int i = blockIdx.x * BX + threadIdx.x;
+    const int j = blockIdx.y * BY + threadIdx.y;
+    if (i >= g.n[0] || j >= g.n[1]) return;
+    const int k0 = blockIdx.z * kz;
+    const int k1 = min(k0 + kz, g.n[2]);
+    for (int k = k0; k < k1; ++k) {
+        const long long c = g.idx(i, j, k);
+        const int par = (g.g0[0] + i + g.g0[1] + j + ((ND > 2) ? (g.g0[2] + k) : 0) + pass) & 1;
+        phiOut[c] = par ? phiIn[c] : gsrb_cell_full<ND>(g, m, phiIn, rhs, i, j, k, c);
+    }
+}
+
+void launch_gsrb_full(Ctx& cx, const Geom& g, const Metric& m, double* phiOut, const double* phiIn,
+                      const double* rhs, int pass) {
+    const int kz = (g.n[2] >= 64) ? 8 : 1;
+    dim3 grid((g.n[0] + BX - 1) / BX, (g.n[1] + BY - 1) / BY, (g.n[2] + kz - 1) / kz), block(BX, BY);
+    if (g.nd == 3) k_gsrb_full<3><<<grid, block, 0, cx.stream>>>(g, m, phiOut, phiIn, rhs, pass, kz);
+    else k_gsrb_full<2><<<grid, block, 0, cx.stream>>>(g, m, phiOut, phiIn, rhs, pass, kz);
+    cx.launches++;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Jacobi / diagonal preconditioner / lapDiag
+// ---------------------------------------------------------------------------------------------------------
+__global__ void k_pointwise_diag(const Geom g, const Metric m, double* __restrict__ phi,
+                                 const double* __restrict__ src, int kind) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    if (i >= g.n[0] || j >= g.n[1]) return;
+    const long long c = g.idx(i, j, k);
+    const double den = g.alpha + g.beta * m.lapdiag[c];
+    if (kind == 0) phi[c] = phi[c] + 0.5 * src[c] / den;   // JACOBIITER
+    else phi[c] = src[c] / den;                            // DIAGPRECOND
+}
+
+void launch_jacobi(Ctx& cx, const Geom& g, const Metric& m, double* phi, const double* res) {
+    dim3 grid((g.n[0] + BX - 1) / BX, (g.n[1] + BY - 1) / BY, g.n[2]), block(BX, BY);
+    k_pointwise_diag<<<grid, block, 0, cx.stream>>>(g, m, phi, res, 0);
+    cx.launches++;
+}
+void launch_diag_precond(Ctx& cx, const Geom& g, const Metric& m, double* phi, const double* rhs) {
+    dim3 grid((g.n[0] + BX - 1) / BX, (g.n[1] + BY - 1) / BY, g.n[2]), block(BX, BY);
+    k_pointwise_diag<<<grid, block, 0, cx.stream>>>(g, m, phi, rhs, 1);
+    cx.launches++;
+}
+
+// FILLMAPPEDLAPDIAG{2,3}D -- MappedAMRPoissonOpF.ChF:149-274
+__global__ void k_lapdiag(const Geom g, const Metric m, double* __restrict__ lap) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    if (i >= g.n[0] || j >= g.n[1]) return;
+    const long long c = g.idx(i, j, k);
+    const double s0 = 1.0 / (g.dx[0] * g.dx[0]), s1 = 1.0 / (g.dx[1] * g.dx[1]);
+    double v;
+    if (g.nd == 2) {
+        v = -m.jinv[c] * ((m.jg[0][0][c + 1] + m.jg[0][0][c]) * s0 + (m.jg[1][1][c + g.sy] + m.jg[1][1][c]) * s1);
+    } else {
+        const double s2 = 1.0 / (g.dx[2] * g.dx[2]);
+        v = -m.jinv[c] * ((m.jg[0][0][c + 1] + m.jg[0][0][c]) * s0 + (m.jg[1][1][c + g.sy] + m.jg[1][1][c]) * s1 +
+                          (m.jg[2][2][c + g.sz] + m.jg[2][2][c]) * s2);
+    }
+    lap[c] = v;
+}
+
+void launch_lapdiag(Ctx& cx, const Geom& g, const Metric& m, double* lapdiag) {
+    dim3 grid((g.n[0] + BX - 1) / BX, (g.n[1] + BY - 1) / BY, g.n[2]), block(BX, BY);
+    k_lapdiag<<<grid, block, 0, cx.stream>>>(g, m, lapdiag);
+    cx.launches++;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// fused restrictResidual: crse = sum_block((rhs - L phi)/Jinv) / sum_block(1/Jinv), block swept x fastest
+// (MappedAMRPoissonOp.cpp:1281-1304; FullWeightingPS::restrict, RestrictionStrategy.cpp:36-99; MAPPEDAVERAGE2,
+// MappedCoarseAverageF.ChF:132-170).  One thread per coarse cell; the fine residual never touches HBM.
+// ---------------------------------------------------------------------------------------------------------
+template <int ND, bool FULL>
+__global__ void __launch_bounds__(BX* BY) k_restrict(const Geom gf, const Metric mf, const Geom gc,
+                                                      double* __restrict__ crse, const double* __restrict__ phi,
+                                                      const double* __restrict__ rhs, int r0, int r1, int r2) {
+    const int ic = blockIdx.x * BX + threadIdx.x;
+    const int jc = blockIdx.y * BY + threadIdx.y;
+    const int kc = blockIdx.z;
+    if (ic >= gc.n[0] || jc >= gc.n[1]) return;
+    double s = 0.0, sj = 0.0;
+    for (int kk = 0; kk < r2; ++kk)
+        for (int jj = 0; jj < r1; ++jj)
+            for (int ii = 0; ii < r0; ++ii) {
+                const int i = ic * r0 + ii, j = jc * r1 + jj, k = kc * r2 + kk;
+                const long long c = gf.idx(i, j, k);
+                double v;
+                if (FULL) v = apply_cell_full<ND>(gf, mf, phi, i, j, k, c, true);
+                else v = apply_cell_ortho<ND>(gf, mf, phi, i, j, k, c, true);
+                const double res = rhs[c] - v;
+                const double ji = mf.jinv[c];
+                s = s + res / ji;
+                sj = sj + 1.0 / ji;
+            }
+    crse[gc.idx(ic, jc, kc)] = s / sj;
+}
+
+void launch_restrict_residual(Ctx& cx, const Geom& gf, const Metric& mf, const Geom& gc, double* crse,
+                              const double* phi, const double* rhs, const int r[3]) {
+    dim3 grid((gc.n[0] + BX - 1) / BX, (gc.n[1] + BY - 1) / BY, gc.n[2]), block(BX, BY);
+    if (mf.diagonal) {
+        if (gf.nd == 3) k_restrict<3, false><<<grid, block, 0, cx.stream>>>(gf, mf, gc, crse, phi, rhs, r[0], r[1], r[2]);
+        else k_restrict<2, false><<<grid, block, 0, cx.stream>>>(gf, mf, gc, crse, phi, rhs, r[0], r[1], r[2]);
+    } else {
+        if (gf.nd == 3) k_restrict<3, true><<<grid, block, 0, cx.stream>>>(gf, mf, gc, crse, phi, rhs, r[0], r[1], r[2]);
+        else k_restrict<2, true><<<grid, block, 0, cx.stream>>>(gf, mf, gc, crse, phi, rhs, r[0], r[1], r[2]);
+    }
+    cx.launches++;
+}
+
+}  // namespace somar

@@ -1,0 +1,244 @@
+// solver.cu -- multigrid drivers on the level stream:
+//   mg_cycle      MappedMultiGrid<T>::cycle              src/calculus/AMRElliptic/MappedMultiGrid.H:555-653
+//   bottom_solve  Chombo 3.1 BiCGStabSolver<T>::solve     (not under the reference tree; configured at
+//                 src/projection/AMRPressureSolver.cpp:253-262; restated from the published algorithm)
+//   mg_solve      MappedAMRMultiGrid<T>::solveNoInitResid src/calculus/AMRElliptic/MappedAMRMultiGrid.H:979-1186
+//                 (l_base == l_max: AMRVCycle :1510-1513 -> oneCycle; postVCycleOps :1189-1215)
+#include "level.hpp"
+#include <cmath>
+#include <cstdio>
+
+namespace somar {
+
+static inline Geom& G(SomarLevel* L, int d) { return L->depths[d].g; }
+
+int mg_cycle(SomarLevel* L, int depth, SomarField* e, const SomarField* r) {
+    const SomarSolverParams& p = L->prm;
+    int rc;
+    if (depth == L->ndepths() - 1) {
+        const Geom& g = G(L, depth);
+        const long long bottomCells = (long long)g.gn[0] * g.gn[1] * g.gn[2];
+        if (bottomCells == 1) return op_relax(L, depth, e, r, 1);                       // :566-568
+        if ((rc = op_relax(L, depth, e, r, p.num_smooth_bottom)) != SOMAR_OK) return rc;
+        int it = 0;
+        if ((rc = bottom_solve(L, e, r, &it)) != SOMAR_OK) return rc;
+        L->bottom_iters_total += it;
+        return SOMAR_OK;
+    }
+    Depth& nx = L->depths[depth + 1];
+    int cycles = p.numMG;
+    if (cycles < 0) {   // F-cycle branch :578-619
+        cycles = -cycles;
+        if ((rc = op_restrict(L, depth, nx.res, e, r))) return rc;
+        launch_fill(L->cx, nx.g, nx.cor->p, 0.0);
+        if ((rc = mg_cycle(L, depth + 1, nx.cor, nx.res))) return rc;
+        if ((rc = op_prolong(L, depth, e, nx.cor))) return rc;
+        if ((rc = op_relax(L, depth, e, r, p.num_smooth_down))) return rc;
+        for (int img = 0; img < cycles; ++img) {
+            if ((rc = op_restrict(L, depth, nx.res, e, r))) return rc;
+            launch_fill(L->cx, nx.g, nx.cor->p, 0.0);
+            const int save = L->prm.numMG;
+            L->prm.numMG = 1;
+            rc = mg_cycle(L, depth + 1, nx.cor, nx.res);
+            L->prm.numMG = save;
+            if (rc) return rc;
+            if ((rc = op_prolong(L, depth, e, nx.cor))) return rc;
+        }
+        return op_relax(L, depth, e, r, p.num_smooth_up);
+    }
+    if ((rc = op_relax(L, depth, e, r, p.num_smooth_down))) return rc;                 // :622
+    if ((rc = op_restrict(L, depth, nx.res, e, r))) return rc;                         // :628
+    launch_fill(L->cx, nx.g, nx.cor->p, 0.0);                                           // :629
+    for (int img = 0; img < cycles; ++img)
+        if ((rc = mg_cycle(L, depth + 1, nx.cor, nx.res))) return rc;                   // :631-633
+    if ((rc = op_prolong(L, depth, e, nx.cor))) return rc;                             // :638
+    return op_relax(L, depth, e, r, p.num_smooth_up);                                   // :641
+}
+
+// ---------------------------------------------------------------------------------------------------------
+int bottom_solve(SomarLevel* L, SomarField* a_phi, const SomarField* a_rhs, int* iters) {
+    const SomarSolverParams& p = L->prm;
+    const int bd = L->ndepths() - 1;
+    const Geom& g = G(L, bd);
+    int rc;
+    if (L->bwork.empty()) {
+        L->bwork.resize(8, nullptr);
+        for (auto& f : L->bwork)
+            if ((rc = field_alloc(L, bd, &f))) return rc;
+    }
+    SomarField *r = L->bwork[0], *r_tilde = L->bwork[1], *e = L->bwork[2], *pv = L->bwork[3], *p_tilde = L->bwork[4],
+               *s_tilde = L->bwork[5], *t = L->bwork[6], *v = L->bwork[7];
+    Ctx& cx = L->cx;
+    auto norm = [&](SomarField* x, double* out) {
+        int kind = (p.bottom_normType == 0) ? 0 : (p.bottom_normType == 1 ? 1 : 2);
+        int rc2 = reduce_global(L, bd, x->p, nullptr, kind, out);
+        if (kind == 2) *out = std::sqrt(*out);
+        return rc2;
+    };
+    auto dot = [&](SomarField* a, SomarField* b, double* out) { return reduce_global(L, bd, a->p, b->p, 3, out); };
+
+    int recount = 0;
+    if ((rc = op_apply(L, bd, r->p, a_phi, a_rhs->p, 1, true))) return rc;
+    launch_copy(cx, g, r_tilde->p, r->p);
+    launch_fill(cx, g, e->p, 0.0);
+    launch_fill(cx, g, p_tilde->p, 0.0);
+    launch_fill(cx, g, s_tilde->p, 0.0);
+    int i = 0;
+    double rho[4] = {0, 0, 0, 0}, nrm[2];
+    if ((rc = norm(r, &nrm[0]))) return rc;
+    double initial_norm = nrm[0];
+    const double initial_rnorm = nrm[0];
+    nrm[1] = nrm[0];
+    double alph[2] = {0, 0}, bet[2] = {0, 0}, omega[2] = {0, 0};
+    bool init = true;
+    int restarts = 0;
+    if (L->bottomMetric > 0) initial_norm = L->bottomMetric;
+    const double eps = L->bottomEps;
+    while ((i < p.bottom_imax && nrm[0] > eps * nrm[1]) && (nrm[1] > 0)) {
+        ++i;
+        nrm[1] = nrm[0];
+        alph[1] = alph[0]; bet[1] = bet[0]; omega[1] = omega[0];
+        rho[3] = rho[2]; rho[2] = rho[1];
+        if ((rc = dot(r_tilde, r, &rho[1]))) return rc;
+        if (rho[1] == 0.0) break;
+        if (init) {
+            launch_copy(cx, g, pv->p, r->p);
+            init = false;
+        } else {
+            bet[1] = (rho[1] / rho[2]) * (alph[1] / omega[1]);
+            launch_scale(cx, g, pv->p, bet[1]);
+            launch_axpy(cx, g, pv->p, v->p, -bet[1] * omega[1]);
+            launch_axpy(cx, g, pv->p, r->p, 1.0);
+        }
+        if ((rc = op_precond(L, bd, p_tilde, pv))) return rc;
+        if ((rc = op_apply(L, bd, v->p, p_tilde, nullptr, 0, true))) return rc;
+        double m;
+        if ((rc = dot(r_tilde, v, &m))) return rc;
+        alph[0] = rho[1] / m;
+        if (std::fabs(m) > p.bottom_small * std::fabs(rho[1])) {
+            launch_axpy(cx, g, r->p, v->p, -alph[0]);
+            if ((rc = norm(r, &nrm[0]))) return rc;
+            launch_axpy(cx, g, e->p, p_tilde->p, alph[0]);
+        } else {
+            launch_fill(cx, g, r->p, 0.0);
+            nrm[0] = 0.0;
+        }
+        if (nrm[0] > eps * initial_norm && nrm[0] > p.bottom_reps * initial_rnorm) {
+            if ((rc = op_precond(L, bd, s_tilde, r))) return rc;
+            if ((rc = op_apply(L, bd, t->p, s_tilde, nullptr, 0, true))) return rc;
+            double tr, tt;
+            if ((rc = dot(t, r, &tr))) return rc;
+            if ((rc = dot(t, t, &tt))) return rc;
+            omega[0] = tr / tt;
+            launch_axpy(cx, g, e->p, s_tilde->p, omega[0]);
+            launch_axpy(cx, g, r->p, t->p, -omega[0]);
+            if ((rc = norm(r, &nrm[0]))) return rc;
+        }
+        if (nrm[0] <= eps * initial_norm || nrm[0] <= p.bottom_reps * initial_rnorm) break;
+        if (omega[0] == 0.0 || nrm[0] > (1.0 - p.bottom_hang) * nrm[1]) {
+            if (recount == 0) {
+                recount = 1;
+            } else {
+                recount = 0;
+                launch_axpy(cx, g, a_phi->p, e->p, 1.0);
+                if (restarts == p.bottom_numRestarts) { launch_fill(cx, g, e->p, 0.0); break; }
+                if ((rc = op_apply(L, bd, r->p, a_phi, a_rhs->p, 1, true))) return rc;
+                if ((rc = norm(r, &nrm[0]))) return rc;
+                rho[0] = rho[1] = rho[2] = rho[3] = 0.0;
+                alph[0] = alph[1] = bet[0] = bet[1] = omega[0] = omega[1] = 0.0;
+                launch_fill(cx, g, e->p, 0.0);
+                ++restarts;
+                init = true;
+                launch_copy(cx, g, r_tilde->p, r->p);
+            }
+        }
+    }
+    launch_axpy(cx, g, a_phi->p, e->p, 1.0);
+    *iters = i;
+    return SOMAR_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+int mg_solve(SomarLevel* L, SomarField* phi, const SomarField* rhs, bool zeroPhi, bool forceHomog,
+             SomarSolveStats* st) {
+    const SomarSolverParams& p = L->prm;
+    const Geom& g = G(L, 0);
+    Ctx& cx = L->cx;
+    int rc;
+    if (L->swork.empty()) {
+        L->swork.resize(3, nullptr);
+        for (auto& f : L->swork)
+            if ((rc = field_alloc(L, 0, &f))) return rc;
+    }
+    SomarField *corr = L->swork[0], *resid = L->swork[1], *best = L->swork[2];
+    const long long launches0 = cx.launches;
+    SOMAR_CUDA(cudaEventRecord(L->ev0, cx.stream));
+    launch_fill(cx, g, corr->p, 0.0);
+    if (zeroPhi) launch_fill(cx, g, phi->p, 0.0);
+    launch_copy(cx, g, best->p, phi->p);
+    auto computeResidual = [&](double* out) {
+        int r2 = op_apply(L, 0, resid->p, phi, rhs->p, 1, forceHomog);
+        if (r2) return r2;
+        return reduce_global(L, 0, resid->p, nullptr, 0, out);
+    };
+    double initial_rnorm;
+    if ((rc = computeResidual(&initial_rnorm))) return rc;
+    double rnorm = initial_rnorm, norm_last = 2 * initial_rnorm, best_rnorm = rnorm;
+    bool useBest = false;
+    L->bottomMetric = initial_rnorm;       // setConvergenceMetrics(initial_rnorm, cushion * eps) :1047
+    L->bottomEps = 1.0 * p.eps;
+    L->bottom_iters_total = 0;
+    int hl = 0;
+    st->history[hl++] = rnorm;
+    int iter = 0;
+    bool goNorm = rnorm > p.normThresh;
+    bool goRedu = rnorm > p.eps * initial_rnorm;
+    bool goIter = iter < p.imax;
+    bool goHang = iter < p.imin || rnorm < (1 - p.hang) * norm_last;
+    while (goIter && goRedu && goHang && goNorm) {
+        norm_last = rnorm;
+        if ((rc = mg_cycle(L, 0, corr, resid))) return rc;       // AMRVCycle, single level
+        launch_axpy(cx, g, phi->p, corr->p, 1.0);                 // postVCycleOps
+        launch_fill(cx, g, corr->p, 0.0);
+        if ((rc = computeResidual(&rnorm))) return rc;
+        ++iter;
+        if (hl < 128) st->history[hl++] = rnorm;
+        if (rnorm <= best_rnorm) {
+            best_rnorm = rnorm;
+            launch_copy(cx, g, best->p, phi->p);
+            useBest = false;
+        } else {
+            useBest = true;
+        }
+        if (p.verbosity >= 3)
+            fprintf(stderr, "   %s somar_b200 MG iteration = %d, residual norm = %.6e, rate = %.3f\n", useBest ? "[D]" : "   ",
+                    iter, rnorm, rnorm > 0 ? norm_last / rnorm : 0.0);
+        goNorm = rnorm > p.normThresh;
+        goRedu = rnorm > p.eps * initial_rnorm;
+        goIter = iter < p.imax;
+        goHang = iter < p.imin || rnorm < (1 - p.hang) * norm_last;
+    }
+    if (useBest) {
+        rnorm = best_rnorm;
+        launch_copy(cx, g, phi->p, best->p);
+    }
+    SOMAR_CUDA(cudaEventRecord(L->ev1, cx.stream));
+    SOMAR_CUDA(cudaEventSynchronize(L->ev1));
+    float ms = 0.f;
+    SOMAR_CUDA(cudaEventElapsedTime(&ms, L->ev0, L->ev1));
+    st->iters = iter;
+    st->initial_rnorm = initial_rnorm;
+    st->final_rnorm = rnorm;
+    st->exitStatus = int(!goRedu) + int(!goIter) * 2 + int(!goHang) * 4 + int(!goNorm) * 8;   // :1148
+    st->bottom_iters_total = L->bottom_iters_total;
+    st->history_len = hl;
+    st->solve_ms = ms;
+    st->launches = cx.launches - launches0;
+    if (rnorm > 10.0 * initial_rnorm && rnorm > 10.0 * p.eps) {   // :1133-1138 "kaboom"
+        set_error("solver diverged (residual > 10 x initial)");
+        return SOMAR_ERR_DIVERGED;
+    }
+    return SOMAR_OK;
+}
+
+}  // namespace somar

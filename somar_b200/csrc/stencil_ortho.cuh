@@ -1,0 +1,149 @@
+// stencil_ortho.cuh -- per-cell device functions for the DIAGONAL-metric operator (J g^{ij} = 0, i != j).
+// The arithmetic order follows the reference's Fortran statement by statement so that, compiled with
+// -fmad=false, results are bit-identical to a non-contracting CPU build of the same statements:
+//   flux      MAPPEDGETFLUXORTHO        src/calculus/AMRElliptic/MappedAMRPoissonOpOrthoF.ChF:33-82
+//   BC flux   EllipticConstNeumBCFluxClass  src/calculus/BCInterface/EllipticBCUtils.cpp:491-546
+//   BC ghost  ELLIPTICCONSTDIRIBCGHOST  src/calculus/BCInterface/EllipticBCUtilsF.ChF:29-120
+//   div       MAPPEDFLUXDIVERGENCE{2,3}D src/calculus/DivCurlGrad/DivCurlGradF.ChF:1034-1214
+//   axby      AXBYIP                    src/calculus/AMRElliptic/MappedAMRPoissonOpF.ChF:62-84
+//   GSRB      GSRBITER{2,3}DORTHO       src/calculus/AMRElliptic/RelaxationMethods/GSRBF.ChF:442-705
+//   GSRB bdry GSRBBOUNDARYITER{2,3}DORTHO  GSRBF.ChF:1233-1505
+#pragma once
+#include "geom.cuh"
+
+namespace somar {
+
+__device__ __forceinline__ double diri_ghost_val(double nearV, double farV, double bcval, int order) {
+    if (order == 0) return bcval;
+    if (order == 1) return (bcval == 0.0) ? -nearV : 2.0 * bcval - nearV;
+    return (bcval == 0.0) ? (1.0 / 3.0) * farV - 2.0 * nearV : (8.0 * bcval - 6.0 * nearV + farV) / 3.0;
+}
+
+// Which physical-boundary sides does local cell (i,j,k) touch?  bit (2*d+s).
+__device__ __forceinline__ unsigned side_mask(const Geom& g, int i, int j, int k) {
+    unsigned m = 0;
+    if (i == 0 && g.bc[0][0] != BC_NONE) m |= 1u;
+    if (i == g.n[0] - 1 && g.bc[0][1] != BC_NONE) m |= 2u;
+    if (j == 0 && g.bc[1][0] != BC_NONE) m |= 4u;
+    if (j == g.n[1] - 1 && g.bc[1][1] != BC_NONE) m |= 8u;
+    if (g.nd > 2) {
+        if (k == 0 && g.bc[2][0] != BC_NONE) m |= 16u;
+        if (k == g.n[2] - 1 && g.bc[2][1] != BC_NONE) m |= 32u;
+    }
+    return m;
+}
+
+// beta * flux through the low (S=0) / high (S=1) face of the cell at address c in direction with stride st.
+// pc = phi(c); the neighbour / ghost is resolved here.
+template <int S>
+__device__ __forceinline__ double face_flux_ortho(const Geom& g, const double* __restrict__ phi,
+                                                  const double* __restrict__ jgd, long long c, long long st, int d,
+                                                  bool atBdry, bool homog, double pc) {
+    const double beta_dx = 1.0 / g.dx[d];
+    const long long f = S ? c + st : c;            // face address
+    double nb;                                      // value on the other side of the face
+    if (atBdry) {
+        const int bct = g.bc[d][S];
+        if (bct == BC_NEUM) return (homog ? 0.0 : g.bcval[d][S]) * g.beta;
+        // Dirichlet: ghost from the interior values
+        const double farV = S ? phi[c - st] : phi[c + st];
+        nb = diri_ghost_val(pc, farV, homog ? 0.0 : g.bcval[d][S], g.diriOrder);
+    } else {
+        nb = S ? phi[c + st] : phi[c - st];
+    }
+    const double diff = S ? (nb - pc) : (pc - nb);
+    return (jgd[f] * beta_dx * diff) * g.beta;
+}
+
+// (alpha I + beta L) phi at one cell, diagonal metric.
+template <int ND>
+__device__ __forceinline__ double apply_cell_ortho(const Geom& g, const Metric& m, const double* __restrict__ phi,
+                                                   int i, int j, int k, long long c, bool homog) {
+    const unsigned sm = side_mask(g, i, j, k);
+    const double pc = phi[c];
+    const double f0l = face_flux_ortho<0>(g, phi, m.jg[0][0], c, 1, 0, sm & 1u, homog, pc);
+    const double f0h = face_flux_ortho<1>(g, phi, m.jg[0][0], c, 1, 0, sm & 2u, homog, pc);
+    const double f1l = face_flux_ortho<0>(g, phi, m.jg[1][1], c, g.sy, 1, sm & 4u, homog, pc);
+    const double f1h = face_flux_ortho<1>(g, phi, m.jg[1][1], c, g.sy, 1, sm & 8u, homog, pc);
+    double s = (f0h - f0l) * (1.0 / g.dx[0]);
+    s = s + (f1h - f1l) * (1.0 / g.dx[1]);
+    if (ND > 2) {
+        const double f2l = face_flux_ortho<0>(g, phi, m.jg[2][2], c, g.sz, 2, sm & 16u, homog, pc);
+        const double f2h = face_flux_ortho<1>(g, phi, m.jg[2][2], c, g.sz, 2, sm & 32u, homog, pc);
+        s = s + (f2h - f2l) * (1.0 / g.dx[2]);
+    }
+    double r = m.jinv[c] * s;
+    if (g.alpha != 0.0) r = g.alpha * pc + 1.0 * r;
+    return r;
+}
+
+// Is the cell on the rim of the DOMAIN (any active direction, periodic or not)?  Such cells are relaxed by the
+// boundary kernels of the reference (BaseGSRB::boundaryGSRB, GSRB.cpp:489-653; domInterior = grow(domain,-1)).
+template <int ND>
+__device__ __forceinline__ bool on_domain_rim(const Geom& g, int i, int j, int k) {
+    const int gi = i + g.g0[0], gj = j + g.g0[1], gk = k + g.g0[2];
+    bool r = (gi == 0) | (gi == g.gn[0] - 1) | (gj == 0) | (gj == g.gn[1] - 1);
+    if (ND > 2) r = r | (gk == 0) | (gk == g.gn[2] - 1);
+    return r;
+}
+
+// One red-black update of one cell, diagonal metric.  Returns the new phi.  `pc` = current phi(c) (only used for
+// Dirichlet ghosts, which the reference fills from the pre-pass state).
+template <int ND>
+__device__ __forceinline__ double gsrb_cell_ortho(const Geom& g, const Metric& m, const double* __restrict__ phi,
+                                                  const double* __restrict__ rhs, int i, int j, int k, long long c) {
+    const double sc0 = 1.0 / (g.dx[0] * g.dx[0]);
+    const double sc1 = 1.0 / (g.dx[1] * g.dx[1]);
+    const double sc2 = (ND > 2) ? 1.0 / (g.dx[2] * g.dx[2]) : 0.0;
+    const double* __restrict__ G0 = m.jg[0][0];
+    const double* __restrict__ G1 = m.jg[1][1];
+    const double* __restrict__ G2 = m.jg[2][2];
+    const double ji = m.jinv[c];
+    if (!on_domain_rim<ND>(g, i, j, k)) {
+        const double JDxx = sc0 * (G0[c + 1] * phi[c + 1] + G0[c] * phi[c - 1]);
+        const double JDyy = sc1 * (G1[c + g.sy] * phi[c + g.sy] + G1[c] * phi[c - g.sy]);
+        double lphi;
+        if (ND > 2) {
+            const double JDzz = sc2 * (G2[c + g.sz] * phi[c + g.sz] + G2[c] * phi[c - g.sz]);
+            lphi = g.beta * ji * (JDxx + JDyy + JDzz);
+        } else {
+            lphi = g.beta * ji * (JDxx + JDyy);
+        }
+        return (rhs[c] - lphi) / (g.alpha + g.beta * m.lapdiag[c]);
+    }
+    // rim cell: Neumann sides are dropped from the stencil and from the diagonal
+    const unsigned sm = side_mask(g, i, j, k);
+    const double pc = phi[c];
+    double JDlo[3] = {0.0, 0.0, 0.0}, JDhi[3] = {0.0, 0.0, 0.0};
+    double lapDiag = 0.0;
+    const long long st[3] = {1, g.sy, g.sz};
+    const double sc[3] = {sc0, sc1, sc2};
+    const double* __restrict__ G[3] = {G0, G1, G2};
+#pragma unroll
+    for (int d = 0; d < ND; ++d) {
+        const bool atB = (sm >> (2 * d)) & 1u;
+        if (!(atB && g.bc[d][0] == BC_NEUM)) {
+            double nb = phi[c - st[d]];
+            if (atB && g.bc[d][0] == BC_DIRI) nb = diri_ghost_val(pc, phi[c + st[d]], 0.0, g.diriOrder);
+            JDlo[d] = G[d][c] * nb;
+            lapDiag = lapDiag - sc[d] * G[d][c];
+        }
+    }
+#pragma unroll
+    for (int d = 0; d < ND; ++d) {
+        const bool atB = (sm >> (2 * d + 1)) & 1u;
+        if (!(atB && g.bc[d][1] == BC_NEUM)) {
+            double nb = phi[c + st[d]];
+            if (atB && g.bc[d][1] == BC_DIRI) nb = diri_ghost_val(pc, phi[c - st[d]], 0.0, g.diriOrder);
+            JDhi[d] = G[d][c + st[d]] * nb;
+            lapDiag = lapDiag - sc[d] * G[d][c + st[d]];
+        }
+    }
+    lapDiag = lapDiag * ji;
+    double s = (JDlo[0] + JDhi[0]) * sc0 + (JDlo[1] + JDhi[1]) * sc1;
+    if (ND > 2) s = s + (JDlo[2] + JDhi[2]) * sc2;
+    const double lphi = g.beta * ji * s;
+    return (rhs[c] - lphi) / (g.alpha + g.beta * lapDiag);
+}
+
+}  // namespace somar

@@ -1,0 +1,155 @@
+"""GPU parity tests: the CUDA path, called through the C ABI, against the CPU oracle on identical seeded inputs.
+
+Bars (BASELINE.json north_star): stencil apply / restriction / prolongation <= 1e-13 relative.  The diagonal-metric
+kernels are compiled with -fmad=false and follow the reference's statement order, so they are held to BIT-EXACT
+equality with the (non-contracting) oracle; full-metric kernels and order-dependent sums to 1e-13.
+"""
+import numpy as np
+import pytest
+
+from common import Problem, rel_err
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-13
+
+CASES = {
+    "stretched3d": dict(n=(32, 24, 16), map_name="stretched", aniso=4.0),
+    "stretched3d_boxes": dict(n=(32, 32, 16), map_name="stretched", aniso=4.0, parts=(1, 4, 1)),
+    "periodic_y": dict(n=(32, 16, 16), map_name="stretched", aniso=2.0, periodic=(0, 1, 0)),
+    "periodic_xy": dict(n=(16, 16, 16), map_name="cartesian", aniso=1.0, periodic=(1, 1, 0)),
+    "dirichlet_top": dict(n=(16, 16, 16), map_name="stretched", aniso=4.0, bc_type=[0, 0, 0, 0, 0, 1],
+                          bc_value=[0, 0, 0, 0, 0, 0.5]),
+    "helmholtz": dict(n=(16, 16, 16), map_name="stretched", aniso=4.0, alpha=1.0, beta=-0.05),
+    "stretched2d": dict(n=(32, 16, 1), dim=2, map_name="stretched", aniso=4.0),
+    "terrain3d": dict(n=(32, 24, 16), map_name="terrain", aniso=4.0),
+    "terrain3d_boxes": dict(n=(32, 32, 16), map_name="terrain", aniso=4.0, parts=(1, 4, 1)),
+    "terrain2d": dict(n=(32, 16, 1), dim=2, map_name="terrain", aniso=4.0),
+    "twisted2d_periodic": dict(n=(32, 32, 1), dim=2, map_name="twisted", aniso=1.0, periodic=(1, 1, 0),
+                               map_params={"pert": 0.05}),
+    "terrain_periodic_y": dict(n=(16, 16, 16), map_name="terrain", aniso=4.0, periodic=(0, 1, 0)),
+}
+DIAG = [k for k, v in CASES.items() if v["map_name"] in ("stretched", "cartesian")]
+FULL = [k for k in CASES if k not in DIAG]
+
+
+def _setup(name, oracle_lib, somar, **params):
+    pb = Problem(**CASES[name])
+    orc = pb.oracle(oracle_lib, **params)
+    lev = pb.level(somar, **params)
+    return pb, orc, lev
+
+
+def _check(got, want, exact, what):
+    if exact:
+        assert np.array_equal(got, want), f"{what}: not bit-exact, rel err {rel_err(got, want):.3e}"
+    else:
+        assert rel_err(got, want) <= TOL, f"{what}: rel err {rel_err(got, want):.3e}"
+
+
+@pytest.mark.parametrize("name", list(CASES))
+def test_hierarchy_and_metrics(name, oracle_lib, somar):
+    pb, orc, lev = _setup(name, oracle_lib, somar)
+    assert lev.ndepths == orc.ndepths
+    for d in range(lev.ndepths):
+        a, b = lev.depth_info(d), orc.depth_info(d)
+        assert a["n"] == b["n"] and a["dx"] == b["dx"] and a["zero_avg"] == b["zero_avg"], (d, a, b)
+        if d + 1 < lev.ndepths:
+            assert a["ratio"] == b["ratio"]
+        jg, jinv, lap = lev.metric(d)
+        ojg, ojinv, olap = orc.metric(d)
+        assert np.array_equal(jinv, ojinv)
+        _check(lap, olap, True, f"lapDiag depth {d}")
+        for dd in range(pb.dim):
+            for c in range(pb.dim):
+                if pb.is_diagonal and c != dd:
+                    continue
+                assert np.array_equal(jg[dd][c], ojg[dd][c]), (d, dd, c)
+
+
+@pytest.mark.parametrize("name", list(CASES))
+@pytest.mark.parametrize("homog", [True, False])
+def test_apply_and_residual(name, homog, oracle_lib, somar):
+    pb, orc, lev = _setup(name, oracle_lib, somar)
+    exact = name in DIAG
+    for d in range(lev.ndepths):
+        shp = orc.shape(d)
+        phi, rhs = pb.rand(shp), pb.rand(shp)
+        fphi, frhs, fout = lev.field(d, phi), lev.field(d, rhs), lev.field(d)
+        lev.apply_op(fout, fphi, homogeneous=homog)
+        _check(fout.get(), orc.apply_op(phi, depth=d, homogeneous=homog), exact, f"applyOp depth {d}")
+        lev.residual(fout, fphi, frhs, homogeneous=homog)
+        _check(fout.get(), orc.residual(phi, rhs, depth=d, homogeneous=homog), exact, f"residual depth {d}")
+
+
+@pytest.mark.parametrize("name", list(CASES))
+@pytest.mark.parametrize("mode", [1, 3, 0])
+def test_relax(name, mode, oracle_lib, somar):
+    pb, orc, lev = _setup(name, oracle_lib, somar, relaxMode=mode)
+    exact = name in DIAG
+    for d in range(lev.ndepths):
+        shp = orc.shape(d)
+        phi, rhs = pb.rand(shp), pb.rand(shp)
+        fphi, frhs = lev.field(d, phi), lev.field(d, rhs)
+        lev.relax(fphi, frhs, iters=2)
+        want = orc.relax(phi, rhs, iters=2, depth=d)
+        if exact:
+            _check(fphi.get(), want, True, f"relax mode {mode} depth {d}")
+        else:
+            # two sweeps amplify rounding differences of the cross terms a little
+            assert rel_err(fphi.get(), want) <= 10 * TOL, rel_err(fphi.get(), want)
+
+
+@pytest.mark.parametrize("name", list(CASES))
+def test_restrict_and_prolong(name, oracle_lib, somar):
+    pb, orc, lev = _setup(name, oracle_lib, somar)
+    exact = name in DIAG
+    for d in range(lev.ndepths - 1):
+        shp, shc = orc.shape(d), orc.shape(d + 1)
+        phi, rhs, crse = pb.rand(shp), pb.rand(shp), pb.rand(shc)
+        fphi, frhs, fc = lev.field(d, phi), lev.field(d, rhs), lev.field(d + 1)
+        lev.restrict_residual(fc, fphi, frhs)
+        _check(fc.get(), orc.restrict_residual(phi, rhs, depth=d), exact, f"restrictResidual depth {d}")
+        fc.set(crse)
+        lev.prolong_increment(fphi, fc)
+        want = orc.prolong_increment(phi, crse, depth=d)
+        # the volume-weighted mean is a sum over all cells: order-dependent, tolerance not bit-exactness
+        assert rel_err(fphi.get(), want) <= TOL, rel_err(fphi.get(), want)
+
+
+@pytest.mark.parametrize("name", ["stretched3d", "periodic_y", "terrain3d"])
+def test_blas1_and_norms(name, oracle_lib, somar):
+    pb, orc, lev = _setup(name, oracle_lib, somar)
+    x, y = pb.rand(), pb.rand()
+    fx, fy, fz = lev.field(0, x), lev.field(0, y), lev.field(0)
+    assert lev.norm(fx, 0) == np.abs(x).max()
+    assert abs(lev.norm(fx, 1) - np.abs(x).sum()) <= 1e-12 * np.abs(x).sum()
+    assert abs(lev.norm(fx, 2) - np.sqrt((x * x).sum())) <= 1e-12 * np.sqrt((x * x).sum())
+    assert abs(lev.dot(fx, fy) - (x * y).sum()) <= 1e-12 * np.abs(x * y).sum()
+    lev.incr(fy, fx, -0.75)
+    assert np.array_equal(fy.get(), y + (-0.75) * x)
+    lev.axby(fz, fx, fy, 2.0, 3.0)
+    assert np.array_equal(fz.get(), 2.0 * x + 3.0 * (y + (-0.75) * x))
+    lev.scale(fz, 0.5)
+    lev.assign(fy, fz)
+    assert np.array_equal(fy.get(), 0.5 * (2.0 * x + 3.0 * (y + (-0.75) * x)))
+    lev.set_to_zero(fy)
+    assert not fy.get().any()
+
+
+@pytest.mark.parametrize("name", ["stretched3d", "stretched3d_boxes", "terrain3d"])
+def test_fab_round_trip(name, oracle_lib, somar):
+    """CHF_FRA path: per-box host FABs with ghost cells in, per-box FABs out."""
+    pb, orc, lev = _setup(name, oracle_lib, somar)
+    x = pb.rand()
+    f = lev.field(0)
+    for lo, hi in pb.boxes:
+        glo, ghi = [l - 1 for l in lo], [h + 1 for h in hi]
+        fab = np.full((ghi[2] - glo[2] + 1, ghi[1] - glo[1] + 1, ghi[0] - glo[0] + 1), np.nan)
+        fab[1:-1, 1:-1, 1:-1] = x[lo[2]:hi[2] + 1, lo[1]:hi[1] + 1, lo[0]:hi[0] + 1]
+        f.set_fab(fab, glo, ghi, lo, hi)
+    assert np.array_equal(f.get(), x)
+    for lo, hi in pb.boxes:
+        out = np.zeros((hi[2] - lo[2] + 1, hi[1] - lo[1] + 1, hi[0] - lo[0] + 1))
+        f.get_fab(out, lo, hi, lo, hi)
+        assert np.array_equal(out, x[lo[2]:hi[2] + 1, lo[1]:hi[1] + 1, lo[0]:hi[0] + 1])
