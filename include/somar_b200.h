@@ -130,6 +130,12 @@ int somar_level_launch_count(const SomarLevel* lev, long long* launches);
 /* Reads back a depth's metric into rank-local arrays without ghosts (tests): comp-outermost for jg. */
 int somar_level_get_metric(SomarLevel* lev, int depth, double* jg0, double* jg1, double* jg2, double* jinv,
                            double* lapdiag);
+/* Phase timers on the level stream (CUDA events; replaces the CH_TIMERS of MappedAMRPoissonOp.cpp:777-781 and
+ * MappedAMRMultiGrid.H:988).  Phases: 0 = depth-0 smoother colour-pass KERNEL (per launch), 1 = smoothing at the
+ * intermediate depths, 2 = restrictResidual, 3 = prolongIncrement, 4 = bottom (relax + BiCGStab), 5 = outer loop
+ * (phi += e, residual, norm, best-phi copy).  profile_read synchronises, fills count[6]/ms[6] and clears. */
+int somar_level_profile_enable(SomarLevel* lev, int on);
+int somar_level_profile_read(SomarLevel* lev, long long count[6], double ms[6]);
 
 /* ---- fields: LinearOp<T>::create / clear (MappedAMRPoissonOp.H:566-575) ---------------------------------- */
 int somar_field_create(SomarLevel* lev, int depth, SomarField** out);

@@ -8,6 +8,7 @@ from __future__ import annotations
 
 import ctypes as C
 import os
+import weakref
 from typing import Optional, Sequence
 
 import numpy as np
@@ -24,6 +25,7 @@ SYMBOLS = [
     "somar_level_create", "somar_level_destroy", "somar_level_set_metric_fab", "somar_level_set_metric_device",
     "somar_level_finalize", "somar_level_set_alpha_beta", "somar_level_num_depths", "somar_level_depth_info",
     "somar_level_sync", "somar_level_stream", "somar_level_launch_count", "somar_level_get_metric",
+    "somar_level_profile_enable", "somar_level_profile_read",
     "somar_field_create", "somar_field_destroy", "somar_field_set_fab", "somar_field_get_fab", "somar_field_set",
     "somar_field_get", "somar_apply_op", "somar_residual", "somar_precond", "somar_set_to_zero", "somar_assign",
     "somar_incr", "somar_axby", "somar_scale", "somar_norm", "somar_local_max_norm", "somar_dot", "somar_relax",
@@ -115,6 +117,7 @@ class Field:
         h = C.c_void_p()
         _ck(lib().somar_field_create(level.h, depth, C.byref(h)))
         self.h = h
+        level._fields.add(self)
 
     def shape(self):
         return self.level.local_shape(self.depth)
@@ -143,9 +146,10 @@ class Field:
         _ck(lib().somar_field_get_fab(self.h, p, _i3(lo), _i3(hi), _i3(vlo), _i3(vhi)))
 
     def destroy(self):
-        if self.h:
+        # a field must die before its level (the C object points back at it); Level.destroy() sees to that
+        if self.h and getattr(self.level, "h", None):
             lib().somar_field_destroy(self.h)
-            self.h = None
+        self.h = None
 
     def __del__(self):
         try:
@@ -161,6 +165,8 @@ class Level:
                  alpha=0.0, beta=1.0, is_diagonal=True, bc_type=None, bc_value=None,
                  params: Optional[SolverParams] = None, device=0, rank=0, nranks=1, comm_id: Optional[bytes] = None):
         L = lib()
+        self.h = None
+        self._fields = weakref.WeakSet()
         self.n = tuple(int(x) for x in n)
         self.dim = dim
         if boxes is None:
@@ -254,6 +260,20 @@ class Level:
     def sync(self):
         _ck(lib().somar_level_sync(self.h))
 
+    def stream(self) -> int:
+        v = C.c_void_p()
+        _ck(lib().somar_level_stream(self.h, C.byref(v)))
+        return v.value or 0
+
+    def profile(self, on: bool):
+        _ck(lib().somar_level_profile_enable(self.h, int(on)))
+
+    def profile_read(self):
+        cnt, ms = (C.c_longlong * 6)(), (C.c_double * 6)()
+        _ck(lib().somar_level_profile_read(self.h, cnt, ms))
+        names = ["smooth0_kernel", "smooth_coarse", "restrict", "prolong", "bottom", "outer"]
+        return {n: {"count": cnt[i], "ms": ms[i]} for i, n in enumerate(names)}
+
     def launches(self) -> int:
         v = C.c_longlong()
         _ck(lib().somar_level_launch_count(self.h, C.byref(v)))
@@ -322,6 +342,8 @@ class Level:
 
     def destroy(self):
         if getattr(self, "h", None):
+            for f in list(self._fields):
+                f.destroy()
             lib().somar_level_destroy(self.h)
             self.h = None
 

@@ -11,6 +11,29 @@ using namespace somar;
 
 extern "C" {
 
+int somar_level_profile_enable(SomarLevel* L, int on) {
+    if (!L) { set_error("null level"); return SOMAR_ERR_ARG; }
+    L->prof_on = on != 0;
+    return SOMAR_OK;
+}
+int somar_level_profile_read(SomarLevel* L, long long count[6], double ms[6]) {
+    if (!L) { set_error("null level"); return SOMAR_ERR_ARG; }
+    cudaSetDevice(L->device);
+    SOMAR_CUDA(cudaStreamSynchronize(L->cx.stream));
+    for (int i = 0; i < 6; ++i) { count[i] = 0; ms[i] = 0.0; }
+    for (auto& r : L->prof) {
+        float t = 0.f;
+        if (cudaEventElapsedTime(&t, r.a, r.b) == cudaSuccess && r.phase >= 0 && r.phase < 6) {
+            count[r.phase]++;
+            ms[r.phase] += t;
+        }
+        L->prof_pool.push_back(r.a);
+        L->prof_pool.push_back(r.b);
+    }
+    L->prof.clear();
+    return SOMAR_OK;
+}
+
 int somar_apply_op(SomarLevel* L, int depth, SomarField* lhs, SomarField* phi, int homogeneous) {
     CHECK_FINAL(L); CHECK_F(lhs, L, depth); CHECK_F(phi, L, depth);
     return op_apply(L, depth, lhs->p, phi, nullptr, 0, homogeneous != 0);

@@ -292,10 +292,13 @@ int op_relax(SomarLevel* L, int depth, SomarField* phi, const SomarField* rhs, i
     Depth& dp = L->depths[depth];
     const int mode = (modeOverride != -100) ? modeOverride : L->prm.relaxMode;
     int rc;
+    const bool coarse = depth > 0 && depth < L->ndepths() - 1;
+    ProfScope psCoarse(L, coarse ? PH_SMOOTH_COARSE : -1);
     for (int it = 0; it < iters; ++it) {
         if (mode == SOMAR_RELAX_LEVEL_GSRB) {          // LevelGSRB::relax, GSRB.cpp:58-98
             for (int pass = 0; pass < 2; ++pass) {
                 if ((rc = exchange(L, depth, phi->p, 1)) != SOMAR_OK) return rc;
+                ProfScope psK(L, depth == 0 ? PH_SMOOTH0_KERNEL : -1);
                 if (dp.m.diagonal) {
                     launch_gsrb(L->cx, dp.g, dp.m, phi->p, rhs->p, pass);
                 } else {
@@ -307,6 +310,7 @@ int op_relax(SomarLevel* L, int depth, SomarField* phi, const SomarField* rhs, i
             if ((rc = ensure_line(L, dp)) != SOMAR_OK) return rc;
             for (int pass = 0; pass < 2; ++pass) {
                 if ((rc = exchange(L, depth, phi->p, 1)) != SOMAR_OK) return rc;
+                ProfScope psK(L, depth == 0 ? PH_SMOOTH0_KERNEL : -1);
                 if (dp.m.diagonal) {
                     launch_line_gsrb(L->cx, dp.g, dp.m, phi->p, phi->p, rhs->p, dp.line_fact, dp.line_dmod, pass);
                 } else {

@@ -64,9 +64,38 @@ struct SomarLevel {
     double bottomMetric = 0.0, bottomEps = 1e-6;
     int bottom_iters_total = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // phase profiler (CUDA events on the level stream; off by default)
+    bool prof_on = false;
+    struct ProfRec { int phase; cudaEvent_t a, b; };
+    std::vector<ProfRec> prof;          // recorded intervals
+    std::vector<cudaEvent_t> prof_pool; // free events
 
     int ndepths() const { return (int)depths.size(); }
 };
+
+namespace somar {
+enum { PH_SMOOTH0_KERNEL = 0, PH_SMOOTH_COARSE = 1, PH_RESTRICT = 2, PH_PROLONG = 3, PH_BOTTOM = 4, PH_OUTER = 5,
+       PH_COUNT = 6 };
+// RAII interval: records two events around a scope when profiling is on.
+struct ProfScope {
+    SomarLevel* L;
+    int idx = -1;
+    ProfScope(SomarLevel* L_, int phase) : L(L_) {
+        if (!L->prof_on || phase < 0) return;
+        cudaEvent_t e[2];
+        for (int i = 0; i < 2; ++i) {
+            if (!L->prof_pool.empty()) { e[i] = L->prof_pool.back(); L->prof_pool.pop_back(); }
+            else cudaEventCreate(&e[i]);
+        }
+        cudaEventRecord(e[0], L->cx.stream);
+        idx = (int)L->prof.size();
+        L->prof.push_back({phase, e[0], e[1]});
+    }
+    ~ProfScope() {
+        if (idx >= 0) cudaEventRecord(L->prof[idx].b, L->cx.stream);
+    }
+};
+}  // namespace somar
 
 namespace somar {
 

@@ -18,6 +18,7 @@ int mg_cycle(SomarLevel* L, int depth, SomarField* e, const SomarField* r) {
     if (depth == L->ndepths() - 1) {
         const Geom& g = G(L, depth);
         const long long bottomCells = (long long)g.gn[0] * g.gn[1] * g.gn[2];
+        ProfScope ps(L, PH_BOTTOM);
         if (bottomCells == 1) return op_relax(L, depth, e, r, 1);                       // :566-568
         if ((rc = op_relax(L, depth, e, r, p.num_smooth_bottom)) != SOMAR_OK) return rc;
         int it = 0;
@@ -47,11 +48,17 @@ int mg_cycle(SomarLevel* L, int depth, SomarField* e, const SomarField* r) {
         return op_relax(L, depth, e, r, p.num_smooth_up);
     }
     if ((rc = op_relax(L, depth, e, r, p.num_smooth_down))) return rc;                 // :622
-    if ((rc = op_restrict(L, depth, nx.res, e, r))) return rc;                         // :628
-    launch_fill(L->cx, nx.g, nx.cor->p, 0.0);                                           // :629
+    {
+        ProfScope ps(L, PH_RESTRICT);
+        if ((rc = op_restrict(L, depth, nx.res, e, r))) return rc;                     // :628
+        launch_fill(L->cx, nx.g, nx.cor->p, 0.0);                                       // :629
+    }
     for (int img = 0; img < cycles; ++img)
         if ((rc = mg_cycle(L, depth + 1, nx.cor, nx.res))) return rc;                   // :631-633
-    if ((rc = op_prolong(L, depth, e, nx.cor))) return rc;                             // :638
+    {
+        ProfScope ps(L, PH_PROLONG);
+        if ((rc = op_prolong(L, depth, e, nx.cor))) return rc;                         // :638
+    }
     return op_relax(L, depth, e, r, p.num_smooth_up);                                   // :641
 }
 
@@ -198,17 +205,20 @@ int mg_solve(SomarLevel* L, SomarField* phi, const SomarField* rhs, bool zeroPhi
     while (goIter && goRedu && goHang && goNorm) {
         norm_last = rnorm;
         if ((rc = mg_cycle(L, 0, corr, resid))) return rc;       // AMRVCycle, single level
-        launch_axpy(cx, g, phi->p, corr->p, 1.0);                 // postVCycleOps
-        launch_fill(cx, g, corr->p, 0.0);
-        if ((rc = computeResidual(&rnorm))) return rc;
-        ++iter;
-        if (hl < 128) st->history[hl++] = rnorm;
-        if (rnorm <= best_rnorm) {
-            best_rnorm = rnorm;
-            launch_copy(cx, g, best->p, phi->p);
-            useBest = false;
-        } else {
-            useBest = true;
+        {
+            ProfScope ps(L, PH_OUTER);
+            launch_axpy(cx, g, phi->p, corr->p, 1.0);             // postVCycleOps
+            launch_fill(cx, g, corr->p, 0.0);
+            if ((rc = computeResidual(&rnorm))) return rc;
+            ++iter;
+            if (hl < 128) st->history[hl++] = rnorm;
+            if (rnorm <= best_rnorm) {
+                best_rnorm = rnorm;
+                launch_copy(cx, g, best->p, phi->p);
+                useBest = false;
+            } else {
+                useBest = true;
+            }
         }
         if (p.verbosity >= 3)
             fprintf(stderr, "   %s somar_b200 MG iteration = %d, residual norm = %.6e, rate = %.3f\n", useBest ? "[D]" : "   ",

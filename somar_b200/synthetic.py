@@ -98,20 +98,22 @@ def _map_fn(spec: GridSpec) -> Callable:
     raise ValueError(f"unknown map {spec.map_name}")
 
 
-def _coords(spec: GridSpec, stagger: Sequence[int], device) -> List[torch.Tensor]:
-    """1-D computational coordinates of the points of a box with centring `stagger` (1 = node)."""
+def _coords(spec: GridSpec, stagger: Sequence[int], device, yrange=None) -> List[torch.Tensor]:
+    """1-D computational coordinates of the points of a box with centring `stagger` (1 = node).
+    yrange = (j0, j1) restricts direction 1 to the cells j0..j1-1 (a rank-local y-slab)."""
     out = []
     for d in range(3):
-        n = spec.n[d] + (1 if stagger[d] else 0)
+        lo, hi = (0, spec.n[d]) if (d != 1 or yrange is None) else yrange
+        n = hi - lo + (1 if stagger[d] else 0)
         off = 0.0 if stagger[d] else 0.5
-        out.append((torch.arange(n, dtype=DT, device=device) + off) * spec.dx[d])
+        out.append((torch.arange(n, dtype=DT, device=device) + (lo + off)) * spec.dx[d])
     return out
 
 
-def _jacobian(spec: GridSpec, stagger: Sequence[int], device):
+def _jacobian(spec: GridSpec, stagger: Sequence[int], device, yrange=None):
     """dx^mu/dXi^nu (list of lists of broadcastable tensors, shape (nz,ny,nx)-compatible) at the given centring."""
     fmap = _map_fn(spec)
-    c = _coords(spec, stagger, device)
+    c = _coords(spec, stagger, device, yrange)
     X = [c[0].view(1, 1, -1), c[1].view(1, -1, 1), c[2].view(-1, 1, 1)]
     dim = spec.dim
     Jm = [[None] * dim for _ in range(dim)]
@@ -154,20 +156,22 @@ class Metric:
     ncomp: int
 
 
-def build_metric(spec: GridSpec, device="cpu", diag_only: Optional[bool] = None) -> Metric:
-    """J g^{ij} on faces and 1/J at cell centres.  diag_only stores only J g^{dd} (diagonal metrics)."""
+def build_metric(spec: GridSpec, device="cpu", diag_only: Optional[bool] = None, yrange=None) -> Metric:
+    """J g^{ij} on faces and 1/J at cell centres.  diag_only stores only J g^{dd} (diagonal metrics).
+    yrange = (j0, j1): only the y-slab of cells j0..j1-1 (what one rank owns)."""
     dim = spec.dim
     if diag_only is None:
         diag_only = spec.is_diagonal
-    shape_c = (spec.n[2], spec.n[1], spec.n[0])
-    det, _ = _det_inv(_jacobian(spec, (0, 0, 0), device), dim)
+    ny = spec.n[1] if yrange is None else yrange[1] - yrange[0]
+    shape_c = (spec.n[2], ny, spec.n[0])
+    det, _ = _det_inv(_jacobian(spec, (0, 0, 0), device, yrange), dim)
     jinv = (1.0 / det).expand(shape_c).contiguous()
     jg = []
     for d in range(dim):
         st = [0, 0, 0]
         st[d] = 1
-        shape_f = (spec.n[2] + st[2], spec.n[1] + st[1], spec.n[0] + st[0])
-        det, inv = _det_inv(_jacobian(spec, st, device), dim)
+        shape_f = (spec.n[2] + st[2], ny + st[1], spec.n[0] + st[0])
+        det, inv = _det_inv(_jacobian(spec, st, device, yrange), dim)
         comps = []
         for c in range(dim):
             if diag_only and c != d:
