@@ -65,7 +65,7 @@ def test_solve_history_matches_oracle(case, mode, oracle_lib, somar):
     # unconverged BiCGStab bottom solve amplifies summation-order differences (see test_one_vcycle_matches_oracle)
     m = min(len(st["history"]), len(st_o["history"]), 5)
     for a, b in zip(st["history"][:m], st_o["history"][:m]):
-        assert abs(a - b) <= 0.02 * b, (st["history"], st_o["history"])
+        assert abs(a - b) <= 0.02 * b + 1e-8 * st["initial_rnorm"], (st["history"], st_o["history"])
     # converged fields agree to the solver tolerance (they are defined up to the null-space constant, which both
     # implementations pin the same way: zero-average prolongation)
     phi = fphi.get()
