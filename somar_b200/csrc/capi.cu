@@ -1,5 +1,6 @@
 // capi.cu -- the extern "C" surface declared in include/somar_b200.h.
 #include "level.hpp"
+#include <cstdlib>
 #include <cstring>
 
 namespace somar { const char* last_error(); }
@@ -91,6 +92,7 @@ int somar_level_create(const SomarLevelDesc* desc, const SomarSolverParams* para
     L->desc.box_hi = L->box_hi.data();
     L->desc.box_rank = L->box_rank.data();
     L->cx.sms = prop.multiProcessorCount;
+    if (const char* e = getenv("SOMAR_B200_FUSED")) L->use_fused = (e[0] != '0');
     int rc;
     cudaError_t ce;
     if ((ce = cudaStreamCreateWithFlags(&L->cx.stream, cudaStreamNonBlocking)) != cudaSuccess ||

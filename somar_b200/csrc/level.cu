@@ -295,7 +295,12 @@ int op_relax(SomarLevel* L, int depth, SomarField* phi, const SomarField* rhs, i
     const bool coarse = depth > 0 && depth < L->ndepths() - 1;
     ProfScope psCoarse(L, coarse ? PH_SMOOTH_COARSE : -1);
     for (int it = 0; it < iters; ++it) {
-        if (mode == SOMAR_RELAX_LEVEL_GSRB) {          // LevelGSRB::relax, GSRB.cpp:58-98
+        if (mode == SOMAR_RELAX_LEVEL_GSRB && L->use_fused && gsrb_fused_usable(dp.g, dp.m)) {
+            // both colour passes in one sweep (no exchange is due between them here)
+            ProfScope psK(L, depth == 0 ? PH_SMOOTH0_KERNEL : -1);
+            launch_gsrb_fused(L->cx, dp.g, dp.m, dp.tmp, phi->p, rhs->p);
+            std::swap(dp.tmp, phi->p);
+        } else if (mode == SOMAR_RELAX_LEVEL_GSRB) {   // LevelGSRB::relax, GSRB.cpp:58-98
             for (int pass = 0; pass < 2; ++pass) {
                 if ((rc = exchange(L, depth, phi->p, 1)) != SOMAR_OK) return rc;
                 ProfScope psK(L, depth == 0 ? PH_SMOOTH0_KERNEL : -1);

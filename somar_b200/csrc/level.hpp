@@ -65,6 +65,7 @@ struct SomarLevel {
     int bottom_iters_total = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     // phase profiler (CUDA events on the level stream; off by default)
+    bool use_fused = true;             // SOMAR_B200_FUSED=0 selects the two-pass colour kernels
     bool prof_on = false;
     struct ProfRec { int phase; cudaEvent_t a, b; };
     std::vector<ProfRec> prof;          // recorded intervals

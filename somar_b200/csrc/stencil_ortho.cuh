@@ -87,63 +87,97 @@ __device__ __forceinline__ bool on_domain_rim(const Geom& g, int i, int j, int k
     return r;
 }
 
-// One red-black update of one cell, diagonal metric.  Returns the new phi.  `pc` = current phi(c) (only used for
-// Dirichlet ghosts, which the reference fills from the pre-pass state).
+// Coefficients one red-black update reads, as VALUES (so that a kernel can prefetch them into registers).
+struct GsrbCoef {
+    double glo[3], ghi[3];   // J g^{dd} on the low / high face of the cell
+    double ji, lap, rhs;     // 1/J, lapDiag, right-hand side
+};
+
 template <int ND>
-__device__ __forceinline__ double gsrb_cell_ortho(const Geom& g, const Metric& m, const double* __restrict__ phi,
-                                                  const double* __restrict__ rhs, int i, int j, int k, long long c) {
+__device__ __forceinline__ GsrbCoef gsrb_load_coef(const Geom& g, const Metric& m, const double* __restrict__ rhs,
+                                                   long long c) {
+    GsrbCoef q;
+    q.glo[0] = m.jg[0][0][c];
+    q.ghi[0] = m.jg[0][0][c + 1];
+    q.glo[1] = m.jg[1][1][c];
+    q.ghi[1] = m.jg[1][1][c + g.sy];
+    q.glo[2] = (ND > 2) ? m.jg[2][2][c] : 0.0;
+    q.ghi[2] = (ND > 2) ? m.jg[2][2][c + g.sz] : 0.0;
+    q.ji = m.jinv[c];
+    q.lap = m.lapdiag[c];
+    q.rhs = rhs[c];
+    return q;
+}
+
+// One red-black update of one cell, diagonal metric, from VALUES: nb[d][s] = phi of the neighbour across side s of
+// direction d (any number where that side is a physical boundary), pc = the cell's own pre-pass value (only used
+// for Dirichlet ghosts, which the reference fills from the pre-pass state).  Shared by the colour-pass kernel
+// (values from global memory) and the fused red+black kernel (phi from the shared-memory planes, coefficients
+// prefetched), so that both execute the same statements in the same order.
+template <int ND>
+__device__ __forceinline__ double gsrb_update_vals(const Geom& g, const GsrbCoef& q, int i, int j, int k, double pc,
+                                                   const double (&nb)[3][2]) {
     const double sc0 = 1.0 / (g.dx[0] * g.dx[0]);
     const double sc1 = 1.0 / (g.dx[1] * g.dx[1]);
     const double sc2 = (ND > 2) ? 1.0 / (g.dx[2] * g.dx[2]) : 0.0;
-    const double* __restrict__ G0 = m.jg[0][0];
-    const double* __restrict__ G1 = m.jg[1][1];
-    const double* __restrict__ G2 = m.jg[2][2];
-    const double ji = m.jinv[c];
+    const double ji = q.ji;
     if (!on_domain_rim<ND>(g, i, j, k)) {
-        const double JDxx = sc0 * (G0[c + 1] * phi[c + 1] + G0[c] * phi[c - 1]);
-        const double JDyy = sc1 * (G1[c + g.sy] * phi[c + g.sy] + G1[c] * phi[c - g.sy]);
+        const double JDxx = sc0 * (q.ghi[0] * nb[0][1] + q.glo[0] * nb[0][0]);
+        const double JDyy = sc1 * (q.ghi[1] * nb[1][1] + q.glo[1] * nb[1][0]);
         double lphi;
         if (ND > 2) {
-            const double JDzz = sc2 * (G2[c + g.sz] * phi[c + g.sz] + G2[c] * phi[c - g.sz]);
+            const double JDzz = sc2 * (q.ghi[2] * nb[2][1] + q.glo[2] * nb[2][0]);
             lphi = g.beta * ji * (JDxx + JDyy + JDzz);
         } else {
             lphi = g.beta * ji * (JDxx + JDyy);
         }
-        return (rhs[c] - lphi) / (g.alpha + g.beta * m.lapdiag[c]);
+        return (q.rhs - lphi) / (g.alpha + g.beta * q.lap);
     }
     // rim cell: Neumann sides are dropped from the stencil and from the diagonal
     const unsigned sm = side_mask(g, i, j, k);
-    const double pc = phi[c];
     double JDlo[3] = {0.0, 0.0, 0.0}, JDhi[3] = {0.0, 0.0, 0.0};
     double lapDiag = 0.0;
-    const long long st[3] = {1, g.sy, g.sz};
     const double sc[3] = {sc0, sc1, sc2};
-    const double* __restrict__ G[3] = {G0, G1, G2};
 #pragma unroll
     for (int d = 0; d < ND; ++d) {
         const bool atB = (sm >> (2 * d)) & 1u;
         if (!(atB && g.bc[d][0] == BC_NEUM)) {
-            double nb = phi[c - st[d]];
-            if (atB && g.bc[d][0] == BC_DIRI) nb = diri_ghost_val(pc, phi[c + st[d]], 0.0, g.diriOrder);
-            JDlo[d] = G[d][c] * nb;
-            lapDiag = lapDiag - sc[d] * G[d][c];
+            double v = nb[d][0];
+            if (atB && g.bc[d][0] == BC_DIRI) v = diri_ghost_val(pc, nb[d][1], 0.0, g.diriOrder);
+            JDlo[d] = q.glo[d] * v;
+            lapDiag = lapDiag - sc[d] * q.glo[d];
         }
     }
 #pragma unroll
     for (int d = 0; d < ND; ++d) {
         const bool atB = (sm >> (2 * d + 1)) & 1u;
         if (!(atB && g.bc[d][1] == BC_NEUM)) {
-            double nb = phi[c + st[d]];
-            if (atB && g.bc[d][1] == BC_DIRI) nb = diri_ghost_val(pc, phi[c - st[d]], 0.0, g.diriOrder);
-            JDhi[d] = G[d][c + st[d]] * nb;
-            lapDiag = lapDiag - sc[d] * G[d][c + st[d]];
+            double v = nb[d][1];
+            if (atB && g.bc[d][1] == BC_DIRI) v = diri_ghost_val(pc, nb[d][0], 0.0, g.diriOrder);
+            JDhi[d] = q.ghi[d] * v;
+            lapDiag = lapDiag - sc[d] * q.ghi[d];
         }
     }
     lapDiag = lapDiag * ji;
     double s = (JDlo[0] + JDhi[0]) * sc0 + (JDlo[1] + JDhi[1]) * sc1;
     if (ND > 2) s = s + (JDlo[2] + JDhi[2]) * sc2;
     const double lphi = g.beta * ji * s;
-    return (rhs[c] - lphi) / (g.alpha + g.beta * lapDiag);
+    return (q.rhs - lphi) / (g.alpha + g.beta * lapDiag);
+}
+
+// Same, reading everything from global memory (in-place colour pass).
+template <int ND>
+__device__ __forceinline__ double gsrb_cell_ortho(const Geom& g, const Metric& m, const double* __restrict__ phi,
+                                                  const double* __restrict__ rhs, int i, int j, int k, long long c) {
+    double nb[3][2];
+    nb[0][0] = phi[c - 1];
+    nb[0][1] = phi[c + 1];
+    nb[1][0] = phi[c - g.sy];
+    nb[1][1] = phi[c + g.sy];
+    nb[2][0] = (ND > 2) ? phi[c - g.sz] : 0.0;
+    nb[2][1] = (ND > 2) ? phi[c + g.sz] : 0.0;
+    const GsrbCoef q = gsrb_load_coef<ND>(g, m, rhs, c);
+    return gsrb_update_vals<ND>(g, q, i, j, k, phi[c], nb);
 }
 
 }  // namespace somar
