@@ -8,10 +8,15 @@
 //            black update of plane k-1 on the tile             (needs NEW red of planes k-2, k-1, k)
 //            plane k-1 is final -> written to HBM (both colours, full sectors); plane k+2 is prefetched.
 // The ring cells' red values are recomputed by the neighbouring CTA (a 1-cell halo of redundant work), phi is
-// read once (+ halo, mostly L2 hits) and written once, every coefficient array is read once: ~64 B/cell/iteration.
+// read once (+ halo, mostly L2 hits) and written once, every coefficient array is read once: measured
+// 70 B/cell/iteration of DRAM traffic (profiles/).
 // Thread (t, r) owns the x-adjacent cell PAIR (2t, 2t+1) of row r of the extended tile: exactly one of the two is red
 // in any plane, and the black cell it updates in plane k-1 sits in the same column as its red cell of plane k,
 // so every thread does one red and one black update per step.
+// Latency and issue slots: the coefficients of step k+1 (9 values per update) and the phi plane k+2 are loaded
+// into registers at the top of step k and consumed one step later (software pipeline, two steps unrolled so the
+// register sets swap roles without copies); all addresses are per-thread bases advanced by one plane stride per
+// step; tiles that do not touch the domain rim skip the boundary-stencil logic (block-uniform branch).
 //
 // Out of place (phiIn -> phiOut): neighbouring CTAs read each other's halo cells of the PRE-iteration state while
 // they run concurrently, so the new values go to a second brick (the level's ping-pong partner); the traffic is
@@ -35,96 +40,154 @@ namespace somar {
 #define FPLANE (FSX * FSY)
 #define FLOADS ((FPLANE + FTHREADS - 1) / FTHREADS)
 
-__device__ __forceinline__ int fslot(int plane) { return ((plane % FSLOTS) + FSLOTS) % FSLOTS; }
+__device__ __forceinline__ int slot_dec(int s) { return s == 0 ? FSLOTS - 1 : s - 1; }
+__device__ __forceinline__ int slot_inc(int s) { return s == FSLOTS - 1 ? 0 : s + 1; }
 
-__global__ void __launch_bounds__(FTHREADS, 2) k_gsrb_fused(const Geom g, const Metric m,
-                                                          double* __restrict__ phiOut,
-                                                          const double* __restrict__ phi,
-                                                          const double* __restrict__ rhs, int kc) {
+// global index (at plane 0) of shared-plane element e of the tile whose extended origin is (x0, y0), or -1
+__device__ __forceinline__ int stage_off(const Geom& g, int e, int x0, int y0) {
+    if (e >= FPLANE) return -1;
+    const int sy_ = e / FSX, sx_ = e - sy_ * FSX;
+    const int xx = x0 - 1 + sx_, yy = y0 - 1 + sy_;
+    if (xx < -2 || xx > g.n[0] + 1 || yy < -2 || yy > g.n[1] + 1) return -1;
+    return (int)g.idx(xx, yy, 0);
+}
+
+// One step of the sweep, written as a macro so that all state stays in named registers (no closures, no local
+// arrays).  (CR, CB) = coefficients of this step's red / black update; (NR, NB) receive those of the next step.
+// Offsets are 32-bit element indices into the brick (the launcher checks that the brick has < 2^31 elements).
+#define FUSED_STEP(K, CR, NR)                                                                                     \
+    {                                                                                                             \
+        const int k_ = (K);                                                                                       \
+        const int par = (parBase + k_) & 1, parn = par ^ 1;                                                       \
+        const int sl = slot_dec(s), sh = slot_inc(s);                                                             \
+        /* software pipeline: everything step k+1 needs from HBM is requested now */                              \
+        {                                                                                                         \
+            const int p2 = k_ + 2;                                                                                \
+            const bool zin = (p2 >= -g.gh[2]) && (p2 < g.n[2] + g.gh[2]);                                         \
+            const int po = kOff + 2 * isz;                                                                        \
+            pre0 = (zin && goff0 >= 0) ? phi[goff0 + po] : 0.0;                                                   \
+            pre1 = (zin && goff1 >= 0) ? phi[goff1 + po] : 0.0;                                                   \
+            pre2 = (zin && goff2 >= 0) ? phi[goff2 + po] : 0.0;                                                   \
+        }                                                                                                         \
+        if (k_ + 1 <= k1 && k_ + 1 >= 0 && k_ + 1 < g.n[2] && ((colMask >> parn) & 1))                            \
+            NR = gsrb_load_coef<3>(g, m, rhs, cbase + parn + kOff + isz);                                         \
+        /* this step's black update (plane k-1, same column as the red one): its sectors were fetched one step   \
+           ago for the red cells next to it, so this is an L1/L2 hit that completes during the red phase */       \
+        GsrbCoef CB = GsrbCoef();                                                                                 \
+        if (k_ - 1 >= k0 && k_ - 1 < k1 && ((coreMask >> par) & 1))                                               \
+            CB = gsrb_load_coef<3>(g, m, rhs, cbase + par + kOff - isz);                                          \
+        const int ex = 2 * t + par;                                                                               \
+        const int x = x0 + ex;                                                                                    \
+        /* red update of plane k (extended tile) */                                                               \
+        if (k_ >= 0 && k_ < g.n[2] && ((colMask >> par) & 1)) {                                                   \
+            const int gk = g.g0[2] + k_;                                                                          \
+            const bool fast = !tileRim && gk != 0 && gk != g.gn[2] - 1;                                           \
+            double nb[3][2];                                                                                      \
+            nb[0][0] = sm[s][r + 1][ex];                                                                          \
+            nb[0][1] = sm[s][r + 1][ex + 2];                                                                      \
+            nb[1][0] = sm[s][r][ex + 1];                                                                          \
+            nb[1][1] = sm[s][r + 2][ex + 1];                                                                      \
+            nb[2][0] = sm[sl][r + 1][ex + 1];                                                                     \
+            nb[2][1] = sm[sh][r + 1][ex + 1];                                                                     \
+            sm[s][r + 1][ex + 1] = gsrb_update_vals<3>(g, CR, x, y, k_, sm[s][r + 1][ex + 1], nb, fast);          \
+        }                                                                                                         \
+        __syncthreads();                                                                                          \
+        /* black update of plane k-1 (core tile), then write the finished plane */                                \
+        if (k_ - 1 >= k0 && k_ - 1 < k1) {                                                                        \
+            const int kb = k_ - 1;                                                                                \
+            const int sll = slot_dec(sl);                                                                         \
+            const int cb0 = cbase + kOff - isz;                                                                   \
+            if ((coreMask >> par) & 1) {                                                                          \
+                const int gk = g.g0[2] + kb;                                                                      \
+                const bool fast = !tileRim && gk != 0 && gk != g.gn[2] - 1;                                       \
+                double nb[3][2];                                                                                  \
+                nb[0][0] = sm[sl][r + 1][ex];                                                                     \
+                nb[0][1] = sm[sl][r + 1][ex + 2];                                                                 \
+                nb[1][0] = sm[sl][r][ex + 1];                                                                     \
+                nb[1][1] = sm[sl][r + 2][ex + 1];                                                                 \
+                nb[2][0] = sm[sll][r + 1][ex + 1];                                                                \
+                nb[2][1] = sm[s][r + 1][ex + 1];                                                                  \
+                phiOut[cb0 + par] = gsrb_update_vals<3>(g, CB, x, y, kb, sm[sl][r + 1][ex + 1], nb, fast);        \
+            }                                                                                                     \
+            /* the other cell of the pair is red in plane k-1: its new value sits in shared memory */             \
+            if ((coreMask >> parn) & 1) phiOut[cb0 + parn] = sm[sl][r + 1][2 * t + parn + 1];                     \
+        }                                                                                                         \
+        /* plane k+2 -> the slot of plane k-3 (dead since the previous step) */                                   \
+        {                                                                                                         \
+            double* dst = smflat + slot_inc(sh) * FPLANE + tid;                                                   \
+            dst[0] = pre0;                                                                                        \
+            dst[FTHREADS] = pre1;                                                                                 \
+            if (tid + 2 * FTHREADS < FPLANE) dst[2 * FTHREADS] = pre2;                                            \
+        }                                                                                                         \
+        s = sh;                                                                                                   \
+        kOff += isz;                                                                                              \
+        __syncthreads();                                                                                          \
+    }
+
+static_assert(FLOADS == 3, "staging code assumes three elements per thread");
+
+__global__ void __launch_bounds__(FTHREADS, 1) k_gsrb_fused(const Geom g, const Metric m,
+                                                             double* __restrict__ phiOut,
+                                                             const double* __restrict__ phi,
+                                                             const double* __restrict__ rhs, int kc) {
     __shared__ double sm[FSLOTS][FSY][FSX];
+    double* const smflat = &sm[0][0][0];
     const int tid = threadIdx.x;
     const int t = tid % FPX, r = tid / FPX;
     const int x0 = blockIdx.x * FCX - 1;      // local x of extended column 0
     const int y0 = blockIdx.y * FCY - 1;
     const int k0 = blockIdx.z * kc;
     const int k1 = min(k0 + kc, g.n[2]);
+    const int isz = (int)g.sz;
 
-    // which plane elements this thread stages (shared-memory plane index e -> (sy, sx))
-    auto load_plane = [&](int plane, double (&v)[FLOADS]) {
-        const bool zin = (plane >= -g.gh[2]) && (plane < g.n[2] + g.gh[2]);
-#pragma unroll
-        for (int q = 0; q < FLOADS; ++q) {
-            const int e = tid + q * FTHREADS;
-            v[q] = 0.0;
-            if (e < FPLANE && zin) {
-                const int sy = e / FSX, sx = e - sy * FSX;
-                const int x = x0 - 1 + sx, y = y0 - 1 + sy;
-                if (x >= -2 && x <= g.n[0] + 1 && y >= -2 && y <= g.n[1] + 1) v[q] = phi[g.idx(x, y, plane)];
-            }
-        }
-    };
-    auto store_plane = [&](int plane, const double (&v)[FLOADS]) {
-        const int s = fslot(plane);
-#pragma unroll
-        for (int q = 0; q < FLOADS; ++q) {
-            const int e = tid + q * FTHREADS;
-            if (e < FPLANE) (&sm[s][0][0])[e] = v[q];
-        }
-    };
-
-    double pre[FLOADS];
-    for (int p = k0 - 2; p <= k0; ++p) {
-        load_plane(p, pre);
-        store_plane(p, pre);
-    }
-    __syncthreads();
-
+    // ---- per-thread constants -------------------------------------------------------------------------------
+    // phi staging: global index (at plane 0) of the three plane elements this thread copies, or -1
+    const int goff0 = stage_off(g, tid, x0, y0);
+    const int goff1 = stage_off(g, tid + FTHREADS, x0, y0);
+    const int goff2 = stage_off(g, tid + 2 * FTHREADS, x0, y0);
     const int y = y0 + r;                      // local row of this thread
     const bool yin = (y >= 0) && (y < g.n[1]);
     const bool ycore = (r >= 1) && (r <= FCY);
-    for (int k = k0 - 1; k <= k1; ++k) {
-        load_plane(k + 2, pre);                // prefetch: consumed at step k+1
-        // ---- red update of plane k (extended tile) ----
-        const int par = (g.g0[0] + x0 + g.g0[1] + y + g.g0[2] + k) & 1;   // parity of extended column 0 in this row/plane
-        const int ex = 2 * t + par;            // this thread's red cell in plane k == its black cell in plane k-1
-        const int x = x0 + ex;
-        const bool xin = (x >= 0) && (x < g.n[0]);
-        if (k >= 0 && k < g.n[2] && xin && yin) {
-            const int s = fslot(k), sl = fslot(k - 1), sh = fslot(k + 1);
-            double nb[3][2];
-            nb[0][0] = sm[s][r + 1][ex];
-            nb[0][1] = sm[s][r + 1][ex + 2];
-            nb[1][0] = sm[s][r][ex + 1];
-            nb[1][1] = sm[s][r + 2][ex + 1];
-            nb[2][0] = sm[sl][r + 1][ex + 1];
-            nb[2][1] = sm[sh][r + 1][ex + 1];
-            const long long c = g.idx(x, y, k);
-            sm[s][r + 1][ex + 1] = gsrb_update_ortho<3>(g, m, rhs, x, y, k, c, sm[s][r + 1][ex + 1], nb);
-        }
-        __syncthreads();
-        // ---- black update of plane k-1 (core tile), then write the finished plane ----
-        const int kb = k - 1;
-        if (kb >= k0 && kb < k1 && yin && ycore) {
-            const int s = fslot(kb), sl = fslot(kb - 1), sh = fslot(kb + 1);
-            const bool xcore = (ex >= 1) && (ex <= FCX);
-            if (xin && xcore) {
-                double nb[3][2];
-                nb[0][0] = sm[s][r + 1][ex];
-                nb[0][1] = sm[s][r + 1][ex + 2];
-                nb[1][0] = sm[s][r][ex + 1];
-                nb[1][1] = sm[s][r + 2][ex + 1];
-                nb[2][0] = sm[sl][r + 1][ex + 1];
-                nb[2][1] = sm[sh][r + 1][ex + 1];
-                const long long c = g.idx(x, y, kb);
-                phiOut[c] = gsrb_update_ortho<3>(g, m, rhs, x, y, kb, c, sm[s][r + 1][ex + 1], nb);
-            }
-            // the other cell of the pair is red in plane k-1: its new value sits in shared memory
-            const int eo = 2 * t + (1 - par);
-            const int xo = x0 + eo;
-            if (xo >= 0 && xo < g.n[0] && eo >= 1 && eo <= FCX) phiOut[g.idx(xo, y, kb)] = sm[s][r + 1][eo + 1];
-        }
-        store_plane(k + 2, pre);               // slot of plane k-3: dead since the previous step
-        __syncthreads();
+    const int parBase = g.g0[0] + x0 + g.g0[1] + y + g.g0[2];
+    const int cbase = (int)g.idx(x0 + 2 * t, y, 0);
+    int colMask = 0, coreMask = 0;
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+        const int ex = 2 * t + p, x = x0 + ex;
+        const bool col = yin && x >= 0 && x < g.n[0];
+        if (col) colMask |= 1 << p;
+        if (col && ycore && ex >= 1 && ex <= FCX) coreMask |= 1 << p;
+    }
+    // block-uniform: does the extended tile touch the domain rim in x or y?
+    const bool tileRim = (g.g0[0] + x0 <= 0) || (g.g0[0] + x0 + FEX - 1 >= g.gn[0] - 1) || (g.g0[1] + y0 <= 0) ||
+                         (g.g0[1] + y0 + FEY - 1 >= g.gn[1] - 1);
+
+    // ---- prologue: planes k0-2 .. k0 into the ring, coefficients of the first step ---------------------------
+    double pre0, pre1, pre2;
+    int s = ((k0 - 2) % FSLOTS + FSLOTS) % FSLOTS;
+    for (int p = k0 - 2; p <= k0; ++p) {
+        const bool zin = (p >= -g.gh[2]) && (p < g.n[2] + g.gh[2]);
+        const int po = p * isz;
+        pre0 = (zin && goff0 >= 0) ? phi[goff0 + po] : 0.0;
+        pre1 = (zin && goff1 >= 0) ? phi[goff1 + po] : 0.0;
+        pre2 = (zin && goff2 >= 0) ? phi[goff2 + po] : 0.0;
+        double* dst = smflat + s * FPLANE + tid;
+        dst[0] = pre0;
+        dst[FTHREADS] = pre1;
+        if (tid + 2 * FTHREADS < FPLANE) dst[2 * FTHREADS] = pre2;
+        s = slot_inc(s);
+    }
+    s = slot_dec(slot_dec(s));                 // slot of plane k0-1 = first red plane
+    int kOff = (k0 - 1) * isz;                 // plane offset of the current step
+    GsrbCoef A_r = GsrbCoef(), B_r = GsrbCoef();
+    {
+        const int par = (parBase + k0 - 1) & 1;
+        if (k0 - 1 >= 0 && ((colMask >> par) & 1)) A_r = gsrb_load_coef<3>(g, m, rhs, cbase + par + kOff);
+    }
+    __syncthreads();
+    for (int k = k0 - 1; k <= k1; k += 2) {
+        FUSED_STEP(k, A_r, B_r)
+        if (k + 1 <= k1) FUSED_STEP(k + 1, B_r, A_r)
     }
 }
 
@@ -132,6 +195,7 @@ bool gsrb_fused_usable(const Geom& g, const Metric& m) {
     if (!m.diagonal || g.nd != 3) return false;
     if (g.periodic[0] || g.periodic[1] || g.periodic[2]) return false;
     if (g.nbr[0] >= 0 || g.nbr[1] >= 0) return false;
+    if (g.total >= (1LL << 31)) return false;  // 32-bit brick indices
     return true;
 }
 

@@ -116,12 +116,13 @@ __device__ __forceinline__ GsrbCoef gsrb_load_coef(const Geom& g, const Metric& 
 // prefetched), so that both execute the same statements in the same order.
 template <int ND>
 __device__ __forceinline__ double gsrb_update_vals(const Geom& g, const GsrbCoef& q, int i, int j, int k, double pc,
-                                                   const double (&nb)[3][2]) {
+                                                   const double (&nb)[3][2], bool knownInterior = false) {
     const double sc0 = 1.0 / (g.dx[0] * g.dx[0]);
     const double sc1 = 1.0 / (g.dx[1] * g.dx[1]);
     const double sc2 = (ND > 2) ? 1.0 / (g.dx[2] * g.dx[2]) : 0.0;
     const double ji = q.ji;
-    if (!on_domain_rim<ND>(g, i, j, k)) {
+    // knownInterior: the caller has established (block-uniformly) that the cell is not on the domain rim
+    if (knownInterior || !on_domain_rim<ND>(g, i, j, k)) {
         const double JDxx = sc0 * (q.ghi[0] * nb[0][1] + q.glo[0] * nb[0][0]);
         const double JDyy = sc1 * (q.ghi[1] * nb[1][1] + q.glo[1] * nb[1][0]);
         double lphi;
