@@ -14,7 +14,7 @@ from typing import Optional, Sequence
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libsomar_b200.so")
+LIB_PATH = os.environ.get("SOMAR_B200_LIB", os.path.join(_HERE, "libsomar_b200.so"))   # override: A/B builds only
 
 BC_NEUM, BC_DIRI, BC_PERIODIC = 0, 1, 2
 RELAX_JACOBI, RELAX_LEVEL_GSRB, RELAX_LOOSE_GSRB, RELAX_LINE_GSRB = 0, 1, 2, 3

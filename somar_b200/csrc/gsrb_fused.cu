@@ -29,7 +29,9 @@
 namespace somar {
 
 #define FPX 32                 // pairs per row of the extended tile  -> 64 cells
+#ifndef FEY
 #define FEY 16                 // rows of the extended tile
+#endif
 #define FEX (2 * FPX)
 #define FCX (FEX - 2)          // core tile: 62 x 14
 #define FCY (FEY - 2)
@@ -126,7 +128,7 @@ __device__ __forceinline__ int stage_off(const Geom& g, int e, int x0, int y0) {
 
 static_assert(FLOADS == 3, "staging code assumes three elements per thread");
 
-__global__ void __launch_bounds__(FTHREADS, 1) k_gsrb_fused(const Geom g, const Metric m,
+__global__ void __launch_bounds__(FTHREADS, (FTHREADS <= 256 ? 2 : 1)) k_gsrb_fused(const Geom g, const Metric m,
                                                              double* __restrict__ phiOut,
                                                              const double* __restrict__ phi,
                                                              const double* __restrict__ rhs, int kc) {

@@ -233,11 +233,15 @@ int exchange(SomarLevel* L, int depth, double* x, int width) {
         for (int s = 0; s < 2; ++s)
             if (g.nbr[s] >= 0) launch_pack_y(L->cx, g, x, dp.sendbuf[s], s, width, false);
         SOMAR_NCCL(ncclGroupStart());
-        for (int s = 0; s < 2; ++s)
-            if (g.nbr[s] >= 0) {
+        // Messages between one pair of ranks match in posting order.  With two ranks and periodic y both
+        // neighbours are the SAME peer, so post by travel direction: first the rows going down (my low rows ->
+        // the peer's high ghosts), then the rows going up.
+        for (int s = 0; s < 2; ++s) {
+            if (g.nbr[s] >= 0)
                 SOMAR_NCCL(ncclSend(dp.sendbuf[s], cnt, ncclDouble, g.nbr[s], L->comm, L->cx.stream));
-                SOMAR_NCCL(ncclRecv(dp.recvbuf[s], cnt, ncclDouble, g.nbr[s], L->comm, L->cx.stream));
-            }
+            if (g.nbr[1 - s] >= 0)
+                SOMAR_NCCL(ncclRecv(dp.recvbuf[1 - s], cnt, ncclDouble, g.nbr[1 - s], L->comm, L->cx.stream));
+        }
         SOMAR_NCCL(ncclGroupEnd());
         for (int s = 0; s < 2; ++s)
             if (g.nbr[s] >= 0) launch_pack_y(L->cx, g, x, dp.recvbuf[s], s, width, true);

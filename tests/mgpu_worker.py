@@ -1,0 +1,160 @@
+"""Multi-rank parity worker (launched by tests/test_multi_rank.py through torch.distributed.run).
+
+backend nccl: one rank per GPU; every rank owns a y-slab of boxes, runs the operators through the C ABI (halo
+exchange and scalar all-reduces inside the library over NCCL), and rank 0 compares the gathered result with the
+same problem solved on a single rank.  backend gloo (CPU, no GPU): only the host-side plumbing is exercised --
+box -> rank assignment, rank-local metric slabs, rhs slabs, unique-id broadcast.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+from somar_b200 import synthetic as syn  # noqa: E402
+
+NB = 8
+SOLVE = dict(eps=1e-10, num_smooth_down=4, num_smooth_up=4, num_smooth_bottom=2, imin=0, imax=30)
+
+
+def partition(n, world):
+    boxes = syn.split_boxes(n, (1, NB, 1))
+    box_rank = [b * world // NB for b in range(NB)]
+    return boxes, box_rank
+
+
+def slab(boxes, box_rank, rank):
+    mine = [b for b in range(len(boxes)) if box_rank[b] == rank]
+    return boxes[mine[0]][0][1], boxes[mine[-1]][1][1] + 1
+
+
+def main():
+    backend = sys.argv[1]
+    map_name = sys.argv[2] if len(sys.argv) > 2 else "stretched"
+    periodic_y = len(sys.argv) > 3 and sys.argv[3] == "periodic"
+    dist.init_process_group(backend)
+    rank, world = dist.get_rank(), dist.get_world_size()
+    n = (32, 64, 16)
+    spec = syn.headline_grid(n=n, aniso=4.0, map_name=map_name, periodic=(False, periodic_y, False))
+    boxes, box_rank = partition(n, world)
+    j0, j1 = slab(boxes, box_rank, rank)
+    full = syn.build_metric(spec)
+    part = syn.build_metric(spec, yrange=(j0, j1))
+    # rank-local metric slabs are exactly the slices of the global metric
+    assert torch.equal(part.jinv, full.jinv[:, j0:j1, :])
+    for d in range(3):
+        hi = j1 + (1 if d == 1 else 0)
+        assert torch.equal(part.jgup[d], full.jgup[d][:, :, j0:hi, :]), d
+    rhs_g = syn.random_rhs(spec, full.jinv)
+    if backend == "gloo":
+        # plumbing only: the communicator id travels from rank 0 to everybody
+        buf = torch.zeros(128, dtype=torch.uint8)
+        if rank == 0:
+            buf.copy_(torch.arange(128, dtype=torch.uint8))
+        dist.broadcast(buf, 0)
+        assert bytes(buf.tolist()) == bytes(range(128))
+        # slabs tile the domain exactly once
+        cover = torch.zeros(n[1], dtype=torch.int32)
+        cover[j0:j1] += 1
+        dist.all_reduce(cover)
+        assert bool((cover == 1).all())
+        dist.barrier()
+        if rank == 0:
+            print("MGPU-OK gloo")
+        dist.destroy_process_group()
+        return
+
+    from somar_b200 import capi
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    buf = torch.zeros(128, dtype=torch.uint8, device=dev)
+    if rank == 0:
+        buf.copy_(torch.tensor(list(capi.comm_unique_id()), dtype=torch.uint8))
+    dist.broadcast(buf, 0)
+    comm_id = bytes(buf.cpu().tolist())
+    diag = spec.is_diagonal
+    per = (0, int(periodic_y), 0)
+
+    def make(nranks, rk, cid, yr):
+        lev = capi.Level(n, spec.dx, dim=3, periodic=per, is_diagonal=diag, boxes=boxes,
+                         box_rank=(box_rank if nranks > 1 else [0] * NB), params=capi.default_params(**SOLVE),
+                         device=local, rank=rk, nranks=nranks, comm_id=cid)
+        jg = [np.ascontiguousarray(j.numpy()[0] if diag else j.numpy()) for j in full.jgup]
+        lev.set_metric_global(jg, np.ascontiguousarray(full.jinv.numpy()))
+        lev.finalize()
+        return lev
+
+    lev = make(world, rank, comm_id, (j0, j1))
+    rng = np.random.default_rng(3)
+    phi_g = rng.uniform(-1, 1, size=(n[2], n[1], n[0]))
+    results = {}
+
+    def run(lv, sl):
+        out = {}
+        for d in range(min(lv.ndepths - 1, 2)):
+            info = lv.depth_info(d)
+            s0, s1 = info["local_lo"][1], info["local_hi"][1] + 1
+            shp = info["n"]
+            rg = np.random.default_rng(10 + d)
+            pg = rg.uniform(-1, 1, size=(shp[2], shp[1], shp[0]))
+            rr = rg.uniform(-1, 1, size=(shp[2], shp[1], shp[0]))
+            fp, fr, fo = lv.field(d, np.ascontiguousarray(pg[:, s0:s1])), lv.field(d, np.ascontiguousarray(rr[:, s0:s1])), lv.field(d)
+            lv.apply_op(fo, fp)
+            out[f"apply{d}"] = fo.get()
+            lv.relax(fp, fr, iters=2)
+            out[f"relax{d}"] = fp.get()
+            fc = lv.field(d + 1)
+            lv.restrict_residual(fc, fp, fr)
+            out[f"restrict{d}"] = fc.get()
+            lv.prolong_increment(fp, fc)
+            out[f"prolong{d}"] = fp.get()
+            out[f"norm{d}"] = np.array([lv.norm(fp, 0), lv.norm(fp, 2), lv.dot(fp, fr)])
+        fphi, frhs = lv.field(0), lv.field(0, np.ascontiguousarray(rhs_g.numpy()[:, sl[0]:sl[1]]))
+        st = lv.solve(fphi, frhs)
+        out["solution"] = fphi.get()
+        out["iters"] = np.array([st["iters"], st["exit_status"]])
+        out["history"] = np.array(st["history"][:6])
+        return out
+
+    mine = run(lev, (j0, j1))
+    # gather the slabs on rank 0
+    gathered = [None] * world
+    dist.gather_object(mine, gathered if rank == 0 else None, dst=0)
+    ok = True
+    if rank == 0:
+        ref_lev = make(1, 0, None, (0, n[1]))
+        ref = run(ref_lev, (0, n[1]))
+        for key in ref:
+            if key.startswith(("norm", "iters", "history")):
+                got = gathered[0][key]
+                for g in gathered[1:]:
+                    assert np.array_equal(g[key], got), f"{key} differs between ranks"
+            else:
+                got = np.concatenate([g[key] for g in gathered], axis=1)
+            want = ref[key]
+            if key.startswith(("apply", "relax", "restrict")) and diag:
+                good = np.array_equal(got, want)            # bit-exact: same arithmetic, halos instead of neighbours
+            elif key.startswith("iters"):
+                good = abs(int(got[0]) - int(want[0])) <= 1
+            else:
+                den = max(np.abs(want).max(), 1e-300)
+                tol = 1e-6 if key in ("solution", "history") else 1e-12
+                good = np.abs(got - want).max() / den <= tol
+            if not good:
+                ok = False
+                print(f"MGPU-FAIL {key}: max diff {np.abs(np.asarray(got, float) - np.asarray(want, float)).max():.3e}")
+        print("MGPU-OK nccl" if ok else "MGPU-FAILED")
+    dist.barrier()
+    dist.destroy_process_group()
+    if not ok:
+        sys.exit(1)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,40 @@
+"""N > 1 path: world_size-2 gloo run on CPU (host-side partition plumbing) and, on a box with >= 2 GPUs, the real
+NCCL path against the single-rank result."""
+import os
+import socket
+import subprocess
+import sys
+
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _launch(nproc, args, timeout=600):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+           "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), os.path.join(HERE, "mgpu_worker.py")] + args
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout)
+    return r.returncode, r.stdout + r.stderr
+
+
+def test_partition_plumbing_gloo_world2():
+    rc, out = _launch(2, ["gloo"])
+    assert rc == 0 and "MGPU-OK gloo" in out, out[-3000:]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("args", [["nccl", "stretched"], ["nccl", "stretched", "periodic"], ["nccl", "terrain"]])
+def test_two_ranks_match_one_rank_nccl(args):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    rc, out = _launch(2, args)
+    assert rc == 0 and "MGPU-OK nccl" in out, out[-4000:]
