@@ -286,7 +286,15 @@ def run_ours(a):
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
     k = prof["smooth0_kernel"]
-    per_cell = (48 if a.relax == 1 else 44) if spec.is_diagonal else (104 if a.relax == 1 else 100)
+    # algorithmic bytes per cell one launch of the depth-0 smoother kernel moves (a red+black GSRB
+    # iteration is 96 B/cell diagonal, 208 full; LineGSRB 88 / 200; a colour pass is half an iteration)
+    kname = lev.relax_kernel(0, a.relax)
+    per_cell = {"k_gsrb_ortho": 48, "k_gsrb_fused": 96, "k_gsrb_full": 104,
+                "k_line_gsrb": 44 if spec.is_diagonal else 100}[kname]
+    kdesc = {"k_gsrb_ortho": "k_gsrb_ortho<3> (depth-0 red/black colour pass, 2 launches per iteration)",
+             "k_gsrb_fused": "k_gsrb_fused (depth-0 red+black iteration in one sweep)",
+             "k_gsrb_full": "k_gsrb_full<3> (depth-0 colour pass, full metric)",
+             "k_line_gsrb": "k_line_gsrb<3> (depth-0 vertical-line colour pass)"}[kname]
     alg_bytes = per_cell * local_cells
     avg_ms = k["ms"] / max(k["count"], 1)
     achieved = alg_bytes / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
@@ -294,7 +302,7 @@ def run_ours(a):
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
         tj = json.load(open(tpath))
-        key = f"{a.map}_{grid[0]}x{grid[1]}x{grid[2]}_relax{a.relax}_gpus{world}"
+        key = f"{kname}_{a.map}_{grid[0]}x{grid[1]}x{grid[2]}_gpus{world}"
         traffic = tj.get(key, {}).get("dram_bytes_per_launch")
     bv = byte_model(schedule, spec.is_diagonal, a.relax, SOLVE["num_smooth_down"], SOLVE["num_smooth_up"])
     vcycle_gbs = bv * iters / (ms * 1e-3) / 1e9
@@ -305,11 +313,10 @@ def run_ours(a):
                 "vcycles_per_solve": iters / a.steps, "final_rel_residual": stats[-1]["final_rnorm"] / stats[-1]["initial_rnorm"],
                 "exit_status": stats[-1]["exit_status"], "bottom_iters_per_solve": stats[-1]["bottom_iters_total"],
                 "schedule": [{"n": list(s["n"]), "ratio": list(s["ratio"])} for s in schedule],
-                "model_bytes_per_vcycle": bv, "vcycle_model_gbs": vcycle_gbs * world ** 0,
+                "model_bytes_per_vcycle": bv, "vcycle_model_gbs": vcycle_gbs,
                 "vcycle_hbm_frac_per_gpu": vcycle_gbs / world / peak,
                 "phase_ms_per_solve": {n: v["ms"] / a.steps for n, v in prof.items()}}),
-            "roofline": {"bound": "hbm", "kernel": "k_gsrb_ortho<3> (depth-0 red/black colour pass)" if spec.is_diagonal
-                         else "k_gsrb_full<3> (depth-0 colour pass)", "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "roofline": {"bound": "hbm", "kernel": kdesc, "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                          "alg_bytes_per_launch": alg_bytes, "avg_launch_ms": avg_ms, "launches_timed": k["count"]},
             "clocks": clk, "gpu_launches": int(launches), "pressure_solve_ms": ms / a.steps}

@@ -25,7 +25,7 @@ SYMBOLS = [
     "somar_level_create", "somar_level_destroy", "somar_level_set_metric_fab", "somar_level_set_metric_device",
     "somar_level_finalize", "somar_level_set_alpha_beta", "somar_level_num_depths", "somar_level_depth_info",
     "somar_level_sync", "somar_level_stream", "somar_level_launch_count", "somar_level_get_metric",
-    "somar_level_profile_enable", "somar_level_profile_read",
+    "somar_level_profile_enable", "somar_level_profile_read", "somar_level_relax_kernel",
     "somar_field_create", "somar_field_destroy", "somar_field_set_fab", "somar_field_get_fab", "somar_field_set",
     "somar_field_get", "somar_apply_op", "somar_residual", "somar_precond", "somar_set_to_zero", "somar_assign",
     "somar_incr", "somar_axby", "somar_scale", "somar_norm", "somar_local_max_norm", "somar_dot", "somar_relax",
@@ -273,6 +273,13 @@ class Level:
         _ck(lib().somar_level_profile_read(self.h, cnt, ms))
         names = ["smooth0_kernel", "smooth_coarse", "restrict", "prolong", "bottom", "outer"]
         return {n: {"count": cnt[i], "ms": ms[i]} for i, n in enumerate(names)}
+
+    RELAX_KERNELS = {0: "k_gsrb_ortho", 1: "k_gsrb_fused", 2: "k_gsrb_full", 3: "k_line_gsrb", 4: "k_jacobi", -1: "none"}
+
+    def relax_kernel(self, depth=0, mode=RELAX_LEVEL_GSRB) -> str:
+        v = C.c_int()
+        _ck(lib().somar_level_relax_kernel(self.h, depth, mode, C.byref(v)))
+        return self.RELAX_KERNELS[v.value]
 
     def launches(self) -> int:
         v = C.c_longlong()

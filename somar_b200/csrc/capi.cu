@@ -251,6 +251,18 @@ int somar_level_launch_count(const SomarLevel* L, long long* n) {
     return SOMAR_OK;
 }
 
+int somar_level_relax_kernel(const SomarLevel* L, int depth, int mode, int* id) {
+    CHECK_LEVEL(L);
+    if (depth < 0 || depth >= L->ndepths() || !id) { set_error("bad depth"); return SOMAR_ERR_ARG; }
+    const Depth& dp = L->depths[depth];
+    if (mode == SOMAR_RELAX_LEVEL_GSRB)
+        *id = (L->use_fused && gsrb_fused_usable(dp.g, dp.m)) ? 1 : (dp.m.diagonal ? 0 : 2);
+    else if (mode == SOMAR_RELAX_LINE_GSRB) *id = 3;
+    else if (mode == SOMAR_RELAX_JACOBI) *id = 4;
+    else *id = -1;
+    return SOMAR_OK;
+}
+
 int somar_level_get_metric(SomarLevel* L, int depth, double* jg0, double* jg1, double* jg2, double* jinv,
                            double* lapdiag) {
     CHECK_LEVEL(L);

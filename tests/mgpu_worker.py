@@ -73,17 +73,22 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
-    buf = torch.zeros(128, dtype=torch.uint8, device=dev)
-    if rank == 0:
-        buf.copy_(torch.tensor(list(capi.comm_unique_id()), dtype=torch.uint8))
-    dist.broadcast(buf, 0)
-    comm_id = bytes(buf.cpu().tolist())
+
+    def new_comm_id():
+        buf = torch.zeros(128, dtype=torch.uint8, device=dev)
+        if rank == 0:
+            buf.copy_(torch.tensor(list(capi.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(buf, 0)
+        return bytes(buf.cpu().tolist())
+
+    comm_id = new_comm_id()
     diag = spec.is_diagonal
     per = (0, int(periodic_y), 0)
 
-    def make(nranks, rk, cid, yr):
+    def make(nranks, rk, cid, yr, **extra):
         lev = capi.Level(n, spec.dx, dim=3, periodic=per, is_diagonal=diag, boxes=boxes,
-                         box_rank=(box_rank if nranks > 1 else [0] * NB), params=capi.default_params(**SOLVE),
+                         box_rank=(box_rank if nranks > 1 else [0] * NB),
+                         params=capi.default_params(**{**SOLVE, **extra}),
                          device=local, rank=rk, nranks=nranks, comm_id=cid)
         jg = [np.ascontiguousarray(j.numpy()[0] if diag else j.numpy()) for j in full.jgup]
         lev.set_metric_global(jg, np.ascontiguousarray(full.jinv.numpy()))
@@ -115,14 +120,21 @@ def main():
             lv.prolong_increment(fp, fc)
             out[f"prolong{d}"] = fp.get()
             out[f"norm{d}"] = np.array([lv.norm(fp, 0), lv.norm(fp, 2), lv.dot(fp, fr)])
-        fphi, frhs = lv.field(0), lv.field(0, np.ascontiguousarray(rhs_g.numpy()[:, sl[0]:sl[1]]))
-        st = lv.solve(fphi, frhs)
-        out["solution"] = fphi.get()
-        out["iters"] = np.array([st["iters"], st["exit_status"]])
-        out["history"] = np.array(st["history"][:6])
+        out.update(solve(lv, sl, ""))
         return out
 
+    def solve(lv, sl, tag):
+        fphi, frhs = lv.field(0), lv.field(0, np.ascontiguousarray(rhs_g.numpy()[:, sl[0]:sl[1]]))
+        st = lv.solve(fphi, frhs)
+        return {"solution" + tag: fphi.get(), "iters" + tag: np.array([st["iters"], st["exit_status"]]),
+                "history" + tag: np.array(st["history"][:6])}
+
+    # strict variant: no BiCGStab at the bottom (two relaxations only), 3 V-cycles -- nothing amplifies the
+    # reduction-order differences between one and two ranks, so the fields must agree to rounding
+    STRICT = dict(bottom_imax=0, imax=3)
     mine = run(lev, (j0, j1))
+    lev_s = make(world, rank, new_comm_id(), (j0, j1), **STRICT)
+    mine.update(solve(lev_s, (j0, j1), "_strict"))
     # gather the slabs on rank 0
     gathered = [None] * world
     dist.gather_object(mine, gathered if rank == 0 else None, dst=0)
@@ -130,6 +142,7 @@ def main():
     if rank == 0:
         ref_lev = make(1, 0, None, (0, n[1]))
         ref = run(ref_lev, (0, n[1]))
+        ref.update(solve(make(1, 0, None, (0, n[1]), **STRICT), (0, n[1]), "_strict"))
         for key in ref:
             if key.startswith(("norm", "iters", "history")):
                 got = gathered[0][key]
@@ -142,9 +155,13 @@ def main():
                 good = np.array_equal(got, want)            # bit-exact: same arithmetic, halos instead of neighbours
             elif key.startswith("iters"):
                 good = abs(int(got[0]) - int(want[0])) <= 1
+            elif key == "history":
+                # same tolerance as the single-rank history test (tests/test_gpu_solve.py): the unconverged
+                # BiCGStab bottom amplifies summation-order differences
+                good = bool(np.all(np.abs(got - want) <= 0.02 * np.abs(want) + 1e-8 * abs(want[0])))
             else:
                 den = max(np.abs(want).max(), 1e-300)
-                tol = 1e-6 if key in ("solution", "history") else 1e-12
+                tol = (1e-6 if diag else 1e-4) if key == "solution" else (1e-10 if "strict" in key else 1e-12)
                 good = np.abs(got - want).max() / den <= tol
             if not good:
                 ok = False
