@@ -25,6 +25,13 @@ void launch_gsrb(Ctx& cx, const Geom& g, const Metric& m, double* phi, const dou
 bool gsrb_fused_usable(const Geom& g, const Metric& m);
 void launch_gsrb_fused(Ctx& cx, const Geom& g, const Metric& m, double* phiOut, const double* phiIn,
                        const double* rhs);
+// the same sweep fed by TMA (cp.async.bulk.tensor) through mbarrier-signalled shared-memory rings; see gsrb_tma.cu.
+// `cache` keeps the tensor maps of the depth's coefficient arrays between launches (free with gsrb_tma_free).
+// Returns false (nothing launched) if the tensor maps cannot be built.
+bool gsrb_tma_usable(const Geom& g, const Metric& m);
+bool launch_gsrb_tma(Ctx& cx, const Geom& g, const Metric& m, double* phiOut, const double* phiIn, const double* rhs,
+                     void** cache);
+void gsrb_tma_free(void* cache);
 // full metric: out-of-place pass, phiOut gets the updated colour AND a copy of the other colour
 void launch_gsrb_full(Ctx& cx, const Geom& g, const Metric& m, double* phiOut, const double* phiIn,
                       const double* rhs, int pass);

@@ -153,3 +153,35 @@ def test_fab_round_trip(name, oracle_lib, somar):
         out = np.zeros((hi[2] - lo[2] + 1, hi[1] - lo[1] + 1, hi[0] - lo[0] + 1))
         f.get_fab(out, lo, hi, lo, hi)
         assert np.array_equal(out, x[lo[2]:hi[2] + 1, lo[1]:hi[1] + 1, lo[0]:hi[0] + 1])
+
+
+# --- the three implementations of a LevelGSRB iteration must be bit-identical -----------------------------------
+# SOMAR_B200_FUSED = 0: two k_gsrb_ortho colour passes, 1: k_gsrb_fused (register pipeline), 2: k_gsrb_tma
+# (TMA + mbarrier rings).  Sizes straddle the 62 x 14 core tile and the 64-plane z chunk; BCs exercise the rim path.
+VARIANT_CASES = {
+    "tile_edges": dict(n=(70, 45, 37), map_name="stretched", aniso=4.0),
+    "exact_tile": dict(n=(62, 14, 8), map_name="stretched", aniso=2.0),
+    "thin": dict(n=(128, 30, 4), map_name="stretched", aniso=1.0),
+    "two_chunks": dict(n=(96, 40, 72), map_name="stretched", aniso=8.0),
+    "dirichlet": dict(n=(66, 30, 20), map_name="stretched", aniso=4.0, bc_type=[1, 0, 0, 1, 0, 1],
+                      bc_value=[0, 0, 0, 0, 0, 0.5]),
+    "helmholtz": dict(n=(64, 32, 16), map_name="stretched", aniso=4.0, alpha=1.0, beta=-0.05),
+}
+
+
+@pytest.mark.parametrize("name", list(VARIANT_CASES))
+def test_gsrb_kernel_variants_bit_identical(name, oracle_lib, somar, monkeypatch):
+    pb = Problem(**VARIANT_CASES[name])
+    phi, rhs = pb.rand(), pb.rand()
+    out = {}
+    for variant, kernel in (("0", "k_gsrb_ortho"), ("1", "k_gsrb_fused"), ("2", "k_gsrb_tma")):
+        monkeypatch.setenv("SOMAR_B200_FUSED", variant)
+        lev = pb.level(somar, relaxMode=1, maxDepth=0)
+        assert lev.relax_kernel(0, 1) == kernel
+        fphi, frhs = lev.field(0, phi), lev.field(0, rhs)
+        lev.relax(fphi, frhs, iters=3)
+        out[variant] = fphi.get()
+        lev.destroy()
+    want = pb.oracle(oracle_lib, relaxMode=1, maxDepth=0).relax(phi, rhs, iters=3, depth=0)
+    for variant in out:
+        assert np.array_equal(out[variant], want), f"variant {variant}: rel err {rel_err(out[variant], want):.3e}"
