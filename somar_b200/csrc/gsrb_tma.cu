@@ -1,33 +1,38 @@
 // gsrb_tma.cu -- the fused red+black Gauss-Seidel ITERATION of gsrb_fused.cu (same tile, same z-march, same
-// arithmetic: bit-identical results) with the B200 data path: every byte comes from HBM through TMA
-// (cp.async.bulk.tensor.3d) into multi-stage shared-memory rings, completion is signalled on mbarriers, and the
-// 512 compute threads never issue a global LOAD.
+// arithmetic: bit-identical results) with the B200 data path: every byte comes from HBM through the TMA engine's
+// bulk copies (cp.async.bulk global -> shared, SASS UBLKCP) into multi-stage shared-memory rings, completion is
+// signalled on mbarriers (complete_tx), and the 512 compute threads never issue a global LOAD.
+//
+// (The tiled flavour, cp.async.bulk.tensor with a CUtensorMap, raises "illegal instruction" on this pool's B200
+// boxes for every descriptor form tried -- tests/cuda/tma_probe.cu, modes 0-16 -- while plain bulk copies work; a
+// tile row is contiguous in the brick, so one bulk copy per row does the same job: 115 copies of 528 B per step,
+// issued by the 32 lanes of the producer warp.)
 //
 // Why (profiles/r1_ncu_k_gsrb_fused_v5.txt): the register-prefetch version is latency/barrier bound -- 63 % of
 // the HBM peak, issue slots 33 % busy, top stalls "barrier" and "long scoreboard": 16 warps run in lock step
 // (two __syncthreads per plane) and the registers can hold only one step of loads in flight.  Here
-//   * one producer thread (warp 16) keeps the loads of the next step(s) in flight at all times:
-//       phi planes      ring of 5  (66 x 18 box incl. the 1-cell ring), plane k+3 is requested at the end of step k
-//       coefficients    ring of 3  (J g^xx 66x16, J g^yy 64x17, 1/J, lapDiag, rhs 64x16), stage k+2
-//       J g^zz planes   ring of 4  (64x16; plane k is the low z-face of cell plane k), plane k+3
+//   * the producer warp keeps the loads of the next step(s) in flight at all times:
+//       phi planes      ring of 5  (18 rows x 66: the extended tile + 1-cell ring), plane k+3 requested at step k
+//       coefficients    ring of 3  (J g^xx 16 rows, J g^yy 17 rows, 1/J, lapDiag, rhs 16 rows; all 66 wide), stage k+2
+//       J g^zz planes   ring of 4  (16 rows x 66; plane k is the low z-face of cell plane k), plane k+3
+//     every row starts at x0-1, which is 16-byte aligned in the brick (SOMAR_XO = 4, even tile pitch);
 //   * there is no CTA-wide barrier in the steady state.  The only cross-thread dependence of the sweep is
 //     "black update of plane k reads the red values of plane k written by OTHER threads one step earlier"
 //     (its z-neighbours are the thread's own red cells), so a split barrier does it: every warp ARRIVES on
 //     `redDone` after its red update of step k and WAITS for it at the top of step k+1, with the black update of
 //     plane k-1 and the stores in between;
 //   * a ring slot is handed back to the producer through two alternating `empty` mbarriers.
-// Shared memory: 5 x 9.4 KB + 3 x 40.75 KB + 4 x 8 KB = 201 KB, one CTA (544 threads) per SM.
+// Shared memory: 5 x 9.4 KB + 3 x 41.8 KB + 4 x 8.25 KB = 205 KB, one CTA (544 threads) per SM.
 //
 // Step k of a CTA (k = k0-1 .. k1), consumers:
 //   wait redDone(k-1), full(phi k+1), full(coef k), full(Jgzz k+1)
 //   red update of plane k on the 64x16 extended tile (in place in the phi ring)       -> arrive redDone(k)
 //   black update of plane k-1 on the 62x14 core tile -> HBM, together with the red values of plane k-1
 //   fence.proxy.async; arrive empty(k)   => producer: phi plane k-2, coef stage k-1, Jgzz plane k-1 are dead
-#include <cuda.h>
 #include <cuda_runtime.h>
 
 #include <cstdint>
-#include <cstdio>
+#include <cstdlib>
 
 #include "kernels.hpp"
 #include "stencil_ortho.cuh"
@@ -38,36 +43,29 @@ namespace {
 
 constexpr int EX = 64, EY = 16;          // extended tile (cells)
 constexpr int CX = EX - 2, CY = EY - 2;  // core tile 62 x 14
-constexpr int PX = EX + 2, PY = EY + 2;  // phi plane in shared memory 66 x 18
+constexpr int PX = EX + 2, PY = EY + 2;  // rows are 66 doubles wide: column c <-> x = x0 - 1 + c
 constexpr int NPHI = 5, NCF = 3, NZF = 4;
 constexpr int CONSUMERS = (EX / 2) * EY; // 512: thread = x-pair of one row
-constexpr int NTHREADS = CONSUMERS + 32; // + producer warp
+constexpr int MAXPROD = 7;               // producer warps (lane 0 of each issues copies)
+constexpr int NTHREADS = CONSUMERS + 32 * MAXPROD;
 constexpr int NWARPS = CONSUMERS / 32;
+constexpr int ROWB = PX * 8;             // 528 bytes per row copy
 
-constexpr int PHI_BYTES = PX * PY * 8;         // 9504 bytes land per plane
-constexpr int PHI_SLOT = 9600;                 // slot pitch, multiple of 128
-constexpr int JG0_BYTES = EY * PX * 8;         // 66 columns: column 64 is the high face of the last cell
-constexpr int JG1_BYTES = (EY + 1) * EX * 8;   // 17 rows
-constexpr int CC_BYTES = EY * EX * 8;
-constexpr int CF_BYTES = JG0_BYTES + JG1_BYTES + 3 * CC_BYTES;   // 41728
+constexpr int PHI_SLOT = 9600;           // 18 rows x 528 B = 9504, padded to a multiple of 128
+// coefficient stage: row offsets of the five arrays
+constexpr int R_JG0 = 0, R_JG1 = R_JG0 + EY, R_JI = R_JG1 + EY + 1, R_LAP = R_JI + EY, R_RHS = R_LAP + EY;
+constexpr int CF_ROWS = R_RHS + EY;      // 81
+constexpr int CF_BYTES = CF_ROWS * ROWB; // 42768
+constexpr int ZF_BYTES = EY * ROWB;      // 8448
 constexpr int OFF_PHI = 0;
 constexpr int OFF_CF = OFF_PHI + NPHI * PHI_SLOT;
 constexpr int OFF_ZF = OFF_CF + NCF * CF_BYTES;
-constexpr int OFF_BAR = OFF_ZF + NZF * CC_BYTES;
+constexpr int OFF_BAR = OFF_ZF + NZF * ZF_BYTES;
 constexpr int NBAR = NPHI + NCF + NZF + 1 + 2;
 constexpr int SMEM_BYTES = OFF_BAR + NBAR * 8;
-static_assert(OFF_CF % 128 == 0 && OFF_ZF % 128 == 0 && OFF_BAR % 8 == 0, "TMA destinations must be 128-byte aligned");
-static_assert(JG0_BYTES % 128 == 0 && JG1_BYTES % 128 == 0 && CC_BYTES % 128 == 0 && CF_BYTES % 128 == 0, "alignment");
+static_assert(OFF_CF % 16 == 0 && OFF_ZF % 16 == 0 && OFF_BAR % 8 == 0 && ROWB % 16 == 0, "bulk copies need 16-byte alignment");
 static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
-
-struct CfStage {
-    double jg0[EY][PX];
-    double jg1[EY + 1][EX];
-    double ji[EY][EX];
-    double lap[EY][EX];
-    double rhs[EY][EX];
-};
-static_assert(sizeof(CfStage) == CF_BYTES, "stage layout");
+static_assert(PY + CF_ROWS + EY == 115, "row copies per steady-state step");
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -96,20 +94,24 @@ __device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity) {
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
-__device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* tm, int c0, int c1, int c2, uint64_t* bar) {
-    asm volatile(
-        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
-        ::"r"(smem_u32(dst)), "l"(tm), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar))
-        : "memory");
+// one row: global -> shared through the TMA engine, completion counted in bytes on `bar`
+__device__ __forceinline__ void bulk_row(void* dst, const double* src, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(ROWB), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+// rows rr in [0, nrows) of a tile segment starting at local row yStart that exist in the brick
+__device__ __forceinline__ int rows_lo(const Geom& g, int yStart) { return max(0, -g.gh[1] - yStart); }
+__device__ __forceinline__ int rows_hi(const Geom& g, int yStart, int nrows) {
+    return min(nrows, g.n[1] + g.gh[1] - yStart);
 }
 
 }  // namespace
 
 __global__ void __launch_bounds__(NTHREADS, 1)
-k_gsrb_tma(const __grid_constant__ CUtensorMap tmPhi, const __grid_constant__ CUtensorMap tmJg0,
-           const __grid_constant__ CUtensorMap tmJg1, const __grid_constant__ CUtensorMap tmJg2,
-           const __grid_constant__ CUtensorMap tmJi, const __grid_constant__ CUtensorMap tmLap,
-           const __grid_constant__ CUtensorMap tmRhs, const Geom g, double* __restrict__ phiOut, int kc) {
+k_gsrb_tma(const Geom g, const Metric m, double* __restrict__ phiOut, const double* __restrict__ phi,
+           const double* __restrict__ rhs, int kc, int nprod, int noload) {
     extern __shared__ __align__(1024) unsigned char smem[];
     uint64_t* const bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
     uint64_t* const fullPhi = bars;
@@ -125,7 +127,9 @@ k_gsrb_tma(const __grid_constant__ CUtensorMap tmPhi, const __grid_constant__ CU
     const int k1 = min(k0 + kc, g.n[2]);
 
     if (tid == 0) {
-        for (int i = 0; i < NPHI + NCF + NZF; ++i) mbar_init(bars + i, 1);
+        for (int i = 0; i < NPHI; ++i) mbar_init(fullPhi + i, nprod);
+        for (int i = 0; i < NCF; ++i) mbar_init(fullCf + i, nprod);
+        for (int i = 0; i < NZF; ++i) mbar_init(fullZf + i, nprod);
         mbar_init(redDone, NWARPS);
         mbar_init(empty, NWARPS);
         mbar_init(empty + 1, NWARPS);
@@ -136,48 +140,75 @@ k_gsrb_tma(const __grid_constant__ CUtensorMap tmPhi, const __grid_constant__ CU
 
     if (tid >= CONSUMERS) {
         // ---------------------------------------------------------------------------------------------------
-        // producer: one thread
+        // producers: lane 0 of each producer warp.  The 115 row copies of a step form one flat list
+        //   [phi 18][J g^xx 16][J g^yy 17][1/J 16][lapDiag 16][rhs 16][J g^zz 16]
+        // cut into nprod equal ranges; every producer arrives once per phase on each full barrier with the bytes
+        // it is about to issue for it (a bulk copy is a per-warp instruction, so one thread issues in a uniform
+        // loop and the producers run in parallel on different schedulers).
         // ---------------------------------------------------------------------------------------------------
-        if (tid != CONSUMERS) return;
-        const int cxP = x0 - 1 + g.gh[0], cyP = y0 - 1 + g.gh[1];   // phi box origin (allocation coordinates)
-        const int cxC = x0 + g.gh[0], cyC = y0 + g.gh[1];           // coefficient box origin
-        const int cz = g.gh[2];
-        auto issue_phi = [&](int p) {
+        if ((tid & 31) != 0) return;
+        const int pw = (tid - CONSUMERS) >> 5;
+        const int qa = (pw * 115) / nprod, qb = ((pw + 1) * 115) / nprod;   // my rows of the flat list
+        const long long rowBase = g.idx(x0 - 1, 0, 0);   // element offset of (x0-1, y = 0, k = 0)
+        auto plane_ok = [&](int p) { return p >= -g.gh[2] && p < g.n[2] + g.gh[2]; };
+        // rows [lo, hi) of segment `s0` (flat start s0, nrows rows, first local y = ys) that are mine and exist
+        auto my_lo = [&](int s0, int ys) { return max(max(qa - s0, 0), -g.gh[1] - ys); };
+        auto my_hi = [&](int s0, int nrows, int ys) { return min(min(qb - s0, nrows), g.n[1] + g.gh[1] - ys); };
+        const int loP = my_lo(0, y0 - 1), hiP = my_hi(0, PY, y0 - 1);
+        const int lo0 = my_lo(18, y0), hi0 = my_hi(18, EY, y0);
+        const int lo1 = my_lo(34, y0), hi1 = my_hi(34, EY + 1, y0);
+        const int lo2 = my_lo(51, y0), hi2 = my_hi(51, EY, y0);
+        const int lo3 = my_lo(67, y0), hi3 = my_hi(67, EY, y0);
+        const int lo4 = my_lo(83, y0), hi4 = my_hi(83, EY, y0);
+        const int loZ = my_lo(99, y0), hiZ = my_hi(99, EY, y0);
+        const int nPhi = max(0, hiP - loP), nZf = max(0, hiZ - loZ);
+        const int nCf = max(0, hi0 - lo0) + max(0, hi1 - lo1) + max(0, hi2 - lo2) + max(0, hi3 - lo3) + max(0, hi4 - lo4);
+        auto arm = [&](uint64_t* bar, bool ok, int rows) {
+            if (ok && rows > 0 && !noload) mbar_expect_tx(bar, rows * ROWB); else mbar_arrive(bar);
+        };
+        auto seg = [&](const double* base, int p, int yStart, unsigned char* dst, int lo, int hi, uint64_t* bar) {
+            if (noload) return;
+            const double* src = base + rowBase + (long long)p * g.sz + (long long)(yStart + lo) * g.sy;
+            unsigned char* d = dst + lo * ROWB;
+            for (int rr = lo; rr < hi; ++rr, src += g.sy, d += ROWB) bulk_row(d, src, bar);
+        };
+        auto load_phi = [&](int p) {
             const int slot = (p - (k0 - 2)) % NPHI;
-            mbar_expect_tx(fullPhi + slot, PHI_BYTES);
-            tma_load_3d(smem + OFF_PHI + slot * PHI_SLOT, &tmPhi, cxP, cyP, p + cz, fullPhi + slot);
+            const bool ok = plane_ok(p);
+            arm(fullPhi + slot, ok, nPhi);
+            if (ok) seg(phi, p, y0 - 1, smem + OFF_PHI + slot * PHI_SLOT, loP, hiP, fullPhi + slot);
         };
-        auto issue_cf = [&](int s) {
+        auto load_cf = [&](int s) {
             const int slot = (s - (k0 - 1)) % NCF;
-            CfStage* st = reinterpret_cast<CfStage*>(smem + OFF_CF + slot * CF_BYTES);
-            mbar_expect_tx(fullCf + slot, CF_BYTES);
-            tma_load_3d(st->jg0, &tmJg0, cxC, cyC, s + cz, fullCf + slot);
-            tma_load_3d(st->jg1, &tmJg1, cxC, cyC, s + cz, fullCf + slot);
-            tma_load_3d(st->ji, &tmJi, cxC, cyC, s + cz, fullCf + slot);
-            tma_load_3d(st->lap, &tmLap, cxC, cyC, s + cz, fullCf + slot);
-            tma_load_3d(st->rhs, &tmRhs, cxC, cyC, s + cz, fullCf + slot);
+            unsigned char* st = smem + OFF_CF + slot * CF_BYTES;
+            uint64_t* bar = fullCf + slot;
+            const bool ok = plane_ok(s);
+            arm(bar, ok, nCf);
+            if (!ok) return;
+            seg(m.jg[0][0], s, y0, st + R_JG0 * ROWB, lo0, hi0, bar);
+            seg(m.jg[1][1], s, y0, st + R_JG1 * ROWB, lo1, hi1, bar);
+            seg(m.jinv, s, y0, st + R_JI * ROWB, lo2, hi2, bar);
+            seg(m.lapdiag, s, y0, st + R_LAP * ROWB, lo3, hi3, bar);
+            seg(rhs, s, y0, st + R_RHS * ROWB, lo4, hi4, bar);
         };
-        auto issue_zf = [&](int p) {
+        auto load_zf = [&](int p) {
             const int slot = (p - (k0 - 1)) % NZF;
-            mbar_expect_tx(fullZf + slot, CC_BYTES);
-            tma_load_3d(smem + OFF_ZF + slot * CC_BYTES, &tmJg2, cxC, cyC, p + cz, fullZf + slot);
+            const bool ok = plane_ok(p);
+            arm(fullZf + slot, ok, nZf);
+            if (ok) seg(m.jg[2][2], p, y0, smem + OFF_ZF + slot * ZF_BYTES, loZ, hiZ, fullZf + slot);
         };
         // prologue: everything steps k0-1 and k0 need
-        issue_phi(k0 - 2);
-        issue_phi(k0 - 1);
-        issue_phi(k0);
-        issue_zf(k0 - 1);
-        issue_zf(k0);
-        issue_cf(k0 - 1);
-        issue_phi(k0 + 1);
-        issue_zf(k0 + 1);
-        if (k0 <= k1) issue_cf(k0);
+        load_phi(k0 - 2); load_phi(k0 - 1); load_phi(k0);
+        load_zf(k0 - 1); load_zf(k0);
+        load_cf(k0 - 1);
+        load_phi(k0 + 1); load_zf(k0 + 1);
+        load_cf(k0);
         for (int k = k0 - 1, j = 0; k + 3 <= k1 + 1; ++k, ++j) {
             mbar_wait(empty + (j & 1), (j >> 1) & 1);   // all consumers are done with step k
             fence_proxy_async();
-            if (k + 3 <= k1 + 1) issue_phi(k + 3);
-            if (k + 2 <= k1) issue_cf(k + 2);
-            if (k + 3 <= k1 + 1) issue_zf(k + 3);
+            load_phi(k + 3);
+            load_zf(k + 3);
+            if (k + 2 <= k1) load_cf(k + 2);
         }
         return;
     }
@@ -203,8 +234,8 @@ k_gsrb_tma(const __grid_constant__ CUtensorMap tmPhi, const __grid_constant__ CU
     // block-uniform: does the extended tile touch the domain rim in x or y?
     const bool tileRim = (g.g0[0] + x0 <= 0) || (g.g0[0] + x0 + EX - 1 >= g.gn[0] - 1) || (g.g0[1] + y0 <= 0) ||
                          (g.g0[1] + y0 + EY - 1 >= g.gn[1] - 1);
-    const int ctr = (r + 1) * PX + 1;   // + ex: this thread's cell in a phi plane
-    const int cfi = r * EX;             // + ex: this thread's cell in a 64-wide coefficient plane
+    const int ctr = (r + 1) * PX + 1;   // + ex: this thread's cell in a phi plane (rows start at y0-1)
+    const int cfi = r * PX + 1;         // + ex: this thread's cell in a coefficient plane (rows start at y0)
 
     mbar_wait(fullPhi + 0, 0);   // planes k0-2, k0-1
     mbar_wait(fullPhi + 1, 0);
@@ -220,11 +251,11 @@ k_gsrb_tma(const __grid_constant__ CUtensorMap tmPhi, const __grid_constant__ CU
         const double* const Pm = reinterpret_cast<const double*>(smem + OFF_PHI + (j % NPHI) * PHI_SLOT);
         const double* const Pp = reinterpret_cast<const double*>(smem + OFF_PHI + ((j + 2) % NPHI) * PHI_SLOT);
         const double* const Pmm = reinterpret_cast<const double*>(smem + OFF_PHI + ((j + 4) % NPHI) * PHI_SLOT);
-        const double* const Zk = reinterpret_cast<const double*>(smem + OFF_ZF + (j % NZF) * CC_BYTES);
-        const double* const Zp = reinterpret_cast<const double*>(smem + OFF_ZF + ((j + 1) % NZF) * CC_BYTES);
-        const double* const Zm = reinterpret_cast<const double*>(smem + OFF_ZF + ((j + 3) % NZF) * CC_BYTES);
-        const CfStage* const C = reinterpret_cast<const CfStage*>(smem + OFF_CF + (j % NCF) * CF_BYTES);
-        const CfStage* const Cm = reinterpret_cast<const CfStage*>(smem + OFF_CF + ((j + 2) % NCF) * CF_BYTES);
+        const double* const Zk = reinterpret_cast<const double*>(smem + OFF_ZF + (j % NZF) * ZF_BYTES);
+        const double* const Zp = reinterpret_cast<const double*>(smem + OFF_ZF + ((j + 1) % NZF) * ZF_BYTES);
+        const double* const Zm = reinterpret_cast<const double*>(smem + OFF_ZF + ((j + 3) % NZF) * ZF_BYTES);
+        const double* const C = reinterpret_cast<const double*>(smem + OFF_CF + (j % NCF) * CF_BYTES);
+        const double* const Cm = reinterpret_cast<const double*>(smem + OFF_CF + ((j + 2) % NCF) * CF_BYTES);
 
         const int par = (parBase + k) & 1, parn = par ^ 1;
         const int ex = 2 * t + par;
@@ -233,16 +264,17 @@ k_gsrb_tma(const __grid_constant__ CUtensorMap tmPhi, const __grid_constant__ CU
         if (k >= 0 && k < g.n[2] && ((colMask >> par) & 1)) {
             const int gk = g.g0[2] + k;
             const bool fast = !tileRim && gk != 0 && gk != g.gn[2] - 1;
+            const int c = cfi + ex;
             GsrbCoef q;
-            q.glo[0] = C->jg0[r][ex];
-            q.ghi[0] = C->jg0[r][ex + 1];
-            q.glo[1] = C->jg1[r][ex];
-            q.ghi[1] = C->jg1[r + 1][ex];
-            q.glo[2] = Zk[cfi + ex];
-            q.ghi[2] = Zp[cfi + ex];
-            q.ji = C->ji[r][ex];
-            q.lap = C->lap[r][ex];
-            q.rhs = C->rhs[r][ex];
+            q.glo[0] = C[R_JG0 * PX + c];
+            q.ghi[0] = C[R_JG0 * PX + c + 1];
+            q.glo[1] = C[R_JG1 * PX + c];
+            q.ghi[1] = C[R_JG1 * PX + c + PX];
+            q.glo[2] = Zk[c];
+            q.ghi[2] = Zp[c];
+            q.ji = C[R_JI * PX + c];
+            q.lap = C[R_LAP * PX + c];
+            q.rhs = C[R_RHS * PX + c];
             double nb[3][2];
             nb[0][0] = Pk[ctr + ex - 1];
             nb[0][1] = Pk[ctr + ex + 1];
@@ -262,16 +294,17 @@ k_gsrb_tma(const __grid_constant__ CUtensorMap tmPhi, const __grid_constant__ CU
             if ((coreMask >> par) & 1) {
                 const int gk = g.g0[2] + kb;
                 const bool fast = !tileRim && gk != 0 && gk != g.gn[2] - 1;
+                const int c = cfi + ex;
                 GsrbCoef q;
-                q.glo[0] = Cm->jg0[r][ex];
-                q.ghi[0] = Cm->jg0[r][ex + 1];
-                q.glo[1] = Cm->jg1[r][ex];
-                q.ghi[1] = Cm->jg1[r + 1][ex];
-                q.glo[2] = Zm[cfi + ex];
-                q.ghi[2] = Zk[cfi + ex];
-                q.ji = Cm->ji[r][ex];
-                q.lap = Cm->lap[r][ex];
-                q.rhs = Cm->rhs[r][ex];
+                q.glo[0] = Cm[R_JG0 * PX + c];
+                q.ghi[0] = Cm[R_JG0 * PX + c + 1];
+                q.glo[1] = Cm[R_JG1 * PX + c];
+                q.ghi[1] = Cm[R_JG1 * PX + c + PX];
+                q.glo[2] = Zm[c];
+                q.ghi[2] = Zk[c];
+                q.ji = Cm[R_JI * PX + c];
+                q.lap = Cm[R_LAP * PX + c];
+                q.rhs = Cm[R_RHS * PX + c];
                 double nb[3][2];
                 nb[0][0] = Pm[ctr + ex - 1];
                 nb[0][1] = Pm[ctr + ex + 1];
@@ -291,61 +324,17 @@ k_gsrb_tma(const __grid_constant__ CUtensorMap tmPhi, const __grid_constant__ CU
     }
 }
 
-// ---------------------------------------------------------------------------------------------------------------
-// host side: tensor maps
-// ---------------------------------------------------------------------------------------------------------------
-namespace {
-
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-EncodeTiledFn encode_fn() {
-    static EncodeTiledFn fn = nullptr;
-    static bool tried = false;
-    if (!tried) {
-        tried = true;
-        void* p = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
-            q == cudaDriverEntryPointSuccess)
-            fn = reinterpret_cast<EncodeTiledFn>(p);
-        else
-            (void)cudaGetLastError();
-    }
-    return fn;
-}
-
-// 3-D map over one brick array: dims (pitch, rows, planes), box (bx, by, 1)
-bool make_map(CUtensorMap* tm, const Geom& g, const double* base, int bx, int by) {
-    EncodeTiledFn fn = encode_fn();
-    if (!fn) return false;
-    const cuuint64_t dims[3] = {(cuuint64_t)g.sy, (cuuint64_t)(g.n[1] + 2 * g.gh[1]), (cuuint64_t)(g.n[2] + 2 * g.gh[2])};
-    const cuuint64_t strides[2] = {(cuuint64_t)g.sy * 8, (cuuint64_t)g.sz * 8};
-    const cuuint32_t box[3] = {(cuuint32_t)bx, (cuuint32_t)by, 1};
-    const cuuint32_t es[3] = {1, 1, 1};
-    return fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, const_cast<double*>(base), dims, strides, box, es,
-              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
-}
-
-struct TmaCache {
-    CUtensorMap jg0, jg1, jg2, ji, lap;
-    const double* key[5];
-};
-
-}  // namespace
-
 bool gsrb_tma_usable(const Geom& g, const Metric& m) {
     if (!gsrb_fused_usable(g, m)) return false;
-    if (g.gh[0] < 2 || g.gh[1] < 2 || g.gh[2] < 2) return false;
-    return encode_fn() != nullptr;
+    if (g.gh[0] < 2 || (g.gh[0] & 1) || g.gh[1] < 2 || g.gh[2] < 2) return false;   // rows start 16-byte aligned
+    if ((g.sy & 1) || (g.off0 & 1)) return false;
+    return true;
 }
 
-void gsrb_tma_free(void* cache) { delete static_cast<TmaCache*>(cache); }
+void gsrb_tma_free(void* /*cache*/) {}
 
 bool launch_gsrb_tma(Ctx& cx, const Geom& g, const Metric& m, double* phiOut, const double* phiIn, const double* rhs,
-                     void** cache) {
+                     void** /*cache*/) {
     static bool attr = false;
     if (!attr) {
         if (cudaFuncSetAttribute(k_gsrb_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES) != cudaSuccess) {
@@ -354,25 +343,16 @@ bool launch_gsrb_tma(Ctx& cx, const Geom& g, const Metric& m, double* phiOut, co
         }
         attr = true;
     }
-    TmaCache* tc = static_cast<TmaCache*>(*cache);
-    const double* key[5] = {m.jg[0][0], m.jg[1][1], m.jg[2][2], m.jinv, m.lapdiag};
-    bool fresh = tc != nullptr;
-    if (tc)
-        for (int i = 0; i < 5; ++i) fresh = fresh && tc->key[i] == key[i];
-    if (!fresh) {
-        if (!tc) *cache = tc = new TmaCache();
-        if (!make_map(&tc->jg0, g, key[0], PX, EY) || !make_map(&tc->jg1, g, key[1], EX, EY + 1) ||
-            !make_map(&tc->jg2, g, key[2], EX, EY) || !make_map(&tc->ji, g, key[3], EX, EY) ||
-            !make_map(&tc->lap, g, key[4], EX, EY))
-            return false;
-        for (int i = 0; i < 5; ++i) tc->key[i] = key[i];
+    static int nprod = 0, noload = 0;
+    if (!nprod) {
+        const char* e = getenv("SOMAR_B200_TMA_PROD");
+        nprod = e ? atoi(e) : MAXPROD;
+        if (nprod < 1 || nprod > MAXPROD) nprod = MAXPROD;
+        noload = getenv("SOMAR_B200_TMA_NOLOAD") != nullptr;   // diagnostic only: wrong results, consumer-side time
     }
-    CUtensorMap tmPhi, tmRhs;
-    if (!make_map(&tmPhi, g, phiIn, PX, PY) || !make_map(&tmRhs, g, rhs, EX, EY)) return false;
     const int kc = (g.n[2] > 64) ? 64 : g.n[2];
     dim3 grid((g.n[0] + CX - 1) / CX, (g.n[1] + CY - 1) / CY, (g.n[2] + kc - 1) / kc);
-    k_gsrb_tma<<<grid, NTHREADS, SMEM_BYTES, cx.stream>>>(tmPhi, tc->jg0, tc->jg1, tc->jg2, tc->ji, tc->lap, tmRhs, g,
-                                                          phiOut, kc);
+    k_gsrb_tma<<<grid, CONSUMERS + 32 * nprod, SMEM_BYTES, cx.stream>>>(g, m, phiOut, phiIn, rhs, kc, nprod, noload);
     cx.launches++;
     return true;
 }
