@@ -289,11 +289,11 @@ def run_ours(a):
     # algorithmic bytes per cell one launch of the depth-0 smoother kernel moves (a red+black GSRB
     # iteration is 96 B/cell diagonal, 208 full; LineGSRB 88 / 200; a colour pass is half an iteration)
     kname = lev.relax_kernel(0, a.relax)
-    per_cell = {"k_gsrb_ortho": 48, "k_gsrb_fused": 96, "k_gsrb_tma": 96, "k_gsrb_full": 104,
+    per_cell = {"k_gsrb_ortho": 48, "k_gsrb_fused": 96, "k_gsrb_async": 96, "k_gsrb_full": 104,
                 "k_line_gsrb": 44 if spec.is_diagonal else 100}[kname]
     kdesc = {"k_gsrb_ortho": "k_gsrb_ortho<3> (depth-0 red/black colour pass, 2 launches per iteration)",
              "k_gsrb_fused": "k_gsrb_fused (depth-0 red+black iteration in one sweep)",
-             "k_gsrb_tma": "k_gsrb_tma (depth-0 red+black iteration in one sweep, TMA + mbarrier pipeline)",
+             "k_gsrb_async": "k_gsrb_async (depth-0 red+black iteration in one sweep, producer/consumer pipeline)",
              "k_gsrb_full": "k_gsrb_full<3> (depth-0 colour pass, full metric)",
              "k_line_gsrb": "k_line_gsrb<3> (depth-0 vertical-line colour pass)"}[kname]
     alg_bytes = per_cell * local_cells

@@ -129,7 +129,7 @@ int somar_level_stream(SomarLevel* lev, void** cuda_stream);
 int somar_level_launch_count(const SomarLevel* lev, long long* launches);
 /* Which kernel does relax(mode) run at `depth` (benchmark bookkeeping): 0 = k_gsrb_ortho, one launch per colour
  * pass; 1 = k_gsrb_fused, one launch per red+black iteration; 2 = k_gsrb_full (colour pass, full metric);
- * 3 = k_line_gsrb (colour pass); 4 = apply + k_jacobi; 5 = k_gsrb_tma (as 1, TMA-fed); -1 = none. */
+ * 3 = k_line_gsrb (colour pass); 4 = apply + k_jacobi; 5 = k_gsrb_async (as 1, pipelined); -1 = none. */
 int somar_level_relax_kernel(const SomarLevel* lev, int depth, int relax_mode, int* kernel_id);
 /* Reads back a depth's metric into rank-local arrays without ghosts (tests): comp-outermost for jg. */
 int somar_level_get_metric(SomarLevel* lev, int depth, double* jg0, double* jg1, double* jg2, double* jinv,

@@ -127,7 +127,6 @@ int somar_level_destroy(SomarLevel* L) {
             for (int c = 0; c < 3; ++c) cudaFree(dp.jg[d][c]);
         cudaFree(dp.jinv); cudaFree(dp.lapdiag); cudaFree(dp.tmp); cudaFree(dp.line_fact); cudaFree(dp.line_dmod);
         for (int s = 0; s < 2; ++s) { cudaFree(dp.sendbuf[s]); cudaFree(dp.recvbuf[s]); }
-        gsrb_tma_free(dp.tma_cache);
         if (dp.res) { cudaFree(dp.res->p); delete dp.res; }
         if (dp.cor) { cudaFree(dp.cor->p); delete dp.cor; }
     }
@@ -258,7 +257,7 @@ int somar_level_relax_kernel(const SomarLevel* L, int depth, int mode, int* id) 
     const Depth& dp = L->depths[depth];
     if (mode == SOMAR_RELAX_LEVEL_GSRB)
         *id = (L->use_fused && gsrb_fused_usable(dp.g, dp.m))
-                  ? ((L->use_fused == 2 && gsrb_tma_usable(dp.g, dp.m)) ? 5 : 1)
+                  ? ((L->use_fused == 2 && gsrb_async_usable(dp.g, dp.m)) ? 5 : 1)
                   : (dp.m.diagonal ? 0 : 2);
     else if (mode == SOMAR_RELAX_LINE_GSRB) *id = 3;
     else if (mode == SOMAR_RELAX_JACOBI) *id = 4;

@@ -25,13 +25,12 @@ void launch_gsrb(Ctx& cx, const Geom& g, const Metric& m, double* phi, const dou
 bool gsrb_fused_usable(const Geom& g, const Metric& m);
 void launch_gsrb_fused(Ctx& cx, const Geom& g, const Metric& m, double* phiOut, const double* phiIn,
                        const double* rhs);
-// the same sweep fed by TMA (cp.async.bulk.tensor) through mbarrier-signalled shared-memory rings; see gsrb_tma.cu.
-// `cache` keeps the tensor maps of the depth's coefficient arrays between launches (free with gsrb_tma_free).
-// Returns false (nothing launched) if the tensor maps cannot be built.
-bool gsrb_tma_usable(const Geom& g, const Metric& m);
-bool launch_gsrb_tma(Ctx& cx, const Geom& g, const Metric& m, double* phiOut, const double* phiIn, const double* rhs,
-                     void** cache);
-void gsrb_tma_free(void* cache);
+// the same sweep as a warp-specialised pipeline: producer warps stream the planes into mbarrier-signalled
+// shared-memory rings with asynchronous copies, consumers never touch global memory for loads; see gsrb_async.cu.
+// Returns false (nothing launched) if the kernel cannot get its shared memory.
+bool gsrb_async_usable(const Geom& g, const Metric& m);
+bool launch_gsrb_async(Ctx& cx, const Geom& g, const Metric& m, double* phiOut, const double* phiIn,
+                       const double* rhs);
 // full metric: out-of-place pass, phiOut gets the updated colour AND a copy of the other colour
 void launch_gsrb_full(Ctx& cx, const Geom& g, const Metric& m, double* phiOut, const double* phiIn,
                       const double* rhs, int pass);

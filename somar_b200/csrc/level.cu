@@ -302,9 +302,9 @@ int op_relax(SomarLevel* L, int depth, SomarField* phi, const SomarField* rhs, i
         if (mode == SOMAR_RELAX_LEVEL_GSRB && L->use_fused && gsrb_fused_usable(dp.g, dp.m)) {
             // both colour passes in one sweep (no exchange is due between them here)
             ProfScope psK(L, depth == 0 ? PH_SMOOTH0_KERNEL : -1);
-            if (L->use_fused == 2 && gsrb_tma_usable(dp.g, dp.m)) {
-                if (!launch_gsrb_tma(L->cx, dp.g, dp.m, dp.tmp, phi->p, rhs->p, &dp.tma_cache)) {
-                    set_error("relax: tensor-map creation failed for k_gsrb_tma");
+            if (L->use_fused == 2 && gsrb_async_usable(dp.g, dp.m)) {
+                if (!launch_gsrb_async(L->cx, dp.g, dp.m, dp.tmp, phi->p, rhs->p)) {
+                    set_error("relax: k_gsrb_async could not reserve its shared memory");
                     return SOMAR_ERR_CUDA;
                 }
             } else {

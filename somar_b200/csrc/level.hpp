@@ -34,7 +34,6 @@ struct Depth {
     SomarField* cor = nullptr;
     double* sendbuf[2] = {nullptr, nullptr};
     double* recvbuf[2] = {nullptr, nullptr};
-    void* tma_cache = nullptr;         // tensor maps of the coefficient arrays (gsrb_tma.cu)
 };
 
 }  // namespace somar
@@ -66,7 +65,7 @@ struct SomarLevel {
     int bottom_iters_total = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     // phase profiler (CUDA events on the level stream; off by default)
-    int use_fused = 1;                 // SOMAR_B200_FUSED: 0 = two colour passes, 1 = k_gsrb_fused, 2 = k_gsrb_tma
+    int use_fused = 2;                 // SOMAR_B200_FUSED: 0 = two colour passes, 1 = k_gsrb_fused, 2 = k_gsrb_async
     bool prof_on = false;
     struct ProfRec { int phase; cudaEvent_t a, b; };
     std::vector<ProfRec> prof;          // recorded intervals

@@ -156,8 +156,9 @@ def test_fab_round_trip(name, oracle_lib, somar):
 
 
 # --- the three implementations of a LevelGSRB iteration must be bit-identical -----------------------------------
-# SOMAR_B200_FUSED = 0: two k_gsrb_ortho colour passes, 1: k_gsrb_fused (register pipeline), 2: k_gsrb_tma
-# (TMA + mbarrier rings).  Sizes straddle the 62 x 14 core tile and the 64-plane z chunk; BCs exercise the rim path.
+# SOMAR_B200_FUSED = 0: two k_gsrb_ortho colour passes, 1: k_gsrb_fused (register pipeline), 2: k_gsrb_async
+# (producer/consumer pipeline over mbarrier rings).  Sizes straddle the 62 x 14 / 60 x 14 core tiles and the
+# 64-plane z chunk; BCs exercise the rim path.
 VARIANT_CASES = {
     "tile_edges": dict(n=(70, 45, 37), map_name="stretched", aniso=4.0),
     "exact_tile": dict(n=(62, 14, 8), map_name="stretched", aniso=2.0),
@@ -174,7 +175,7 @@ def test_gsrb_kernel_variants_bit_identical(name, oracle_lib, somar, monkeypatch
     pb = Problem(**VARIANT_CASES[name])
     phi, rhs = pb.rand(), pb.rand()
     out = {}
-    for variant, kernel in (("0", "k_gsrb_ortho"), ("1", "k_gsrb_fused"), ("2", "k_gsrb_tma")):
+    for variant, kernel in (("0", "k_gsrb_ortho"), ("1", "k_gsrb_fused"), ("2", "k_gsrb_async")):
         monkeypatch.setenv("SOMAR_B200_FUSED", variant)
         lev = pb.level(somar, relaxMode=1, maxDepth=0)
         assert lev.relax_kernel(0, 1) == kernel
