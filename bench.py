@@ -160,6 +160,8 @@ def byte_model(schedule, diagonal, relax, pre, post):
 
 
 def run_ours(a):
+    # NCCL prints its version banner (NCCL_DEBUG=VERSION) on stdout; stdout carries exactly one JSON line
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     import numpy as np
     import torch
     import torch.distributed as dist
