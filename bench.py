@@ -88,7 +88,7 @@ def run_reference(a):
                              "sample": sample},
             "e2e": {"value": mc, "unit": "Mcell-updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line))
+    emit(line)
 
 
 def workload_config(a, extra):
@@ -160,8 +160,6 @@ def byte_model(schedule, diagonal, relax, pre, post):
 
 
 def run_ours(a):
-    # NCCL prints its version banner (NCCL_DEBUG=VERSION) on stdout; stdout carries exactly one JSON line
-    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     import numpy as np
     import torch
     import torch.distributed as dist
@@ -330,12 +328,25 @@ def run_ours(a):
         line["cpu_baseline"] = {"value": r["mcups"], "unit": "Mcell-updates/s", "cores": r["cores"], "kind": "port",
                                 "sample": f"{CPU_SAMPLE_GRID[0]}x{CPU_SAMPLE_GRID[1]}x{CPU_SAMPLE_GRID[2]} {a.map} grid, "
                                           f"{r['iters']} V-cycles in {r['secs']:.2f} s, OpenMP over {r['boxes']} y-slab boxes"}
-    print(json.dumps(line))
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+_JSON_OUT = None
+
+
+def emit(line):
+    _JSON_OUT.write(json.dumps(line) + "\n")
+    _JSON_OUT.flush()
+
+
 if __name__ == "__main__":
+    # stdout carries exactly ONE JSON line: keep a private handle to it and point fd 1 at stderr, so that library
+    # banners (NCCL prints its version on stdout) cannot get in front of it
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     args = parse()
     if args.impl == "reference":
         run_reference(args)

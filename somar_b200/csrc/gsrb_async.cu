@@ -332,16 +332,20 @@ k_gsrb_async(const Geom g, const Metric m, double* __restrict__ phiOut, const do
     copy_commit();
 
     // ---- per-thread constants of the sweep ---------------------------------------------------------------------
-    const bool yin = (L.y >= 0) && (L.y < g.n[1]);
+    // Rows that take part: my own, plus -- for the red updates only -- the first ghost row towards a neighbour
+    // rank (its phi, metric and right-hand side were exchanged; relaxing its red cells here, exactly as the
+    // owner does, spares the exchange between the colour passes).
+    const bool yown = (L.y >= 0) && (L.y < g.n[1]);
+    const bool yred = (L.y >= (g.nbr[0] >= 0 ? -1 : 0)) && (L.y < g.n[1] + (g.nbr[1] >= 0 ? 1 : 0));
     const bool ycore = (L.r >= 1) && (L.r <= CY);
     L.redMask = 0;
     L.coreMask = 0;
 #pragma unroll
     for (int p = 0; p < 2; ++p) {
         const int col = 2 * L.t + p, x = L.x0 + col;
-        const bool in = yin && x >= 0 && x < g.n[0];
-        if (in && col >= 1 && col <= PX - 2) L.redMask |= 1 << p;
-        if (in && ycore && col >= 2 && col <= PX - 3) L.coreMask |= 1 << p;
+        const bool xin = x >= 0 && x < g.n[0];
+        if (yred && xin && col >= 1 && col <= PX - 2) L.redMask |= 1 << p;
+        if (yown && xin && ycore && col >= 2 && col <= PX - 3) L.coreMask |= 1 << p;
     }
     L.tileRim = (g.g0[0] + L.x0 + 1 <= 0) || (g.g0[0] + L.x0 + PX - 2 >= g.gn[0] - 1) || (g.g0[1] + y0 <= 0) ||
                 (g.g0[1] + y0 + EY - 1 >= g.gn[1] - 1);
@@ -383,7 +387,9 @@ k_gsrb_async(const Geom g, const Metric m, double* __restrict__ phiOut, const do
 }
 
 bool gsrb_async_usable(const Geom& g, const Metric& m) {
-    if (!gsrb_fused_usable(g, m)) return false;
+    if (!m.diagonal || g.nd != 3) return false;
+    if (g.periodic[0] || g.periodic[1] || g.periodic[2]) return false;   // periodic images need a fill between passes
+    if (g.total >= (1LL << 31)) return false;                             // 32-bit brick indices
     if (g.gh[0] < 2 || (g.gh[0] & 1) || g.gh[1] < 2 || g.gh[2] < 2) return false;   // rows start 16-byte aligned
     if ((g.sy & 1) || (g.off0 & 1)) return false;
     return true;

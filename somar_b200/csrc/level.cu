@@ -299,17 +299,24 @@ int op_relax(SomarLevel* L, int depth, SomarField* phi, const SomarField* rhs, i
     const bool coarse = depth > 0 && depth < L->ndepths() - 1;
     ProfScope psCoarse(L, coarse ? PH_SMOOTH_COARSE : -1);
     for (int it = 0; it < iters; ++it) {
-        if (mode == SOMAR_RELAX_LEVEL_GSRB && L->use_fused && gsrb_fused_usable(dp.g, dp.m)) {
-            // both colour passes in one sweep (no exchange is due between them here)
+        if (mode == SOMAR_RELAX_LEVEL_GSRB && L->use_fused == 2 && gsrb_async_usable(dp.g, dp.m)) {
+            // Both colour passes in one sweep.  With y-neighbour ranks the sweep also relaxes the red cells of the
+            // first ghost row on each side (same inputs, same arithmetic as their owner), so ONE exchange of two
+            // ghost rows of phi per iteration replaces the reference's exchange before each colour pass; the
+            // metric's ghost rows were filled at finalize, the right-hand side's are filled here once.
+            const bool ranks = dp.g.nbr[0] >= 0 || dp.g.nbr[1] >= 0;
+            if (ranks && it == 0 && (rc = exchange(L, depth, const_cast<double*>(rhs->p), 1)) != SOMAR_OK) return rc;
+            if (ranks && (rc = exchange(L, depth, phi->p, 2)) != SOMAR_OK) return rc;
             ProfScope psK(L, depth == 0 ? PH_SMOOTH0_KERNEL : -1);
-            if (L->use_fused == 2 && gsrb_async_usable(dp.g, dp.m)) {
-                if (!launch_gsrb_async(L->cx, dp.g, dp.m, dp.tmp, phi->p, rhs->p)) {
-                    set_error("relax: k_gsrb_async could not reserve its shared memory");
-                    return SOMAR_ERR_CUDA;
-                }
-            } else {
-                launch_gsrb_fused(L->cx, dp.g, dp.m, dp.tmp, phi->p, rhs->p);
+            if (!launch_gsrb_async(L->cx, dp.g, dp.m, dp.tmp, phi->p, rhs->p)) {
+                set_error("relax: k_gsrb_async could not reserve its shared memory");
+                return SOMAR_ERR_CUDA;
             }
+            std::swap(dp.tmp, phi->p);
+        } else if (mode == SOMAR_RELAX_LEVEL_GSRB && L->use_fused && gsrb_fused_usable(dp.g, dp.m)) {
+            // register-pipelined variant (single rank only)
+            ProfScope psK(L, depth == 0 ? PH_SMOOTH0_KERNEL : -1);
+            launch_gsrb_fused(L->cx, dp.g, dp.m, dp.tmp, phi->p, rhs->p);
             std::swap(dp.tmp, phi->p);
         } else if (mode == SOMAR_RELAX_LEVEL_GSRB) {   // LevelGSRB::relax, GSRB.cpp:58-98
             for (int pass = 0; pass < 2; ++pass) {
@@ -399,10 +406,17 @@ int level_finalize(SomarLevel* L) {
                     if (dp.jg[d][c]) launch_avg_face(L->cx, fn.g, dp.g, dp.jg[d][c], fn.jg[d][c], d, fn.ratio);
             launch_avg_harmonic(L->cx, fn.g, dp.g, dp.jinv, fn.jinv, fn.ratio);
         }
-        // No metric halo is needed: a cell only reads its own faces, and the high face of the last cell of a
-        // row/column is supplied by the caller's FluxBox (stored in the first ghost slot).
+        // The operator needs no metric halo: a cell only reads its own faces, and the high face of the last cell of
+        // a row/column is supplied by the caller's FluxBox (stored in the first ghost slot).
         launch_lapdiag(L->cx, dp.g, dp.m, dp.lapdiag);
         dp.line_valid = false;
+        // The fused smoother also relaxes the red cells of the first ghost row towards a neighbour rank
+        // (op_relax), so the diagonal metric gets two ghost rows from the neighbours, once.
+        if (L->desc.nranks > 1 && dp.m.diagonal) {
+            double* arr[5] = {dp.jg[0][0], dp.jg[1][1], nd > 2 ? dp.jg[2][2] : nullptr, dp.jinv, dp.lapdiag};
+            for (double* a : arr)
+                if (a && (rc = exchange(L, k, a, SOMAR_GHOST)) != SOMAR_OK) return rc;
+        }
     }
     // null-space probe per depth: rhs = L[0]; res = rhs - L[1]; zeroAvg iff |max(res)| < 0.01 * eps
     for (int k = 0; k < L->ndepths(); ++k) {
