@@ -30,6 +30,8 @@ struct Geom {
     int bs[3];       // box size of the level's (uniform) DisjointBoxLayout tiling at this depth (full metric only)
     double bcval[3][2];
     double dx[3];
+    double rdx[3];   // 1 / dx[d]            (exact IEEE quotients computed once on the host: kernels that
+    double rdx2[3];  // 1 / (dx[d] * dx[d])   hoisted these divisions paid for them in registers)
     double alpha, beta;
     int diriOrder;   // EllipticConstDiriBCGhostClass order (1)
     int periodic[3];

@@ -52,7 +52,8 @@ void launch_restrict_residual(Ctx& cx, const Geom& gf, const Metric& mf, const G
 void launch_prolong(Ctx& cx, const Geom& gf, const Metric& mf, const Geom& gc, double* fine, const double* crse,
                     const int ratio[3], double dxProduct, double* sums);
 // x -= sums[0]/sums[1] over the whole brick (ZeroAvgConstInterpPS::prolongIncrement, ProlongationStrategy.cpp:163)
-void launch_sub_mean(Ctx& cx, const Geom& g, double* x, const double* sums);
+void launch_prolong_finish(Ctx& cx, const Geom& gf, const Geom& gc, double* fine, const double* crse, const int r[3],
+                           const double* sums);
 
 // ---- set-up ----
 void launch_lapdiag(Ctx& cx, const Geom& g, const Metric& m, double* lapdiag);           // FILLMAPPEDLAPDIAG*

@@ -83,6 +83,8 @@ static void make_geom(const SomarLevel* L, const int coarsening[3], const double
         g.g0[d] = L->local_lo[d] / coarsening[d];
         g.n[d] = (L->local_hi[d] + 1) / coarsening[d] - g.g0[d];
         g.dx[d] = dx[d];
+        g.rdx[d] = 1.0 / dx[d];
+        g.rdx2[d] = 1.0 / (dx[d] * dx[d]);
         g.periodic[d] = (d < D.dim) && D.periodic[d];
         g.bs[d] = (L->box_size[d] > 0) ? L->box_size[d] / coarsening[d] : g.gn[d];
         if (g.bs[d] < 1) g.bs[d] = 1;
@@ -385,7 +387,7 @@ int op_prolong(SomarLevel* L, int depth, SomarField* phi, const SomarField* crse
     if (dp.zeroAvg) {
         if (L->desc.nranks > 1)   // the two MPI_Allreduce(SUM) of ProlongationStrategy.cpp:141,148 in one call
             SOMAR_NCCL(ncclAllReduce(sums, sums, 2, ncclDouble, ncclSum, L->comm, L->cx.stream));
-        launch_sub_mean(L->cx, dp.g, phi->p, sums);
+        launch_prolong_finish(L->cx, dp.g, L->depths[depth + 1].g, phi->p, crse->p, dp.ratio, sums);
     }
     return SOMAR_OK;
 }

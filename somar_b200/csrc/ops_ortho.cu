@@ -30,8 +30,88 @@ __global__ void __launch_bounds__(BX* BY) k_apply(const Geom g, const Metric m, 
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Diagonal metric, 3-D: the same operator marching through z with the column's phi (planes k-1, k, k+1) and
+// the low z-face coefficient in registers, so every array is read once per cell from HBM/L2 (x/y neighbours
+// are L1 hits: the plane was fetched one step earlier).  MODE 0: out = L phi, 1: out = rhs - L phi,
+// 2: restrictResidual for mgRefRatio (1,1,2): crse = J-weighted average of the residual of two planes
+// (restrictResidual + MAPPEDAVERAGE2, MappedAMRPoissonOp.cpp:1281-1304, MappedCoarseAverageF.ChF:132-168);
+// the accumulation order is the reference's (kk = 0, 1).
+// ---------------------------------------------------------------------------------------------------------
+template <int MODE>
+__global__ void __launch_bounds__(BX* BY, 3) k_march(const Geom g, const Metric m, const Geom gc, double* __restrict__ out,
+                                                   const double* __restrict__ phi, const double* __restrict__ rhs,
+                                                   bool homog, int kz) {
+    const int i = blockIdx.x * BX + threadIdx.x;
+    const int j = blockIdx.y * BY + threadIdx.y;
+    if (i >= g.n[0] || j >= g.n[1]) return;
+    const int k0 = blockIdx.z * kz;
+    const int k1 = min(k0 + kz, g.n[2]);
+    const double* __restrict__ jg0 = m.jg[0][0];
+    const double* __restrict__ jg1 = m.jg[1][1];
+    const double* __restrict__ jg2 = m.jg[2][2];
+    const double* __restrict__ jinv = m.jinv;
+    long long c = g.idx(i, j, k0);
+    double pm = phi[c - g.sz], pc = phi[c], zlo = jg2[c];
+    double s = 0.0, sj = 0.0;
+    // side bits that do not depend on k
+    unsigned smxy = 0;
+    if (i == 0 && g.bc[0][0] != BC_NONE) smxy |= 1u;
+    if (i == g.n[0] - 1 && g.bc[0][1] != BC_NONE) smxy |= 2u;
+    if (j == 0 && g.bc[1][0] != BC_NONE) smxy |= 4u;
+    if (j == g.n[1] - 1 && g.bc[1][1] != BC_NONE) smxy |= 8u;
+    for (int k = k0; k < k1; ++k, c += g.sz) {
+        const double pn = phi[c + g.sz], zhi = jg2[c + g.sz];
+        double nb[3][2], glo[3], ghi[3];
+        nb[0][0] = phi[c - 1];
+        nb[0][1] = phi[c + 1];
+        nb[1][0] = phi[c - g.sy];
+        nb[1][1] = phi[c + g.sy];
+        nb[2][0] = pm;
+        nb[2][1] = pn;
+        glo[0] = jg0[c];
+        ghi[0] = jg0[c + 1];
+        glo[1] = jg1[c];
+        ghi[1] = jg1[c + g.sy];
+        glo[2] = zlo;
+        ghi[2] = zhi;
+        const double ji = jinv[c];
+        unsigned sm = smxy;
+        if (k == 0 && g.bc[2][0] != BC_NONE) sm |= 16u;
+        if (k == g.n[2] - 1 && g.bc[2][1] != BC_NONE) sm |= 32u;
+        const double v = apply_vals_ortho3(g, sm, homog, pc, nb, glo, ghi, ji);
+        if (MODE == 0) {
+            out[c] = v;
+        } else if (MODE == 1) {
+            out[c] = rhs[c] - v;
+        } else {
+            const double res = rhs[c] - v;
+            s = s + res / ji;
+            sj = sj + 1.0 / ji;
+            if ((k - k0) & 1) {
+                out[gc.idx(i, j, k >> 1)] = s / sj;
+                s = 0.0;
+                sj = 0.0;
+            }
+        }
+        pm = pc;
+        pc = pn;
+        zlo = zhi;
+    }
+}
+
+static int march_kz(const Geom& g) { return (g.n[2] >= 32) ? 16 : ((g.n[2] + 1) / 2) * 2; }
+
 void launch_apply(Ctx& cx, const Geom& g, const Metric& m, double* out, const double* phi, const double* rhs,
                   int mode, bool homog) {
+    if (m.diagonal && g.nd == 3) {
+        const int kzm = march_kz(g);
+        dim3 gridm((g.n[0] + BX - 1) / BX, (g.n[1] + BY - 1) / BY, (g.n[2] + kzm - 1) / kzm), blockm(BX, BY);
+        if (mode) k_march<1><<<gridm, blockm, 0, cx.stream>>>(g, m, g, out, phi, rhs, homog, kzm);
+        else k_march<0><<<gridm, blockm, 0, cx.stream>>>(g, m, g, out, phi, rhs, homog, kzm);
+        cx.launches++;
+        return;
+    }
     const int kz = (g.n[2] >= 64) ? 8 : 1;
     dim3 grid((g.n[0] + BX - 1) / BX, (g.n[1] + BY - 1) / BY, (g.n[2] + kz - 1) / kz), block(BX, BY);
     if (m.diagonal) {
@@ -185,6 +265,14 @@ __global__ void __launch_bounds__(BX* BY) k_restrict(const Geom gf, const Metric
 
 void launch_restrict_residual(Ctx& cx, const Geom& gf, const Metric& mf, const Geom& gc, double* crse,
                               const double* phi, const double* rhs, const int r[3]) {
+    if (mf.diagonal && gf.nd == 3 && r[0] == 1 && r[1] == 1 && r[2] == 2 && (gf.n[2] & 1) == 0) {
+        // vertical semicoarsening (the anisotropic case): z-marching kernel
+        const int kzm = march_kz(gf);
+        dim3 gridm((gf.n[0] + BX - 1) / BX, (gf.n[1] + BY - 1) / BY, (gf.n[2] + kzm - 1) / kzm), blockm(BX, BY);
+        k_march<2><<<gridm, blockm, 0, cx.stream>>>(gf, mf, gc, crse, phi, rhs, true, kzm);
+        cx.launches++;
+        return;
+    }
     dim3 grid((gc.n[0] + BX - 1) / BX, (gc.n[1] + BY - 1) / BY, gc.n[2]), block(BX, BY);
     if (mf.diagonal) {
         if (gf.nd == 3) k_restrict<3, false><<<grid, block, 0, cx.stream>>>(gf, mf, gc, crse, phi, rhs, r[0], r[1], r[2]);

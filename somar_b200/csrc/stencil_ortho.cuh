@@ -39,7 +39,7 @@ template <int S>
 __device__ __forceinline__ double face_flux_ortho(const Geom& g, const double* __restrict__ phi,
                                                   const double* __restrict__ jgd, long long c, long long st, int d,
                                                   bool atBdry, bool homog, double pc) {
-    const double beta_dx = 1.0 / g.dx[d];
+    const double beta_dx = g.rdx[d];
     const long long f = S ? c + st : c;            // face address
     double nb;                                      // value on the other side of the face
     if (atBdry) {
@@ -65,14 +65,48 @@ __device__ __forceinline__ double apply_cell_ortho(const Geom& g, const Metric& 
     const double f0h = face_flux_ortho<1>(g, phi, m.jg[0][0], c, 1, 0, sm & 2u, homog, pc);
     const double f1l = face_flux_ortho<0>(g, phi, m.jg[1][1], c, g.sy, 1, sm & 4u, homog, pc);
     const double f1h = face_flux_ortho<1>(g, phi, m.jg[1][1], c, g.sy, 1, sm & 8u, homog, pc);
-    double s = (f0h - f0l) * (1.0 / g.dx[0]);
-    s = s + (f1h - f1l) * (1.0 / g.dx[1]);
+    double s = (f0h - f0l) * g.rdx[0];
+    s = s + (f1h - f1l) * g.rdx[1];
     if (ND > 2) {
         const double f2l = face_flux_ortho<0>(g, phi, m.jg[2][2], c, g.sz, 2, sm & 16u, homog, pc);
         const double f2h = face_flux_ortho<1>(g, phi, m.jg[2][2], c, g.sz, 2, sm & 32u, homog, pc);
-        s = s + (f2h - f2l) * (1.0 / g.dx[2]);
+        s = s + (f2h - f2l) * g.rdx[2];
     }
     double r = m.jinv[c] * s;
+    if (g.alpha != 0.0) r = g.alpha * pc + 1.0 * r;
+    return r;
+}
+
+// The same two functions from VALUES (for kernels that march through z with phi and J g^zz in registers): nbv = phi
+// across the face, farV = phi across the opposite face (Dirichlet ghosts), jgf = J g^{dd} on the face.  Statement
+// for statement the arithmetic of face_flux_ortho / apply_cell_ortho.
+template <int S>
+__device__ __forceinline__ double face_flux_vals(const Geom& g, int d, bool atBdry, bool homog, double pc, double nbv,
+                                                 double farV, double jgf) {
+    const double beta_dx = g.rdx[d];
+    double nb = nbv;
+    if (atBdry) {
+        const int bct = g.bc[d][S];
+        if (bct == BC_NEUM) return (homog ? 0.0 : g.bcval[d][S]) * g.beta;
+        nb = diri_ghost_val(pc, farV, homog ? 0.0 : g.bcval[d][S], g.diriOrder);
+    }
+    const double diff = S ? (nb - pc) : (pc - nb);
+    return (jgf * beta_dx * diff) * g.beta;
+}
+
+__device__ __forceinline__ double apply_vals_ortho3(const Geom& g, unsigned sm, bool homog, double pc,
+                                                    const double (&nb)[3][2], const double (&glo)[3],
+                                                    const double (&ghi)[3], double ji) {
+    const double f0l = face_flux_vals<0>(g, 0, sm & 1u, homog, pc, nb[0][0], nb[0][1], glo[0]);
+    const double f0h = face_flux_vals<1>(g, 0, sm & 2u, homog, pc, nb[0][1], nb[0][0], ghi[0]);
+    const double f1l = face_flux_vals<0>(g, 1, sm & 4u, homog, pc, nb[1][0], nb[1][1], glo[1]);
+    const double f1h = face_flux_vals<1>(g, 1, sm & 8u, homog, pc, nb[1][1], nb[1][0], ghi[1]);
+    double s = (f0h - f0l) * g.rdx[0];
+    s = s + (f1h - f1l) * g.rdx[1];
+    const double f2l = face_flux_vals<0>(g, 2, sm & 16u, homog, pc, nb[2][0], nb[2][1], glo[2]);
+    const double f2h = face_flux_vals<1>(g, 2, sm & 32u, homog, pc, nb[2][1], nb[2][0], ghi[2]);
+    s = s + (f2h - f2l) * g.rdx[2];
+    double r = ji * s;
     if (g.alpha != 0.0) r = g.alpha * pc + 1.0 * r;
     return r;
 }
@@ -117,9 +151,9 @@ __device__ __forceinline__ GsrbCoef gsrb_load_coef(const Geom& g, const Metric& 
 template <int ND>
 __device__ __forceinline__ double gsrb_update_vals(const Geom& g, const GsrbCoef& q, int i, int j, int k, double pc,
                                                    const double (&nb)[3][2], bool knownInterior = false) {
-    const double sc0 = 1.0 / (g.dx[0] * g.dx[0]);
-    const double sc1 = 1.0 / (g.dx[1] * g.dx[1]);
-    const double sc2 = (ND > 2) ? 1.0 / (g.dx[2] * g.dx[2]) : 0.0;
+    const double sc0 = g.rdx2[0];
+    const double sc1 = g.rdx2[1];
+    const double sc2 = (ND > 2) ? g.rdx2[2] : 0.0;
     const double ji = q.ji;
     // knownInterior: the caller has established (block-uniformly) that the cell is not on the domain rim
     if (knownInterior || !on_domain_rim<ND>(g, i, j, k)) {

@@ -34,11 +34,59 @@ static inline int row_blocks(const Geom& g, int sms) {
         }                                                                                                 \
     }
 
+// The same iteration with FOUR cells of the row per lane and step (i = lane, lane+32, lane+64, lane+96): LOAD is
+// expanded for all four before USE, so a thread keeps four independent loads per array in flight -- a streaming
+// kernel with one 8-byte load per thread in flight reaches less than half of the HBM bandwidth.  The order in
+// which a lane visits its cells is the same as in FOR_VALID_CELLS (reductions stay bit-identical).
+#define FOR_VALID_CELLS4(g, c, u, LOAD, USE)                                                              \
+    {                                                                                                     \
+        const int lane_ = threadIdx.x & 31;                                                               \
+        const long long warp_ = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);           \
+        const long long nwarps_ = (long long)gridDim.x * (blockDim.x >> 5);                               \
+        const long long rows_ = (long long)(g).n[1] * (g).n[2];                                           \
+        for (long long r_ = warp_; r_ < rows_; r_ += nwarps_) {                                           \
+            const int k = (int)(r_ / (g).n[1]);                                                           \
+            const int j = (int)(r_ - (long long)k * (g).n[1]);                                            \
+            const long long row0_ = (g).idx(0, j, k);                                                     \
+            (void)k; (void)j;                                                                             \
+            for (int i0_ = lane_; i0_ < (g).n[0]; i0_ += 128) {                                           \
+                _Pragma("unroll") for (int u = 0; u < 4; ++u) {                                           \
+                    const int i = i0_ + 32 * u;                                                           \
+                    const long long c = row0_ + i;                                                        \
+                    if (i < (g).n[0]) { LOAD }                                                            \
+                }                                                                                         \
+                _Pragma("unroll") for (int u = 0; u < 4; ++u) {                                           \
+                    const int i = i0_ + 32 * u;                                                           \
+                    const long long c = row0_ + i;                                                        \
+                    (void)c;                                                                              \
+                    if (i < (g).n[0]) { USE }                                                             \
+                }                                                                                         \
+            }                                                                                             \
+        }                                                                                                 \
+    }
+
+// whole-brick fill / copy: 16-byte accesses, two per thread and step (the brick size is a multiple of 16 doubles)
 __global__ void k_fill_all(double* __restrict__ x, long long n, double v) {
-    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) x[t] = v;
+    double2* __restrict__ x2 = reinterpret_cast<double2*>(x);
+    const long long n2 = n >> 1, stride = (long long)gridDim.x * blockDim.x;
+    const double2 vv = make_double2(v, v);
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n2; t += 2 * stride) {
+        x2[t] = vv;
+        if (t + stride < n2) x2[t + stride] = vv;
+    }
 }
 __global__ void k_copy_all(double* __restrict__ y, const double* __restrict__ x, long long n) {
-    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) y[t] = x[t];
+    double2* __restrict__ y2 = reinterpret_cast<double2*>(y);
+    const double2* __restrict__ x2 = reinterpret_cast<const double2*>(x);
+    const long long n2 = n >> 1, stride = (long long)gridDim.x * blockDim.x;
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n2; t += 2 * stride) {
+        const double2 a = x2[t];
+        const bool more = t + stride < n2;
+        double2 b = a;
+        if (more) b = x2[t + stride];
+        y2[t] = a;
+        if (more) y2[t + stride] = b;
+    }
 }
 static inline int flat_blocks(long long n, int sms) {
     long long nb = (n + TPB - 1) / TPB;
@@ -55,14 +103,17 @@ void launch_copy(Ctx& cx, const Geom& g, double* y, const double* x) {
 }
 
 __global__ void k_axpy(const Geom g, double* __restrict__ y, const double* __restrict__ x, double a) {
-    FOR_VALID_CELLS(g, c, i, j, k, { y[c] += a * x[c]; })
+    double xv[4], yv[4];
+    FOR_VALID_CELLS4(g, c, u, { xv[u] = x[c]; yv[u] = y[c]; }, { y[c] = yv[u] + a * xv[u]; })
 }
 __global__ void k_axby(const Geom g, double* __restrict__ out, const double* __restrict__ x,
                        const double* __restrict__ y, double a, double b) {
-    FOR_VALID_CELLS(g, c, i, j, k, { out[c] = a * x[c] + b * y[c]; })
+    double xv[4], yv[4];
+    FOR_VALID_CELLS4(g, c, u, { xv[u] = x[c]; yv[u] = y[c]; }, { out[c] = a * xv[u] + b * yv[u]; })
 }
 __global__ void k_scale(const Geom g, double* __restrict__ x, double a) {
-    FOR_VALID_CELLS(g, c, i, j, k, { x[c] *= a; })
+    double xv[4];
+    FOR_VALID_CELLS4(g, c, u, { xv[u] = x[c]; }, { x[c] = xv[u] * a; })
 }
 void launch_axpy(Ctx& cx, const Geom& g, double* y, const double* x, double a) {
     k_axpy<<<row_blocks(g, cx.sms), TPB, 0, cx.stream>>>(g, y, x, a);
@@ -134,12 +185,13 @@ __global__ void k_reduce(const Geom g, const double* __restrict__ x, const doubl
     const bool isMax = (kind == 0 || kind == 4);
     const double ident = (kind == 4) ? -1e300 : 0.0;
     double acc = ident;
-    FOR_VALID_CELLS(g, c, i, j, k, {
-        const double v = x[c];
+    double xv[4], yv[4] = {0.0, 0.0, 0.0, 0.0};
+    FOR_VALID_CELLS4(g, c, u, { xv[u] = x[c]; if (kind == 3) yv[u] = y[c]; }, {
+        const double v = xv[u];
         if (kind == 0) acc = fmax(acc, fabs(v));
         else if (kind == 1) acc += fabs(v);
         else if (kind == 2) acc += v * v;
-        else if (kind == 3) acc += v * y[c];
+        else if (kind == 3) acc += v * yv[u];
         else acc = fmax(acc, v);
     })
     acc = block_red(acc, isMax, ident);
@@ -158,16 +210,24 @@ __global__ void k_prolong(const Geom gf, const double* __restrict__ jinv, const 
                           const double* __restrict__ crse, int r0, int r1, int r2, double dxProduct, bool withAvg,
                           double* __restrict__ scratch, unsigned int* __restrict__ tickets,
                           double* __restrict__ sums) {
+    // Without the average: fine += coarse.  With it (zero-average strategy): this pass only FORMS the sums of
+    // v = fine + coarse (nothing is written); k_prolong_finish then stores v - sums[0]/sums[1].  The values are the
+    // ones the reference gets from "add, reduce, subtract"; the fine field is read twice but written once
+    // (40 B/cell instead of 52).
     double aS = 0.0, aV = 0.0;
-    FOR_VALID_CELLS(gf, c, i, j, k, {
-        const double v = fine[c] + crse[gc.idx(i / r0, j / r1, k / r2)];
-        fine[c] = v;
-        if (withAvg) {
-            const double dvol = dxProduct / jinv[c];
-            aS = aS + dvol * v;
-            aV = aV + dvol;
-        }
-    })
+    double fv[4], cv[4], jv[4] = {1.0, 1.0, 1.0, 1.0};
+    FOR_VALID_CELLS4(gf, c, u,
+                     { fv[u] = fine[c]; cv[u] = crse[gc.idx(i / r0, j / r1, k / r2)]; if (withAvg) jv[u] = jinv[c]; },
+                     {
+                         const double v = fv[u] + cv[u];
+                         if (withAvg) {
+                             const double dvol = dxProduct / jv[u];
+                             aS = aS + dvol * v;
+                             aV = aV + dvol;
+                         } else {
+                             fine[c] = v;
+                         }
+                     })
     if (withAvg) {
         aS = block_red(aS, false, 0.0);
         aV = block_red(aV, false, 0.0);
@@ -184,12 +244,17 @@ void launch_prolong(Ctx& cx, const Geom& gf, const Metric& mf, const Geom& gc, d
     cx.launches++;
 }
 
-__global__ void k_sub_mean(double* __restrict__ x, long long n, const double* __restrict__ sums) {
+// fine = (fine + coarse[i/m]) - sums[0]/sums[1]     (ZeroAvgConstInterpPS::prolongIncrement, ProlongationStrategy.cpp:163)
+__global__ void k_prolong_finish(const Geom gf, const Geom gc, double* __restrict__ fine, const double* __restrict__ crse,
+                                 int r0, int r1, int r2, const double* __restrict__ sums) {
     const double avg = sums[0] / sums[1];
-    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) x[t] -= avg;
+    double fv[4], cv[4];
+    FOR_VALID_CELLS4(gf, c, u, { fv[u] = fine[c]; cv[u] = crse[gc.idx(i / r0, j / r1, k / r2)]; },
+                     { fine[c] = (fv[u] + cv[u]) - avg; })
 }
-void launch_sub_mean(Ctx& cx, const Geom& g, double* x, const double* sums) {
-    k_sub_mean<<<flat_blocks(g.total, cx.sms), TPB, 0, cx.stream>>>(x, g.total, sums);
+void launch_prolong_finish(Ctx& cx, const Geom& gf, const Geom& gc, double* fine, const double* crse, const int r[3],
+                           const double* sums) {
+    k_prolong_finish<<<row_blocks(gf, cx.sms), TPB, 0, cx.stream>>>(gf, gc, fine, crse, r[0], r[1], r[2], sums);
     cx.launches++;
 }
 
