@@ -1,0 +1,401 @@
+// bicg_persistent.cuh -- the whole bottom visit of the V-cycle as ONE persistent cooperative kernel.
+//
+// MappedMultiGrid<T>::cycle at the bottom depth (src/calculus/AMRElliptic/MappedMultiGrid.H:566-573) is
+// num_smooth_bottom relaxations followed by Chombo's BiCGStabSolver (bicgstab.cu has the algorithm's provenance),
+// whose every iteration is two preconditioner applications (diagonal scaling + point GSRB relaxations,
+// MappedAMRPoissonOp.cpp:684-734), two operator applications and five global reductions.  The bottom depth holds
+// a few hundred thousand cells -- L2 resident, a microsecond of work per pass -- so as separate kernels the
+// iteration is launch latency, and even as one kernel it is INSTRUCTION latency unless the passes are spread over
+// many warps.  Hence:
+//   * dependent passes are separated by grid.sync() instead of kernel boundaries (15 per iteration);
+//   * a pass hands 32-cell pieces of rows ("items") to the warps of the whole grid round-robin, one cell per
+//     lane, with as many co-resident warps as the register budget allows (__launch_bounds__(256, 4));
+//     colour passes use 64-cell items (lane l owns cell 2l + parity) so that no lane idles;
+//   * every block keeps a copy of the scalar state in shared memory and advances it with the same ctl1..ctl5
+//     steps as the launch-per-step versions;
+//   * the sums keep the order of k_reduce / finish_reduce: the light passes (axpy-like updates, dot products,
+//     norms) run in the "canonical" mapping -- the first cb blocks iterate exactly as a k_reduce grid of cb
+//     blocks would -- and every block folds the cb partials in finish_reduce's order.  The unconverged BiCGStab
+//     of a singular bottom problem amplifies rounding differences enough to move the V-cycle count, so this is
+//     what keeps the solve bit-identical to the launch-per-step modes (and to the parity established for them);
+//   * <r_tilde, r> of the next iteration is accumulated by the pass that produces r.
+// The fields are deliberately NOT const/__restrict__: they are written and re-read across grid.sync() by other
+// SMs, so no load may go through the non-coherent path.
+// Usable for: single rank, diagonal metric, point GSRB smoother/preconditioner, no periodic direction.
+#pragma once
+#include "cells.cuh"
+#include "stencil_ortho.cuh"
+#include <cooperative_groups.h>
+
+namespace somar {
+
+namespace cg = cooperative_groups;
+
+struct BicgFields {
+    double *phi, *rhs;                          // the bottom depth's correction and residual (MG fields)
+    double *r, *rt, *e, *pv, *pt, *stl, *t, *v; // BiCGStab work fields
+};
+struct BicgArgs {
+    int presmooth;       // num_smooth_bottom
+    int nprecond;        // relaxations in preCond (0: preCond is a copy)
+    int numRestarts;
+    double bottomMetric; // > 0: convergence metric set by the outer solver
+    double eps, reps, small, one_minus_hang;
+    int imax, normKind;
+};
+
+// ---- scalar state of the iteration and its steps (shared with the launch-per-step version in bicgstab.cu) ----
+struct BicgState {
+    double red[4];                 // landing slots of the reductions
+    double rho[4], nrm[2], alph[2], bet[2], omega[2];
+    double c_pv;                   // -beta * omega_old        (coefficient of v in the p update)
+    double neg_alpha, neg_omega;
+    double initial_norm, initial_rnorm, eps, reps, small, one_minus_hang;
+    int i, imax, init, recount;
+    int status;                    // 0 iterating, 1 finished, 2 restart requested
+    int doA, doB, normKind;
+};
+
+__device__ __forceinline__ double norm_finish(double v, int kind) { return kind == 2 ? sqrt(v) : v; }
+
+// ---- the scalar steps of one iteration (shared by the one-thread control kernels and the persistent kernel) ----
+// after  red[0] = <r_tilde, r>
+__device__ __forceinline__ void ctl1(BicgState* st) {
+    ++st->i;
+    st->nrm[1] = st->nrm[0];
+    st->alph[1] = st->alph[0]; st->bet[1] = st->bet[0]; st->omega[1] = st->omega[0];
+    st->rho[3] = st->rho[2]; st->rho[2] = st->rho[1];
+    st->rho[1] = st->red[0];
+    if (st->rho[1] == 0.0) { st->status = 1; return; }
+    if (!st->init) {
+        st->bet[1] = (st->rho[1] / st->rho[2]) * (st->alph[1] / st->omega[1]);
+        st->c_pv = -st->bet[1] * st->omega[1];
+    }
+}
+// after  red[0] = <r_tilde, v>
+__device__ __forceinline__ void ctl2(BicgState* st) {
+    st->init = 0;
+    const double m = st->red[0];
+    st->alph[0] = st->rho[1] / m;
+    st->neg_alpha = -st->alph[0];
+    st->doA = fabs(m) > st->small * fabs(st->rho[1]);
+}
+// after the alpha step's norm landed in red[0]
+__device__ __forceinline__ void ctl3(BicgState* st) {
+    st->nrm[0] = st->doA ? norm_finish(st->red[0], st->normKind) : 0.0;
+    st->doB = st->nrm[0] > st->eps * st->initial_norm && st->nrm[0] > st->reps * st->initial_rnorm;
+}
+// after  red[0] = <t, r>, red[1] = <t, t>
+__device__ __forceinline__ void ctl4(BicgState* st) {
+    if (!st->doB) return;
+    st->omega[0] = st->red[0] / st->red[1];
+    st->neg_omega = -st->omega[0];
+}
+// end of the iteration: convergence, hang / restart bookkeeping, and the loop condition of the next one
+__device__ __forceinline__ bool loop_top(const BicgState* st) {
+    return (st->i < st->imax && st->nrm[0] > st->eps * st->nrm[1]) && (st->nrm[1] > 0);
+}
+__device__ __forceinline__ void ctl5(BicgState* st) {
+    if (st->doB) st->nrm[0] = norm_finish(st->red[0], st->normKind);
+    const double n0 = st->nrm[0], n1 = st->nrm[1];
+    if (n0 <= st->eps * st->initial_norm || n0 <= st->reps * st->initial_rnorm) { st->status = 1; return; }
+    if (st->omega[0] == 0.0 || n0 > st->one_minus_hang * n1) {
+        if (st->recount == 0) {
+            st->recount = 1;
+        } else {
+            st->recount = 0;
+            st->status = 2;
+            return;
+        }
+    }
+    if (!loop_top(st)) st->status = 1;
+}
+#define BP_TPB 256
+#ifndef BP_MINBLOCKS
+#define BP_MINBLOCKS 4
+#endif
+
+// items of W cells of one row; i0 = first cell of the item.  j, k, i0 visible in BODY.
+#define BP_FOR_ITEMS(g, W, BODY)                                                                           \
+    {                                                                                                      \
+        const int segs_ = ((g).n[0] + (W) - 1) / (W);                                                      \
+        const int items_ = (g).n[1] * (g).n[2] * segs_;                                                    \
+        for (int it_ = gwarp; it_ < items_; it_ += nwarps) {                                               \
+            const int r_ = it_ / segs_;                                                                    \
+            const int i0 = (it_ - r_ * segs_) * (W);                                                       \
+            const int k = r_ / (g).n[1];                                                                   \
+            const int j = r_ - k * (g).n[1];                                                               \
+            BODY                                                                                           \
+        }                                                                                                  \
+    }
+// one cell per lane
+#define BP_FOR_CELLS(g, c, BODY)                                                                           \
+    BP_FOR_ITEMS(g, 32, {                                                                                  \
+        const int i = i0 + lane;                                                                           \
+        if (i < (g).n[0]) {                                                                                \
+            const long long c = (g).idx(i, j, k);                                                          \
+            BODY                                                                                           \
+        }                                                                                                  \
+    })
+
+// The "canonical" iteration: exactly FOR_VALID_CELLSN as a grid of cb blocks of TPB threads would run it (the
+// launch shape of k_reduce and of the BLAS-1 kernels), executed by the first cb blocks of this grid.  Sums
+// accumulated in it, block-reduced and folded over cb partials are bit-identical to k_reduce / finish_reduce.
+#define BP_CANON_CELLS(g, cb, c, u, U, LOAD, USE)                                                          \
+    if ((int)blockIdx.x < (cb)) {                                                                          \
+        const long long cwarp_ = (long long)blockIdx.x * (BP_TPB >> 5) + (threadIdx.x >> 5);               \
+        const long long cnw_ = (long long)(cb) * (BP_TPB >> 5);                                            \
+        const long long rows_ = (long long)(g).n[1] * (g).n[2];                                            \
+        for (long long r_ = cwarp_; r_ < rows_; r_ += cnw_) {                                              \
+            const int k = (int)(r_ / (g).n[1]);                                                            \
+            const int j = (int)(r_ - (long long)k * (g).n[1]);                                             \
+            const long long row0_ = (g).idx(0, j, k);                                                      \
+            for (int i0_ = lane; i0_ < (g).n[0]; i0_ += 32 * (U)) {                                        \
+                _Pragma("unroll") for (int u = 0; u < (U); ++u) {                                          \
+                    const int i = i0_ + 32 * u;                                                            \
+                    const long long c = row0_ + i;                                                         \
+                    (void)c;                                                                               \
+                    if (i < (g).n[0]) { LOAD }                                                             \
+                }                                                                                          \
+                _Pragma("unroll") for (int u = 0; u < (U); ++u) {                                          \
+                    const int i = i0_ + 32 * u;                                                            \
+                    const long long c = row0_ + i;                                                         \
+                    (void)c;                                                                               \
+                    if (i < (g).n[0]) { USE }                                                              \
+                }                                                                                          \
+            }                                                                                              \
+        }                                                                                                  \
+    }
+#define BP_U 4
+
+template <int ND>
+__global__ void __launch_bounds__(BP_TPB, BP_MINBLOCKS)
+    k_bicg_persistent(const Geom g, const Metric m, const BicgFields f, const BicgArgs a, double* part,
+                      int* itersAccum, const int cb) {
+    cg::grid_group grid = cg::this_grid();
+    __shared__ BicgState s;
+    __shared__ double rhoNext;   // <r_tilde, r> formed by the pass that wrote r
+    int buf = 0;
+    const int tid = threadIdx.x;
+    const int lane = tid & 31;
+    const int gwarp = blockIdx.x * (BP_TPB / 32) + (tid >> 5);
+    const int nwarps = gridDim.x * (BP_TPB / 32);
+    const int kind = a.normKind;
+    const bool nmax = kind == 0;
+
+    // Two per-thread partial results -> s.red[0..n-1] in every block.  Lane 0 is a sum or (max norm) a maximum,
+    // lane 1 always a sum.  The partials of consecutive reductions alternate between two buffers: a block can be
+    // one grid.sync() ahead of another, never two.
+    auto reduce = [&](double p0, double p1, int n, bool isMax0) {
+        p0 = block_red(p0, isMax0, 0.0);
+        if (n > 1) p1 = block_red(p1, false, 0.0);
+        double* pb = part + (size_t)buf * 2 * MAX_RED_BLOCKS;
+        if (tid == 0 && (int)blockIdx.x < cb) {
+            pb[blockIdx.x] = p0;
+            if (n > 1) pb[MAX_RED_BLOCKS + blockIdx.x] = p1;
+        }
+        grid.sync();
+        for (int q = 0; q < n; ++q) {
+            const bool isMax = isMax0 && q == 0;
+            double v = 0.0;
+            for (int b = tid; b < cb; b += BP_TPB) {
+                const double w = __ldcg(pb + q * MAX_RED_BLOCKS + b);
+                v = isMax ? fmax(v, w) : v + w;
+            }
+            v = block_red(v, isMax, 0.0);
+            if (tid == 0) s.red[q] = v;
+        }
+        __syncthreads();
+        buf ^= 1;
+    };
+    auto nacc = [&](double acc, double v) {
+        if (kind == 0) return fmax(acc, fabs(v));
+        if (kind == 1) return acc + fabs(v);
+        return acc + v * v;
+    };
+    // one colour of point Gauss-Seidel, in place (LevelGSRB::relax, GSRB.cpp:58-98): lane l of a 64-cell item owns
+    // the cell 2l + parity
+    auto colour_pass = [&](double* phi, const double* rhs, int pass) {
+        BP_FOR_ITEMS(g, 64, {
+            const int par = (g.g0[0] + g.g0[1] + j + ((ND > 2) ? (g.g0[2] + k) : 0) + pass) & 1;
+            const int i = i0 + 2 * lane + par;
+            if (i < g.n[0]) {
+                const long long c = g.idx(i, j, k);
+                phi[c] = gsrb_cell_ortho<ND>(g, m, phi, rhs, i, j, k, c);
+            }
+        })
+    };
+    auto relax = [&](double* phi, const double* rhs, int iters) {   // enters and leaves with phi complete
+        for (int it = 0; it < iters; ++it) {
+            colour_pass(phi, rhs, 0);
+            grid.sync();
+            colour_pass(phi, rhs, 1);
+            grid.sync();
+        }
+    };
+    // r = rhs - L phi, r_tilde = r, e = 0, norm(r), <r, r>      (phi complete on entry)
+    auto true_residual = [&]() {
+        BP_FOR_CELLS(g, c, {
+            const double rv = f.rhs[c] - apply_cell_ortho<ND>(g, m, f.phi, i, j, k, c, true);
+            f.r[c] = rv;
+            f.rt[c] = rv;
+            f.e[c] = 0.0;
+        })
+        grid.sync();
+        double acc = 0.0, rho = 0.0;
+        double rv[BP_U];
+        BP_CANON_CELLS(g, cb, c, u, BP_U, { rv[u] = f.r[c]; }, {
+            acc = nacc(acc, rv[u]);
+            rho += rv[u] * rv[u];
+        })
+        reduce(acc, rho, 2, nmax);
+        if (tid == 0) rhoNext = s.red[1];
+    };
+
+    relax(f.phi, f.rhs, a.presmooth);
+    true_residual();
+    if (tid == 0) {
+        const double n0 = norm_finish(s.red[0], kind);
+        BicgState z = {};
+        z.nrm[0] = z.nrm[1] = n0;
+        z.initial_norm = (a.bottomMetric > 0) ? a.bottomMetric : n0;
+        z.initial_rnorm = n0;
+        z.eps = a.eps; z.reps = a.reps; z.small = a.small; z.one_minus_hang = a.one_minus_hang;
+        z.imax = a.imax; z.init = 1; z.normKind = kind;
+        z.status = loop_top(&z) ? 0 : 1;
+        s = z;
+    }
+    __syncthreads();
+    int restarts = 0;
+    while (s.status == 0) {
+        __syncthreads();   // every thread has read the loop condition before ctl1 may change it
+        if (tid == 0) {   // rho = <r_tilde, r> came with the pass that produced r
+            s.red[0] = rhoNext;
+            ctl1(&s);
+        }
+        __syncthreads();
+        if (s.status != 0) break;
+        {   // p = r  or  ((beta p) + (-beta omega) v) + r;   p_tilde = preCond(p): diagonal scaling, then relaxations
+            const bool init = s.init != 0;
+            const double b = s.bet[1], cv = s.c_pv;
+            double rr[BP_U], pp[BP_U], vv[BP_U], ld[BP_U];
+            BP_CANON_CELLS(g, cb, c, u, BP_U,
+                           {
+                               rr[u] = f.r[c];
+                               if (!init) { pp[u] = f.pv[c]; vv[u] = f.v[c]; }
+                               if (a.nprecond) ld[u] = m.lapdiag[c];
+                           },
+                           {
+                               double pn = rr[u];
+                               if (!init) {
+                                   const double t1 = pp[u] * b;
+                                   const double t2 = t1 + cv * vv[u];
+                                   pn = t2 + 1.0 * pn;
+                               }
+                               f.pv[c] = pn;
+                               f.pt[c] = a.nprecond ? pn / (g.alpha + g.beta * ld[u]) : pn;
+                           })
+            grid.sync();
+            relax(f.pt, f.pv, a.nprecond);
+        }
+        {   // v = L p_tilde (spread over the grid), then <r_tilde, v> in the canonical order
+            BP_FOR_CELLS(g, c, { f.v[c] = apply_cell_ortho<ND>(g, m, f.pt, i, j, k, c, true); })
+            grid.sync();
+            double acc = 0.0;
+            double tv[BP_U], vv[BP_U];
+            BP_CANON_CELLS(g, cb, c, u, BP_U, { tv[u] = f.rt[c]; vv[u] = f.v[c]; }, { acc += tv[u] * vv[u]; })
+            reduce(acc, 0.0, 1, false);
+        }
+        if (tid == 0) ctl2(&s);
+        __syncthreads();
+        {   // r -= alpha v (norm, next rho), e += alpha p_tilde, s_tilde = diagonal scaling of the new r
+            const bool on = s.doA != 0;
+            const double na = s.neg_alpha, al = s.alph[0];
+            double acc = 0.0, rho = 0.0;
+            double rr[BP_U], vv[BP_U], ee[BP_U], pp[BP_U], ld[BP_U], tv[BP_U];
+            BP_CANON_CELLS(g, cb, c, u, BP_U,
+                           {
+                               if (on) { rr[u] = f.r[c]; vv[u] = f.v[c]; ee[u] = f.e[c]; pp[u] = f.pt[c]; }
+                               if (a.nprecond) ld[u] = m.lapdiag[c];
+                               tv[u] = f.rt[c];
+                           },
+                           {
+                               double nv = 0.0;
+                               if (on) {
+                                   nv = rr[u] + na * vv[u];
+                                   f.e[c] = ee[u] + al * pp[u];
+                               }
+                               f.r[c] = nv;
+                               acc = nacc(acc, nv);
+                               rho += tv[u] * nv;
+                               f.stl[c] = a.nprecond ? nv / (g.alpha + g.beta * ld[u]) : nv;
+                           })
+            reduce(acc, rho, 2, nmax);
+            if (tid == 0) rhoNext = s.red[1];
+        }
+        if (tid == 0) ctl3(&s);
+        __syncthreads();
+        if (s.doB) {
+            relax(f.stl, f.r, a.nprecond);
+            {   // t = L s_tilde (spread over the grid), then <t, r>, <t, t> in the canonical order
+                BP_FOR_CELLS(g, c, { f.t[c] = apply_cell_ortho<ND>(g, m, f.stl, i, j, k, c, true); })
+                grid.sync();
+                double a0 = 0.0, a1 = 0.0;
+                double tv[BP_U], rr[BP_U];
+                BP_CANON_CELLS(g, cb, c, u, BP_U, { tv[u] = f.t[c]; rr[u] = f.r[c]; }, {
+                    a0 += tv[u] * rr[u];
+                    a1 += tv[u] * tv[u];
+                })
+                reduce(a0, a1, 2, false);
+            }
+            if (tid == 0) ctl4(&s);
+            __syncthreads();
+            {   // e += omega s_tilde, r -= omega t (norm, next rho)
+                const double om = s.omega[0], no = s.neg_omega;
+                double acc = 0.0, rho = 0.0;
+                double ee[BP_U], ss[BP_U], rr[BP_U], tt[BP_U], tv[BP_U];
+                BP_CANON_CELLS(g, cb, c, u, BP_U,
+                               { ee[u] = f.e[c]; ss[u] = f.stl[c]; rr[u] = f.r[c]; tt[u] = f.t[c]; tv[u] = f.rt[c]; },
+                               {
+                                   f.e[c] = ee[u] + om * ss[u];
+                                   const double nv = rr[u] + no * tt[u];
+                                   f.r[c] = nv;
+                                   acc = nacc(acc, nv);
+                                   rho += tv[u] * nv;
+                               })
+                reduce(acc, rho, 2, nmax);
+                if (tid == 0) rhoNext = s.red[1];
+            }
+        }
+        if (tid == 0) ctl5(&s);
+        __syncthreads();
+        if (s.status == 2) {   // restart: fold the correction into phi and begin again from the true residual
+            {
+                double pp[BP_U], ee[BP_U];
+                BP_CANON_CELLS(g, cb, c, u, BP_U, { pp[u] = f.phi[c]; ee[u] = f.e[c]; }, {
+                    f.phi[c] = pp[u] + 1.0 * ee[u];
+                    f.e[c] = 0.0;
+                })
+            }
+            if (restarts == a.numRestarts) break;
+            grid.sync();
+            true_residual();
+            if (tid == 0) {
+                s.nrm[0] = norm_finish(s.red[0], kind);
+                for (int q = 0; q < 4; ++q) s.rho[q] = 0.0;
+                s.alph[0] = s.alph[1] = s.bet[0] = s.bet[1] = s.omega[0] = s.omega[1] = 0.0;
+                s.init = 1;
+                s.status = loop_top(&s) ? 0 : 1;
+            }
+            ++restarts;
+            __syncthreads();
+        }
+    }
+    {   // phi += e   (e was last written in the canonical mapping; phi before the last grid.sync())
+        double pp[BP_U], ee[BP_U];
+        BP_CANON_CELLS(g, cb, c, u, BP_U, { pp[u] = f.phi[c]; ee[u] = f.e[c]; }, { f.phi[c] = pp[u] + 1.0 * ee[u]; })
+    }
+    if (blockIdx.x == 0 && tid == 0) *itersAccum += s.i;
+}
+
+}  // namespace somar

@@ -93,6 +93,7 @@ int somar_level_create(const SomarLevelDesc* desc, const SomarSolverParams* para
     L->desc.box_rank = L->box_rank.data();
     L->cx.sms = prop.multiProcessorCount;
     if (const char* e = getenv("SOMAR_B200_FUSED")) L->use_fused = (e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 2;
+    if (const char* e = getenv("SOMAR_B200_BOTTOM")) L->bottom_mode = (e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 2;
     int rc;
     cudaError_t ce;
     if ((ce = cudaStreamCreateWithFlags(&L->cx.stream, cudaStreamNonBlocking)) != cudaSuccess ||
@@ -134,6 +135,8 @@ int somar_level_destroy(SomarLevel* L) {
     for (auto* f : L->swork) if (f) { cudaFree(f->p); delete f; }
     if (L->comm) ncclCommDestroy(L->comm);
     cudaFree(L->cx.scratch); cudaFree(L->cx.tickets); cudaFree(L->d_scal); cudaFreeHost(L->h_scal);
+    if (L->d_bicg) cudaFree(L->d_bicg);
+    if (L->h_bicg) cudaFreeHost(L->h_bicg);
     cudaFree(L->stage);
     cudaEventDestroy(L->ev0); cudaEventDestroy(L->ev1);
     cudaStreamDestroy(L->cx.stream);

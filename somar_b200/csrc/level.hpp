@@ -54,6 +54,12 @@ struct SomarLevel {
     // scalars
     double* d_scal = nullptr;          // 8 doubles on device
     double* h_scal = nullptr;          // pinned mirror
+    void* d_bicg = nullptr;            // BicgState of the bottom solver (bicgstab.cu) and its pinned mirror
+    void* h_bicg = nullptr;
+    int bottom_mode = 2;               // SOMAR_B200_BOTTOM: 0 host-sequenced BiCGStab, 1 scalars on the device,
+                                       // 2 one persistent kernel per bottom visit where usable (else 1)
+    int bottom_coop_blocks = -1;       // co-resident blocks of the persistent kernel (-1: not yet queried)
+    bool bottom_iters_pending = false; // the device-side iteration counter holds uncollected counts
     // staging for host FAB transfers
     double* stage = nullptr;
     size_t stage_bytes = 0;
@@ -132,6 +138,9 @@ int reduce_global(SomarLevel* L, int depth, const double* x, const double* y, in
 // solver.cu
 int mg_cycle(SomarLevel* L, int depth, SomarField* e, const SomarField* r);
 int bottom_solve(SomarLevel* L, SomarField* e, const SomarField* r, int* iters);
+bool bottom_persistent_usable(SomarLevel* L);
+int bottom_persistent(SomarLevel* L, SomarField* e, const SomarField* r);
+int bottom_collect_iters(SomarLevel* L);
 int mg_solve(SomarLevel* L, SomarField* phi, const SomarField* rhs, bool zeroPhi, bool forceHomog,
              SomarSolveStats* st);
 

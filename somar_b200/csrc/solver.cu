@@ -1,7 +1,6 @@
 // solver.cu -- multigrid drivers on the level stream:
 //   mg_cycle      MappedMultiGrid<T>::cycle              src/calculus/AMRElliptic/MappedMultiGrid.H:555-653
-//   bottom_solve  Chombo 3.1 BiCGStabSolver<T>::solve     (not under the reference tree; configured at
-//                 src/projection/AMRPressureSolver.cpp:253-262; restated from the published algorithm)
+//   bottom_solve  Chombo 3.1 BiCGStabSolver<T>::solve     -> bicgstab.cu
 //   mg_solve      MappedAMRMultiGrid<T>::solveNoInitResid src/calculus/AMRElliptic/MappedAMRMultiGrid.H:979-1186
 //                 (l_base == l_max: AMRVCycle :1510-1513 -> oneCycle; postVCycleOps :1189-1215)
 #include "level.hpp"
@@ -20,6 +19,7 @@ int mg_cycle(SomarLevel* L, int depth, SomarField* e, const SomarField* r) {
         const long long bottomCells = (long long)g.gn[0] * g.gn[1] * g.gn[2];
         ProfScope ps(L, PH_BOTTOM);
         if (bottomCells == 1) return op_relax(L, depth, e, r, 1);                       // :566-568
+        if (bottom_persistent_usable(L)) return bottom_persistent(L, e, r);             // both steps, one launch
         if ((rc = op_relax(L, depth, e, r, p.num_smooth_bottom)) != SOMAR_OK) return rc;
         int it = 0;
         if ((rc = bottom_solve(L, e, r, &it)) != SOMAR_OK) return rc;
@@ -63,109 +63,6 @@ int mg_cycle(SomarLevel* L, int depth, SomarField* e, const SomarField* r) {
 }
 
 // ---------------------------------------------------------------------------------------------------------
-int bottom_solve(SomarLevel* L, SomarField* a_phi, const SomarField* a_rhs, int* iters) {
-    const SomarSolverParams& p = L->prm;
-    const int bd = L->ndepths() - 1;
-    const Geom& g = G(L, bd);
-    int rc;
-    if (L->bwork.empty()) {
-        L->bwork.resize(8, nullptr);
-        for (auto& f : L->bwork)
-            if ((rc = field_alloc(L, bd, &f))) return rc;
-    }
-    SomarField *r = L->bwork[0], *r_tilde = L->bwork[1], *e = L->bwork[2], *pv = L->bwork[3], *p_tilde = L->bwork[4],
-               *s_tilde = L->bwork[5], *t = L->bwork[6], *v = L->bwork[7];
-    Ctx& cx = L->cx;
-    auto norm = [&](SomarField* x, double* out) {
-        int kind = (p.bottom_normType == 0) ? 0 : (p.bottom_normType == 1 ? 1 : 2);
-        int rc2 = reduce_global(L, bd, x->p, nullptr, kind, out);
-        if (kind == 2) *out = std::sqrt(*out);
-        return rc2;
-    };
-    auto dot = [&](SomarField* a, SomarField* b, double* out) { return reduce_global(L, bd, a->p, b->p, 3, out); };
-
-    int recount = 0;
-    if ((rc = op_apply(L, bd, r->p, a_phi, a_rhs->p, 1, true))) return rc;
-    launch_copy(cx, g, r_tilde->p, r->p);
-    launch_fill(cx, g, e->p, 0.0);
-    launch_fill(cx, g, p_tilde->p, 0.0);
-    launch_fill(cx, g, s_tilde->p, 0.0);
-    int i = 0;
-    double rho[4] = {0, 0, 0, 0}, nrm[2];
-    if ((rc = norm(r, &nrm[0]))) return rc;
-    double initial_norm = nrm[0];
-    const double initial_rnorm = nrm[0];
-    nrm[1] = nrm[0];
-    double alph[2] = {0, 0}, bet[2] = {0, 0}, omega[2] = {0, 0};
-    bool init = true;
-    int restarts = 0;
-    if (L->bottomMetric > 0) initial_norm = L->bottomMetric;
-    const double eps = L->bottomEps;
-    while ((i < p.bottom_imax && nrm[0] > eps * nrm[1]) && (nrm[1] > 0)) {
-        ++i;
-        nrm[1] = nrm[0];
-        alph[1] = alph[0]; bet[1] = bet[0]; omega[1] = omega[0];
-        rho[3] = rho[2]; rho[2] = rho[1];
-        if ((rc = dot(r_tilde, r, &rho[1]))) return rc;
-        if (rho[1] == 0.0) break;
-        if (init) {
-            launch_copy(cx, g, pv->p, r->p);
-            init = false;
-        } else {
-            bet[1] = (rho[1] / rho[2]) * (alph[1] / omega[1]);
-            launch_scale(cx, g, pv->p, bet[1]);
-            launch_axpy(cx, g, pv->p, v->p, -bet[1] * omega[1]);
-            launch_axpy(cx, g, pv->p, r->p, 1.0);
-        }
-        if ((rc = op_precond(L, bd, p_tilde, pv))) return rc;
-        if ((rc = op_apply(L, bd, v->p, p_tilde, nullptr, 0, true))) return rc;
-        double m;
-        if ((rc = dot(r_tilde, v, &m))) return rc;
-        alph[0] = rho[1] / m;
-        if (std::fabs(m) > p.bottom_small * std::fabs(rho[1])) {
-            launch_axpy(cx, g, r->p, v->p, -alph[0]);
-            if ((rc = norm(r, &nrm[0]))) return rc;
-            launch_axpy(cx, g, e->p, p_tilde->p, alph[0]);
-        } else {
-            launch_fill(cx, g, r->p, 0.0);
-            nrm[0] = 0.0;
-        }
-        if (nrm[0] > eps * initial_norm && nrm[0] > p.bottom_reps * initial_rnorm) {
-            if ((rc = op_precond(L, bd, s_tilde, r))) return rc;
-            if ((rc = op_apply(L, bd, t->p, s_tilde, nullptr, 0, true))) return rc;
-            double tr, tt;
-            if ((rc = dot(t, r, &tr))) return rc;
-            if ((rc = dot(t, t, &tt))) return rc;
-            omega[0] = tr / tt;
-            launch_axpy(cx, g, e->p, s_tilde->p, omega[0]);
-            launch_axpy(cx, g, r->p, t->p, -omega[0]);
-            if ((rc = norm(r, &nrm[0]))) return rc;
-        }
-        if (nrm[0] <= eps * initial_norm || nrm[0] <= p.bottom_reps * initial_rnorm) break;
-        if (omega[0] == 0.0 || nrm[0] > (1.0 - p.bottom_hang) * nrm[1]) {
-            if (recount == 0) {
-                recount = 1;
-            } else {
-                recount = 0;
-                launch_axpy(cx, g, a_phi->p, e->p, 1.0);
-                if (restarts == p.bottom_numRestarts) { launch_fill(cx, g, e->p, 0.0); break; }
-                if ((rc = op_apply(L, bd, r->p, a_phi, a_rhs->p, 1, true))) return rc;
-                if ((rc = norm(r, &nrm[0]))) return rc;
-                rho[0] = rho[1] = rho[2] = rho[3] = 0.0;
-                alph[0] = alph[1] = bet[0] = bet[1] = omega[0] = omega[1] = 0.0;
-                launch_fill(cx, g, e->p, 0.0);
-                ++restarts;
-                init = true;
-                launch_copy(cx, g, r_tilde->p, r->p);
-            }
-        }
-    }
-    launch_axpy(cx, g, a_phi->p, e->p, 1.0);
-    *iters = i;
-    return SOMAR_OK;
-}
-
-// ---------------------------------------------------------------------------------------------------------
 int mg_solve(SomarLevel* L, SomarField* phi, const SomarField* rhs, bool zeroPhi, bool forceHomog,
              SomarSolveStats* st) {
     const SomarSolverParams& p = L->prm;
@@ -194,6 +91,7 @@ int mg_solve(SomarLevel* L, SomarField* phi, const SomarField* rhs, bool zeroPhi
     bool useBest = false;
     L->bottomMetric = initial_rnorm;       // setConvergenceMetrics(initial_rnorm, cushion * eps) :1047
     L->bottomEps = 1.0 * p.eps;
+    if ((rc = bottom_collect_iters(L))) return rc;    // counts left by direct mg_cycle calls
     L->bottom_iters_total = 0;
     int hl = 0;
     st->history[hl++] = rnorm;
@@ -236,6 +134,7 @@ int mg_solve(SomarLevel* L, SomarField* phi, const SomarField* rhs, bool zeroPhi
     SOMAR_CUDA(cudaEventSynchronize(L->ev1));
     float ms = 0.f;
     SOMAR_CUDA(cudaEventElapsedTime(&ms, L->ev0, L->ev1));
+    if ((rc = bottom_collect_iters(L))) return rc;    // iterations the persistent bottom kernel counted on the device
     st->iters = iter;
     st->initial_rnorm = initial_rnorm;
     st->final_rnorm = rnorm;

@@ -73,6 +73,43 @@ def test_solve_history_matches_oracle(case, mode, oracle_lib, somar):
     assert np.abs((phi - phi.mean()) - (phi_o - phi_o.mean())).max() <= 1e-6 * scale
 
 
+@pytest.mark.parametrize("case,extra", [
+    (dict(n=(64, 64, 16), map_name="stretched", aniso=16.0), {}),
+    (dict(n=(64, 64, 16), map_name="stretched", aniso=16.0), dict(bottom_normType=0)),
+    (dict(n=(48, 32, 16), map_name="stretched", aniso=4.0, periodic=(0, 1, 0)), {}),
+    (dict(n=(32, 32, 16), map_name="terrain", aniso=8.0, map_params={"amp": 0.1}), dict(relaxMode=3)),
+    # a generous hang criterion forces the restart branch (two slow iterations -> fold e into phi, start again)
+    (dict(n=(64, 64, 16), map_name="stretched", aniso=16.0), dict(bottom_hang=0.9, bottom_numRestarts=3)),
+    (dict(n=(64, 64, 16), map_name="stretched", aniso=16.0), dict(bottom_hang=0.9, bottom_numRestarts=0)),
+])
+def test_device_resident_bicgstab_equals_host_sequenced(case, extra, somar, monkeypatch):
+    """bicgstab.cu: SOMAR_B200_BOTTOM=0 reads every scalar back to the host, 1 keeps rho/alpha/beta/omega and the
+    branch flags in HBM, 2 runs the whole bottom visit as one persistent cooperative kernel (where usable: single
+    rank, diagonal metric, no periodic direction; else it is mode 1).  Same arithmetic, same order: identical bits."""
+    pb = Problem(**case)
+    prm = dict(SOLVE)
+    prm.setdefault("relaxMode", 1)
+    prm.update(extra)
+    rhs = pb.rhs()
+    got = {}
+    for variant in ("0", "1", "2"):
+        monkeypatch.setenv("SOMAR_B200_BOTTOM", variant)
+        lev = pb.level(somar, **prm)
+        fphi, frhs = lev.field(0), lev.field(0, rhs)
+        st = lev.solve(fphi, frhs)
+        got[variant] = (fphi.get(), st)
+        lev.destroy()
+    p0, s0 = got["0"]
+    assert s0["bottom_iters_total"] > 0
+    for variant in ("1", "2"):
+        p1, s1 = got[variant]
+        assert s0["bottom_iters_total"] == s1["bottom_iters_total"], variant
+        assert s0["iters"] == s1["iters"] and s0["history"] == s1["history"], variant
+        assert np.array_equal(p0, p1), variant
+    if pb.is_diagonal and not any(pb.periodic):   # the persistent kernel was usable
+        assert got["2"][1]["launches"] < 0.5 * s0["launches"]
+
+
 def test_manufactured_solution_second_order(oracle_lib, somar):
     """rhs = L[phi*] for a smooth Neumann-compatible phi*: the solve must return phi* (up to a constant)."""
     from somar_b200 import synthetic as syn
