@@ -166,7 +166,7 @@ __device__ __forceinline__ void ctl5(BicgState* st) {
             }                                                                                              \
         }                                                                                                  \
     }
-#define BP_U 4
+#define BP_U 8
 
 template <int ND>
 __global__ void __launch_bounds__(BP_TPB, BP_MINBLOCKS)
@@ -213,6 +213,17 @@ __global__ void __launch_bounds__(BP_TPB, BP_MINBLOCKS)
         if (kind == 1) return acc + fabs(v);
         return acc + v * v;
     };
+    // norm(r) and <r_tilde, r> in the canonical order (r complete on entry) -> s.red[0], rhoNext
+    auto norm_and_rho = [&]() {
+        double acc = 0.0, rho = 0.0;
+        double tv[BP_U], rv[BP_U];
+        BP_CANON_CELLS(g, cb, c, u, BP_U, { tv[u] = f.rt[c]; rv[u] = f.r[c]; }, {
+            acc = nacc(acc, rv[u]);
+            rho += tv[u] * rv[u];
+        })
+        reduce(acc, rho, 2, nmax);
+        if (tid == 0) rhoNext = s.red[1];
+    };
     // one colour of point Gauss-Seidel, in place (LevelGSRB::relax, GSRB.cpp:58-98): lane l of a 64-cell item owns
     // the cell 2l + parity
     auto colour_pass = [&](double* phi, const double* rhs, int pass) {
@@ -242,14 +253,7 @@ __global__ void __launch_bounds__(BP_TPB, BP_MINBLOCKS)
             f.e[c] = 0.0;
         })
         grid.sync();
-        double acc = 0.0, rho = 0.0;
-        double rv[BP_U];
-        BP_CANON_CELLS(g, cb, c, u, BP_U, { rv[u] = f.r[c]; }, {
-            acc = nacc(acc, rv[u]);
-            rho += rv[u] * rv[u];
-        })
-        reduce(acc, rho, 2, nmax);
-        if (tid == 0) rhoNext = s.red[1];
+        norm_and_rho();
     };
 
     relax(f.phi, f.rhs, a.presmooth);
@@ -278,23 +282,16 @@ __global__ void __launch_bounds__(BP_TPB, BP_MINBLOCKS)
         {   // p = r  or  ((beta p) + (-beta omega) v) + r;   p_tilde = preCond(p): diagonal scaling, then relaxations
             const bool init = s.init != 0;
             const double b = s.bet[1], cv = s.c_pv;
-            double rr[BP_U], pp[BP_U], vv[BP_U], ld[BP_U];
-            BP_CANON_CELLS(g, cb, c, u, BP_U,
-                           {
-                               rr[u] = f.r[c];
-                               if (!init) { pp[u] = f.pv[c]; vv[u] = f.v[c]; }
-                               if (a.nprecond) ld[u] = m.lapdiag[c];
-                           },
-                           {
-                               double pn = rr[u];
-                               if (!init) {
-                                   const double t1 = pp[u] * b;
-                                   const double t2 = t1 + cv * vv[u];
-                                   pn = t2 + 1.0 * pn;
-                               }
-                               f.pv[c] = pn;
-                               f.pt[c] = a.nprecond ? pn / (g.alpha + g.beta * ld[u]) : pn;
-                           })
+            BP_FOR_CELLS(g, c, {
+                double pn = f.r[c];
+                if (!init) {
+                    const double t1 = f.pv[c] * b;
+                    const double t2 = t1 + cv * f.v[c];
+                    pn = t2 + 1.0 * pn;
+                }
+                f.pv[c] = pn;
+                f.pt[c] = a.nprecond ? pn / (g.alpha + g.beta * m.lapdiag[c]) : pn;
+            })
             grid.sync();
             relax(f.pt, f.pv, a.nprecond);
         }
@@ -308,30 +305,20 @@ __global__ void __launch_bounds__(BP_TPB, BP_MINBLOCKS)
         }
         if (tid == 0) ctl2(&s);
         __syncthreads();
-        {   // r -= alpha v (norm, next rho), e += alpha p_tilde, s_tilde = diagonal scaling of the new r
+        {   // r -= alpha v, e += alpha p_tilde, s_tilde = diagonal scaling of the new r;  then norm(r), next rho
             const bool on = s.doA != 0;
             const double na = s.neg_alpha, al = s.alph[0];
-            double acc = 0.0, rho = 0.0;
-            double rr[BP_U], vv[BP_U], ee[BP_U], pp[BP_U], ld[BP_U], tv[BP_U];
-            BP_CANON_CELLS(g, cb, c, u, BP_U,
-                           {
-                               if (on) { rr[u] = f.r[c]; vv[u] = f.v[c]; ee[u] = f.e[c]; pp[u] = f.pt[c]; }
-                               if (a.nprecond) ld[u] = m.lapdiag[c];
-                               tv[u] = f.rt[c];
-                           },
-                           {
-                               double nv = 0.0;
-                               if (on) {
-                                   nv = rr[u] + na * vv[u];
-                                   f.e[c] = ee[u] + al * pp[u];
-                               }
-                               f.r[c] = nv;
-                               acc = nacc(acc, nv);
-                               rho += tv[u] * nv;
-                               f.stl[c] = a.nprecond ? nv / (g.alpha + g.beta * ld[u]) : nv;
-                           })
-            reduce(acc, rho, 2, nmax);
-            if (tid == 0) rhoNext = s.red[1];
+            BP_FOR_CELLS(g, c, {
+                double nv = 0.0;
+                if (on) {
+                    nv = f.r[c] + na * f.v[c];
+                    f.e[c] = f.e[c] + al * f.pt[c];
+                }
+                f.r[c] = nv;
+                f.stl[c] = a.nprecond ? nv / (g.alpha + g.beta * m.lapdiag[c]) : nv;
+            })
+            grid.sync();
+            norm_and_rho();
         }
         if (tid == 0) ctl3(&s);
         __syncthreads();
@@ -352,19 +339,12 @@ __global__ void __launch_bounds__(BP_TPB, BP_MINBLOCKS)
             __syncthreads();
             {   // e += omega s_tilde, r -= omega t (norm, next rho)
                 const double om = s.omega[0], no = s.neg_omega;
-                double acc = 0.0, rho = 0.0;
-                double ee[BP_U], ss[BP_U], rr[BP_U], tt[BP_U], tv[BP_U];
-                BP_CANON_CELLS(g, cb, c, u, BP_U,
-                               { ee[u] = f.e[c]; ss[u] = f.stl[c]; rr[u] = f.r[c]; tt[u] = f.t[c]; tv[u] = f.rt[c]; },
-                               {
-                                   f.e[c] = ee[u] + om * ss[u];
-                                   const double nv = rr[u] + no * tt[u];
-                                   f.r[c] = nv;
-                                   acc = nacc(acc, nv);
-                                   rho += tv[u] * nv;
-                               })
-                reduce(acc, rho, 2, nmax);
-                if (tid == 0) rhoNext = s.red[1];
+                BP_FOR_CELLS(g, c, {
+                    f.e[c] = f.e[c] + om * f.stl[c];
+                    f.r[c] = f.r[c] + no * f.t[c];
+                })
+                grid.sync();
+                norm_and_rho();
             }
         }
         if (tid == 0) ctl5(&s);
