@@ -332,11 +332,15 @@ static int ensure_state(SomarLevel* L) {
 
 bool bottom_persistent_usable(SomarLevel* L) {
     if (L->bottom_mode != 2) return false;
-    const SomarSolverParams& p = L->prm;
-    const int bd = L->ndepths() - 1;
-    const Depth& dp = L->depths[bd];
+    const Depth& dp = L->depths[L->ndepths() - 1];
     const Geom& g = dp.g;
     if (!dp.m.diagonal || L->desc.nranks > 1 || g.nbr[0] >= 0 || g.nbr[1] >= 0) return false;
+    return bottom_persistent_params_ok(L, g);
+}
+
+// solver parameters and size the persistent kernel supports, for a single-rank diagonal-metric geometry g
+bool bottom_persistent_params_ok(SomarLevel* L, const Geom& g) {
+    const SomarSolverParams& p = L->prm;
     if (g.periodic[0] || g.periodic[1] || (g.nd > 2 && g.periodic[2])) return false;
     if (p.relaxMode != SOMAR_RELAX_LEVEL_GSRB) return false;
     const bool precond = !(p.num_smooth_precond == 0 || p.precondMode == 0);
@@ -365,7 +369,6 @@ static int persistent_blocks(const Geom& g, int cap) {
 
 // bottom of the V-cycle: num_smooth_bottom relaxations + BiCGStab (MappedMultiGrid.H:566-573) in one launch
 int bottom_persistent(SomarLevel* L, SomarField* e_mg, const SomarField* r_mg) {
-    const SomarSolverParams& p = L->prm;
     const int bd = L->ndepths() - 1;
     Depth& dp = L->depths[bd];
     int rc;
@@ -374,12 +377,22 @@ int bottom_persistent(SomarLevel* L, SomarField* e_mg, const SomarField* r_mg) {
         for (auto& f : L->bwork)
             if ((rc = field_alloc(L, bd, &f))) return rc;
     }
+    double* work[8];
+    for (int q = 0; q < 8; ++q) work[q] = L->bwork[q]->p;
+    return launch_bottom_persistent(L, dp.g, dp.m, e_mg->p, r_mg->p, work);
+}
+
+// the launch, on any single-rank geometry (the rank's own bottom depth, or the gathered one of bottom_gather.cu)
+int launch_bottom_persistent(SomarLevel* L, const Geom& g_, const Metric& m_, double* phi, double* rhs,
+                             double* const work[8]) {
+    const SomarSolverParams& p = L->prm;
+    int rc;
     if ((rc = ensure_state(L))) return rc;
     BicgDev* dv = static_cast<BicgDev*>(L->d_bicg);
     BicgFields f;
-    f.phi = e_mg->p; f.rhs = r_mg->p;
-    f.r = L->bwork[0]->p; f.rt = L->bwork[1]->p; f.e = L->bwork[2]->p; f.pv = L->bwork[3]->p; f.pt = L->bwork[4]->p;
-    f.stl = L->bwork[5]->p; f.t = L->bwork[6]->p; f.v = L->bwork[7]->p;
+    f.phi = phi; f.rhs = rhs;
+    f.r = work[0]; f.rt = work[1]; f.e = work[2]; f.pv = work[3]; f.pt = work[4];
+    f.stl = work[5]; f.t = work[6]; f.v = work[7];
     BicgArgs a;
     a.presmooth = p.num_smooth_bottom;
     a.nprecond = (p.num_smooth_precond == 0 || p.precondMode == 0) ? 0 : p.num_smooth_precond;
@@ -388,8 +401,8 @@ int bottom_persistent(SomarLevel* L, SomarField* e_mg, const SomarField* r_mg) {
     a.eps = L->bottomEps; a.reps = p.bottom_reps; a.small = p.bottom_small; a.one_minus_hang = 1.0 - p.bottom_hang;
     a.imax = p.bottom_imax;
     a.normKind = (p.bottom_normType == 0) ? 0 : (p.bottom_normType == 1 ? 1 : 2);
-    Geom g = dp.g;
-    Metric m = dp.m;
+    Geom g = g_;
+    Metric m = m_;
     double* part = dv->part;
     int* itersAccum = &dv->iters;
     int cb = row_blocks(g, L->cx.sms);   // the blocks k_reduce would use: the canonical summation order

@@ -434,6 +434,7 @@ int level_finalize(SomarLevel* L) {
         cudaFree(phi->p); cudaFree(rhs->p); cudaFree(res->p);
         delete phi; delete rhs; delete res;
     }
+    if ((rc = gathered_bottom_build(L)) != SOMAR_OK) return rc;   // multi-rank: replicate the bottom depth
     L->finalized = true;
     return SOMAR_OK;
 }

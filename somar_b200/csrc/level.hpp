@@ -36,6 +36,22 @@ struct Depth {
     double* recvbuf[2] = {nullptr, nullptr};
 };
 
+// Full-domain copy of the bottom depth kept by every rank of a multi-rank level (bottom_gather.cu).
+struct GatheredBottom {
+    Geom g;                            // the bottom depth with all rows, no neighbours
+    Metric m;
+    double* jg[3] = {nullptr, nullptr, nullptr};
+    double* jinv = nullptr;
+    double* lapdiag = nullptr;
+    double* phi = nullptr;             // correction / residual of the bottom visit on the full domain
+    double* rhs = nullptr;
+    double* work[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    double* sendbuf = nullptr;         // my slabs, dense
+    double* allbuf = nullptr;          // every rank's slabs
+    std::vector<int> row0, rows;       // first row / number of rows of each rank at the bottom depth
+    int maxRows = 0;
+};
+
 }  // namespace somar
 
 struct SomarLevel {
@@ -60,6 +76,7 @@ struct SomarLevel {
                                        // 2 one persistent kernel per bottom visit where usable (else 1)
     int bottom_coop_blocks = -1;       // co-resident blocks of the persistent kernel (-1: not yet queried)
     bool bottom_iters_pending = false; // the device-side iteration counter holds uncollected counts
+    somar::GatheredBottom* gb = nullptr; // multi-rank: replicated bottom depth (built at finalize when usable)
     // staging for host FAB transfers
     double* stage = nullptr;
     size_t stage_bytes = 0;
@@ -141,6 +158,14 @@ int bottom_solve(SomarLevel* L, SomarField* e, const SomarField* r, int* iters);
 bool bottom_persistent_usable(SomarLevel* L);
 int bottom_persistent(SomarLevel* L, SomarField* e, const SomarField* r);
 int bottom_collect_iters(SomarLevel* L);
+bool bottom_persistent_params_ok(SomarLevel* L, const Geom& g);
+int launch_bottom_persistent(SomarLevel* L, const Geom& g, const Metric& m, double* phi, double* rhs,
+                             double* const work[8]);
+// bottom_gather.cu
+int gathered_bottom_build(SomarLevel* L);
+void gathered_bottom_free(SomarLevel* L);
+bool bottom_gathered_usable(SomarLevel* L);
+int bottom_gathered(SomarLevel* L, SomarField* e, const SomarField* r);
 int mg_solve(SomarLevel* L, SomarField* phi, const SomarField* rhs, bool zeroPhi, bool forceHomog,
              SomarSolveStats* st);
 

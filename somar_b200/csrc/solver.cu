@@ -20,6 +20,7 @@ int mg_cycle(SomarLevel* L, int depth, SomarField* e, const SomarField* r) {
         ProfScope ps(L, PH_BOTTOM);
         if (bottomCells == 1) return op_relax(L, depth, e, r, 1);                       // :566-568
         if (bottom_persistent_usable(L)) return bottom_persistent(L, e, r);             // both steps, one launch
+        if (bottom_gathered_usable(L)) return bottom_gathered(L, e, r);                 // the same on the replicated depth
         if ((rc = op_relax(L, depth, e, r, p.num_smooth_bottom)) != SOMAR_OK) return rc;
         int it = 0;
         if ((rc = bottom_solve(L, e, r, &it)) != SOMAR_OK) return rc;
