@@ -230,7 +230,14 @@ int level_build(SomarLevel* L) {
 int exchange(SomarLevel* L, int depth, double* x, int width) {
     Depth& dp = L->depths[depth];
     const Geom& g = dp.g;
+    int p2p = 0;
     if (L->desc.nranks > 1 && (g.nbr[0] >= 0 || g.nbr[1] >= 0)) {
+        p2p = halo_p2p_exchange(L, depth, x, width);   // peer-memory path (two launches), when the arenas are mapped
+        if (p2p < 0) return SOMAR_ERR_COMM;
+    }
+    if (p2p == 1) {
+        // done
+    } else if (L->desc.nranks > 1 && (g.nbr[0] >= 0 || g.nbr[1] >= 0)) {
         const size_t cnt = (size_t)width * (g.n[0] + 2 * SOMAR_GHOST) * (g.n[2] + 2 * g.gh[2]);
         for (int s = 0; s < 2; ++s)
             if (g.nbr[s] >= 0) launch_pack_y(L->cx, g, x, dp.sendbuf[s], s, width, false);

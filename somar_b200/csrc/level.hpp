@@ -36,6 +36,16 @@ struct Depth {
     double* recvbuf[2] = {nullptr, nullptr};
 };
 
+// Peer-memory halo exchange (halo_p2p.cu): my arena, my y-neighbours' arenas mapped through CUDA IPC.
+struct HaloArena {
+    int state = 0;                     // 0 not set up yet, 1 in use, -1 unavailable (NCCL send/recv is used)
+    char* base = nullptr;              // my arena: per depth 2 sides x 2 receive slots, then counters, then tickets
+    char* peer[2] = {nullptr, nullptr};// the low / high neighbour's arena
+    size_t bytes = 0, flagOff = 0, ticketOff = 0;
+    std::vector<size_t> slotOff, slotBytes;          // per depth
+    std::vector<unsigned long long> seq[2];          // per side, per depth: messages exchanged so far
+};
+
 // Full-domain copy of the bottom depth kept by every rank of a multi-rank level (bottom_gather.cu).
 struct GatheredBottom {
     Geom g;                            // the bottom depth with all rows, no neighbours
@@ -77,6 +87,7 @@ struct SomarLevel {
     int bottom_coop_blocks = -1;       // co-resident blocks of the persistent kernel (-1: not yet queried)
     bool bottom_iters_pending = false; // the device-side iteration counter holds uncollected counts
     somar::GatheredBottom* gb = nullptr; // multi-rank: replicated bottom depth (built at finalize when usable)
+    somar::HaloArena halo;             // multi-rank: peer-memory halo exchange
     // staging for host FAB transfers
     double* stage = nullptr;
     size_t stage_bytes = 0;
@@ -161,6 +172,9 @@ int bottom_collect_iters(SomarLevel* L);
 bool bottom_persistent_params_ok(SomarLevel* L, const Geom& g);
 int launch_bottom_persistent(SomarLevel* L, const Geom& g, const Metric& m, double* phi, double* rhs,
                              double* const work[8]);
+// halo_p2p.cu
+int halo_p2p_exchange(SomarLevel* L, int depth, double* x, int width);   // 1 done, 0 use NCCL, < 0 error
+void halo_p2p_free(SomarLevel* L);
 // bottom_gather.cu
 int gathered_bottom_build(SomarLevel* L);
 void gathered_bottom_free(SomarLevel* L);
