@@ -311,6 +311,7 @@ def run_ours(a):
             "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms / a.steps, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": workload_config(a, {
+                "halo_path": lev.halo_path(),
                 "vcycles_per_solve": iters / a.steps, "final_rel_residual": stats[-1]["final_rnorm"] / stats[-1]["initial_rnorm"],
                 "exit_status": stats[-1]["exit_status"], "bottom_iters_per_solve": stats[-1]["bottom_iters_total"],
                 "schedule": [{"n": list(s["n"]), "ratio": list(s["ratio"])} for s in schedule],

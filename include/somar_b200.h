@@ -131,6 +131,9 @@ int somar_level_launch_count(const SomarLevel* lev, long long* launches);
  * pass; 1 = k_gsrb_fused, one launch per red+black iteration; 2 = k_gsrb_full (colour pass, full metric);
  * 3 = k_line_gsrb (colour pass); 4 = apply + k_jacobi; 5 = k_gsrb_async (as 1, pipelined); -1 = none. */
 int somar_level_relax_kernel(const SomarLevel* lev, int depth, int relax_mode, int* kernel_id);
+/* Which path do y-halo exchanges take on this level: 0 = none needed (one rank), 1 = pack + ncclSend/Recv + unpack,
+ * 2 = peer-memory push/pull kernels over CUDA IPC (halo_p2p.cu); valid after somar_level_finalize. */
+int somar_level_halo_path(const SomarLevel* lev, int* path);
 /* Reads back a depth's metric into rank-local arrays without ghosts (tests): comp-outermost for jg. */
 int somar_level_get_metric(SomarLevel* lev, int depth, double* jg0, double* jg1, double* jg2, double* jinv,
                            double* lapdiag);
@@ -173,6 +176,26 @@ int somar_restrict_residual(SomarLevel* lev, int depth, SomarField* res_coarse, 
                             const SomarField* rhs_fine);                                  /* restrictResidual :1281 */
 int somar_prolong_increment(SomarLevel* lev, int depth, SomarField* phi_fine, const SomarField* cor_coarse);
 
+/* ---- projector calculus: the callers either side of the solve ----------------------------------
+ * Face fields are ordinary SomarFields of depth 0 holding face-centred data: face (i,j,k) of direction d is the low
+ * face of cell (i,j,k), the high face of a row's last cell sits in the first ghost slot.  Upload / download them
+ * with somar_field_set_fab/get_fab and the FluxBox FAB's own (surroundingNodes) box, or densely with
+ * somar_field_set_face/get_face (rank-local array with n[dir]+1 points in direction dir).
+ * somar_mac_gradient:   g_d = J g^{dj} d_j phi with the level's BCs      Gradient::levelGradientMAC, Gradient.cpp:85-170,
+ *                       946-1100 -> MAPPEDMACGRAD[ORTHO], DivCurlGradF.ChF:87-262 (LevelMACProjector.cpp:186-218)
+ * somar_mac_divergence: div = Jinv sum_d (F_d(+) - F_d(-)) / dx_d, then / divide_by unless that is 0
+ *                       Divergence::levelDivergenceMAC, Divergence.cpp:44-127 -> MAPPEDFLUXDIVERGENCE*, DivCurlGradF.ChF:1034-1214
+ * somar_mac_apply_correction: v_d -= dt * (J g^{dj} d_j phi)  (dt == 0: scale -1); gradient never stored
+ *                       LevelMACProjector::applyCorrection, LevelMACProjector.cpp:221-240
+ * somar_project:        BaseProjector::project with a_velIsFlux = true on one level (BaseProjectorI.H:176-300):
+ *                       rhs = Div[v]/dt, solve L[pressure] = rhs, v -= dt Grad[pressure]. */
+int somar_field_set_face(SomarField* f, const double* data, int dir, int on_device);
+int somar_field_get_face(const SomarField* f, double* data, int dir, int on_device);
+int somar_mac_gradient(SomarLevel* lev, SomarField* gx, SomarField* gy, SomarField* gz, SomarField* phi, int homogeneous);
+int somar_mac_divergence(SomarLevel* lev, SomarField* div, const SomarField* fx, const SomarField* fy,
+                         const SomarField* fz, double divide_by);
+int somar_mac_apply_correction(SomarLevel* lev, SomarField* vx, SomarField* vy, SomarField* vz, SomarField* phi, double dt);
+
 /* ---- drivers --------------------------------------------------------------------------------------------
  * somar_mg_cycle: MappedMultiGrid<T>::cycle (MappedMultiGrid.H:555-653) from `depth` down.
  * somar_solve: AMRPressureSolver::solve -> MappedAMRMultiGrid<T>::solveNoInitResid, single level
@@ -180,6 +203,8 @@ int somar_prolong_increment(SomarLevel* lev, int depth, SomarField* phi_fine, co
 int somar_mg_cycle(SomarLevel* lev, int depth, SomarField* e, const SomarField* r);
 int somar_solve(SomarLevel* lev, SomarField* phi, const SomarField* rhs, int zero_phi, int force_homogeneous,
                 SomarSolveStats* stats);
+int somar_project(SomarLevel* lev, SomarField* vx, SomarField* vy, SomarField* vz, SomarField* pressure, double dt,
+                  int zero_pressure, int force_homogeneous, SomarSolveStats* stats);
 
 #ifdef __cplusplus
 }

@@ -305,4 +305,70 @@ double orc_timed_solve(void* hv, const double* rhs, int ncycles_cap, OrcStats* o
     return t1 - t0;
 }
 
+// ---- projector calculus.  Face arrays: global, +1 point in their own direction, one component. ----
+static void scatter_faces(const Op& op, FluxLevelData& fl, const double* const* g) {
+    const long nx = op.domain.box.size(0), ny = op.domain.box.size(1);
+    for (size_t b = 0; b < op.grids.size(); ++b)
+        for (int d = 0; d < op.nd; ++d) {
+            const long fx = nx + (d == 0), fy = ny + (d == 1);
+            FAB& f = fl.fabs[b][d];
+            ORC_LOOP(f.box(), i, j, k) f(i, j, k) = g[d][i + fx * (j + fy * (long)k)];
+        }
+}
+static void gather_faces(const Op& op, const FluxLevelData& fl, double* const* g) {
+    const long nx = op.domain.box.size(0), ny = op.domain.box.size(1);
+    for (size_t b = 0; b < op.grids.size(); ++b)     // ascending boxes: an interface face ends up as its high-side box wrote it
+        for (int d = 0; d < op.nd; ++d) {
+            const long fx = nx + (d == 0), fy = ny + (d == 1);
+            const FAB& f = fl.fabs[b][d];
+            ORC_LOOP(f.box(), i, j, k) g[d][i + fx * (j + fy * (long)k)] = f(i, j, k);
+        }
+}
+
+void orc_mac_gradient(void* hv, int depth, double* g0, double* g1, double* g2, const double* phi, int homog) {
+    Op& op = *((OrcHandle*)hv)->mg->ops[depth];
+    LevelData p;
+    op.create(p, 1);
+    scatter(op, p, phi);
+    FluxLevelData gr;
+    gr.define(op.grids, 1, op.nd);
+    op.macGradient(gr, p, homog != 0);
+    double* g[3] = {g0, g1, g2};
+    gather_faces(op, gr, g);
+}
+
+void orc_mac_divergence(void* hv, int depth, double* div, const double* f0, const double* f1, const double* f2) {
+    Op& op = *((OrcHandle*)hv)->mg->ops[depth];
+    FluxLevelData fl;
+    fl.define(op.grids, 1, op.nd);
+    const double* f[3] = {f0, f1, f2};
+    scatter_faces(op, fl, f);
+    LevelData d;
+    op.create(d, 0);
+    op.macDivergence(d, fl);
+    gather(op, d, div);
+}
+
+void orc_project(void* hv, double* v0, double* v1, double* v2, double* pressure, double dt, int zeroPressure,
+                 int forceHomogeneous, OrcStats* out) {
+    MG& mg = *((OrcHandle*)hv)->mg;
+    Op& op = *mg.ops[0];
+    FluxLevelData vel;
+    vel.define(op.grids, 1, op.nd);
+    double* v[3] = {v0, v1, v2};
+    scatter_faces(op, vel, v);
+    LevelData p;
+    op.create(p, 1);
+    scatter(op, p, pressure);
+    SolveStats st;
+    mg.project(vel, p, dt, zeroPressure != 0, forceHomogeneous != 0, st);
+    gather(op, p, pressure);
+    gather_faces(op, vel, v);
+    out->iters = st.iters; out->exitStatus = st.exitStatus;
+    out->initial_rnorm = st.initial_rnorm; out->final_rnorm = st.final_rnorm;
+    out->bottom_iters_total = st.bottom_iters_total;
+    out->history_len = (int)std::min<size_t>(128, st.history.size());
+    for (int i = 0; i < out->history_len; ++i) out->history[i] = st.history[i];
+}
+
 }  // extern "C"

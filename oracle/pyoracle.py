@@ -229,6 +229,33 @@ class Oracle:
         self.L.orc_solve(self.h, _ptr(phi), _ptr(rhs), int(zero_phi), int(force_homogeneous), C.byref(st))
         return phi, _stats(st)
 
+    # -- projector calculus (face arrays: +1 point in their own direction) ---------------------
+    def face_shapes(self, depth=0):
+        n = self.depth_info(depth)["n"]
+        return [(n[2] + (d == 2), n[1] + (d == 1), n[0] + (d == 0)) for d in range(self.dim)]
+
+    def mac_gradient(self, phi, depth=0, homogeneous=False):
+        phi = _f64(phi)
+        g = [np.zeros(sh) for sh in self.face_shapes(depth)] + [None] * (3 - self.dim)
+        self.L.orc_mac_gradient(self.h, depth, *[(_ptr(x) if x is not None else None) for x in g], _ptr(phi),
+                                int(homogeneous))
+        return g[:self.dim]
+
+    def mac_divergence(self, flux, depth=0):
+        f = [_f64(x) for x in flux] + [None] * (3 - self.dim)
+        out = np.zeros(self.shape(depth))
+        self.L.orc_mac_divergence(self.h, depth, _ptr(out), *[(_ptr(x) if x is not None else None) for x in f])
+        return out
+
+    def project(self, vel, dt, pressure0=None, zero_pressure=True, force_homogeneous=False):
+        v = [_f64(x).copy() for x in vel] + [None] * (3 - self.dim)
+        p = np.zeros(self.shape(0)) if pressure0 is None else _f64(pressure0).copy()
+        st = OrcStats()
+        self.L.orc_project.argtypes = [C.c_void_p] * 5 + [C.c_double, C.c_int, C.c_int, C.POINTER(OrcStats)]
+        self.L.orc_project(self.h, *[(_ptr(x) if x is not None else None) for x in v], _ptr(p), float(dt),
+                           int(zero_pressure), int(force_homogeneous), C.byref(st))
+        return v[:self.dim], p, _stats(st)
+
     def timed_solve(self, rhs, ncycles_cap=0):
         rhs = _f64(rhs)
         st = OrcStats()

@@ -468,6 +468,106 @@ void Op::create(LevelData& y, int ghosts) const { y.define(grids, 1, activeDirs 
 
 
 // ----------------------------------------------------------------------------------------------
+// Projector calculus: the MAC gradient and divergence around the pressure solve.
+// ----------------------------------------------------------------------------------------------
+
+// MAPPEDMACGRADORTHO, normal derivative -- DivCurlGradF.ChF:221-262.
+static void macgrad_ortho(FAB& grad, const FAB& phi, const FAB& Jga, const Box& edgeBox, double dxDir, int dir) {
+    const int gi = dir == 0, gj = dir == 1, gk = dir == 2;
+    const double dxinv = 1.0 / dxDir;
+    ORC_LOOP(edgeBox, i, j, k) grad(i, j, k) = dxinv * Jga(i, j, k, dir) * (phi(i, j, k) - phi(i - gi, j - gj, k - gk));
+}
+
+// MAPPEDMACGRAD, normal derivative (gradDir == edgeDir) -- DivCurlGradF.ChF:87-147.
+static void macgrad_full(FAB& grad, const FAB& phi, const FAB& ex, const FAB& Jga, const Box& edgeBox, const double* dx,
+                         int adir, int nd) {
+    const int bdir = (adir + 1) % nd, cdir = (adir + 2) % nd;
+    const int ai = adir == 0, aj = adir == 1, ak = adir == 2;
+    const int bi = bdir == 0, bj = bdir == 1, bk = bdir == 2;
+    const int ci = cdir == 0, cj = cdir == 1, ck = cdir == 2;
+    const double dxinva = 1.0 / dx[adir];
+    const double dxinvb = 0.25 / dx[bdir];
+    const double dxinvc = (nd > 2) ? 0.25 / dx[cdir] : 0.0;
+    ORC_LOOP(edgeBox, i, j, k) {
+        double f = Jga(i, j, k, adir) * dxinva * (phi(i, j, k) - phi(i - ai, j - aj, k - ak)) +
+                   Jga(i, j, k, bdir) * dxinvb *
+                       (ex(i + bi, j + bj, k + bk) - ex(i - bi, j - bj, k - bk) + ex(i + bi - ai, j + bj - aj, k + bk - ak) -
+                        ex(i - bi - ai, j - bj - aj, k - bk - ak));
+        if (nd > 2)
+            f += Jga(i, j, k, cdir) * dxinvc *
+                 (ex(i + ci, j + cj, k + ck) - ex(i - ci, j - cj, k - ck) + ex(i + ci - ai, j + cj - aj, k + ck - ak) -
+                  ex(i - ci - ai, j - cj - aj, k - ck - ak));
+        grad(i, j, k) = f;
+    }
+}
+
+// Gradient::levelGradientMAC, one component = normal gradients only -- Gradient.cpp:85-170, with
+// singleBoxMacGrad -- :946-1100 (the non-USE_OLD_EXTRAP branch): exchange with corners, order-2
+// extrapolation of the transverse-derivative copy past the DOMAIN (validPhi = FAB box & validDomain),
+// BC ghosts (a_fluxBC->setGhosts, non-homogeneous unless asked), MAPPEDMACGRAD[ORTHO], BC fluxes.
+// LevelMACProjector::computeGrad -- LevelMACProjector.cpp:186-218 calls it with the pressure BC.
+void Op::macGradient(FluxLevelData& grad, LevelData& phi, bool homog) const {
+    exchange(phi, true);                                               // Gradient.cpp:120-121
+    Box vdom = domain.box;                                             // :117,123-127
+    for (int d = 0; d < nd; ++d)
+        if (domain.periodic[d]) vdom.grow(d, 1);
+    for (size_t b = 0; b < grids.size(); ++b) {
+        FAB& phiFAB = phi[b];
+        const Box validPhi = phiFAB.box() & vdom;                      // :137-141
+        for (int dir = 0; dir < nd; ++dir) {
+            FAB& g = grad.fabs[b][dir];
+            const Box edgeBox = surroundingNodes(grids[b], dir);      // :148-149
+            FAB ex(phiFAB.box(), 1);
+            if (!isDiagonal) {                                         // :984-998
+                ex.copy(phiFAB);
+                Box valid = validPhi;
+                for (int fdir = 0; fdir < nd; ++fdir) {
+                    ExtrapolateFaceAndCopy(ex, ex, valid, fdir, Lo, 2, nd);
+                    ExtrapolateFaceAndCopy(ex, ex, valid, fdir, Hi, 2, nd);
+                    valid.grow(fdir, 1);
+                }
+            }
+            setGhosts(phiFAB, &ex, grids[b], b, homog);                // :1004-1020
+            if (isDiagonal) macgrad_ortho(g, phiFAB, Jgup.fabs[b][dir], edgeBox, dx[dir], dir);        // :1070-1078
+            else macgrad_full(g, phiFAB, ex, Jgup.fabs[b][dir], edgeBox, dx, dir, nd);                 // :1060-1067
+        }
+        setFluxes(grad.fabs[b], grids[b], homog);                      // :1082-1096 (each direction touches its own FAB)
+    }
+}
+
+// Divergence::levelDivergenceMAC with a_fluxBC == NULL (the caller's fluxes carry their boundary values)
+// -- Divergence.cpp:44-127 -> MAPPEDFLUXDIVERGENCE{2,3}D, DivCurlGradF.ChF:1034-1214.
+void Op::macDivergence(LevelData& div, const FluxLevelData& flux) const {
+    for (size_t b = 0; b < grids.size(); ++b) flux_divergence(div[b], flux.fabs[b].data(), Jinv[b], grids[b], dx, nd);
+}
+
+// BaseProjector::project with a_velIsFlux = true on one level -- BaseProjectorI.H:176-300:
+// rhs = Div[J u] / dt; solve L[p] = rhs; J u -= dt * (J g^{ij} d_j p)  (applyCorrection,
+// LevelMACProjector.cpp:221-240: dtScale = -dt, or -1 when dt == 0).
+void MG::project(FluxLevelData& vel, LevelData& pressure, double dt, bool zeroPressure, bool forceHomogeneous,
+                 SolveStats& st) {
+    Op& op = *ops[0];
+    LevelData rhs;
+    op.create(rhs, 0);
+    op.macDivergence(rhs, vel);
+    if (dt != 0.0)
+        for (size_t b = 0; b < op.grids.size(); ++b)
+            ORC_LOOP(op.grids[b], i, j, k) rhs[b](i, j, k) /= dt;      // FArrayBox::operator/=(Real)
+    solve(pressure, rhs, zeroPressure, forceHomogeneous, st);
+    FluxLevelData corr;
+    corr.define(op.grids, 1, op.nd);
+    op.macGradient(corr, pressure, false);
+    const double dtScale = (dt == 0.0) ? -1.0 : -dt;
+    for (size_t b = 0; b < op.grids.size(); ++b)
+        for (int d = 0; d < op.nd; ++d) {
+            FAB& v = vel.fabs[b][d];
+            const FAB& c = corr.fabs[b][d];
+            ORC_LOOP(v.box(), i, j, k) v(i, j, k) += c(i, j, k) * dtScale;   // FArrayBox::plus(src, scale)
+        }
+}
+
+
+// ----------------------------------------------------------------------------------------------
 // Factory: MappedAMRPoissonOpFactory::MGnewOp -- MappedAMRPoissonOpFactory.cpp:362-702 (single AMR
 // level, unforced ratios) and fill_MGfields -- :1069-1236.
 // ----------------------------------------------------------------------------------------------

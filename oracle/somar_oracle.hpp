@@ -140,6 +140,9 @@ struct Op {
     void assign(LevelData& y, const LevelData& x) const;
     void scale(LevelData& y, double s) const;
     void create(LevelData& y, int ghosts) const;
+    // projector calculus (Gradient::levelGradientMAC, Divergence::levelDivergenceMAC)
+    void macGradient(FluxLevelData& grad, LevelData& phi, bool homog) const;
+    void macDivergence(LevelData& div, const FluxLevelData& flux) const;
 };
 
 struct MG {
@@ -155,6 +158,8 @@ struct MG {
     void cycle(int depth, LevelData& e, const LevelData& r);
     int bottomSolve(LevelData& e, const LevelData& r);
     void solve(LevelData& phi, const LevelData& rhs, bool zeroPhi, bool forceHomogeneous, SolveStats& st);
+    void project(FluxLevelData& vel, LevelData& pressure, double dt, bool zeroPressure, bool forceHomogeneous,
+                 SolveStats& st);   // BaseProjector::project, a_velIsFlux = true
 };
 
 // Factory: builds all depths (MGnewOp schedule + coarse metrics).

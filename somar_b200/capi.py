@@ -25,11 +25,13 @@ SYMBOLS = [
     "somar_level_create", "somar_level_destroy", "somar_level_set_metric_fab", "somar_level_set_metric_device",
     "somar_level_finalize", "somar_level_set_alpha_beta", "somar_level_num_depths", "somar_level_depth_info",
     "somar_level_sync", "somar_level_stream", "somar_level_launch_count", "somar_level_get_metric",
-    "somar_level_profile_enable", "somar_level_profile_read", "somar_level_relax_kernel",
+    "somar_level_profile_enable", "somar_level_profile_read", "somar_level_relax_kernel", "somar_level_halo_path",
     "somar_field_create", "somar_field_destroy", "somar_field_set_fab", "somar_field_get_fab", "somar_field_set",
     "somar_field_get", "somar_apply_op", "somar_residual", "somar_precond", "somar_set_to_zero", "somar_assign",
     "somar_incr", "somar_axby", "somar_scale", "somar_norm", "somar_local_max_norm", "somar_dot", "somar_relax",
     "somar_restrict_residual", "somar_prolong_increment", "somar_mg_cycle", "somar_solve",
+    "somar_field_set_face", "somar_field_get_face", "somar_mac_gradient", "somar_mac_divergence",
+    "somar_mac_apply_correction", "somar_project",
 ]
 
 
@@ -133,6 +135,23 @@ class Field:
             out = np.empty(self.shape(), dtype=np.float64)
         p, dev = _ptr(out)
         _ck(lib().somar_field_get(self.h, p, dev))
+        if dev:
+            self.level.sync()
+        return out
+
+    def set_face(self, data, dir: int):
+        """dense rank-local face array of direction dir: shape = cell shape with +1 point in that direction"""
+        p, dev = _ptr(data)
+        _ck(lib().somar_field_set_face(self.h, p, int(dir), dev))
+        return self
+
+    def get_face(self, dir: int, out=None):
+        if out is None:
+            sh = list(self.shape())
+            sh[2 - dir] += 1
+            out = np.empty(sh, dtype=np.float64)
+        p, dev = _ptr(out)
+        _ck(lib().somar_field_get_face(self.h, p, int(dir), dev))
         if dev:
             self.level.sync()
         return out
@@ -281,6 +300,11 @@ class Level:
         _ck(lib().somar_level_relax_kernel(self.h, depth, mode, C.byref(v)))
         return self.RELAX_KERNELS[v.value]
 
+    def halo_path(self) -> str:
+        v = C.c_int()
+        _ck(lib().somar_level_halo_path(self.h, C.byref(v)))
+        return {0: "none", 1: "nccl", 2: "p2p"}[v.value]
+
     def launches(self) -> int:
         v = C.c_longlong()
         _ck(lib().somar_level_launch_count(self.h, C.byref(v)))
@@ -342,6 +366,36 @@ class Level:
     def solve(self, phi: Field, rhs: Field, zero_phi=True, force_homogeneous=True) -> dict:
         st = SolveStats()
         _ck(lib().somar_solve(self.h, phi.h, rhs.h, int(zero_phi), int(force_homogeneous), C.byref(st)))
+        return {"iters": st.iters, "exit_status": st.exitStatus, "initial_rnorm": st.initial_rnorm,
+                "final_rnorm": st.final_rnorm, "bottom_iters_total": st.bottom_iters_total,
+                "history": [st.history[i] for i in range(st.history_len)], "solve_ms": st.solve_ms,
+                "launches": st.launches}
+
+    # -- projector calculus -----------------------------------------------------------------
+    @staticmethod
+    def _h3(fs):
+        fs = list(fs) + [None] * (3 - len(fs))
+        return [f.h if f is not None else None for f in fs]
+
+    def mac_gradient(self, grad, phi: Field, homogeneous=False):
+        _ck(lib().somar_mac_gradient(self.h, *self._h3(grad), phi.h, int(homogeneous)))
+
+    def mac_divergence(self, div: Field, flux, divide_by=0.0):
+        L = lib()
+        L.somar_mac_divergence.argtypes = [C.c_void_p] * 5 + [C.c_double]
+        _ck(L.somar_mac_divergence(self.h, div.h, *self._h3(flux), float(divide_by)))
+
+    def mac_apply_correction(self, vel, phi: Field, dt: float):
+        L = lib()
+        L.somar_mac_apply_correction.argtypes = [C.c_void_p] * 5 + [C.c_double]
+        _ck(L.somar_mac_apply_correction(self.h, *self._h3(vel), phi.h, float(dt)))
+
+    def project(self, vel, pressure: Field, dt: float, zero_pressure=True, force_homogeneous=False) -> dict:
+        st = SolveStats()
+        L = lib()
+        L.somar_project.argtypes = [C.c_void_p] * 5 + [C.c_double, C.c_int, C.c_int, C.POINTER(SolveStats)]
+        _ck(L.somar_project(self.h, *self._h3(vel), pressure.h, float(dt), int(zero_pressure), int(force_homogeneous),
+                            C.byref(st)))
         return {"iters": st.iters, "exit_status": st.exitStatus, "initial_rnorm": st.initial_rnorm,
                 "final_rnorm": st.final_rnorm, "bottom_iters_total": st.bottom_iters_total,
                 "history": [st.history[i] for i in range(st.history_len)], "solve_ms": st.solve_ms,

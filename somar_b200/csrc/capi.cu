@@ -133,6 +133,7 @@ int somar_level_destroy(SomarLevel* L) {
     }
     for (auto* f : L->bwork) if (f) { cudaFree(f->p); delete f; }
     for (auto* f : L->swork) if (f) { cudaFree(f->p); delete f; }
+    if (L->pwork) { cudaFree(L->pwork->p); delete L->pwork; }
     halo_p2p_free(L);   // (collective: needs the communicator)
     if (L->comm) ncclCommDestroy(L->comm);
     cudaFree(L->cx.scratch); cudaFree(L->cx.tickets); cudaFree(L->d_scal); cudaFreeHost(L->h_scal);
@@ -270,6 +271,13 @@ int somar_level_relax_kernel(const SomarLevel* L, int depth, int mode, int* id) 
     return SOMAR_OK;
 }
 
+int somar_level_halo_path(const SomarLevel* L, int* path) {
+    CHECK_LEVEL(L);
+    if (!path) { set_error("null out pointer"); return SOMAR_ERR_ARG; }
+    *path = (L->desc.nranks <= 1) ? 0 : (L->halo.state == 1 ? 2 : 1);
+    return SOMAR_OK;
+}
+
 int somar_level_get_metric(SomarLevel* L, int depth, double* jg0, double* jg1, double* jg2, double* jinv,
                            double* lapdiag) {
     CHECK_LEVEL(L);
@@ -342,6 +350,32 @@ static int field_dense(SomarField* f, double* data, int on_device, bool toDevice
     if (rc) return rc;
     if (!toDevice) SOMAR_CUDA(cudaStreamSynchronize(L->cx.stream));
     return SOMAR_OK;
+}
+// Dense rank-local FACE array of direction dir (n[dir] + 1 points in that direction, x fastest).
+static int field_dense_face(SomarField* f, double* data, int dir, int on_device, bool toDevice) {
+    if (!f || !data || dir < 0 || dir > 2) { set_error("bad argument"); return SOMAR_ERR_ARG; }
+    SomarLevel* L = f->lev;
+    cudaSetDevice(L->device);
+    const Geom& g = L->depths[f->depth].g;
+    if (dir >= g.nd) { set_error("face direction is not active"); return SOMAR_ERR_ARG; }
+    if (on_device) {
+        int ext[3] = {0, 0, 0};
+        ext[dir] = 1;
+        launch_dense_copy(L->cx, g, f->p, data, ext, toDevice);
+        return SOMAR_OK;
+    }
+    int lo[3], hi[3];
+    for (int d = 0; d < 3; ++d) { lo[d] = g.g0[d]; hi[d] = g.g0[d] + g.n[d] - 1 + (d == dir); }
+    int rc = copy3d(L, g, f->p, data, lo, hi, lo, hi, toDevice);
+    if (rc) return rc;
+    if (!toDevice) SOMAR_CUDA(cudaStreamSynchronize(L->cx.stream));
+    return SOMAR_OK;
+}
+int somar_field_set_face(SomarField* f, const double* data, int dir, int on_device) {
+    return field_dense_face(f, const_cast<double*>(data), dir, on_device, true);
+}
+int somar_field_get_face(const SomarField* f, double* data, int dir, int on_device) {
+    return field_dense_face(const_cast<SomarField*>(f), data, dir, on_device, false);
 }
 int somar_field_set(SomarField* f, const double* data, int on_device) {
     return field_dense(f, const_cast<double*>(data), on_device, true);

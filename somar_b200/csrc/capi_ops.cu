@@ -119,4 +119,50 @@ int somar_solve(SomarLevel* L, SomarField* phi, const SomarField* rhs, int zero_
     return mg_solve(L, phi, rhs, zero_phi != 0, force_homogeneous != 0, stats);
 }
 
+// ---- projector calculus ------------------------------------------------------------------
+static int check_faces(SomarLevel* L, SomarField* const f[3]) {
+    const int nd = L->desc.dim;
+    for (int d = 0; d < nd; ++d)
+        if (!f[d] || f[d]->lev != L || f[d]->depth != 0) { set_error("face field does not belong to depth 0 of this level"); return SOMAR_ERR_ARG; }
+    for (int a = 0; a < nd; ++a)
+        for (int b = a + 1; b < nd; ++b)
+            if (f[a] == f[b]) { set_error("face fields must be distinct"); return SOMAR_ERR_ARG; }
+    return SOMAR_OK;
+}
+int somar_mac_gradient(SomarLevel* L, SomarField* gx, SomarField* gy, SomarField* gz, SomarField* phi, int homogeneous) {
+    CHECK_FINAL(L); CHECK_F(phi, L, 0);
+    SomarField* g[3] = {gx, gy, gz};
+    int rc = check_faces(L, g);
+    if (rc) return rc;
+    for (int d = 0; d < L->desc.dim; ++d) if (g[d] == phi) { set_error("macGradient: output aliases phi"); return SOMAR_ERR_ARG; }
+    return op_mac_gradient(L, g, phi, homogeneous != 0, 1.0, false);
+}
+int somar_mac_divergence(SomarLevel* L, SomarField* div, const SomarField* fx, const SomarField* fy, const SomarField* fz,
+                         double divide_by) {
+    CHECK_FINAL(L); CHECK_F(div, L, 0);
+    SomarField* f[3] = {const_cast<SomarField*>(fx), const_cast<SomarField*>(fy), const_cast<SomarField*>(fz)};
+    int rc = check_faces(L, f);
+    if (rc) return rc;
+    for (int d = 0; d < L->desc.dim; ++d) if (f[d] == div) { set_error("macDivergence: output aliases a flux"); return SOMAR_ERR_ARG; }
+    return op_mac_divergence(L, div, f, divide_by);
+}
+int somar_mac_apply_correction(SomarLevel* L, SomarField* vx, SomarField* vy, SomarField* vz, SomarField* phi, double dt) {
+    CHECK_FINAL(L); CHECK_F(phi, L, 0);
+    SomarField* v[3] = {vx, vy, vz};
+    int rc = check_faces(L, v);
+    if (rc) return rc;
+    const double dtScale = (dt == 0.0) ? -1.0 : -dt;
+    return op_mac_gradient(L, v, phi, false, dtScale, true);
+}
+int somar_project(SomarLevel* L, SomarField* vx, SomarField* vy, SomarField* vz, SomarField* pressure, double dt,
+                  int zero_pressure, int force_homogeneous, SomarSolveStats* stats) {
+    CHECK_FINAL(L); CHECK_F(pressure, L, 0);
+    if (!stats) { set_error("null stats"); return SOMAR_ERR_ARG; }
+    SomarField* v[3] = {vx, vy, vz};
+    int rc = check_faces(L, v);
+    if (rc) return rc;
+    for (int d = 0; d < L->desc.dim; ++d) if (v[d] == pressure) { set_error("project: pressure aliases a velocity component"); return SOMAR_ERR_ARG; }
+    return project(L, v, pressure, dt, zero_pressure != 0, force_homogeneous != 0, stats);
+}
+
 }  // extern "C"

@@ -55,6 +55,13 @@ void launch_prolong(Ctx& cx, const Geom& gf, const Metric& mf, const Geom& gc, d
 void launch_prolong_finish(Ctx& cx, const Geom& gf, const Geom& gc, double* fine, const double* crse, const int r[3],
                            const double* sums);
 
+// ---- projector calculus (projector.cu) ----
+// out[d](face) = J g^{dj} d_j phi with the operator's BCs; accumulate: out[d] += scale * that
+void launch_mac_grad(Ctx& cx, const Geom& g, const Metric& m, double* const out[3], const double* phi, bool homog,
+                     double scale, bool accumulate);
+// div = Jinv * sum_d (F_d(+) - F_d(-)) / dx_d, divided by divideBy when that is non-zero
+void launch_mac_div(Ctx& cx, const Geom& g, const Metric& m, double* div, const double* const flux[3], double divideBy);
+
 // ---- set-up ----
 void launch_lapdiag(Ctx& cx, const Geom& g, const Metric& m, double* lapdiag);           // FILLMAPPEDLAPDIAG*
 void launch_avg_face(Ctx& cx, const Geom& gf, const Geom& gc, double* crse, const double* fine, int dir,

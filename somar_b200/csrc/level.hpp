@@ -95,6 +95,7 @@ struct SomarLevel {
     std::vector<SomarField*> bwork;
     // outer-solve work fields (depth 0)
     std::vector<SomarField*> swork;
+    SomarField* pwork = nullptr;       // projector: the divergence / right-hand side (depth 0)
     double bottomMetric = 0.0, bottomEps = 1e-6;
     int bottom_iters_total = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -172,6 +173,11 @@ int bottom_collect_iters(SomarLevel* L);
 bool bottom_persistent_params_ok(SomarLevel* L, const Geom& g);
 int launch_bottom_persistent(SomarLevel* L, const Geom& g, const Metric& m, double* phi, double* rhs,
                              double* const work[8]);
+// projector.cu
+int op_mac_gradient(SomarLevel* L, SomarField* const grad[3], SomarField* phi, bool homog, double scale, bool accumulate);
+int op_mac_divergence(SomarLevel* L, SomarField* div, const SomarField* const flux[3], double divideBy);
+int project(SomarLevel* L, SomarField* const vel[3], SomarField* pressure, double dt, bool zeroPressure, bool forceHomog,
+            SomarSolveStats* st);
 // halo_p2p.cu
 int halo_p2p_exchange(SomarLevel* L, int depth, double* x, int width);   // 1 done, 0 use NCCL, < 0 error
 void halo_p2p_free(SomarLevel* L);
