@@ -196,6 +196,26 @@ int somar_mac_divergence(SomarLevel* lev, SomarField* div, const SomarField* fx,
                          const SomarField* fz, double divide_by);
 int somar_mac_apply_correction(SomarLevel* lev, SomarField* vx, SomarField* vy, SomarField* vz, SomarField* phi, double dt);
 
+/* ---- leptic-solver sweeps (SURVEY 8(a) LevelLepticSolver row; the leptic iteration itself is host logic not built yet) --
+ * "Flat" arguments are depth-0 fields whose vertical index 0 holds a horizontal array (the reference's VertShifter,
+ * LevelLepticSolver.cpp:1213-1226).  BC codes are the reference's BCType values: 0 Neum, 1 Diri, 3 CF.
+ * somar_leptic_vertical_solve:  per column, d_z (J g^zz d_z phi) = rhs with homogeneous vertical BCs; Neumann boundary
+ *      VALUES (bdry_lo / bdry_hi, flat, may be NULL) are rolled into rhs as rhs -/+ bc/dz and unrolled afterwards.
+ *      LevelLepticSolver::verticalLineSolver, LevelLepticSolver.cpp:1247-1425 -> TRIDIAGPOISSONNN1DFAB
+ *      (src/utils/TridiagUtilsF.ChF:85-164) for Neum-Neum, else LEPTICLAPACKVERTICALSOLVER -> LAPACK dptsv
+ *      (LevelLepticSolverF.ChF:161-289).  A column whose factorisation breaks down before the last pivot is an error.
+ * somar_leptic_vert_integral:   flat += sum_k func * dz_scale               UNMAPPEDVERTINTEGRAL, SubspaceF.ChF:33-58
+ * somar_leptic_vertical_excess: excess = bdry_hi - bdry_lo - Integral[rhs]  computeVerticalExcess, LevelLepticSolver.cpp:1183-1240
+ * somar_leptic_add_extrusion:   dest(i,j,k) += flat(i,j)                    ADDEXTRUSION, SubspaceF.ChF:66-110
+ * somar_leptic_accum_div:       flat_rhs += (flux(i+e) - flux(i)) * dx_scale LEPTICACCUMDIV, LevelLepticSolverF.ChF:291-331 */
+int somar_leptic_vertical_solve(SomarLevel* lev, SomarField* phi, SomarField* rhs, int lo_bc, int hi_bc, double dz_crse,
+                                const SomarField* bdry_lo, const SomarField* bdry_hi);
+int somar_leptic_vert_integral(SomarLevel* lev, SomarField* flat_sum, const SomarField* func, double dz_scale);
+int somar_leptic_vertical_excess(SomarLevel* lev, SomarField* excess, const SomarField* rhs, const SomarField* bdry_lo,
+                                 const SomarField* bdry_hi);
+int somar_leptic_add_extrusion(SomarLevel* lev, SomarField* dest, const SomarField* flat_src);
+int somar_leptic_accum_div(SomarLevel* lev, SomarField* flat_rhs, const SomarField* flat_flux, int fc_dir, double dx_scale);
+
 /* ---- drivers --------------------------------------------------------------------------------------------
  * somar_mg_cycle: MappedMultiGrid<T>::cycle (MappedMultiGrid.H:555-653) from `depth` down.
  * somar_solve: AMRPressureSolver::solve -> MappedAMRMultiGrid<T>::solveNoInitResid, single level

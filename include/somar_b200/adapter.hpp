@@ -277,4 +277,38 @@ private:
     Field phi_, rhs_;
 };
 
+// LevelMACProjector / BaseProjector<FluxBox> on one level (src/projection/LevelMACProjector.cpp:156-240,
+// BaseProjectorI.H:176-300) over device-resident fields.  The velocity is the flux J u^i on faces: one Field per
+// direction (face (i,j,k) = low face of cell (i,j,k); upload a FluxBox FAB with its own surroundingNodes box
+// through somar_field_set_fab).  multByJ / divByJ stay with the caller's LevelGeometry (a_velIsFlux = true).
+class MACProjector {
+public:
+    explicit MACProjector(PressureSolver& solver) : solver_(solver) {}
+    // computeDiv: div = Jinv d_i (J u^i)
+    void computeDiv(Field& div, const Field& ux, const Field& uy, const Field* uz = nullptr) {
+        check(somar_mac_divergence(L(), div.handle(), ux.handle(), uy.handle(), uz ? uz->handle() : nullptr, 0.0), "computeDiv");
+    }
+    // computeGrad: flux_d = J g^{dj} d_j phi with the pressure BCs
+    void computeGrad(Field& gx, Field& gy, Field* gz, Field& phi) {
+        check(somar_mac_gradient(L(), gx.handle(), gy.handle(), gz ? gz->handle() : nullptr, phi.handle(), 0), "computeGrad");
+    }
+    // applyCorrection: vel -= dt * Grad[phi] (dt == 0: vel -= Grad[phi]); the gradient is formed on the fly
+    void applyCorrection(Field& ux, Field& uy, Field* uz, Field& phi, double dt) {
+        check(somar_mac_apply_correction(L(), ux.handle(), uy.handle(), uz ? uz->handle() : nullptr, phi.handle(), dt), "applyCorrection");
+    }
+    // project: rhs = Div[vel]/dt; solve; vel -= dt Grad[pressure].  Non-convergence is reported in the stats.
+    SomarSolveStats project(Field& ux, Field& uy, Field* uz, Field& pressure, double dt, bool zeroPressure = true,
+                            bool forceHomogeneous = false) {
+        SomarSolveStats st{};
+        const int rc = somar_project(L(), ux.handle(), uy.handle(), uz ? uz->handle() : nullptr, pressure.handle(), dt,
+                                     zeroPressure, forceHomogeneous, &st);
+        if (rc != SOMAR_OK && rc != SOMAR_ERR_DIVERGED) check(rc, "MACProjector::project");
+        return st;
+    }
+
+private:
+    SomarLevel* L() const { return solver_.level().handle(); }
+    PressureSolver& solver_;
+};
+
 }  // namespace somar_b200

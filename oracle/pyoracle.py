@@ -276,3 +276,66 @@ def set_threads(n: int):
 
 def max_threads() -> int:
     return int(lib().orc_max_threads())
+
+
+# ---- leptic-solver sweeps (oracle/leptic.cpp): plain global arrays, no Oracle object needed --------------------
+BCT_NEUM, BCT_DIRI, BCT_CF = 0, 1, 3
+
+
+def leptic_vertical_solve(rhs, jgzz, dz, lo_bc, hi_bc, dz_crse=None, bdry_lo=None, bdry_hi=None):
+    """returns (phi, rhs_after, info); rhs (nv, ..., nx), jgzz (nv+1, ..., nx), bdry_* flat (..., nx) or None"""
+    L = lib()
+    rhs = _f64(rhs).copy()
+    jgzz = _f64(jgzz)
+    nv = rhs.shape[0]
+    nh = rhs.size // nv
+    phi = np.zeros_like(rhs)
+    bl = _f64(bdry_lo) if bdry_lo is not None else None
+    bh = _f64(bdry_hi) if bdry_hi is not None else None
+    L.orc_leptic_vertical_solve.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_long, C.c_int, C.c_double, C.c_double,
+                                            C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+    info = L.orc_leptic_vertical_solve(_ptr(phi), _ptr(rhs), _ptr(jgzz), nh, nv, float(dz),
+                                       float(dz if dz_crse is None else dz_crse), int(lo_bc), int(hi_bc),
+                                       _ptr(bl) if bl is not None else None, _ptr(bh) if bh is not None else None)
+    return phi, rhs, int(info)
+
+
+def leptic_vert_integral(flat, func, dz):
+    L = lib()
+    flat = _f64(flat).copy()
+    func = _f64(func)
+    nv = func.shape[0]
+    L.orc_leptic_vert_integral.argtypes = [C.c_void_p, C.c_void_p, C.c_long, C.c_int, C.c_double]
+    L.orc_leptic_vert_integral(_ptr(flat), _ptr(func), func.size // nv, nv, float(dz))
+    return flat
+
+
+def leptic_add_extrusion(dest, flat):
+    L = lib()
+    dest = _f64(dest).copy()
+    flat = _f64(flat)
+    nv = dest.shape[0]
+    L.orc_leptic_add_extrusion.argtypes = [C.c_void_p, C.c_void_p, C.c_long, C.c_int]
+    L.orc_leptic_add_extrusion(_ptr(dest), _ptr(flat), dest.size // nv, nv)
+    return dest
+
+
+def leptic_accum_div(rhs, flux, dir, dx_scale):
+    """flat (ny, nx) rhs; flux has +1 point in direction dir"""
+    L = lib()
+    rhs = _f64(rhs).copy()
+    flux = _f64(flux)
+    ny, nx = (rhs.shape if rhs.ndim == 2 else (1, rhs.shape[0]))
+    L.orc_leptic_accum_div.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_double]
+    L.orc_leptic_accum_div(_ptr(rhs), _ptr(flux), nx, ny, int(dir), float(dx_scale))
+    return rhs
+
+
+def leptic_vertical_excess(rhs, bdry_lo, bdry_hi, dz):
+    L = lib()
+    rhs = _f64(rhs)
+    nv = rhs.shape[0]
+    out = np.zeros(rhs.shape[1:])
+    L.orc_leptic_vertical_excess.argtypes = [C.c_void_p] * 4 + [C.c_long, C.c_int, C.c_double]
+    L.orc_leptic_vertical_excess(_ptr(out), _ptr(rhs), _ptr(_f64(bdry_lo)), _ptr(_f64(bdry_hi)), rhs.size // nv, nv, float(dz))
+    return out

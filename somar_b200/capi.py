@@ -31,7 +31,8 @@ SYMBOLS = [
     "somar_incr", "somar_axby", "somar_scale", "somar_norm", "somar_local_max_norm", "somar_dot", "somar_relax",
     "somar_restrict_residual", "somar_prolong_increment", "somar_mg_cycle", "somar_solve",
     "somar_field_set_face", "somar_field_get_face", "somar_mac_gradient", "somar_mac_divergence",
-    "somar_mac_apply_correction", "somar_project",
+    "somar_mac_apply_correction", "somar_project", "somar_leptic_vertical_solve", "somar_leptic_vert_integral",
+    "somar_leptic_vertical_excess", "somar_leptic_add_extrusion", "somar_leptic_accum_div",
 ]
 
 
@@ -400,6 +401,33 @@ class Level:
                 "final_rnorm": st.final_rnorm, "bottom_iters_total": st.bottom_iters_total,
                 "history": [st.history[i] for i in range(st.history_len)], "solve_ms": st.solve_ms,
                 "launches": st.launches}
+
+    # -- leptic-solver sweeps ---------------------------------------------------------------------------------
+    def leptic_vertical_solve(self, phi: Field, rhs: Field, lo_bc: int, hi_bc: int, dz_crse=None, bdry_lo=None,
+                              bdry_hi=None):
+        L = lib()
+        L.somar_leptic_vertical_solve.argtypes = [C.c_void_p] * 3 + [C.c_int, C.c_int, C.c_double, C.c_void_p, C.c_void_p]
+        vd = self.dim - 1
+        dzc = self.depth_info(0)["dx"][vd] if dz_crse is None else dz_crse
+        _ck(L.somar_leptic_vertical_solve(self.h, phi.h, rhs.h, int(lo_bc), int(hi_bc), float(dzc),
+                                          bdry_lo.h if bdry_lo is not None else None,
+                                          bdry_hi.h if bdry_hi is not None else None))
+
+    def leptic_vert_integral(self, flat: Field, func: Field, dz_scale: float):
+        L = lib()
+        L.somar_leptic_vert_integral.argtypes = [C.c_void_p] * 3 + [C.c_double]
+        _ck(L.somar_leptic_vert_integral(self.h, flat.h, func.h, float(dz_scale)))
+
+    def leptic_vertical_excess(self, excess: Field, rhs: Field, bdry_lo: Field, bdry_hi: Field):
+        _ck(lib().somar_leptic_vertical_excess(self.h, excess.h, rhs.h, bdry_lo.h, bdry_hi.h))
+
+    def leptic_add_extrusion(self, dest: Field, flat: Field):
+        _ck(lib().somar_leptic_add_extrusion(self.h, dest.h, flat.h))
+
+    def leptic_accum_div(self, flat_rhs: Field, flat_flux: Field, fc_dir: int, dx_scale: float):
+        L = lib()
+        L.somar_leptic_accum_div.argtypes = [C.c_void_p] * 3 + [C.c_int, C.c_double]
+        _ck(L.somar_leptic_accum_div(self.h, flat_rhs.h, flat_flux.h, int(fc_dir), float(dx_scale)))
 
     def destroy(self):
         if getattr(self, "h", None):

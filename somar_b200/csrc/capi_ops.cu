@@ -165,4 +165,36 @@ int somar_project(SomarLevel* L, SomarField* vx, SomarField* vy, SomarField* vz,
     return project(L, v, pressure, dt, zero_pressure != 0, force_homogeneous != 0, stats);
 }
 
+// ---- leptic-solver sweeps (SURVEY 8(a) LevelLepticSolver row) ---------------------------------------------
+#define CHECK_F0(f, L) do { if (!(f) || (f)->lev != (L) || (f)->depth != 0) { set_error("field does not belong to depth 0 of this level"); return SOMAR_ERR_ARG; } } while (0)
+int somar_leptic_vertical_solve(SomarLevel* L, SomarField* phi, SomarField* rhs, int lo_bc, int hi_bc, double dz_crse,
+                                const SomarField* bdry_lo, const SomarField* bdry_hi) {
+    CHECK_FINAL(L); CHECK_F0(phi, L); CHECK_F0(rhs, L);
+    if (phi == rhs) { set_error("leptic vertical solve: phi aliases rhs"); return SOMAR_ERR_ARG; }
+    if (bdry_lo) CHECK_F0(bdry_lo, L);
+    if (bdry_hi) CHECK_F0(bdry_hi, L);
+    return leptic_vertical_solve(L, phi, rhs, lo_bc, hi_bc, dz_crse, bdry_lo, bdry_hi);
+}
+int somar_leptic_vert_integral(SomarLevel* L, SomarField* flat_sum, const SomarField* func, double dz_scale) {
+    CHECK_FINAL(L); CHECK_F0(flat_sum, L); CHECK_F0(func, L);
+    if (flat_sum == func) { set_error("vertical integral: output aliases input"); return SOMAR_ERR_ARG; }
+    return leptic_vert_integral(L, flat_sum, func, dz_scale);
+}
+int somar_leptic_vertical_excess(SomarLevel* L, SomarField* excess, const SomarField* rhs, const SomarField* bdry_lo,
+                                 const SomarField* bdry_hi) {
+    CHECK_FINAL(L); CHECK_F0(excess, L); CHECK_F0(rhs, L); CHECK_F0(bdry_lo, L); CHECK_F0(bdry_hi, L);
+    if (excess == rhs) { set_error("vertical excess: output aliases rhs"); return SOMAR_ERR_ARG; }
+    return leptic_vertical_excess(L, excess, rhs, bdry_lo, bdry_hi);
+}
+int somar_leptic_add_extrusion(SomarLevel* L, SomarField* dest, const SomarField* flat_src) {
+    CHECK_FINAL(L); CHECK_F0(dest, L); CHECK_F0(flat_src, L);
+    if (dest == flat_src) { set_error("add extrusion: dest aliases src"); return SOMAR_ERR_ARG; }
+    return leptic_add_extrusion(L, dest, flat_src);
+}
+int somar_leptic_accum_div(SomarLevel* L, SomarField* flat_rhs, const SomarField* flat_flux, int fc_dir, double dx_scale) {
+    CHECK_FINAL(L); CHECK_F0(flat_rhs, L); CHECK_F0(flat_flux, L);
+    if (flat_rhs == flat_flux) { set_error("accum div: rhs aliases flux"); return SOMAR_ERR_ARG; }
+    return leptic_accum_div(L, flat_rhs, flat_flux, fc_dir, dx_scale);
+}
+
 }  // extern "C"

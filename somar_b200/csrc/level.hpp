@@ -178,6 +178,14 @@ int op_mac_gradient(SomarLevel* L, SomarField* const grad[3], SomarField* phi, b
 int op_mac_divergence(SomarLevel* L, SomarField* div, const SomarField* const flux[3], double divideBy);
 int project(SomarLevel* L, SomarField* const vel[3], SomarField* pressure, double dt, bool zeroPressure, bool forceHomog,
             SomarSolveStats* st);
+// leptic.cu
+int leptic_vertical_solve(SomarLevel* L, SomarField* phi, SomarField* rhs, int loBC, int hiBC, double dzCrse,
+                          const SomarField* bdryLo, const SomarField* bdryHi);
+int leptic_vert_integral(SomarLevel* L, SomarField* flat, const SomarField* func, double dzScale);
+int leptic_vertical_excess(SomarLevel* L, SomarField* excess, const SomarField* rhs, const SomarField* bdryLo,
+                           const SomarField* bdryHi);
+int leptic_add_extrusion(SomarLevel* L, SomarField* dest, const SomarField* flat);
+int leptic_accum_div(SomarLevel* L, SomarField* flatRhs, const SomarField* flatFlux, int dir, double dxScale);
 // halo_p2p.cu
 int halo_p2p_exchange(SomarLevel* L, int depth, double* x, int width);   // 1 done, 0 use NCCL, < 0 error
 void halo_p2p_free(SomarLevel* L);
