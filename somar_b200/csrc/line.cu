@@ -13,6 +13,15 @@
 
 namespace somar {
 
+#ifndef LINE_UNROLL
+#define LINE_UNROLL 1
+#endif
+#ifndef LINE_MINB
+#define LINE_MINB 8
+#endif
+#define LINE_PRAGMA_(x) _Pragma(#x)
+#define LINE_PRAGMA(n) LINE_PRAGMA_(unroll n)
+
 __device__ __forceinline__ double vert_coeff(int bct) { return (bct == BC_DIRI) ? 2.0 : 0.0; }
 
 // diagonal entry of the column matrix at cell (i,j,k) (without alpha/Jinv) -- GSRBF.ChF:1596-1660 / 1800-1880
@@ -76,33 +85,41 @@ void launch_line_factor(Ctx& cx, const Geom& g, const Metric& m, double* fact, d
     cx.launches++;
 }
 
-template <int ND, bool FULL>
-__global__ void k_line_gsrb(const Geom g, const Metric m, double* __restrict__ phiOut,
-                            const double* __restrict__ phiIn, const double* __restrict__ rhs,
-                            const double* __restrict__ fact, const double* __restrict__ dmod, int pass) {
+// RIMFREE: the block's columns touch no x/y side of the domain, so the boundary tests of the horizontal terms
+// vanish at compile time and the k loops become straight-line code the compiler can unroll and batch loads for.
+template <int ND, bool FULL, bool RIMFREE>
+__device__ __forceinline__ void line_column(const Geom& g, const Metric& m, double* __restrict__ phiOut,
+                                            const double* __restrict__ phiIn, const double* __restrict__ rhs,
+                                            const double* __restrict__ fact, const double* __restrict__ dmod,
+                                            int pass) {
     constexpr int VD = ND - 1;
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    // thread t of a row owns the column i = 2t + (parity of this pass in row j): every lane of a warp is active
+    // (a thread-per-cell mapping idles the lanes of the other colour: 16 of 32, measured)
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
     const int j = (ND == 3) ? blockIdx.y * blockDim.y + threadIdx.y : 0;
-    if (i >= g.n[0] || (ND == 3 && j >= g.n[1])) return;
+    if (ND == 3 && j >= g.n[1]) return;
     const long long stv = (VD == 1) ? g.sy : g.sz;
     const int N = g.n[VD];
-    const int par = (g.g0[0] + i + ((ND == 3) ? (g.g0[1] + j) : 0) + pass) & 1;
-    if (par) {   // other colour: carried over unchanged
-        if (phiOut != phiIn)
+    const int par = (g.g0[0] + ((ND == 3) ? (g.g0[1] + j) : 0) + pass) & 1;
+    const int i = 2 * t + par;
+    if (phiOut != phiIn) {   // other colour: carried over unchanged (full metric, out of place)
+        const int io = 2 * t + (par ^ 1);
+        if (io < g.n[0])
             for (int r = 0; r < N; ++r) {
-                const long long c = (ND == 3) ? g.idx(i, j, r) : g.idx(i, r, 0);
+                const long long c = (ND == 3) ? g.idx(io, j, r) : g.idx(io, r, 0);
                 phiOut[c] = phiIn[c];
             }
-        return;
     }
+    if (i >= g.n[0]) return;
     const double vv = g.beta * 1.0 / (g.dx[VD] * g.dx[VD]);
     const long long st[2] = {1, g.sy};
     double bprev = 0.0;
+    LINE_PRAGMA(LINE_UNROLL)
     for (int r = 0; r < N; ++r) {
         const int jj = (ND == 3) ? j : r, kk = (ND == 3) ? r : 0;
         const long long c = g.idx(i, jj, kk);
-        const unsigned sm = side_mask(g, i, jj, kk);
-        const double pc = phiIn[c];
+        const unsigned sm = RIMFREE ? 0u : side_mask(g, i, jj, kk);
+        const double pc = RIMFREE ? 0.0 : phiIn[c];   // only Dirichlet ghosts of x/y sides read it
         double JD[2] = {0.0, 0.0};
 #pragma unroll
         for (int h = 0; h < VD; ++h) {
@@ -143,6 +160,7 @@ __global__ void k_line_gsrb(const Geom g, const Metric m, double* __restrict__ p
     long long c = (ND == 3) ? g.idx(i, j, N - 1) : g.idx(i, N - 1, 0);
     double x = phiOut[c] / dmod[c];
     phiOut[c] = x;
+    LINE_PRAGMA(LINE_UNROLL)
     for (int r = N - 2; r >= 0; --r) {
         c -= stv;
         const double du = m.jg[VD][VD][c + stv] * vv;
@@ -151,14 +169,31 @@ __global__ void k_line_gsrb(const Geom g, const Metric m, double* __restrict__ p
     }
 }
 
+template <int ND, bool FULL>
+__global__ void __launch_bounds__(128, LINE_MINB) k_line_gsrb(const Geom g, const Metric m, double* __restrict__ phiOut,
+                                                   const double* __restrict__ phiIn, const double* __restrict__ rhs,
+                                                   const double* __restrict__ fact, const double* __restrict__ dmod,
+                                                   int pass) {
+    // block-uniform: do this block's cells (both colours of its x range, its rows) stay off the x/y domain sides?
+    const int iLo = 2 * (int)(blockIdx.x * blockDim.x), iHi = iLo + 2 * (int)blockDim.x - 1;
+    bool rimfree = !FULL && (iLo > 0 || g.bc[0][0] == BC_NONE) && (iHi < g.n[0] - 1 || g.bc[0][1] == BC_NONE);
+    if (ND == 3) {
+        const int jLo = blockIdx.y * blockDim.y, jHi = jLo + blockDim.y - 1;
+        rimfree = rimfree && (jLo > 0 || g.bc[1][0] == BC_NONE) && (jHi < g.n[1] - 1 || g.bc[1][1] == BC_NONE);
+    }
+    if (rimfree) line_column<ND, FULL, true>(g, m, phiOut, phiIn, rhs, fact, dmod, pass);
+    else line_column<ND, FULL, false>(g, m, phiOut, phiIn, rhs, fact, dmod, pass);
+}
+
 void launch_line_gsrb(Ctx& cx, const Geom& g, const Metric& m, double* phiOut, const double* phiIn,
                       const double* rhs, const double* fact, const double* dmod, int pass) {
+    const int half = (g.n[0] + 1) / 2;
     if (g.nd == 3) {
-        dim3 block(64, 2), grid((g.n[0] + 63) / 64, (g.n[1] + 1) / 2);
+        dim3 block(32, 4), grid((half + 31) / 32, (g.n[1] + 3) / 4);
         if (m.diagonal) k_line_gsrb<3, false><<<grid, block, 0, cx.stream>>>(g, m, phiOut, phiIn, rhs, fact, dmod, pass);
         else k_line_gsrb<3, true><<<grid, block, 0, cx.stream>>>(g, m, phiOut, phiIn, rhs, fact, dmod, pass);
     } else {
-        const int nb = (g.n[0] + 63) / 64;
+        const int nb = (half + 63) / 64;
         if (m.diagonal) k_line_gsrb<2, false><<<nb, 64, 0, cx.stream>>>(g, m, phiOut, phiIn, rhs, fact, dmod, pass);
         else k_line_gsrb<2, true><<<nb, 64, 0, cx.stream>>>(g, m, phiOut, phiIn, rhs, fact, dmod, pass);
     }
