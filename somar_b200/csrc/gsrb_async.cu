@@ -31,7 +31,7 @@
 //   phi planes      ring of 5   read at step k: k-1, k, k+1     in flight: k+2, k+3
 //   coefficients    ring of 3   read at step k: k               in flight: k+1, k+2
 //   J g^zz planes   ring of 4   read at step k: k+1             in flight: k+2, k+3   (plane k = low z-face of cells k)
-// Shared memory: 5 x 9 KB + 3 x 40.5 KB + 4 x 8 KB = 198.5 KB, one CTA of 512 threads per SM, <= 128 registers.
+// Shared memory: 5 x 9 KB + 3 x 32.5 KB + 4 x 8 KB = 174.5 KB, one CTA of 512 threads per SM, <= 128 registers.
 //
 // Step k of a warp (k = k0-1 .. k1):
 //   wait redDone(k-1)        => all red values of plane k-1 are in the ring, and copy group k-2 has landed:
@@ -63,8 +63,8 @@ constexpr int NWARPS = NTHREADS / 32;
 constexpr int ROWB = PX * 8;             // 512 bytes per row
 
 constexpr int PHI_BYTES = PY * ROWB;     // 9216
-constexpr int R_JG0 = 0, R_JG1 = R_JG0 + EY, R_JI = R_JG1 + EY + 1, R_LAP = R_JI + EY, R_RHS = R_LAP + EY;
-constexpr int CF_ROWS = R_RHS + EY;      // 81
+constexpr int R_JG0 = 0, R_JG1 = R_JG0 + EY, R_JI = R_JG1 + EY + 1, R_RHS = R_JI + EY;   // lapDiag is not streamed:
+constexpr int CF_ROWS = R_RHS + EY;      // 65            gsrb_update_vals<3, true> forms it from the faces
 constexpr int CF_BYTES = CF_ROWS * ROWB;
 constexpr int ZF_BYTES = EY * ROWB;
 constexpr int OFF_PHI = 0;
@@ -154,7 +154,6 @@ __device__ __forceinline__ void sweep_step(const Geom& g, const Metric& m, const
     const double2 Y0 = *reinterpret_cast<const double2*>(C + R_JG1 * PX + L.cown);
     const double2 Y1 = *reinterpret_cast<const double2*>(C + (R_JG1 + 1) * PX + L.cown);
     const double2 JI = *reinterpret_cast<const double2*>(C + R_JI * PX + L.cown);
-    const double2 LP = *reinterpret_cast<const double2*>(C + R_LAP * PX + L.cown);
     const double2 RH = *reinterpret_cast<const double2*>(C + R_RHS * PX + L.cown);
     const double2 Zn = *reinterpret_cast<const double2*>(Zp + L.cown);
     const double J0n = __shfl_down_sync(FULL, J0.x, 1);       // x-face 2t+2 (lane 31: unused)
@@ -174,7 +173,7 @@ __device__ __forceinline__ void sweep_step(const Geom& g, const Metric& m, const
         q.glo[2] = PAR ? s.Zc.y : s.Zc.x;
         q.ghi[2] = PAR ? Zn.y : Zn.x;
         q.ji = PAR ? JI.y : JI.x;
-        q.lap = PAR ? LP.y : LP.x;
+        q.lap = 0.0;
         q.rhs = PAR ? RH.y : RH.x;
         double nb[3][2];
         nb[0][0] = PAR ? s.A0.x : xnK;
@@ -183,7 +182,7 @@ __device__ __forceinline__ void sweep_step(const Geom& g, const Metric& m, const
         nb[1][1] = Pk[L.ctr + col + PX];
         nb[2][0] = PAR ? s.Am1.y : s.Am1.x;
         nb[2][1] = PAR ? Ap1.y : Ap1.x;
-        const double v = gsrb_update_vals<3>(g, q, x, L.y, k, PAR ? s.A0.y : s.A0.x, nb, fast);
+        const double v = gsrb_update_vals<3, true>(g, q, x, L.y, k, PAR ? s.A0.y : s.A0.x, nb, fast);
         Pk[L.ctr + col] = v;          // for the rows above and below
         if (PAR) s.A0.y = v; else s.A0.x = v;
     }
@@ -198,7 +197,6 @@ __device__ __forceinline__ void sweep_step(const Geom& g, const Metric& m, const
             copy16(d + R_JG0 * ROWB, m.jg[0][0] + o);
             copy16(d + R_JG1 * ROWB, m.jg[1][1] + o);
             copy16(d + R_JI * ROWB, m.jinv + o);
-            copy16(d + R_LAP * ROWB, m.lapdiag + o);
             copy16(d + R_RHS * ROWB, rhs + o);
         }
         if (L.r == EY - 1 && L.rowUp) copy16(d + (R_JG1 + 1) * ROWB, m.jg[1][1] + o + g.sy);   // 17th row of J g^yy
@@ -233,7 +231,7 @@ __device__ __forceinline__ void sweep_step(const Geom& g, const Metric& m, const
             nb[1][1] = Pm[L.ctr + col + PX];
             nb[2][0] = PAR ? s.Am2.y : s.Am2.x;
             nb[2][1] = PAR ? s.A0.y : s.A0.x;
-            vb = gsrb_update_vals<3>(g, s.carry, x, L.y, kb, vb, nb, fast);
+            vb = gsrb_update_vals<3, true>(g, s.carry, x, L.y, kb, vb, nb, fast);
         }
         // plane k-1 of my pair is final: the black result and the red value next to it, one 16-byte store
         double* const o = phiOut + (s.gk - L.isz);
@@ -252,7 +250,7 @@ __device__ __forceinline__ void sweep_step(const Geom& g, const Metric& m, const
     s.carry.glo[2] = PAR ? s.Zc.x : s.Zc.y;
     s.carry.ghi[2] = PAR ? Zn.x : Zn.y;
     s.carry.ji = PAR ? JI.x : JI.y;
-    s.carry.lap = PAR ? LP.x : LP.y;
+    s.carry.lap = 0.0;
     s.carry.rhs = PAR ? RH.x : RH.y;
     s.Am2 = s.Am1;
     s.Am1 = s.A0;
@@ -314,7 +312,6 @@ k_gsrb_async(const Geom g, const Metric m, double* __restrict__ phiOut, const do
             copy16(d + R_JG0 * ROWB, m.jg[0][0] + o);
             copy16(d + R_JG1 * ROWB, m.jg[1][1] + o);
             copy16(d + R_JI * ROWB, m.jinv + o);
-            copy16(d + R_LAP * ROWB, m.lapdiag + o);
             copy16(d + R_RHS * ROWB, rhs + o);
         }
         if (L.r == EY - 1 && L.rowUp) copy16(d + (R_JG1 + 1) * ROWB, m.jg[1][1] + o + g.sy);

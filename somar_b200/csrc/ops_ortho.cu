@@ -8,6 +8,10 @@ namespace somar {
 
 #define BX 64
 #define BY 4
+// k_march tuning, measured at 1024x1024x256 (unroll x CTAs/SM sweep): occupancy beats register comfort.
+// residual (modes 0/1): unroll 4, 4 CTAs/SM (64 regs): 3.91 -> 2.86 ms; restrict (mode 2): no unroll, 5 CTAs/SM: 4.21 -> 3.36 ms
+#define MARCH_UNROLL(MODE) ((MODE) == 2 ? 1 : 4)
+#define MARCH_MINB(MODE) ((MODE) == 2 ? 5 : 4)
 
 // ---------------------------------------------------------------------------------------------------------
 // apply / residual: one thread per cell of an (BX x BY) tile, marching KZ planes in z.
@@ -39,7 +43,7 @@ __global__ void __launch_bounds__(BX* BY) k_apply(const Geom g, const Metric m, 
 // the accumulation order is the reference's (kk = 0, 1).
 // ---------------------------------------------------------------------------------------------------------
 template <int MODE>
-__global__ void __launch_bounds__(BX* BY, 3) k_march(const Geom g, const Metric m, const Geom gc, double* __restrict__ out,
+__global__ void __launch_bounds__(BX* BY, MARCH_MINB(MODE)) k_march(const Geom g, const Metric m, const Geom gc, double* __restrict__ out,
                                                    const double* __restrict__ phi, const double* __restrict__ rhs,
                                                    bool homog, int kz) {
     const int i = blockIdx.x * BX + threadIdx.x;
@@ -60,6 +64,8 @@ __global__ void __launch_bounds__(BX* BY, 3) k_march(const Geom g, const Metric 
     if (i == g.n[0] - 1 && g.bc[0][1] != BC_NONE) smxy |= 2u;
     if (j == 0 && g.bc[1][0] != BC_NONE) smxy |= 4u;
     if (j == g.n[1] - 1 && g.bc[1][1] != BC_NONE) smxy |= 8u;
+    constexpr int UNR = MARCH_UNROLL(MODE);
+#pragma unroll UNR
     for (int k = k0; k < k1; ++k, c += g.sz) {
         const double pn = phi[c + g.sz], zhi = jg2[c + g.sz];
         double nb[3][2], glo[3], ghi[3];

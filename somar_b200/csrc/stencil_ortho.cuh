@@ -148,7 +148,9 @@ __device__ __forceinline__ GsrbCoef gsrb_load_coef(const Geom& g, const Metric& 
 // for Dirichlet ghosts, which the reference fills from the pre-pass state).  Shared by the colour-pass kernel
 // (values from global memory) and the fused red+black kernel (phi from the shared-memory planes, coefficients
 // prefetched), so that both execute the same statements in the same order.
-template <int ND>
+// LAPFLY: do not read q.lap; form lapDiag from the six face coefficients and 1/J the update holds anyway, with the
+// statements of FILLMAPPEDLAPDIAG (k_lapdiag) -- the same bits, one array less to stream (8 of 64 B/cell).
+template <int ND, bool LAPFLY = false>
 __device__ __forceinline__ double gsrb_update_vals(const Geom& g, const GsrbCoef& q, int i, int j, int k, double pc,
                                                    const double (&nb)[3][2], bool knownInterior = false) {
     const double sc0 = g.rdx2[0];
@@ -166,7 +168,12 @@ __device__ __forceinline__ double gsrb_update_vals(const Geom& g, const GsrbCoef
         } else {
             lphi = g.beta * ji * (JDxx + JDyy);
         }
-        return (q.rhs - lphi) / (g.alpha + g.beta * q.lap);
+        double lap = q.lap;
+        if (LAPFLY) {
+            if (ND > 2) lap = -ji * ((q.ghi[0] + q.glo[0]) * sc0 + (q.ghi[1] + q.glo[1]) * sc1 + (q.ghi[2] + q.glo[2]) * sc2);
+            else lap = -ji * ((q.ghi[0] + q.glo[0]) * sc0 + (q.ghi[1] + q.glo[1]) * sc1);
+        }
+        return (q.rhs - lphi) / (g.alpha + g.beta * lap);
     }
     // rim cell: Neumann sides are dropped from the stencil and from the diagonal
     const unsigned sm = side_mask(g, i, j, k);
