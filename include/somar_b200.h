@@ -216,6 +216,27 @@ int somar_leptic_vertical_excess(SomarLevel* lev, SomarField* excess, const Soma
 int somar_leptic_add_extrusion(SomarLevel* lev, SomarField* dest, const SomarField* flat_src);
 int somar_leptic_accum_div(SomarLevel* lev, SomarField* flat_rhs, const SomarField* flat_flux, int fc_dir, double dx_scale);
 
+/* ---- advection: the PPM / corner-transport-upwind scalar predictor (SURVEY 8(a) predictScalar row, 8(f)-3) -----------
+ * MappedAdvectionUtil::predictScalar, src/advection/AdvectUtil.cpp:520-933 (PPMNormalPred :1158, PPMFaceValues :1246,
+ * RiemannSolver :944, quasilinearUpdate :1009; kernels MappedGodunovUtilitiesF.ChF:35-468, AdvectUtilF.ChF:28-159).
+ * whalf_d (face fields, out): time-centred face states, times adv_vel_d when return_flux (the flux whose
+ * somar_mac_divergence gives the advective update, AMRNavierStokesAdvancePPM.cpp:379-620).  w_old, source (may be NULL),
+ * old_vel_d (cell-centred components) and cc_j (cell-centred J, LevelGeometry::fill_J) are cell fields, adv_vel_d face
+ * fields.  Built for FULLY PERIODIC single-rank levels, normal_pred_order 2 (PPM), use_high_order_limiter 0; anything else
+ * returns SOMAR_ERR_ARG (non-periodic sides need the physics BC holders, which are outside this library). */
+typedef struct SomarAdvectParams {
+    int normal_pred_order;        /* ProblemContext normalPredOrder{Vel,Scal}: 2 = PPM */
+    int use_limiting;             /* useLimiting{Vel,Scal}: van Leer + PPM limiters */
+    int use_high_order_limiter;   /* useHighOrderLimiter{Vel,Scal}: must be 0 */
+    int use_upwinding;            /* useUpwinding{Vel,Scal}: 1 = RiemannSolver, 0 = AvgStates */
+    int return_flux;              /* a_returnFlux */
+} SomarAdvectParams;
+int somar_advect_predict_scalar(SomarLevel* lev, SomarField* whalf_x, SomarField* whalf_y, SomarField* whalf_z,
+                                const SomarField* w_old, const SomarField* source, const SomarField* old_vel_x,
+                                const SomarField* old_vel_y, const SomarField* old_vel_z, const SomarField* adv_vel_x,
+                                const SomarField* adv_vel_y, const SomarField* adv_vel_z, const SomarField* cc_j,
+                                double dt, const SomarAdvectParams* prm);
+
 /* ---- drivers --------------------------------------------------------------------------------------------
  * somar_mg_cycle: MappedMultiGrid<T>::cycle (MappedMultiGrid.H:555-653) from `depth` down.
  * somar_solve: AMRPressureSolver::solve -> MappedAMRMultiGrid<T>::solveNoInitResid, single level

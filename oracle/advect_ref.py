@@ -1,0 +1,143 @@
+"""oracle/advect_ref.py -- TEST INFRASTRUCTURE ONLY (CPU oracle; never the product path).
+
+numpy restatement of SOMAR's PPM/CTU scalar predictor (SURVEY.md 8(a) "MappedAdvectionUtil::predictScalar" row,
+8(f)-3) for a FULLY PERIODIC level -- the TaylorGreen configuration of BASELINE.json.  Statement order follows
+  MappedAdvectionUtil::predictScalar      src/advection/AdvectUtil.cpp:520-933   (the non-USE_OLD_METHOD version)
+  ::PPMNormalPred / ::PPMFaceValues       AdvectUtil.cpp:1158-1418               (m_useHighOrderLimiter = false branch)
+  ::RiemannSolver / ::quasilinearUpdate   AdvectUtil.cpp:944-1037
+  MappedGodunovUtilities::vanLeerSlopes   src/advection/MappedGodunovUtilities.cpp:49-102
+  ::PPMLimiter / ::PPMNormalPred          MappedGodunovUtilities.cpp:373-500
+  SecondSlopeDiffsF, VanLeerLimiterF, PPMLimiterF, PPMFaceValuesF, PPMNormalPredF
+                                          src/advection/MappedGodunovUtilitiesF.ChF:35-95,151-186,315-468
+  RiemannSolver, AvgStates, QuasilinearUpdateF   src/advection/AdvectUtilF.ChF:28-159
+With every direction periodic the lo/hi one-sided boxes of PeriodicLoHiCenter are empty and no a_BCValues method runs,
+so each stage is one whole-domain array statement; numpy evaluates them elementwise in IEEE double without
+contraction, in the Fortran's operation order.  A level of several boxes gives the same numbers (every stage is a
+pure stencil on exchanged ghosts), so the restatement works on global arrays with wrapped indices.
+
+NOT covered (the device path rejects them too): non-periodic sides (the physics BC holders scalarRiemannBC /
+scalarSlopeBC), normalPredOrder 0/1 (CTU/PLM), the high-order (Colella-Sekora) limiter.
+PARITY UNPINNED against reference output (the reference cannot be built here and ships no vectors); pinned by
+tests/test_advect.py to exactness properties of the scheme (constants, uniform translation, conservation).
+
+Arrays are (nz, ny, nx) C-ordered (nz = 1 in 2-D); direction d lives on numpy axis 2 - d.  Face f of direction d is
+the LOW face of cell f (periodic: n faces per direction)."""
+import numpy as np
+
+SMALLNUMBER = 1.0e-9    # AdvectUtilF.ChF:26
+
+
+def _sh(a, d, o):
+    """a at index + o in direction d (periodic)"""
+    return np.roll(a, -o, axis=2 - d)
+
+
+def van_leer_slopes(W, d, use_limiting):
+    """vanLeerSlopes -> slopes (SecondSlopeDiffsF, centre box) [+ slopeLimiter -> VanLeerLimiterF]"""
+    dWR = _sh(W, d, 1) - W
+    dWL = W - _sh(W, d, -1)
+    dWC = 0.5 * (dWR + dWL)
+    if use_limiting:
+        lim = np.minimum(2.0 * np.abs(dWL), 2.0 * np.abs(dWR))
+        lim = np.minimum(lim, np.abs(dWC))
+        dWC = np.where(dWL * dWR < 0.0, 0.0, lim * np.copysign(1.0, dWL))
+    return dWC
+
+
+def _ppm_face(X, dX, d):
+    """PPMFaceValuesF, centre box: face f between cells f-1 and f"""
+    w_right = X - dX / 3.0
+    w_left = _sh(X, d, -1) + _sh(dX, d, -1) / 3.0
+    return (w_left + w_right) * 0.5
+
+
+def ppm_face_values(W, J, d, use_limiting):
+    """MappedAdvectionUtil::PPMFaceValues: 4th-order face values of J W divided by those of J"""
+    edge_j = _ppm_face(J, van_leer_slopes(J, d, use_limiting), d)
+    JW = W * J
+    w_face = _ppm_face(JW, van_leer_slopes(JW, d, use_limiting), d)
+    return w_face / edge_j
+
+
+def ppm_normal_pred(W, J, vel_d, d, dtbydx, use_limiting):
+    """MappedAdvectionUtil::PPMNormalPred: returns (WMinus, WPlus) on cells"""
+    w_face = ppm_face_values(W, J, d, use_limiting)
+    dm = (0.0 - W) + w_face                   # low face of the cell
+    dp = (0.0 - W) + _sh(w_face, d, 1)        # high face
+    if use_limiting:                          # PPMLimiterF
+        opp = dm * dp < 0.0
+        dwc = (dp + dm) * 0.5
+        d2w = dp - dm
+        s = np.copysign(1.0, dwc)
+        up = dwc * d2w > 0.0
+        new_p = s * np.minimum(-2.0 * s * dm, s * dp)
+        new_m = s * np.minimum(s * dm, -2.0 * s * dp)
+        dp2 = np.where(opp, np.where(up, new_p, dp), 0.0)
+        dm2 = np.where(opp, np.where(up, dm, new_m), 0.0)
+        dm, dp = dm2, dp2
+    # PPMNormalPredF, nSlope = 1
+    lam = vel_d
+    sigmin = -np.minimum(lam * dtbydx, 0.0)
+    sigmax = np.maximum(lam * dtbydx, 0.0)
+    pos = lam > 0.0
+    sig_m = np.where(pos, sigmin, -lam * dtbydx)
+    sig_p = np.where(pos, lam * dtbydx, sigmax)
+    new_m = dm + sig_m * ((dp - dm) - (dp + dm) * (3.0 - 2.0 * sig_m)) * 0.5
+    new_p = dp + sig_p * ((dm - dp) - (dp + dm) * (3.0 - 2.0 * sig_p)) * 0.5
+    return new_m + W, new_p + W
+
+
+def riemann(w_plus, w_minus, adv_vel_d, d, upwind):
+    """RiemannSolver / AvgStates at face f: left state = WPlus of cell f-1, right state = WMinus of cell f"""
+    wl = _sh(w_plus, d, -1)
+    wr = w_minus
+    if not upwind:
+        return 0.5 * (wl + wr)
+    return np.where(adv_vel_d > SMALLNUMBER, wl, np.where(adv_vel_d < -SMALLNUMBER, wr, 0.5 * (wl + wr)))
+
+
+def quasilinear_update(w_half_d, vel_d, scale, d):
+    """QuasilinearUpdateF: AdWdx = scale * u_d * (WHalf(i + e_d) - WHalf(i))"""
+    return scale * vel_d * (_sh(w_half_d, d, 1) - w_half_d)
+
+
+def predict_scalar(W, J, old_vel, adv_vel, dt, dx, dim, source=None, use_limiting=False, use_upwinding=True,
+                   return_flux=True):
+    """old_vel[d]: cell-centred velocity components; adv_vel[d]: face-centred advecting velocity of direction d.
+    Returns the list of face-centred, time-centred states (times adv_vel when return_flux)."""
+    dtondx = [dt / dx[d] for d in range(dim)]
+    wm, wp, wh1 = [], [], []
+    for d in range(dim):
+        m, p = ppm_normal_pred(W, J, old_vel[d], d, dt / dx[d], use_limiting)
+        if source is not None:
+            m = m + source * (0.5 * dt)
+            p = p + source * (0.5 * dt)
+        wm.append(m)
+        wp.append(p)
+        wh1.append(riemann(p, m, adv_vel[d], d, use_upwinding))
+    wh2 = {}
+    if dim == 3:
+        for d1 in range(3):
+            for d2 in range(3):
+                if d2 == d1:
+                    continue
+                a = quasilinear_update(wh1[d2], old_vel[d2], -(1.0 / 3.0) * dtondx[d2], d2)
+                wh2[(d1, d2)] = riemann(wp[d1] + a, wm[d1] + a, adv_vel[d1], d1, use_upwinding)
+    out = []
+    for d1 in range(dim):
+        m, p = wm[d1], wp[d1]
+        for d2 in range(dim):
+            if d2 == d1:
+                continue
+            if dim == 2:
+                a = quasilinear_update(wh1[d2], old_vel[d2], -(1.0 / 2.0) * dtondx[d2], d2)
+            else:
+                d3 = 3 - d1 - d2
+                a = quasilinear_update(wh2[(d2, d3)], old_vel[d2], -(1.0 / 2.0) * dtondx[d2], d2)
+            m = m + a
+            p = p + a
+        wh = riemann(p, m, adv_vel[d1], d1, use_upwinding)
+        if return_flux:
+            wh = wh * adv_vel[d1]
+        out.append(wh)
+    return out

@@ -33,6 +33,7 @@ SYMBOLS = [
     "somar_field_set_face", "somar_field_get_face", "somar_mac_gradient", "somar_mac_divergence",
     "somar_mac_apply_correction", "somar_project", "somar_leptic_vertical_solve", "somar_leptic_vert_integral",
     "somar_leptic_vertical_excess", "somar_leptic_add_extrusion", "somar_leptic_accum_div",
+    "somar_advect_predict_scalar",
 ]
 
 
@@ -56,6 +57,11 @@ class SolveStats(C.Structure):
     _fields_ = [("iters", C.c_int), ("exitStatus", C.c_int), ("initial_rnorm", C.c_double), ("final_rnorm", C.c_double),
                 ("bottom_iters_total", C.c_int), ("history_len", C.c_int), ("history", C.c_double * 128),
                 ("solve_ms", C.c_double), ("launches", C.c_longlong)]
+
+
+class AdvectParams(C.Structure):
+    _fields_ = [("normal_pred_order", C.c_int), ("use_limiting", C.c_int), ("use_high_order_limiter", C.c_int),
+                ("use_upwinding", C.c_int), ("return_flux", C.c_int)]
 
 
 class SomarError(RuntimeError):
@@ -428,6 +434,17 @@ class Level:
         L = lib()
         L.somar_leptic_accum_div.argtypes = [C.c_void_p] * 3 + [C.c_int, C.c_double]
         _ck(L.somar_leptic_accum_div(self.h, flat_rhs.h, flat_flux.h, int(fc_dir), float(dx_scale)))
+
+    # -- advection predictor --------------------------------------------------------------------------------
+    def advect_predict_scalar(self, whalf, w_old: Field, old_vel, adv_vel, cc_j: Field, dt: float, source=None,
+                              normal_pred_order=2, use_limiting=False, use_high_order_limiter=False, use_upwinding=True,
+                              return_flux=True):
+        prm = AdvectParams(int(normal_pred_order), int(use_limiting), int(use_high_order_limiter), int(use_upwinding),
+                           int(return_flux))
+        L = lib()
+        L.somar_advect_predict_scalar.argtypes = [C.c_void_p] * 13 + [C.c_double, C.POINTER(AdvectParams)]
+        _ck(L.somar_advect_predict_scalar(self.h, *self._h3(whalf), w_old.h, source.h if source is not None else None,
+                                          *self._h3(old_vel), *self._h3(adv_vel), cc_j.h, float(dt), C.byref(prm)))
 
     def destroy(self):
         if getattr(self, "h", None):

@@ -1,0 +1,256 @@
+// advect.cu -- the PPM / corner-transport-upwind scalar predictor of SOMAR's advection step (SURVEY.md 8(a)
+// "MappedAdvectionUtil::predictScalar" row, 8(f)-3) on a FULLY PERIODIC level (BASELINE.json's TaylorGreen config):
+//   k_adv_face     MappedAdvectionUtil::PPMFaceValues   src/advection/AdvectUtil.cpp:1246-1418 (old-limiter branch)
+//                  -> vanLeerSlopes (MappedGodunovUtilities.cpp:49-102; SecondSlopeDiffsF, VanLeerLimiterF,
+//                  MappedGodunovUtilitiesF.ChF:35-95,151-186) + PPMFaceValuesF (:353-414), for J and J W, then W = JW / J
+//   k_adv_normal   MappedAdvectionUtil::PPMNormalPred   AdvectUtil.cpp:1158-1240 -> PPMLimiterF (:315-351),
+//                  PPMNormalPredF (:416-468), + the half-step source term (AdvectUtil.cpp:699-705)
+//   k_adv_riemann  RiemannSolver / AvgStates (AdvectUtilF.ChF:28-132) with the transverse corrections of
+//                  quasilinearUpdate (QuasilinearUpdateF, AdvectUtilF.ChF:134-159) applied on the fly to both states:
+//                  the three uses in predictScalar (AdvectUtil.cpp:707-713, 748-775, 818-866) and "flux = state * u_adv" (:911)
+// Every stage is a pure stencil, so on a periodic level the box decomposition does not matter and the kernels
+// index the rank's brick with wrapped indices (no ghost cells are read); the final states are also written to the
+// periodic image in the first ghost slot, where somar_mac_divergence expects the high face of the last cell.
+// The arithmetic is the Fortran's, statement for statement (-fmad=false): bit-identical to oracle/advect_ref.py.
+// Not built: non-periodic sides (they need the physics BC holders scalarRiemannBC / scalarSlopeBC), CTU / PLM normal
+// predictors, the high-order limiter, more than one rank -- the entry point rejects them.
+// HBM-bound streaming passes (18 launches in 3-D); intermediate states live in scratch fields, not yet fused.
+#include "level.hpp"
+
+namespace somar {
+
+#define ATPB 256
+
+struct AGeom {
+    int n[3];
+    int nd;
+    long long sy, sz, off0;
+};
+
+__device__ __forceinline__ int awrap(int i, int n) { return i < 0 ? i + n : (i >= n ? i - n : i); }
+__device__ __forceinline__ long long aidx(const AGeom& g, int i, int j, int k) {
+    return g.off0 + awrap(i, g.n[0]) + g.sy * awrap(j, g.n[1]) + g.sz * awrap(k, g.n[2]);
+}
+// cell (i,j,k) shifted by o along direction d
+__device__ __forceinline__ long long aoff(const AGeom& g, int i, int j, int k, int d, int o) {
+    return aidx(g, i + (d == 0 ? o : 0), j + (d == 1 ? o : 0), k + (d == 2 ? o : 0));
+}
+__device__ __forceinline__ bool acell(const AGeom& g, int& i, int& j, int& k) {
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long tot = (long long)g.n[0] * g.n[1] * g.n[2];
+    if (t >= tot) return false;
+    i = (int)(t % g.n[0]);
+    const long long r = t / g.n[0];
+    j = (int)(r % g.n[1]);
+    k = (int)(r / g.n[1]);
+    return true;
+}
+
+// vanLeerSlopes at one cell from its neighbours along the direction
+template <bool LIM>
+__device__ __forceinline__ double vl_slope(double xm, double x0, double xp) {
+    const double dWR = xp - x0;
+    const double dWL = x0 - xm;
+    double dWC = 0.5 * (dWR + dWL);
+    if (LIM) {
+        double lim = fmin(2.0 * fabs(dWL), 2.0 * fabs(dWR));
+        lim = fmin(lim, fabs(dWC));
+        dWC = (dWL * dWR < 0.0) ? 0.0 : lim * copysign(1.0, dWL);
+    }
+    return dWC;
+}
+// PPMFaceValuesF (centre box): the face between cells -1 and 0
+template <bool LIM>
+__device__ __forceinline__ double ppm_face(double xm2, double xm1, double x0, double xp1) {
+    const double d0 = vl_slope<LIM>(xm1, x0, xp1);
+    const double dm1 = vl_slope<LIM>(xm2, xm1, x0);
+    const double wr = x0 - d0 / 3.0;
+    const double wl = xm1 + dm1 / 3.0;
+    return (wl + wr) * 0.5;
+}
+
+template <bool LIM>
+__global__ void __launch_bounds__(ATPB) k_adv_face(const AGeom g, int d, const double* __restrict__ W,
+                                                   const double* __restrict__ J, double* __restrict__ wface) {
+    int i, j, k;
+    if (!acell(g, i, j, k)) return;
+    double jj[4], jw[4];
+#pragma unroll
+    for (int o = 0; o < 4; ++o) {
+        const long long c = aoff(g, i, j, k, d, o - 2);
+        jj[o] = J[c];
+        jw[o] = W[c] * jj[o];
+    }
+    const double edgeJ = ppm_face<LIM>(jj[0], jj[1], jj[2], jj[3]);
+    const double fw = ppm_face<LIM>(jw[0], jw[1], jw[2], jw[3]);
+    wface[aidx(g, i, j, k)] = fw / edgeJ;
+}
+
+template <bool LIM>
+__global__ void __launch_bounds__(ATPB) k_adv_normal(const AGeom g, int d, const double* __restrict__ W,
+                                                     const double* __restrict__ wface, const double* __restrict__ vel,
+                                                     const double* __restrict__ src, double srcScale, double dtbydx,
+                                                     double* __restrict__ wminus, double* __restrict__ wplus) {
+    int i, j, k;
+    if (!acell(g, i, j, k)) return;
+    const long long c = aidx(g, i, j, k);
+    const double w = W[c];
+    double dm = (0.0 - w) + wface[c];
+    double dp = (0.0 - w) + wface[aoff(g, i, j, k, d, 1)];
+    if (LIM) {   // PPMLimiterF
+        if (dm * dp < 0.0) {
+            const double dwc = (dp + dm) * 0.5;
+            const double d2w = dp - dm;
+            const double s = copysign(1.0, dwc);
+            if (dwc * d2w > 0.0) dp = s * fmin(-2.0 * s * dm, s * dp);
+            else dm = s * fmin(s * dm, -2.0 * s * dp);
+        } else {
+            dp = 0.0;
+            dm = 0.0;
+        }
+    }
+    // PPMNormalPredF, one slope
+    const double lam = vel[c];
+    double sigmin = lam * dtbydx;
+    sigmin = fmin(sigmin, 0.0);
+    sigmin = -sigmin;
+    double sigmax = lam * dtbydx;
+    sigmax = fmax(sigmax, 0.0);
+    double sigM, sigP;
+    if (lam > 0.0) { sigM = sigmin; sigP = lam * dtbydx; }
+    else { sigM = -lam * dtbydx; sigP = sigmax; }
+    double nm = dm + sigM * ((dp - dm) - (dp + dm) * (3.0 - 2.0 * sigM)) * 0.5;
+    double np = dp + sigP * ((dm - dp) - (dp + dm) * (3.0 - 2.0 * sigP)) * 0.5;
+    nm = nm + w;
+    np = np + w;
+    if (src) {
+        const double s = src[c] * srcScale;
+        nm = nm + s;
+        np = np + s;
+    }
+    wminus[c] = nm;
+    wplus[c] = np;
+}
+
+// up to two transverse corrections  A = scale * u_d2 * (WHalf(i + e_d2) - WHalf(i))  added to both states, in order
+struct ACorr {
+    const double* wh[2];
+    const double* vel[2];
+    double scale[2];
+    int dir[2];
+    int n;
+};
+
+__global__ void __launch_bounds__(ATPB) k_adv_riemann(const AGeom g, int d, const double* __restrict__ wplus,
+                                                      const double* __restrict__ wminus,
+                                                      const double* __restrict__ advVel, ACorr cr, int upwind,
+                                                      int timesVel, int image, double* __restrict__ out) {
+    int i, j, k;
+    if (!acell(g, i, j, k)) return;
+    const long long cR = aidx(g, i, j, k);
+    const int iL = i - (d == 0), jL = j - (d == 1), kL = k - (d == 2);
+    const long long cL = aidx(g, iL, jL, kL);
+    double wl = wplus[cL];
+    double wr = wminus[cR];
+    for (int t = 0; t < cr.n; ++t) {
+        const int d2 = cr.dir[t];
+        const double aL = cr.scale[t] * cr.vel[t][cL] * (cr.wh[t][aoff(g, iL, jL, kL, d2, 1)] - cr.wh[t][cL]);
+        const double aR = cr.scale[t] * cr.vel[t][cR] * (cr.wh[t][aoff(g, i, j, k, d2, 1)] - cr.wh[t][cR]);
+        wl = wl + aL;
+        wr = wr + aR;
+    }
+    const double u = advVel[cR];
+    double v;
+    if (!upwind) v = 0.5 * (wl + wr);
+    else if (u > 1.0e-9) v = wl;
+    else if (u < -1.0e-9) v = wr;
+    else v = 0.5 * (wl + wr);
+    if (timesVel) v = v * u;
+    out[cR] = v;
+    if (image) {   // the periodic image of face 0 = the high face of the last cell (first ghost slot)
+        const int q = (d == 0) ? i : (d == 1 ? j : k);
+        if (q == 0) out[cR + (d == 0 ? (long long)g.n[0] : (d == 1 ? g.sy * g.n[1] : g.sz * g.n[2]))] = v;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+int advect_predict_scalar(SomarLevel* L, SomarField* const whalf[3], const SomarField* wold, const SomarField* source,
+                          const SomarField* const oldVel[3], const SomarField* const advVel[3], const SomarField* ccJ,
+                          double dt, const SomarAdvectParams* prm) {
+    const Geom& G = L->depths[0].g;
+    const int nd = G.nd;
+    if (L->desc.nranks > 1) { set_error("predictScalar: more than one rank is not built"); return SOMAR_ERR_ARG; }
+    for (int d = 0; d < nd; ++d)
+        if (!G.periodic[d]) {
+            set_error("predictScalar: only fully periodic levels are built (non-periodic sides need the physics BC holders "
+                      "scalarRiemannBC / scalarSlopeBC, AdvectUtil.cpp:715-740)");
+            return SOMAR_ERR_ARG;
+        }
+    if (prm->normal_pred_order != 2) { set_error("predictScalar: only the PPM normal predictor (order 2) is built"); return SOMAR_ERR_ARG; }
+    if (prm->use_high_order_limiter) { set_error("predictScalar: the high-order limiter is not built"); return SOMAR_ERR_ARG; }
+    AGeom g;
+    for (int d = 0; d < 3; ++d) g.n[d] = G.n[d];
+    g.nd = nd;
+    g.sy = G.sy; g.sz = G.sz; g.off0 = G.off0;
+    const size_t need = (nd == 3) ? 15 : 6;     // WMinus, WPlus, WHalf1 per direction (+ six WHalf2 in 3-D)
+    int rc;
+    while (L->awork.size() < need) {
+        SomarField* f = nullptr;
+        if ((rc = field_alloc(L, 0, &f)) != SOMAR_OK) return rc;
+        L->awork.push_back(f);
+    }
+    double *wm[3], *wp[3], *wh1[3], *wh2[3][3] = {};
+    for (int d = 0; d < nd; ++d) { wm[d] = L->awork[d]->p; wp[d] = L->awork[nd + d]->p; wh1[d] = L->awork[2 * nd + d]->p; }
+    if (nd == 3) {
+        int q = 9;
+        for (int d1 = 0; d1 < 3; ++d1)
+            for (int d2 = 0; d2 < 3; ++d2)
+                if (d2 != d1) wh2[d1][d2] = L->awork[q++]->p;
+    }
+    const long long tot = (long long)g.n[0] * g.n[1] * g.n[2];
+    const unsigned nb = (unsigned)((tot + ATPB - 1) / ATPB);
+    cudaStream_t st = L->cx.stream;
+    const bool lim = prm->use_limiting != 0;
+    const int up = prm->use_upwinding != 0;
+    double dtondx[3];
+    for (int d = 0; d < nd; ++d) dtondx[d] = dt / G.dx[d];
+    const ACorr none = {{nullptr, nullptr}, {nullptr, nullptr}, {0.0, 0.0}, {0, 0}, 0};
+    for (int d = 0; d < nd; ++d) {
+        double* wface = whalf[d]->p;            // the output's memory holds the face values until they are consumed
+        if (lim) k_adv_face<true><<<nb, ATPB, 0, st>>>(g, d, wold->p, ccJ->p, wface);
+        else k_adv_face<false><<<nb, ATPB, 0, st>>>(g, d, wold->p, ccJ->p, wface);
+        const double* src = source ? source->p : nullptr;
+        if (lim) k_adv_normal<true><<<nb, ATPB, 0, st>>>(g, d, wold->p, wface, oldVel[d]->p, src, 0.5 * dt, dtondx[d], wm[d], wp[d]);
+        else k_adv_normal<false><<<nb, ATPB, 0, st>>>(g, d, wold->p, wface, oldVel[d]->p, src, 0.5 * dt, dtondx[d], wm[d], wp[d]);
+        k_adv_riemann<<<nb, ATPB, 0, st>>>(g, d, wp[d], wm[d], advVel[d]->p, none, up, 0, 0, wh1[d]);
+        L->cx.launches += 3;
+    }
+    if (nd == 3) {
+        for (int d1 = 0; d1 < 3; ++d1)
+            for (int d2 = 0; d2 < 3; ++d2) {
+                if (d2 == d1) continue;
+                ACorr c = none;
+                c.n = 1;
+                c.wh[0] = wh1[d2]; c.vel[0] = oldVel[d2]->p; c.scale[0] = -(1.0 / 3.0) * dtondx[d2]; c.dir[0] = d2;
+                k_adv_riemann<<<nb, ATPB, 0, st>>>(g, d1, wp[d1], wm[d1], advVel[d1]->p, c, up, 0, 0, wh2[d1][d2]);
+                L->cx.launches++;
+            }
+    }
+    for (int d1 = 0; d1 < nd; ++d1) {
+        ACorr c = none;
+        for (int d2 = 0; d2 < nd; ++d2) {
+            if (d2 == d1) continue;
+            const int t = c.n++;
+            c.wh[t] = (nd == 2) ? wh1[d2] : wh2[d2][3 - d1 - d2];
+            c.vel[t] = oldVel[d2]->p;
+            c.scale[t] = -(1.0 / 2.0) * dtondx[d2];
+            c.dir[t] = d2;
+        }
+        k_adv_riemann<<<nb, ATPB, 0, st>>>(g, d1, wp[d1], wm[d1], advVel[d1]->p, c, up, prm->return_flux != 0, 1, whalf[d1]->p);
+        L->cx.launches++;
+    }
+    SOMAR_CUDA(cudaGetLastError());
+    return SOMAR_OK;
+}
+
+}  // namespace somar

@@ -197,4 +197,26 @@ int somar_leptic_accum_div(SomarLevel* L, SomarField* flat_rhs, const SomarField
     return leptic_accum_div(L, flat_rhs, flat_flux, fc_dir, dx_scale);
 }
 
+// ---- advection predictor (SURVEY 8(a) predictScalar row) --------------------------------------------------
+int somar_advect_predict_scalar(SomarLevel* L, SomarField* whalf_x, SomarField* whalf_y, SomarField* whalf_z,
+                                const SomarField* w_old, const SomarField* source, const SomarField* old_vel_x,
+                                const SomarField* old_vel_y, const SomarField* old_vel_z, const SomarField* adv_vel_x,
+                                const SomarField* adv_vel_y, const SomarField* adv_vel_z, const SomarField* cc_j,
+                                double dt, const SomarAdvectParams* prm) {
+    CHECK_FINAL(L); CHECK_F0(w_old, L); CHECK_F0(cc_j, L);
+    if (!prm) { set_error("null parameters"); return SOMAR_ERR_ARG; }
+    if (source) CHECK_F0(source, L);
+    SomarField* wh[3] = {whalf_x, whalf_y, whalf_z};
+    const SomarField* ov[3] = {old_vel_x, old_vel_y, old_vel_z};
+    const SomarField* av[3] = {adv_vel_x, adv_vel_y, adv_vel_z};
+    const int nd = L->desc.dim;
+    for (int d = 0; d < nd; ++d) {
+        CHECK_F0(wh[d], L); CHECK_F0(ov[d], L); CHECK_F0(av[d], L);
+        if (wh[d] == w_old || wh[d] == cc_j || wh[d] == source) { set_error("predictScalar: an output aliases an input"); return SOMAR_ERR_ARG; }
+        for (int e = 0; e < nd; ++e)
+            if (wh[d] == ov[e] || wh[d] == av[e] || (e != d && wh[d] == wh[e])) { set_error("predictScalar: an output aliases another field"); return SOMAR_ERR_ARG; }
+    }
+    return advect_predict_scalar(L, wh, w_old, source, ov, av, cc_j, dt, prm);
+}
+
 }  // extern "C"

@@ -95,6 +95,7 @@ struct SomarLevel {
     std::vector<SomarField*> bwork;
     // outer-solve work fields (depth 0)
     std::vector<SomarField*> swork;
+    std::vector<SomarField*> awork;    // advection: WMinus/WPlus/WHalf scratch (depth 0, allocated on first use)
     SomarField* pwork = nullptr;       // projector: the divergence / right-hand side (depth 0)
     double bottomMetric = 0.0, bottomEps = 1e-6;
     int bottom_iters_total = 0;
@@ -178,6 +179,10 @@ int op_mac_gradient(SomarLevel* L, SomarField* const grad[3], SomarField* phi, b
 int op_mac_divergence(SomarLevel* L, SomarField* div, const SomarField* const flux[3], double divideBy);
 int project(SomarLevel* L, SomarField* const vel[3], SomarField* pressure, double dt, bool zeroPressure, bool forceHomog,
             SomarSolveStats* st);
+// advect.cu
+int advect_predict_scalar(SomarLevel* L, SomarField* const whalf[3], const SomarField* wold, const SomarField* source,
+                          const SomarField* const oldVel[3], const SomarField* const advVel[3], const SomarField* ccJ,
+                          double dt, const SomarAdvectParams* prm);
 // leptic.cu
 int leptic_vertical_solve(SomarLevel* L, SomarField* phi, SomarField* rhs, int loBC, int hiBC, double dzCrse,
                           const SomarField* bdryLo, const SomarField* bdryHi);
