@@ -236,6 +236,11 @@ int somar_advect_predict_scalar(SomarLevel* lev, SomarField* whalf_x, SomarField
                                 const SomarField* old_vel_y, const SomarField* old_vel_z, const SomarField* adv_vel_x,
                                 const SomarField* adv_vel_y, const SomarField* adv_vel_z, const SomarField* cc_j,
                                 double dt, const SomarAdvectParams* prm);
+/* The finite-volume update of AMRNavierStokes::getNewScalar (AMRNavierStokesAdvancePPM.cpp:561-584, no background /
+ * sponge / diffusive sources):  w_new = w_old + (-Div[flux]) * dt,  Div = MAPPEDFLUXDIVERGENCE with the level's Jinv.
+ * flux_d are face fields (high face of the last cell in the first ghost slot, as predict_scalar leaves them). */
+int somar_advect_update(SomarLevel* lev, SomarField* w_new, const SomarField* w_old, const SomarField* flux_x,
+                        const SomarField* flux_y, const SomarField* flux_z, double dt);
 
 /* ---- drivers --------------------------------------------------------------------------------------------
  * somar_mg_cycle: MappedMultiGrid<T>::cycle (MappedMultiGrid.H:555-653) from `depth` down.

@@ -33,7 +33,7 @@ SYMBOLS = [
     "somar_field_set_face", "somar_field_get_face", "somar_mac_gradient", "somar_mac_divergence",
     "somar_mac_apply_correction", "somar_project", "somar_leptic_vertical_solve", "somar_leptic_vert_integral",
     "somar_leptic_vertical_excess", "somar_leptic_add_extrusion", "somar_leptic_accum_div",
-    "somar_advect_predict_scalar",
+    "somar_advect_predict_scalar", "somar_advect_update",
 ]
 
 
@@ -71,12 +71,28 @@ class SomarError(RuntimeError):
 _LIB = None
 
 
+def _preload_bundled_nccl():
+    """One NCCL per process.  libsomar_b200.so needs libnccl.so.2; a process that also imports PyTorch gets PyTorch's
+    bundled copy (newer than the system one), and whichever is loaded first serves both.  Loading the system copy
+    first breaks `import torch` later (missing newer symbols), so take the bundled one when it exists."""
+    import sys
+    for d in sys.path:
+        cand = os.path.join(d, "nvidia", "nccl", "lib", "libnccl.so.2")
+        if os.path.exists(cand):
+            try:
+                C.CDLL(cand, mode=C.RTLD_GLOBAL)
+            except OSError:
+                pass
+            return
+
+
 def lib():
     """Loads libsomar_b200.so; raises (never falls back) when it is missing."""
     global _LIB
     if _LIB is None:
         if not os.path.exists(LIB_PATH):
             raise SomarError(f"{LIB_PATH} is not built: run __graft_entry__.build() (there is no CPU fallback)")
+        _preload_bundled_nccl()
         L = C.CDLL(LIB_PATH, mode=C.RTLD_GLOBAL)
         L.somar_last_error.restype = C.c_char_p
         L.somar_version.restype = C.c_char_p
@@ -445,6 +461,11 @@ class Level:
         L.somar_advect_predict_scalar.argtypes = [C.c_void_p] * 13 + [C.c_double, C.POINTER(AdvectParams)]
         _ck(L.somar_advect_predict_scalar(self.h, *self._h3(whalf), w_old.h, source.h if source is not None else None,
                                           *self._h3(old_vel), *self._h3(adv_vel), cc_j.h, float(dt), C.byref(prm)))
+
+    def advect_update(self, w_new: Field, w_old: Field, flux, dt: float):
+        L = lib()
+        L.somar_advect_update.argtypes = [C.c_void_p] * 6 + [C.c_double]
+        _ck(L.somar_advect_update(self.h, w_new.h, w_old.h, *self._h3(flux), float(dt)))
 
     def destroy(self):
         if getattr(self, "h", None):

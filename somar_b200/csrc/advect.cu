@@ -253,4 +253,35 @@ int advect_predict_scalar(SomarLevel* L, SomarField* const whalf[3], const Somar
     return SOMAR_OK;
 }
 
+// The finite-volume update of getNewScalar (src/NavierStokes/AMRNavierStokesAdvancePPM.cpp:561-584, no background,
+// sponge or diffusive terms): adv = Div[flux] (MAPPEDFLUXDIVERGENCE) * -1.0;  new = old + adv * dt.
+template <int ND>
+__global__ void __launch_bounds__(ATPB) k_adv_update(const Geom g, const double* __restrict__ jinv,
+                                                     double* __restrict__ wnew, const double* __restrict__ wold,
+                                                     const double* __restrict__ f0, const double* __restrict__ f1,
+                                                     const double* __restrict__ f2, double dt) {
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= g.cells()) return;
+    const int i = (int)(t % g.n[0]);
+    const long long r = t / g.n[0];
+    const int j = (int)(r % g.n[1]), k = (int)(r / g.n[1]);
+    const long long c = g.idx(i, j, k);
+    double s = (f0[c + 1] - f0[c]) * g.rdx[0];
+    s = s + (f1[c + g.sy] - f1[c]) * g.rdx[1];
+    if (ND > 2) s = s + (f2[c + g.sz] - f2[c]) * g.rdx[2];
+    double adv = jinv[c] * s;
+    adv = adv * -1.0;
+    wnew[c] = wold[c] + adv * dt;
+}
+
+int advect_update(SomarLevel* L, SomarField* wnew, const SomarField* wold, const SomarField* const flux[3], double dt) {
+    const Depth& dp = L->depths[0];
+    const Geom& g = dp.g;
+    const unsigned nb = (unsigned)((g.cells() + ATPB - 1) / ATPB);
+    if (g.nd == 3) k_adv_update<3><<<nb, ATPB, 0, L->cx.stream>>>(g, dp.m.jinv, wnew->p, wold->p, flux[0]->p, flux[1]->p, flux[2]->p, dt);
+    else k_adv_update<2><<<nb, ATPB, 0, L->cx.stream>>>(g, dp.m.jinv, wnew->p, wold->p, flux[0]->p, flux[1]->p, nullptr, dt);
+    L->cx.launches++;
+    return SOMAR_OK;
+}
+
 }  // namespace somar

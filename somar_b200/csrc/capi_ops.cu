@@ -219,4 +219,15 @@ int somar_advect_predict_scalar(SomarLevel* L, SomarField* whalf_x, SomarField* 
     return advect_predict_scalar(L, wh, w_old, source, ov, av, cc_j, dt, prm);
 }
 
+int somar_advect_update(SomarLevel* L, SomarField* w_new, const SomarField* w_old, const SomarField* flux_x,
+                        const SomarField* flux_y, const SomarField* flux_z, double dt) {
+    CHECK_FINAL(L); CHECK_F0(w_new, L); CHECK_F0(w_old, L);
+    const SomarField* f[3] = {flux_x, flux_y, flux_z};
+    for (int d = 0; d < L->desc.dim; ++d) {
+        CHECK_F0(f[d], L);
+        if (f[d] == w_new) { set_error("advect update: the output aliases a flux"); return SOMAR_ERR_ARG; }
+    }
+    return advect_update(L, w_new, w_old, f, dt);
+}
+
 }  // extern "C"

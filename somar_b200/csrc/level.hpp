@@ -183,6 +183,7 @@ int project(SomarLevel* L, SomarField* const vel[3], SomarField* pressure, doubl
 int advect_predict_scalar(SomarLevel* L, SomarField* const whalf[3], const SomarField* wold, const SomarField* source,
                           const SomarField* const oldVel[3], const SomarField* const advVel[3], const SomarField* ccJ,
                           double dt, const SomarAdvectParams* prm);
+int advect_update(SomarLevel* L, SomarField* wnew, const SomarField* wold, const SomarField* const flux[3], double dt);
 // leptic.cu
 int leptic_vertical_solve(SomarLevel* L, SomarField* phi, SomarField* rhs, int loBC, int hiBC, double dzCrse,
                           const SomarField* bdryLo, const SomarField* bdryHi);

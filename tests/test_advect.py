@@ -116,6 +116,12 @@ def test_predict_scalar_parity(dim, n, somar):
     if dim == 3:
         s = s + (np.roll(want[2], -1, 0) - want[2]) * (1.0 / pb.spec.dx[2])
     assert np.array_equal(div.get(), pb.jinv * s)
+    # the finite-volume update of getNewScalar: new = old + (-Div[flux]) * dt
+    new = lev.field(0)
+    lev.advect_update(new, fW, out, dt)
+    assert np.array_equal(new.get(), W + ((pb.jinv * s) * -1.0) * dt)
+    # conservation on the periodic domain: sum of dV-weighted change is zero (dV = prod(dx) / Jinv)
+    assert abs(((new.get() - W) / pb.jinv).sum()) <= 1e-11 * np.abs(W / pb.jinv).sum()
 
 
 @pytest.mark.gpu
