@@ -166,13 +166,54 @@ __device__ __forceinline__ void ctl5(BicgState* st) {
             }                                                                                              \
         }                                                                                                  \
     }
+// Grid-wide barrier for a cooperatively launched (co-resident) grid: arrivals are spread over BP_BAR_GROUPS padded
+// counters, the last arrival of a group bumps a top counter, the last group publishes the epoch; everybody polls one
+// flag.  Counters only grow (zeroed by the host before the launch), so there is no reset race.  Same fence /
+// __syncthreads structure as cooperative groups' software barrier, i.e. the same visibility guarantees.
+#define BP_BAR_GROUPS 8
+#define BP_BAR_WORDS (16 * (BP_BAR_GROUPS + 2))
+__device__ __forceinline__ void tree_barrier(unsigned long long* bar, unsigned& epoch) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        ++epoch;
+        const unsigned nb = gridDim.x;
+        const unsigned grp = blockIdx.x % BP_BAR_GROUPS;
+        const unsigned members = (nb - grp + BP_BAR_GROUPS - 1) / BP_BAR_GROUPS;
+        const unsigned ngroups = nb < BP_BAR_GROUPS ? nb : BP_BAR_GROUPS;
+        volatile unsigned long long* flag = bar + 16 * (BP_BAR_GROUPS + 1);
+        __threadfence();
+        const unsigned long long old = atomicAdd(bar + 16 * grp, 1ULL);
+        if (old + 1 == (unsigned long long)members * epoch) {
+            __threadfence();
+            const unsigned long long t = atomicAdd(bar + 16 * BP_BAR_GROUPS, 1ULL);
+            if (t + 1 == (unsigned long long)ngroups * epoch) {
+                __threadfence();
+                *flag = epoch;
+            }
+        }
+        const long long t0 = clock64();
+        while (*flag < epoch) {
+            if (clock64() - t0 > (20ll << 30)) __trap();   // ~10 s: a bug must not hang the GPU
+        }
+        __threadfence();
+    }
+    __syncthreads();
+}
+
 #define BP_U 8
 
 template <int ND>
 __global__ void __launch_bounds__(BP_TPB, BP_MINBLOCKS)
     k_bicg_persistent(const Geom g, const Metric m, const BicgFields f, const BicgArgs a, double* part,
-                      int* itersAccum, const int cb) {
+                      int* itersAccum, const int cb, unsigned long long* bar) {
     cg::grid_group grid = cg::this_grid();
+    unsigned epoch = 0;
+    // bar != nullptr: the two-level counter barrier below instead of cg::grid_group::sync() (one atomic word for all
+    // blocks: ~600 serialised arrivals per barrier at 4 blocks/SM)
+    auto gsync = [&]() {
+        if (bar) tree_barrier(bar, epoch);
+        else grid.sync();
+    };
     __shared__ BicgState s;
     __shared__ double rhoNext;   // <r_tilde, r> formed by the pass that wrote r
     int buf = 0;
@@ -194,7 +235,7 @@ __global__ void __launch_bounds__(BP_TPB, BP_MINBLOCKS)
             pb[blockIdx.x] = p0;
             if (n > 1) pb[MAX_RED_BLOCKS + blockIdx.x] = p1;
         }
-        grid.sync();
+        gsync();
         for (int q = 0; q < n; ++q) {
             const bool isMax = isMax0 && q == 0;
             double v = 0.0;
@@ -239,9 +280,9 @@ __global__ void __launch_bounds__(BP_TPB, BP_MINBLOCKS)
     auto relax = [&](double* phi, const double* rhs, int iters) {   // enters and leaves with phi complete
         for (int it = 0; it < iters; ++it) {
             colour_pass(phi, rhs, 0);
-            grid.sync();
+            gsync();
             colour_pass(phi, rhs, 1);
-            grid.sync();
+            gsync();
         }
     };
     // r = rhs - L phi, r_tilde = r, e = 0, norm(r), <r, r>      (phi complete on entry)
@@ -252,7 +293,7 @@ __global__ void __launch_bounds__(BP_TPB, BP_MINBLOCKS)
             f.rt[c] = rv;
             f.e[c] = 0.0;
         })
-        grid.sync();
+        gsync();
         norm_and_rho();
     };
 
@@ -292,12 +333,12 @@ __global__ void __launch_bounds__(BP_TPB, BP_MINBLOCKS)
                 f.pv[c] = pn;
                 f.pt[c] = a.nprecond ? pn / (g.alpha + g.beta * m.lapdiag[c]) : pn;
             })
-            grid.sync();
+            gsync();
             relax(f.pt, f.pv, a.nprecond);
         }
         {   // v = L p_tilde (spread over the grid), then <r_tilde, v> in the canonical order
             BP_FOR_CELLS(g, c, { f.v[c] = apply_cell_ortho<ND>(g, m, f.pt, i, j, k, c, true); })
-            grid.sync();
+            gsync();
             double acc = 0.0;
             double tv[BP_U], vv[BP_U];
             BP_CANON_CELLS(g, cb, c, u, BP_U, { tv[u] = f.rt[c]; vv[u] = f.v[c]; }, { acc += tv[u] * vv[u]; })
@@ -317,7 +358,7 @@ __global__ void __launch_bounds__(BP_TPB, BP_MINBLOCKS)
                 f.r[c] = nv;
                 f.stl[c] = a.nprecond ? nv / (g.alpha + g.beta * m.lapdiag[c]) : nv;
             })
-            grid.sync();
+            gsync();
             norm_and_rho();
         }
         if (tid == 0) ctl3(&s);
@@ -326,7 +367,7 @@ __global__ void __launch_bounds__(BP_TPB, BP_MINBLOCKS)
             relax(f.stl, f.r, a.nprecond);
             {   // t = L s_tilde (spread over the grid), then <t, r>, <t, t> in the canonical order
                 BP_FOR_CELLS(g, c, { f.t[c] = apply_cell_ortho<ND>(g, m, f.stl, i, j, k, c, true); })
-                grid.sync();
+                gsync();
                 double a0 = 0.0, a1 = 0.0;
                 double tv[BP_U], rr[BP_U];
                 BP_CANON_CELLS(g, cb, c, u, BP_U, { tv[u] = f.t[c]; rr[u] = f.r[c]; }, {
@@ -343,7 +384,7 @@ __global__ void __launch_bounds__(BP_TPB, BP_MINBLOCKS)
                     f.e[c] = f.e[c] + om * f.stl[c];
                     f.r[c] = f.r[c] + no * f.t[c];
                 })
-                grid.sync();
+                gsync();
                 norm_and_rho();
             }
         }
@@ -358,7 +399,7 @@ __global__ void __launch_bounds__(BP_TPB, BP_MINBLOCKS)
                 })
             }
             if (restarts == a.numRestarts) break;
-            grid.sync();
+            gsync();
             true_residual();
             if (tid == 0) {
                 s.nrm[0] = norm_finish(s.red[0], kind);

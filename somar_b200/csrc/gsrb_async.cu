@@ -402,7 +402,24 @@ bool launch_gsrb_async(Ctx& cx, const Geom& g, const Metric& m, double* phiOut, 
         }
         attr = true;
     }
-    const int kc = (g.n[2] > 64) ? 64 : g.n[2];
+    // z-chunking: one CTA per SM, so the launch runs in ceil(CTAs / SMs) waves of (kc + ~4 pipeline-fill planes) steps.
+    // With few tiles (a rank's slab at 8 GPUs: 180 tiles on 148 SMs) one chunk per tile wastes most of the second
+    // wave; pick the chunk count that minimises waves x steps.  Many tiles: this keeps 64-plane chunks.
+    const int tiles = ((g.n[0] + CX - 1) / CX) * ((g.n[1] + CY - 1) / CY);
+    int kc = g.n[2];
+    {
+        long long best = -1;
+        const int maxChunks = g.n[2] >= 8 ? g.n[2] / 4 : 1;
+        for (int ch = 1; ch <= maxChunks; ++ch) {
+            const int len = (g.n[2] + ch - 1) / ch;
+            if (len > 64) continue;
+            const int nch = (g.n[2] + len - 1) / len;
+            const long long waves = ((long long)tiles * nch + cx.sms - 1) / cx.sms;
+            const long long cost = waves * (len + 4);
+            if (best < 0 || cost < best) { best = cost; kc = len; }
+        }
+        if (best < 0) kc = 64;
+    }
     dim3 grid((g.n[0] + CX - 1) / CX, (g.n[1] + CY - 1) / CY, (g.n[2] + kc - 1) / kc);
     k_gsrb_async<<<grid, NTHREADS, SMEM_BYTES, cx.stream>>>(g, m, phiOut, phiIn, rhs, kc);
     cx.launches++;

@@ -40,6 +40,29 @@ def test_one_vcycle_matches_oracle(case, mode, bottom_imax, oracle_lib, somar):
         tol = 1e-6 if pb.is_diagonal else 1e-4
     assert rel_err(fe.get(), want) <= tol, rel_err(fe.get(), want)
 
+@pytest.mark.parametrize("numMG", [2, -1, -2])
+@pytest.mark.parametrize("case", [
+    dict(n=(32, 32, 32), map_name="stretched", aniso=4.0, parts=(1, 2, 1)),
+    dict(n=(32, 32, 16), map_name="terrain", aniso=8.0, map_params={"amp": 0.1}),
+])
+def test_w_and_f_cycles_match_oracle(case, numMG, oracle_lib, somar):
+    """MappedMultiGrid::cycle with m_cycle = numMG: > 1 W-cycle (:631-633), < 0 F-cycle (:578-619).  bottom_imax = 0
+    keeps the Krylov bottom out, so the comparison is as tight as for the V-cycle."""
+    pb = Problem(**case)
+    kw = dict(SOLVE, numMG=numMG, bottom_imax=0)
+    orc, lev = pb.oracle(oracle_lib, **kw), pb.level(somar, **kw)
+    r = pb.rhs()
+    e0 = np.zeros_like(r)
+    fe, fr = lev.field(0, e0), lev.field(0, r)
+    lev.mg_cycle(fe, fr)
+    want = orc.cycle(e0, r)
+    assert rel_err(fe.get(), want) <= (1e-12 if pb.is_diagonal else 1e-11), rel_err(fe.get(), want)
+    # and it is a different cycle from the V-cycle
+    lev1 = pb.level(somar, **dict(SOLVE, numMG=1, bottom_imax=0))
+    f1 = lev1.field(0, e0)
+    lev1.mg_cycle(f1, lev1.field(0, r))
+    assert rel_err(f1.get(), want) > 1e-6
+
 
 @pytest.mark.parametrize("case,mode", [
     (dict(n=(64, 64, 16), map_name="stretched", aniso=16.0), 1),
