@@ -267,6 +267,7 @@ int somar_level_relax_kernel(const SomarLevel* L, int depth, int mode, int* id) 
               : (L->use_fused && gsrb_fused_usable(dp.g, dp.m))     ? 1
                                                                     : (dp.m.diagonal ? 0 : 2);
     else if (mode == SOMAR_RELAX_LINE_GSRB) *id = 3;
+    else if (mode == SOMAR_RELAX_LOOSE_GSRB) *id = dp.m.diagonal ? 6 : -1;
     else if (mode == SOMAR_RELAX_JACOBI) *id = 4;
     else *id = -1;
     return SOMAR_OK;

@@ -21,6 +21,10 @@ void launch_apply(Ctx& cx, const Geom& g, const Metric& m, double* out, const do
                   int mode, bool homog);
 // one colour pass of point Gauss-Seidel (pass 0 = red: (i+j+k) even in global indices)
 void launch_gsrb(Ctx& cx, const Geom& g, const Metric& m, double* phi, const double* rhs, int pass);
+// LooseGSRB stages (diagonal metric): stage 0 = box interiors, stage 1 = box rims (boundary-kernel statements;
+// pass 1 reads cross-box neighbours from `snap`)
+void launch_gsrb_loose(Ctx& cx, const Geom& g, const Metric& m, double* phi, const double* snap, const double* rhs,
+                       int pass, int stage);
 // one whole iteration (red then black) in one sweep, out of place; see gsrb_fused.cu
 bool gsrb_fused_usable(const Geom& g, const Metric& m);
 void launch_gsrb_fused(Ctx& cx, const Geom& g, const Metric& m, double* phiOut, const double* phiIn,

@@ -355,8 +355,21 @@ int op_relax(SomarLevel* L, int depth, SomarField* phi, const SomarField* rhs, i
             launch_jacobi(L->cx, dp.g, dp.m, phi->p, dp.tmp);
         } else if (mode == SOMAR_RELAX_NONE) {
             return SOMAR_OK;
+        } else if (mode == SOMAR_RELAX_LOOSE_GSRB) {   // LooseGSRB::relax, GSRB.cpp:104-141 (see k_gsrb_loose)
+            if (!dp.m.diagonal) {
+                set_error("relax: LooseGSRB with a full metric is not built (its extrap copy carries box-interface ghosts "
+                          "of the previous iteration)");
+                return SOMAR_ERR_ARG;
+            }
+            if (L->box_size[0] == 0) { set_error("relax: LooseGSRB needs a uniform box tiling"); return SOMAR_ERR_LAYOUT; }
+            launch_gsrb_loose(L->cx, dp.g, dp.m, phi->p, nullptr, rhs->p, 0, 0);
+            launch_gsrb_loose(L->cx, dp.g, dp.m, phi->p, nullptr, rhs->p, 1, 0);
+            if ((rc = exchange(L, depth, phi->p, 1)) != SOMAR_OK) return rc;      // exchangeEnd
+            launch_copy(L->cx, dp.g, dp.tmp, phi->p);                               // what the box ghosts hold from here on
+            launch_gsrb_loose(L->cx, dp.g, dp.m, phi->p, dp.tmp, rhs->p, 0, 1);
+            launch_gsrb_loose(L->cx, dp.g, dp.m, phi->p, dp.tmp, rhs->p, 1, 1);
         } else {
-            set_error("relax: relax_mode 2 (LooseGSRB) is not implemented on the device path");
+            set_error("relax: unknown relax_mode");
             return SOMAR_ERR_ARG;
         }
     }

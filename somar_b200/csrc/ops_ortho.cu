@@ -161,6 +161,63 @@ void launch_gsrb(Ctx& cx, const Geom& g, const Metric& m, double* phi, const dou
     cx.launches++;
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// LooseGSRB::relax (GSRB.cpp:104-141), diagonal metric: one exchange per iteration instead of two.  Per box the
+// reference relaxes the interior grow(box,-1) red then black with the interior kernel, finishes the exchange it began
+// before, and then relaxes the 1-cell box rim red then black with the BOUNDARY kernel (boundaryGSRB(..., true),
+// GSRBBOUNDARYITER*ORTHO).  The ghosts are not refreshed between the two rim passes, so a rim black cell reads the
+// PRE-ITERATION value of red cells that belong to another box.  In the brick there are no per-box ghosts: stage 1
+// reads those cross-box neighbours from `snap`, a copy of phi taken after the interior stages (the rim is still
+// untouched then), everything else from phi in place.  stage 0 = interior, stage 1 = rim.
+// ---------------------------------------------------------------------------------------------------------
+template <int ND>
+__global__ void __launch_bounds__(BX* BY) k_gsrb_loose(const Geom g, const Metric m, double* __restrict__ phi,
+                                                        const double* __restrict__ snap,
+                                                        const double* __restrict__ rhs, int pass, int stage, int kz) {
+    const int t = blockIdx.x * BX + threadIdx.x;
+    const int j = blockIdx.y * BY + threadIdx.y;
+    if (j >= g.n[1]) return;
+    const int k0 = blockIdx.z * kz;
+    const int k1 = min(k0 + kz, g.n[2]);
+    for (int k = k0; k < k1; ++k) {
+        const int par = (g.g0[0] + g.g0[1] + j + ((ND > 2) ? (g.g0[2] + k) : 0) + pass) & 1;
+        const int i = 2 * t + par;
+        if (i >= g.n[0]) continue;
+        const long long c = g.idx(i, j, k);
+        const BoxOf b = box_of<ND>(g, i, j, k);
+        if (stage == 0) {
+            if (!b.rim) phi[c] = gsrb_cell_ortho<ND>(g, m, phi, rhs, i, j, k, c);
+            continue;
+        }
+        if (!b.rim) continue;
+        const int q[3] = {i, j, k};
+        const long long st[3] = {1, g.sy, g.sz};
+        double nb[3][2] = {{0.0, 0.0}, {0.0, 0.0}, {0.0, 0.0}};
+#pragma unroll
+        for (int d = 0; d < ND; ++d) {
+#pragma unroll
+            for (int s = 0; s < 2; ++s) {
+                const bool atSide = q[d] == (s ? b.hi[d] : b.lo[d]);
+                const bool cross = atSide && (b.st[d][s] == SIDE_INTERNAL || b.st[d][s] == BC_PERIODIC);
+                const double* __restrict__ src = (pass == 1 && cross) ? snap : phi;
+                nb[d][s] = src[s ? c + st[d] : c - st[d]];
+            }
+        }
+        const GsrbCoef qc = gsrb_load_coef<ND>(g, m, rhs, c);
+        phi[c] = gsrb_update_vals<ND>(g, qc, i, j, k, phi[c], nb, false, true);
+    }
+}
+
+void launch_gsrb_loose(Ctx& cx, const Geom& g, const Metric& m, double* phi, const double* snap, const double* rhs,
+                       int pass, int stage) {
+    const int kz = (g.n[2] >= 64) ? 8 : 1;
+    const int half = (g.n[0] + 1) / 2;
+    dim3 grid((half + BX - 1) / BX, (g.n[1] + BY - 1) / BY, (g.n[2] + kz - 1) / kz), block(BX, BY);
+    if (g.nd == 3) k_gsrb_loose<3><<<grid, block, 0, cx.stream>>>(g, m, phi, snap, rhs, pass, stage, kz);
+    else k_gsrb_loose<2><<<grid, block, 0, cx.stream>>>(g, m, phi, snap, rhs, pass, stage, kz);
+    cx.launches++;
+}
+
 // full metric: out of place (cross terms read same-colour cells of the pre-pass state = the `extrap` snapshot,
 // RelaxationMethod.cpp:411).  Every cell is written: updated colour gets the new value, the other a copy.
 template <int ND>

@@ -152,13 +152,15 @@ __device__ __forceinline__ GsrbCoef gsrb_load_coef(const Geom& g, const Metric& 
 // statements of FILLMAPPEDLAPDIAG (k_lapdiag) -- the same bits, one array less to stream (8 of 64 B/cell).
 template <int ND, bool LAPFLY = false>
 __device__ __forceinline__ double gsrb_update_vals(const Geom& g, const GsrbCoef& q, int i, int j, int k, double pc,
-                                                   const double (&nb)[3][2], bool knownInterior = false) {
+                                                   const double (&nb)[3][2], bool knownInterior = false,
+                                                   bool forceRim = false) {
     const double sc0 = g.rdx2[0];
     const double sc1 = g.rdx2[1];
     const double sc2 = (ND > 2) ? g.rdx2[2] : 0.0;
     const double ji = q.ji;
     // knownInterior: the caller has established (block-uniformly) that the cell is not on the domain rim
-    if (knownInterior || !on_domain_rim<ND>(g, i, j, k)) {
+    // forceRim: use the boundary kernel's statements even off the domain rim (LooseGSRB relaxes every BOX rim with them)
+    if (!forceRim && (knownInterior || !on_domain_rim<ND>(g, i, j, k))) {
         const double JDxx = sc0 * (q.ghi[0] * nb[0][1] + q.glo[0] * nb[0][0]);
         const double JDyy = sc1 * (q.ghi[1] * nb[1][1] + q.glo[1] * nb[1][0]);
         double lphi;

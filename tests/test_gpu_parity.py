@@ -99,6 +99,46 @@ def test_relax(name, mode, oracle_lib, somar):
             # two sweeps amplify rounding differences of the cross terms a little
             assert rel_err(fphi.get(), want) <= 10 * TOL, rel_err(fphi.get(), want)
 
+LOOSE_CASES = {
+    "boxes_y4": dict(n=(32, 32, 16), map_name="stretched", aniso=4.0, parts=(1, 4, 1)),
+    "boxes_xy": dict(n=(32, 32, 16), map_name="stretched", aniso=4.0, parts=(2, 2, 1)),
+    "boxes_xyz": dict(n=(32, 32, 16), map_name="stretched", aniso=2.0, parts=(2, 2, 2)),
+    "periodic_y_boxes": dict(n=(32, 32, 16), map_name="stretched", aniso=2.0, periodic=(0, 1, 0), parts=(1, 2, 1)),
+    "periodic_xy_onebox": dict(n=(16, 16, 16), map_name="cartesian", aniso=1.0, periodic=(1, 1, 0)),
+    "dirichlet_top_boxes": dict(n=(16, 32, 16), map_name="stretched", aniso=4.0, bc_type=[0, 0, 0, 0, 0, 1],
+                                bc_value=[0, 0, 0, 0, 0, 0.5], parts=(1, 2, 1)),
+    "helmholtz_boxes": dict(n=(16, 32, 16), map_name="stretched", aniso=4.0, alpha=1.0, beta=-0.05, parts=(1, 2, 1)),
+    "stretched2d_boxes": dict(n=(32, 16, 1), dim=2, map_name="stretched", aniso=4.0, parts=(2, 2, 1)),
+}
+
+
+@pytest.mark.parametrize("name", list(LOOSE_CASES))
+def test_relax_loose_gsrb(name, oracle_lib, somar):
+    """LooseGSRB (relax mode 2, GSRB.cpp:104-141): box interiors, then box rims with stale cross-box ghosts.  The
+    result depends on the box layout, which is the point of the test; bit-exact for diagonal metrics."""
+    pb = Problem(**LOOSE_CASES[name])
+    orc, lev = pb.oracle(oracle_lib, relaxMode=2), pb.level(somar, relaxMode=2)
+    assert lev.relax_kernel(0, 2) == "k_gsrb_loose"
+    for d in range(lev.ndepths):
+        shp = orc.shape(d)
+        phi, rhs = pb.rand(shp), pb.rand(shp)
+        fphi, frhs = lev.field(d, phi), lev.field(d, rhs)
+        lev.relax(fphi, frhs, iters=3)
+        want = orc.relax(phi, rhs, iters=3, depth=d)
+        _check(fphi.get(), want, True, f"LooseGSRB depth {d}")
+    # it is not LevelGSRB in disguise: with more than one box (or a periodic side) the two smoothers differ
+    phi, rhs = pb.rand(orc.shape(0)), pb.rand(orc.shape(0))
+    lvl = pb.oracle(oracle_lib, relaxMode=1).relax(phi, rhs, iters=1)
+    assert not np.array_equal(lvl, orc.relax(phi, rhs, iters=1))
+
+
+def test_relax_loose_gsrb_full_metric_is_rejected(somar):
+    pb = Problem(n=(16, 16, 8), map_name="terrain", aniso=4.0)
+    lev = pb.level(somar, relaxMode=2)
+    a, b = lev.field(0), lev.field(0)
+    with pytest.raises(somar.SomarError):
+        lev.relax(a, b, 1)
+
 
 @pytest.mark.parametrize("name", list(CASES))
 def test_restrict_and_prolong(name, oracle_lib, somar):

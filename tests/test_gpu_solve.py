@@ -70,6 +70,7 @@ def test_w_and_f_cycles_match_oracle(case, numMG, oracle_lib, somar):
     (dict(n=(48, 32, 16), map_name="stretched", aniso=4.0, periodic=(0, 1, 0)), 1),
     (dict(n=(64, 32, 1), dim=2, map_name="stretched", aniso=4.0), 1),
     (dict(n=(32, 32, 16), map_name="terrain", aniso=8.0, map_params={"amp": 0.1}), 3),
+    (dict(n=(32, 32, 32), map_name="stretched", aniso=4.0, parts=(1, 2, 1)), 2),      # LooseGSRB, two boxes
 ])
 def test_solve_history_matches_oracle(case, mode, oracle_lib, somar):
     pb = Problem(**case)
