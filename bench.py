@@ -320,7 +320,10 @@ def run_ours(a):
                 "phase_ms_per_solve": {n: v["ms"] / a.steps for n, v in prof.items()}}),
             "roofline": {"bound": "hbm", "kernel": kdesc, "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                         "alg_bytes_per_launch": alg_bytes, "avg_launch_ms": avg_ms, "launches_timed": k["count"]},
+                         "alg_bytes_per_launch": alg_bytes, "avg_launch_ms": avg_ms, "launches_timed": k["count"],
+                         # the same launch time against the DRAM bytes ncu saw (profiles/traffic.json): the fused sweep
+                         # moves fewer bytes than the SURVEY 8(d) model charges, so `frac` can exceed 1; this one cannot
+                         "frac_of_peak_by_dram_traffic": (traffic / (avg_ms * 1e-3) / 1e9 / peak) if (traffic and avg_ms > 0) else None},
             "clocks": clk, "gpu_launches": int(launches), "pressure_solve_ms": ms / a.steps}
     if e2e:
         line["e2e"] = e2e
