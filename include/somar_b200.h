@@ -197,7 +197,7 @@ int somar_mac_divergence(SomarLevel* lev, SomarField* div, const SomarField* fx,
                          const SomarField* fz, double divide_by);
 int somar_mac_apply_correction(SomarLevel* lev, SomarField* vx, SomarField* vy, SomarField* vz, SomarField* phi, double dt);
 
-/* ---- leptic-solver sweeps (SURVEY 8(a) LevelLepticSolver row; the leptic iteration itself is host logic not built yet) --
+/* ---- leptic-solver sweeps (SURVEY 8(a) LevelLepticSolver row; the iteration that drives them is somar_leptic_solve below) --
  * "Flat" arguments are depth-0 fields whose vertical index 0 holds a horizontal array (the reference's VertShifter,
  * LevelLepticSolver.cpp:1213-1226).  BC codes are the reference's BCType values: 0 Neum, 1 Diri, 3 CF.
  * somar_leptic_vertical_solve:  per column, d_z (J g^zz d_z phi) = rhs with homogeneous vertical BCs; Neumann boundary
@@ -216,6 +216,47 @@ int somar_leptic_vertical_excess(SomarLevel* lev, SomarField* excess, const Soma
                                  const SomarField* bdry_hi);
 int somar_leptic_add_extrusion(SomarLevel* lev, SomarField* dest, const SomarField* flat_src);
 int somar_leptic_accum_div(SomarLevel* lev, SomarField* flat_rhs, const SomarField* flat_flux, int fc_dir, double dx_scale);
+
+/* ---- the leptic iteration: LevelLepticSolver (src/calculus/LepticSolver/LevelLepticSolver.cpp) ------------------------
+ * somar_leptic_create  = LevelLepticSolver::define (:147-437) on a finalized level (the LepticOperator handed to define):
+ *      builds the "vertical" level (same J g^{ij}, Jinv = 1, :197-205; it carries m_opPtr and the 3-D multigrid of the
+ *      fall-back, :219-300, with the `full` parameters) and, when both vertical sides are Neumann
+ *      (gatherVerticalBCTypes, :1522-1644), the flattened "horizontal" level with vertically averaged J g^{ab}
+ *      (LevelGeometry::createVertAvgFCJgupPtr, src/geometry/LevelGeometryBasics.cpp:499-571), zero-Neumann BCs (:363-368)
+ *      and the `horiz` multigrid parameters.  Everything is built on the device from the level's own metric.
+ * somar_leptic_solve   = LevelLepticSolver::solve (:646-956): J*residual to the vertical problem, then per order the
+ *      excess bookkeeping, the batched vertical solves, the horizontal right-hand side (computeHorizRHS, :981-1097) and
+ *      multigrid solve, the new residual, the multigrid fall-back at the last order when the iteration hangs, and
+ *      phi += sum of corrections.  `homogeneous` is setHomogeneous (:444).
+ * Scope: one level without a coarser one, diagonal metric, one rank, vertical sides Neumann or Dirichlet; with a
+ * horizontal solve the level must be 3-D with non-periodic horizontal directions (the reference leaves the boundary
+ * faces of a periodic direction unset in computeHorizRHS).  Anything else is an error, never a CPU path. */
+typedef struct SomarLepticParams {
+    int max_order;             /* setParameters (:524-541); defaults setDefaultParameters (:463-514) */
+    double eps, hang;
+    int norm_type;
+    double horiz_rhs_tol;
+    SomarSolverParams horiz;   /* setHorizMGParameters + setHorizBottomParameters */
+    SomarSolverParams full;    /* setFullMGParameters + setFullBottomParameters */
+} SomarLepticParams;
+typedef struct SomarLepticStats {
+    int orders;                /* O(eps^n) steps taken */
+    int exit_status;           /* LevelLepticSolver::ExitStatus (LevelLepticSolver.H:156-165): -1 NONE, 0 CONVERGE, 1 ITER,
+                                  2 HANG, 3 DIVERGE, 4 KABOOM */
+    int horiz_solves, krylov_used;
+    int horiz_iters_total;     /* V-cycles of the horizontal solves */
+    int num_res_norms;         /* m_resNorms: [0] initial, then one per order */
+    double res_norms[16];
+    double solve_ms;           /* device time (CUDA events on the vertical level's stream, host-synchronised) */
+    long long launches;        /* kernels launched on the three levels during the solve */
+} SomarLepticStats;
+typedef struct SomarLeptic SomarLeptic;
+int somar_leptic_default_params(SomarLepticParams* p);
+int somar_leptic_create(SomarLevel* lev, const SomarLepticParams* params, SomarLeptic** out);
+int somar_leptic_destroy(SomarLeptic* s);
+int somar_leptic_solve(SomarLeptic* s, SomarField* phi, const SomarField* rhs, int homogeneous, SomarLepticStats* stats);
+/* The derived levels (tests, diagnostics): which = 0 vertical, 1 horizontal (NULL when no horizontal solve is needed). */
+int somar_leptic_level(SomarLeptic* s, int which, SomarLevel** out);
 
 /* ---- advection: the PPM / corner-transport-upwind scalar predictor (SURVEY 8(a) predictScalar row, 8(f)-3) -----------
  * MappedAdvectionUtil::predictScalar, src/advection/AdvectUtil.cpp:520-933 (PPMNormalPred :1158, PPMFaceValues :1246,

@@ -311,4 +311,56 @@ private:
     PressureSolver& solver_;
 };
 
+// LevelLepticSolver (src/calculus/LepticSolver/LevelLepticSolver.H:40-347): the LinearSolver<LevelData<FArrayBox>> built
+// on a LepticOperator.  define() takes the level that plays the operator's part (its metric, BCs and boxes are what
+// LepticOperator::getFCJgup/getCCJinv/getBCs/smallestGridSize hand over, LepticOperator.H:33-44); the parameter setters
+// mirror setParameters / setHorizMGParameters / setHorizBottomParameters / setFullMGParameters /
+// setFullBottomParameters (LevelLepticSolver.cpp:524-640) and must be called before define, as in the reference.
+class LevelLepticSolver {
+public:
+    LevelLepticSolver() { check(somar_leptic_default_params(&prm_), "LevelLepticSolver"); }
+    ~LevelLepticSolver() { undefine(); }
+    LevelLepticSolver(const LevelLepticSolver&) = delete;
+    LevelLepticSolver& operator=(const LevelLepticSolver&) = delete;
+
+    void setParameters(int maxOrder, double eps, double hang, int normType, double horizRhsTol) {
+        prm_.max_order = maxOrder; prm_.eps = eps; prm_.hang = hang; prm_.norm_type = normType; prm_.horiz_rhs_tol = horizRhsTol;
+    }
+    SomarSolverParams& horizParameters() { return prm_.horiz; }   // multigrid + bottom solver of the flattened problem
+    SomarSolverParams& fullParameters() { return prm_.full; }     // multigrid + bottom solver of the 3-D fall-back
+    void setHomogeneous(bool homogeneous) { homogeneous_ = homogeneous; }
+
+    void define(Level& op, bool homogeneous = false) {
+        undefine();
+        homogeneous_ = homogeneous;
+        check(somar_leptic_create(op.handle(), &prm_, &h_), "LevelLepticSolver::define");
+    }
+    void undefine() {
+        if (h_) somar_leptic_destroy(h_);
+        h_ = nullptr;
+    }
+    bool isDefined() const { return h_ != nullptr; }
+
+    // solve: phi += the leptic corrections for L[phi] = rhs.  Like the reference, running out of orders, hanging or
+    // diverging is a status, not an error.
+    SomarLepticStats solve(Field& phi, const Field& rhs) {
+        if (!h_) throw Error(SOMAR_ERR_ARG, "LevelLepticSolver::solve before define");
+        check(somar_leptic_solve(h_, phi.handle(), rhs.handle(), homogeneous_, &stats_), "LevelLepticSolver::solve");
+        return stats_;
+    }
+    int exitStatusInt() const { return stats_.exit_status; }
+    const char* exitStatusStr() const {
+        static const char* names[] = {"NONE", "CONVERGE", "ITER", "HANG", "DIVERGE", "KABOOM"};
+        const int s = stats_.exit_status;
+        return (s >= -1 && s <= 4) ? names[s + 1] : "UNKNOWN!";
+    }
+    std::vector<double> resNorms() const { return std::vector<double>(stats_.res_norms, stats_.res_norms + stats_.num_res_norms); }
+
+private:
+    SomarLepticParams prm_{};
+    SomarLepticStats stats_{0, -1, 0, 0, 0, 0, {0.0}, 0.0, 0};
+    SomarLeptic* h_ = nullptr;
+    bool homogeneous_ = false;
+};
+
 }  // namespace somar_b200

@@ -34,6 +34,8 @@ SYMBOLS = [
     "somar_mac_apply_correction", "somar_project", "somar_leptic_vertical_solve", "somar_leptic_vert_integral",
     "somar_leptic_vertical_excess", "somar_leptic_add_extrusion", "somar_leptic_accum_div",
     "somar_advect_predict_scalar", "somar_advect_update",
+    "somar_leptic_default_params", "somar_leptic_create", "somar_leptic_destroy", "somar_leptic_solve",
+    "somar_leptic_level",
 ]
 
 
@@ -62,6 +64,17 @@ class SolveStats(C.Structure):
 class AdvectParams(C.Structure):
     _fields_ = [("normal_pred_order", C.c_int), ("use_limiting", C.c_int), ("use_high_order_limiter", C.c_int),
                 ("use_upwinding", C.c_int), ("return_flux", C.c_int)]
+
+
+class LepticParams(C.Structure):
+    _fields_ = [("max_order", C.c_int), ("eps", C.c_double), ("hang", C.c_double), ("norm_type", C.c_int),
+                ("horiz_rhs_tol", C.c_double), ("horiz", SolverParams), ("full", SolverParams)]
+
+
+class LepticStats(C.Structure):
+    _fields_ = [("orders", C.c_int), ("exit_status", C.c_int), ("horiz_solves", C.c_int), ("krylov_used", C.c_int),
+                ("horiz_iters_total", C.c_int), ("num_res_norms", C.c_int), ("res_norms", C.c_double * 16),
+                ("solve_ms", C.c_double), ("launches", C.c_longlong)]
 
 
 class SomarError(RuntimeError):
@@ -113,6 +126,66 @@ def default_params(**kw) -> SolverParams:
             raise KeyError(k)
         setattr(p, k, v)
     return p
+
+
+def leptic_default_params(horiz=None, full=None, **kw) -> LepticParams:
+    """LevelLepticSolver::setDefaultParameters; `horiz` / `full` are dicts of SolverParams overrides"""
+    p = LepticParams()
+    _ck(lib().somar_leptic_default_params(C.byref(p)))
+    for k, v in kw.items():
+        if not hasattr(p, k):
+            raise KeyError(k)
+        setattr(p, k, v)
+    for sub, d in ((p.horiz, horiz), (p.full, full)):
+        for k, v in (d or {}).items():
+            if not hasattr(sub, k):
+                raise KeyError(k)
+            setattr(sub, k, v)
+    return p
+
+
+class LepticSolver:
+    """LevelLepticSolver (define + solve) on a finalized Level: somar_leptic_create / _solve / _destroy"""
+
+    def __init__(self, level: "Level", params: Optional[LepticParams] = None):
+        self.level = level
+        self.params = params if params is not None else leptic_default_params()
+        self.h = None
+        h = C.c_void_p()
+        _ck(lib().somar_leptic_create(level.h, C.byref(self.params), C.byref(h)))
+        self.h = h
+
+    def solve(self, phi: "Field", rhs: "Field", homogeneous=False) -> dict:
+        st = LepticStats()
+        _ck(lib().somar_leptic_solve(self.h, phi.h, rhs.h, int(homogeneous), C.byref(st)))
+        return {"orders": st.orders, "exit_status": st.exit_status, "horiz_solves": st.horiz_solves,
+                "krylov_used": bool(st.krylov_used), "horiz_iters_total": st.horiz_iters_total,
+                "res_norms": [st.res_norms[i] for i in range(st.num_res_norms)], "solve_ms": st.solve_ms,
+                "launches": st.launches}
+
+    def horiz_metric(self):
+        """(J g^00, J g^11) of the flattened level, as (ny, nx+1) and (ny+1, nx) arrays (None without one)"""
+        hv = C.c_void_p()
+        _ck(lib().somar_leptic_level(self.h, 1, C.byref(hv)))
+        if not hv.value:
+            return None
+        nx, ny = self.level.n[0], self.level.n[1]
+        j0 = np.zeros((2, ny, nx + 1))
+        j1 = np.zeros((2, ny + 1, nx))
+        _ck(lib().somar_level_get_metric(hv, 0, j0.ctypes.data_as(C.c_void_p), j1.ctypes.data_as(C.c_void_p), None, None,
+                                         None))
+        return j0[0], j1[1]
+
+    def destroy(self):
+        if getattr(self, "h", None):
+            lib().somar_leptic_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.destroy()
+        except Exception:
+            pass
 
 
 def comm_unique_id() -> bytes:

@@ -407,7 +407,13 @@ int launch_bottom_persistent(SomarLevel* L, const Geom& g_, const Metric& m_, do
     double* part = dv->part;
     int* itersAccum = &dv->iters;
     int cb = row_blocks(g, L->cx.sms);   // the blocks k_reduce would use: the canonical summation order
-    int nb = persistent_blocks(g, L->bottom_coop_blocks);
+    int cap = L->bottom_coop_blocks;
+    {   // SOMAR_B200_BOTTOM_BPS = blocks per SM of the persistent kernel (fewer blocks: cheaper grid barriers,
+        // more cells per thread); default: everything that is co-resident
+        static const int bps = []() { const char* e = getenv("SOMAR_B200_BOTTOM_BPS"); return e ? atoi(e) : 0; }();
+        if (bps > 0 && bps * L->cx.sms < cap) cap = bps * L->cx.sms;
+    }
+    int nb = persistent_blocks(g, cap);
     if (nb < cb) nb = cb;
     // SOMAR_B200_GBAR=1 swaps cooperative groups' grid.sync() for the two-level counter barrier (tree_barrier).
     // Measured on B200 (headline, 380 BiCGStab iterations per solve): bottom 59.5 ms with it, 55.1 ms without --

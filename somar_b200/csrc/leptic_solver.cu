@@ -1,0 +1,469 @@
+// leptic_solver.cu -- the leptic ITERATION (SURVEY.md 8(a) "LevelLepticSolver" row, 8(f)-2), device-resident:
+//   somar_leptic_create   LevelLepticSolver::define   src/calculus/LepticSolver/LevelLepticSolver.cpp:147-437
+//   somar_leptic_solve    LevelLepticSolver::solve    :646-956
+//       k_horiz_rhs       ::computeHorizRHS           :981-1097  (MAPPEDMACGRADORTHO, DivCurlGradF.ChF:221-262 ->
+//                                                      UNMAPPEDVERTINTEGRAL, SubspaceF.ChF:33-58 -> LEPTICACCUMDIV,
+//                                                      LevelLepticSolverF.ChF:291-331, fused: the face gradients and their
+//                                                      vertical averages are never stored)
+//       k_vert_avg_dense  LevelGeometry::createVertAvgFCJgupPtr  src/geometry/LevelGeometryBasics.cpp:499-571
+//       setZeroAvg        :1665-1709 (k_reduce kind 5 + k_sub_scalar)
+// The sweeps it sequences (vertical solves, excess, extrusion) are leptic.cu's; the operator, norms and the two
+// multigrid solvers are the library's own (level.cu / solver.cu) on two derived levels:
+//   vert   the level's J g^{ij} with Jinv = 1 (:197-205): residuals/norms of the J-scaled equation and the 3-D multigrid
+//          of the fall-back (:251-300);
+//   horiz  the flattened level with vertically averaged J g^{ab}, Jinv = 1, zero-Neumann sides (:355-407).
+// Flat fields (excess, boundary data, horizontal right-hand side) are SomarFields of the vertical level that own only
+// the planes the flat kernels touch.  Each level has its own stream; the driver is host-sequenced (it reads a norm
+// back every order, as the reference does), so hand-overs between levels are stream synchronisations.
+// Scope: diagonal metric, one rank, one level; see include/somar_b200.h.
+#include "level.hpp"
+#include "cells.cuh"
+#include <cmath>
+#include <cstring>
+#include <utility>
+
+struct SomarLeptic {
+    SomarLevel* orig = nullptr;    // not owned
+    SomarLevel* vert = nullptr;
+    SomarLevel* horiz = nullptr;
+    SomarLepticParams prm;
+    bool doHoriz = false;
+    int vertBC[2] = {0, 0};
+    // vertical level: full fields
+    SomarField *phiTotal = nullptr, *vertPhi = nullptr, *rhsA = nullptr, *rhsB = nullptr;
+    // flat fields (short allocations on the vertical level)
+    SomarField *bdryLo = nullptr, *bdryHi = nullptr, *excess = nullptr, *flatRhs = nullptr, *flatPhi = nullptr;
+    size_t flatDoubles = 0;
+    // original level
+    SomarField* res = nullptr;
+    // horizontal level
+    SomarField *hPhi = nullptr, *hRhs = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+};
+
+namespace somar {
+
+#define QTPB 128
+
+// out = a / b on the valid cells (FArrayBox::divide, LevelLepticSolver.cpp:712)
+__global__ void __launch_bounds__(QTPB) k_div_cells(const Geom g, double* __restrict__ out, const double* __restrict__ a,
+                                                    const double* __restrict__ b, int kz) {
+    const int i = blockIdx.x * QTPB + threadIdx.x;
+    const int j = blockIdx.y;
+    if (i >= g.n[0]) return;
+    const int k0 = blockIdx.z * kz, k1 = min(k0 + kz, g.n[2]);
+    for (int k = k0; k < k1; ++k) {
+        const long long c = g.idx(i, j, k);
+        out[c] = a[c] / b[c];
+    }
+}
+
+// flat y = y + x * a (FArrayBox::plus(src, scale) on a flat holder: BoundaryData::vertPlus, :766,787; :806)
+__global__ void __launch_bounds__(QTPB) k_flat_axpy(const Geom g, double* __restrict__ y, const double* __restrict__ x, double a) {
+    const int i = blockIdx.x * QTPB + threadIdx.x;
+    const int j = blockIdx.y;
+    if (i >= g.n[0]) return;
+    const long long c = g.idx(i, j, 0);
+    y[c] = y[c] + x[c] * a;
+}
+
+// computeHorizRHS, diagonal metric, one thread per column:
+//   F_d(face) = sum_k [ (1/dx_d * J g^{dd}) * (phi(i) - phi(i - e_d)) ] * (1/Nz)   on interior faces, k ascending,
+//             = 0 on domain-boundary faces (the BoundaryData values, zero for a diagonal metric, :1063-1069)
+//   rhs = 0 + (F_0(i+1) - F_0(i)) * (-1/dx_0) + (F_1(j+1) - F_1(j)) * (-1/dx_1)  [+ excess * exScale, :803-808]
+__global__ void __launch_bounds__(QTPB) k_horiz_rhs(const Geom g, double* __restrict__ rhs, const double* __restrict__ phi,
+                                                    const double* __restrict__ jg0, const double* __restrict__ jg1,
+                                                    const double* __restrict__ excess, double exScale, double dzScale) {
+    const int i = blockIdx.x * QTPB + threadIdx.x;
+    const int j = blockIdx.y;
+    if (i >= g.n[0]) return;
+    const int gi = g.g0[0] + i, gj = g.g0[1] + j;
+    const bool xl = gi >= 1, xh = gi + 1 <= g.gn[0] - 1, yl = gj >= 1, yh = gj + 1 <= g.gn[1] - 1;
+    const double rx = g.rdx[0], ry = g.rdx[1];
+    double fxl = 0.0, fxh = 0.0, fyl = 0.0, fyh = 0.0;
+    const long long c0 = g.idx(i, j, 0);
+    const int nz = g.n[2];
+#pragma unroll 2
+    for (int k = 0; k < nz; ++k) {
+        const long long c = c0 + g.sz * k;
+        const double p = phi[c];
+        if (xl) fxl = fxl + (rx * jg0[c]) * (p - phi[c - 1]) * dzScale;
+        if (xh) fxh = fxh + (rx * jg0[c + 1]) * (phi[c + 1] - p) * dzScale;
+        if (yl) fyl = fyl + (ry * jg1[c]) * (p - phi[c - g.sy]) * dzScale;
+        if (yh) fyh = fyh + (ry * jg1[c + g.sy]) * (phi[c + g.sy] - p) * dzScale;
+    }
+    double r = 0.0;
+    r = r + (fxh - fxl) * (-1.0 / g.dx[0]);
+    r = r + (fyh - fyl) * (-1.0 / g.dx[1]);
+    if (excess) r = r + excess[c0] * exScale;
+    rhs[c0] = r;
+}
+
+// dense out(i, j) = 0 + sum_k jg(i, j, k) * scale over (nx + ex) x (ny + ey) faces
+__global__ void __launch_bounds__(QTPB) k_vert_avg_dense(const Geom g, double* __restrict__ out, const double* __restrict__ jg,
+                                                         int ex, int ey, double scale) {
+    const int i = blockIdx.x * QTPB + threadIdx.x;
+    const int j = blockIdx.y;
+    if (i >= g.n[0] + ex || j >= g.n[1] + ey) return;
+    const long long c0 = g.idx(i, j, 0);
+    double s = 0.0;
+    for (int k = 0; k < g.n[2]; ++k) s = s + jg[c0 + g.sz * k] * scale;
+    out[i + (long long)(g.n[0] + ex) * j] = s;
+}
+
+__global__ void k_fill_dense(double* __restrict__ x, long long n, double v) {
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) x[t] = v;
+}
+
+// x = x - a on the valid cells of a 2-D level (FArrayBox::operator-=, :1707)
+__global__ void __launch_bounds__(QTPB) k_sub_scalar(const Geom g, double* __restrict__ x, const double* __restrict__ sum,
+                                                     double count) {
+    const int i = blockIdx.x * QTPB + threadIdx.x;
+    const int j = blockIdx.y;
+    if (i >= g.n[0]) return;
+    const double avg = sum[0] / count;
+    const long long c = g.idx(i, j, 0);
+    x[c] = x[c] - avg;
+}
+
+static inline dim3 plane_grid(const Geom& g, int ex = 0, int ey = 0, int nz = 1) {
+    return dim3((g.n[0] + ex + QTPB - 1) / QTPB, g.n[1] + ey, nz);
+}
+
+static int flat_alloc(SomarLeptic* S, SomarField** out) {
+    SomarField* f = new SomarField{S->vert, 0, nullptr};
+    if (cudaMalloc(&f->p, S->flatDoubles * sizeof(double)) != cudaSuccess) {
+        delete f;
+        set_error("leptic: out of device memory (flat field)");
+        return SOMAR_ERR_CUDA;
+    }
+    *out = f;
+    return SOMAR_OK;
+}
+static inline int flat_zero(SomarLeptic* S, SomarField* f) {
+    SOMAR_CUDA(cudaMemsetAsync(f->p, 0, S->flatDoubles * sizeof(double), S->vert->cx.stream));
+    return SOMAR_OK;
+}
+static void field_free(SomarField* f) {
+    if (!f) return;
+    cudaFree(f->p);
+    delete f;
+}
+static inline int sync(SomarLevel* L) {
+    SOMAR_CUDA(cudaStreamSynchronize(L->cx.stream));
+    return SOMAR_OK;
+}
+static int norm_of(SomarLevel* L, const SomarField* x, int ord, double* out) {
+    int rc = reduce_global(L, x->depth, x->p, nullptr, ord, out);
+    if (rc) return rc;
+    if (ord == 2) *out = std::sqrt(*out);
+    return SOMAR_OK;
+}
+
+}  // namespace somar
+
+using namespace somar;
+
+extern "C" {
+
+int somar_leptic_default_params(SomarLepticParams* p) {
+    if (!p) { set_error("null argument"); return SOMAR_ERR_ARG; }
+    // LevelLepticSolver::setDefaultParameters, LevelLepticSolver.cpp:463-514
+    p->max_order = 4; p->eps = 1.0e-15; p->hang = 1.0e-15; p->norm_type = 0; p->horiz_rhs_tol = 1.0e-14;
+    somar_default_params(&p->horiz);
+    SomarSolverParams& h = p->horiz;
+    h.imin = 5; h.imax = 20; h.num_smooth_down = 4; h.num_smooth_bottom = 4; h.num_smooth_up = 4; h.num_smooth_precond = 2;
+    h.relaxMode = SOMAR_RELAX_LEVEL_GSRB; h.precondMode = 1; h.maxDepth = -1; h.eps = 1.0e-12; h.hang = 1.0e-15;
+    h.normThresh = 1.0e-30; h.numMG = 1;   // "hardcoding this because 1 is all that seems to work" (:565)
+    h.bottom_imax = 80; h.bottom_eps = 1.0e-12; h.bottom_numRestarts = 5; h.bottom_hang = 1.0e-15;
+    somar_default_params(&p->full);
+    SomarSolverParams& f = p->full;
+    f.imin = 5; f.imax = 20; f.num_smooth_down = 4; f.num_smooth_bottom = 4; f.num_smooth_up = 4; f.num_smooth_precond = 4;
+    f.relaxMode = SOMAR_RELAX_LINE_GSRB; f.precondMode = 2; f.maxDepth = -1; f.eps = 1.0e-6; f.hang = 1.0e-15;
+    f.normThresh = 1.0e-30; f.numMG = 1;
+    f.bottom_imax = 80; f.bottom_numRestarts = 5;   // eps / hang of this BiCGStab are never set (:269-274)
+    return SOMAR_OK;
+}
+
+int somar_leptic_destroy(SomarLeptic* S) {
+    if (!S) return SOMAR_OK;
+    if (S->vert) { cudaSetDevice(S->vert->device); cudaStreamSynchronize(S->vert->cx.stream); }
+    if (S->horiz) cudaStreamSynchronize(S->horiz->cx.stream);
+    for (SomarField* f : {S->phiTotal, S->vertPhi, S->rhsA, S->rhsB, S->bdryLo, S->bdryHi, S->excess, S->flatRhs,
+                          S->flatPhi, S->res, S->hPhi, S->hRhs})
+        field_free(f);
+    if (S->ev0) cudaEventDestroy(S->ev0);
+    if (S->ev1) cudaEventDestroy(S->ev1);
+    somar_level_destroy(S->horiz);
+    somar_level_destroy(S->vert);
+    delete S;
+    return SOMAR_OK;
+}
+
+int somar_leptic_create(SomarLevel* L, const SomarLepticParams* prm, SomarLeptic** out) {
+    if (!L || !prm || !out) { set_error("null argument"); return SOMAR_ERR_ARG; }
+    if (!L->finalized) { set_error("leptic: the level is not finalized"); return SOMAR_ERR_ARG; }
+    const SomarLevelDesc& D = L->desc;
+    const int nd = D.dim, vd = nd - 1;
+    if (D.nranks > 1) { set_error("leptic solver: one rank only"); return SOMAR_ERR_ARG; }
+    if (!D.is_diagonal) { set_error("leptic solver: diagonal metrics only (levelVertHorizGradient / MAPPEDMACGRAD not built)"); return SOMAR_ERR_ARG; }
+    if (D.periodic[vd]) { set_error("leptic solver: the vertical direction is periodic (LevelLepticSolver.cpp:1316)"); return SOMAR_ERR_ARG; }
+    if (prm->max_order < 0 || prm->max_order > 14) { set_error("leptic solver: max_order must be in 0..14"); return SOMAR_ERR_ARG; }
+    cudaSetDevice(L->device);
+    SomarLeptic* S = new SomarLeptic;
+    S->orig = L;
+    S->prm = *prm;
+    // gatherVerticalBCTypes (:1522-1644): one box column per (i,j), both ends on the physical boundary
+    for (int s = 0; s < 2; ++s) {
+        S->vertBC[s] = D.bc_type[2 * vd + s];
+        if (S->vertBC[s] != 0 && S->vertBC[s] != 1) {
+            set_error("leptic solver: vertical sides must be Neumann (0) or Dirichlet (1)");
+            delete S;
+            return SOMAR_ERR_ARG;
+        }
+    }
+    S->doHoriz = (S->vertBC[0] == 0 && S->vertBC[1] == 0);
+    if (S->doHoriz && (nd != 3 || D.periodic[0] || D.periodic[1])) {
+        set_error("leptic solver: a horizontal solve needs a 3-D level with non-periodic horizontal directions "
+                  "(computeHorizRHS leaves periodic boundary faces unset, LevelLepticSolver.cpp:997-1001,1064-1069)");
+        delete S;
+        return SOMAR_ERR_ARG;
+    }
+    int rc;
+    auto fail = [&](int code) { somar_leptic_destroy(S); return code; };
+    // ---- vertical level: metric copied, Jinv = 1 (:197-205); multigrid of the fall-back with the `full` parameters
+    {
+        SomarLevelDesc dv = D;
+        dv.alpha = 0.0;
+        dv.beta = 1.0;
+        SomarSolverParams pv = prm->full;
+        pv.bottom_normType = prm->norm_type;   // :274
+        if ((rc = somar_level_create(&dv, &pv, L->device, nullptr, &S->vert))) return fail(rc);
+        Depth& src = L->depths[0];
+        Depth& dst = S->vert->depths[0];
+        if (src.g.total != dst.g.total) { set_error("leptic: vertical level layout differs"); return fail(SOMAR_ERR_ARG); }
+        for (int d = 0; d < nd; ++d)
+            if (cudaMemcpyAsync(dst.jg[d][d], src.jg[d][d], sizeof(double) * src.g.total, cudaMemcpyDeviceToDevice,
+                                S->vert->cx.stream) != cudaSuccess) { set_error("leptic: metric copy failed"); return fail(SOMAR_ERR_CUDA); }
+        if ((rc = sync(L))) return fail(rc);
+        launch_fill(S->vert->cx, dst.g, dst.jinv, 1.0);
+        if ((rc = level_finalize(S->vert))) return fail(rc);
+        if ((rc = sync(S->vert))) return fail(rc);
+    }
+    const Geom& g = S->vert->depths[0].g;
+    S->flatDoubles = (size_t)(g.off0 + g.sz);
+    for (SomarField** f : {&S->phiTotal, &S->vertPhi, &S->rhsA, &S->rhsB})
+        if ((rc = field_alloc(S->vert, 0, f))) return fail(rc);
+    if ((rc = field_alloc(L, 0, &S->res))) return fail(rc);
+    for (SomarField** f : {&S->bdryLo, &S->bdryHi})
+        if ((rc = flat_alloc(S, f)) || (rc = flat_zero(S, *f))) return fail(rc);
+    // ---- horizontal level (:303-434)
+    if (S->doHoriz) {
+        for (SomarField** f : {&S->excess, &S->flatRhs, &S->flatPhi})
+            if ((rc = flat_alloc(S, f)) || (rc = flat_zero(S, *f))) return fail(rc);
+        SomarLevelDesc dh = D;
+        dh.dim = 2;
+        dh.n[2] = 1;
+        dh.periodic[2] = 0;
+        dh.dx[2] = 1.0;
+        dh.alpha = 0.0;
+        dh.beta = 1.0;
+        dh.is_diagonal = 1;
+        for (int s = 0; s < 6; ++s) { dh.bc_type[s] = 0; dh.bc_value[s] = 0.0; }   // EllipticConstNeumBCFluxClass(0,0) (:363-368)
+        // flattened boxes of the level, each footprint once (LepticBoxUtils::FlattenTransform; the reference then
+        // re-balances them, createHorizontalSolverGrids -- the layout only enters through the multigrid schedule)
+        std::vector<int> lo, hi;
+        for (int b = 0; b < D.nboxes; ++b) {
+            const int* bl = &L->box_lo[3 * b];
+            const int* bh = &L->box_hi[3 * b];
+            bool seen = false;
+            for (size_t q = 0; q < lo.size() / 3; ++q)
+                if (lo[3 * q] == bl[0] && lo[3 * q + 1] == bl[1] && hi[3 * q] == bh[0] && hi[3 * q + 1] == bh[1]) seen = true;
+            if (seen) continue;
+            lo.insert(lo.end(), {bl[0], bl[1], 0});
+            hi.insert(hi.end(), {bh[0], bh[1], 0});
+        }
+        dh.nboxes = (int)(lo.size() / 3);
+        dh.box_lo = lo.data();
+        dh.box_hi = hi.data();
+        dh.box_rank = nullptr;
+        SomarSolverParams ph = prm->horiz;
+        ph.bottom_normType = prm->norm_type;   // :387
+        if ((rc = somar_level_create(&dh, &ph, L->device, nullptr, &S->horiz))) return fail(rc);
+        // vertically averaged J g^{00}, J g^{11}: scale = 1 / Nz (LevelGeometryBasics.cpp:545-568)
+        const long long n0 = (long long)(g.n[0] + 1) * g.n[1], n1 = (long long)g.n[0] * (g.n[1] + 1), nc = (long long)g.n[0] * g.n[1];
+        double* dense = nullptr;
+        if (cudaMalloc(&dense, sizeof(double) * (n0 + n1 + nc)) != cudaSuccess) { set_error("leptic: out of device memory"); return fail(SOMAR_ERR_CUDA); }
+        cudaStream_t st = S->vert->cx.stream;
+        const double scale = 1.0 / (double)g.n[2];
+        const Depth& dv = S->vert->depths[0];
+        k_vert_avg_dense<<<plane_grid(g, 1, 0), QTPB, 0, st>>>(g, dense, dv.jg[0][0], 1, 0, scale);
+        k_vert_avg_dense<<<plane_grid(g, 0, 1), QTPB, 0, st>>>(g, dense + n0, dv.jg[1][1], 0, 1, scale);
+        k_fill_dense<<<64, 256, 0, st>>>(dense + n0 + n1, nc, 1.0);   // "because we are solving L[phi] = J*rhs" (:428-430)
+        S->vert->cx.launches += 3;
+        cudaError_t ce = cudaStreamSynchronize(st);
+        if (ce == cudaSuccess) {
+            rc = somar_level_set_metric_device(S->horiz, 1, dense, dense + n0, nullptr, dense + n0 + n1);
+            if (!rc) rc = somar_level_finalize(S->horiz);
+        }
+        cudaFree(dense);
+        if (ce != cudaSuccess) { set_error(std::string("leptic: ") + cudaGetErrorString(ce)); return fail(SOMAR_ERR_CUDA); }
+        if (rc) return fail(rc);
+        if ((rc = field_alloc(S->horiz, 0, &S->hPhi)) || (rc = field_alloc(S->horiz, 0, &S->hRhs))) return fail(rc);
+        launch_fill(S->horiz->cx, S->horiz->depths[0].g, S->hPhi->p, 0.0);
+        launch_fill(S->horiz->cx, S->horiz->depths[0].g, S->hRhs->p, 0.0);
+    }
+    if (cudaEventCreate(&S->ev0) != cudaSuccess || cudaEventCreate(&S->ev1) != cudaSuccess) { set_error("leptic: event"); return fail(SOMAR_ERR_CUDA); }
+    if ((rc = sync(S->vert))) return fail(rc);
+    *out = S;
+    return SOMAR_OK;
+}
+
+int somar_leptic_level(SomarLeptic* S, int which, SomarLevel** out) {
+    if (!S || !out || which < 0 || which > 1) { set_error("leptic_level: bad argument"); return SOMAR_ERR_ARG; }
+    *out = which == 0 ? S->vert : S->horiz;
+    return SOMAR_OK;
+}
+
+int somar_leptic_solve(SomarLeptic* S, SomarField* phi, const SomarField* rhs, int homogeneous, SomarLepticStats* st) {
+    if (!S || !phi || !rhs || !st) { set_error("null argument"); return SOMAR_ERR_ARG; }
+    SomarLevel *L = S->orig, *V = S->vert, *Hz = S->horiz;
+    if (phi->lev != L || rhs->lev != L || phi->depth != 0 || rhs->depth != 0 || phi == rhs) {
+        set_error("leptic solve: phi and rhs must be distinct depth-0 fields of the level handed to somar_leptic_create");
+        return SOMAR_ERR_ARG;
+    }
+    cudaSetDevice(L->device);
+    const SomarLepticParams& P = S->prm;
+    const Geom& g = V->depths[0].g;
+    const Depth& dv = V->depths[0];
+    const int vd = g.nd - 1;
+    const double dz = g.dx[vd];
+    const double H = dz * (double)g.gn[vd];       // LevelGeometry::getDomainLength(SpaceDim-1) (:661-662)
+    const int maxOrder = P.max_order;
+    const int kz = 8;
+    int rc;
+    std::memset(st, 0, sizeof(*st));
+    st->exit_status = -1;
+    const long long launches0 = L->cx.launches + V->cx.launches + (Hz ? Hz->cx.launches : 0);
+    if ((rc = sync(L))) return rc;
+    SOMAR_CUDA(cudaEventRecord(S->ev0, V->cx.stream));
+
+    // J * residual to the vertical grids (:698-716); the bricks of the two levels have the same layout
+    if ((rc = op_apply(L, 0, S->res->p, phi, rhs->p, 1, homogeneous != 0))) return rc;
+    k_div_cells<<<plane_grid(g, 0, 0, (g.n[2] + kz - 1) / kz), QTPB, 0, L->cx.stream>>>(g, S->rhsA->p, S->res->p,
+                                                                                      L->depths[0].jinv, kz);
+    L->cx.launches++;
+    if ((rc = sync(L))) return rc;
+    SomarField *rhsP = S->rhsA, *tmpP = S->rhsB;
+
+    double resNorm = 0.0;
+    if ((rc = norm_of(V, rhsP, P.norm_type, &resNorm))) return rc;
+    st->res_norms[st->num_res_norms++] = resNorm;
+    const double res0 = resNorm;
+    if ((rc = flat_zero(S, S->bdryLo)) || (rc = flat_zero(S, S->bdryHi))) return rc;      // bdryData.setVal(0) (:733)
+    launch_fill(V->cx, g, S->phiTotal->p, 0.0);                                            // :746
+    launch_fill(V->cx, g, S->vertPhi->p, 0.0);
+    bool useExcess = S->doHoriz, useHoriz = S->doHoriz;
+    cudaStream_t vs = V->cx.stream;
+
+    for (int order = 0; order <= maxOrder; ++order) {
+        st->orders = order + 1;
+        if (S->doHoriz) {
+            if (order >= 1) {
+                // levelVertHorizGradient: zero for a diagonal metric (:1122-1125)
+                if ((rc = flat_zero(S, S->bdryLo)) || (rc = flat_zero(S, S->bdryHi))) return rc;
+            }
+            if (order >= 1 && useExcess) {                                                 // vertPlus(excess, 1, Hi) (:766)
+                k_flat_axpy<<<plane_grid(g), QTPB, 0, vs>>>(g, S->bdryHi->p, S->excess->p, 1.0);
+                V->cx.launches++;
+            }
+            if (useExcess) {
+                if ((rc = leptic_vertical_excess(V, S->excess, rhsP, S->bdryLo, S->bdryHi))) return rc;
+                if (order == 1) useExcess = false;
+            }
+            if (order == 0 && useExcess) {                                                 // :786-788
+                k_flat_axpy<<<plane_grid(g), QTPB, 0, vs>>>(g, S->bdryHi->p, S->excess->p, -1.0);
+                V->cx.launches++;
+            }
+        }
+        // vertical problem (:795); dzCrse is only read on coarse-fine sides, which one level does not have
+        if ((rc = leptic_vertical_solve(V, S->vertPhi, rhsP, S->vertBC[0], S->vertBC[1], dz, S->bdryLo, S->bdryHi))) return rc;
+
+        if (useHoriz) {
+            // flatRhs = computeHorizRHS [- excess / H] (:800-808)
+            k_horiz_rhs<<<plane_grid(g), QTPB, 0, vs>>>(g, S->flatRhs->p, S->vertPhi->p, dv.jg[0][0], dv.jg[1][1],
+                                                        useExcess ? S->excess->p : nullptr, -1.0 / H, 1.0 / (double)g.n[2]);
+            V->cx.launches++;
+            // to the horizontal grids (:811-812)
+            const Geom& gh = Hz->depths[0].g;
+            SOMAR_CUDA(cudaMemcpy2DAsync(S->hRhs->p + gh.idx(0, 0, 0), gh.sy * sizeof(double), S->flatRhs->p + g.idx(0, 0, 0),
+                                         g.sy * sizeof(double), g.n[0] * sizeof(double), g.n[1], cudaMemcpyDeviceToDevice, vs));
+            if ((rc = sync(V))) return rc;
+            double hnorm = 0.0;
+            if ((rc = norm_of(Hz, S->hRhs, P.norm_type, &hnorm))) return rc;
+            if (P.horiz_rhs_tol * res0 > hnorm) useHoriz = false;                          // :820-825
+        }
+        if (useHoriz) {
+            // horizontalSolver (:1427-1462) + addHorizontalCorrection (:1489-1515)
+            const Geom& gh = Hz->depths[0].g;
+            SomarSolveStats hs;
+            if ((rc = mg_solve(Hz, S->hPhi, S->hRhs, true, true, &hs))) return rc;
+            st->horiz_iters_total += hs.iters;
+            st->horiz_solves++;
+            // setZeroAvg: the flattened boxes cover the horizontal domain (:410-433)
+            launch_reduce(Hz->cx, gh, S->hPhi->p, nullptr, 5, Hz->d_scal + 5);
+            k_sub_scalar<<<plane_grid(gh), QTPB, 0, Hz->cx.stream>>>(gh, S->hPhi->p, Hz->d_scal + 5, (double)gh.cells());
+            Hz->cx.launches++;
+            SOMAR_CUDA(cudaMemcpy2DAsync(S->flatPhi->p + g.idx(0, 0, 0), g.sy * sizeof(double), S->hPhi->p + gh.idx(0, 0, 0),
+                                         gh.sy * sizeof(double), g.n[0] * sizeof(double), g.n[1], cudaMemcpyDeviceToDevice,
+                                         Hz->cx.stream));
+            if ((rc = sync(Hz))) return rc;
+            if ((rc = leptic_add_extrusion(V, S->vertPhi, S->flatPhi))) return rc;
+        }
+
+        // finalize the order (:837-927)
+        if ((rc = op_apply(V, 0, tmpP->p, S->vertPhi, rhsP->p, 1, true))) return rc;
+        if ((rc = norm_of(V, tmpP, P.norm_type, &resNorm))) return rc;
+        double relResNorm = resNorm / res0;
+        const double prevRel = st->res_norms[st->num_res_norms - 1] / res0;
+        double redu = prevRel - relResNorm;
+        if (redu <= P.hang && order == maxOrder) {
+            // not converging: the 3-D multigrid solver, zero initial guess, homogeneous (:851-875)
+            SomarSolveStats fs;
+            if ((rc = mg_solve(V, S->vertPhi, rhsP, true, true, &fs))) return rc;
+            if ((rc = op_apply(V, 0, tmpP->p, S->vertPhi, rhsP->p, 1, true))) return rc;
+            if ((rc = norm_of(V, tmpP, P.norm_type, &resNorm))) return rc;
+            relResNorm = resNorm / res0;
+            st->krylov_used = 1;
+        }
+        std::swap(rhsP, tmpP);                                                             // :878
+        st->res_norms[st->num_res_norms++] = resNorm;
+        redu = prevRel - relResNorm;
+        if (redu > P.hang || order < maxOrder) {
+            launch_axpy(V->cx, g, S->phiTotal->p, S->vertPhi->p, 1.0);                     // addVerticalCorrection (:885)
+            st->exit_status = (order < maxOrder - 1) ? 0 : 1;
+        } else if (-redu > P.hang) {
+            st->exit_status = (order == 0) ? 4 : 3;
+            break;
+        } else {
+            st->exit_status = (order == 0) ? 4 : 2;
+            break;
+        }
+        useHoriz = false;                                                                  // LevelGeometry::isDiagonal() (:924-926)
+    }
+
+    if ((rc = sync(V))) return rc;
+    if (st->exit_status != 4) {                                                            // :932-939
+        launch_axpy(L->cx, L->depths[0].g, phi->p, S->phiTotal->p, 1.0);
+        if ((rc = sync(L))) return rc;
+    }
+    SOMAR_CUDA(cudaEventRecord(S->ev1, V->cx.stream));
+    SOMAR_CUDA(cudaEventSynchronize(S->ev1));
+    float ms = 0.f;
+    SOMAR_CUDA(cudaEventElapsedTime(&ms, S->ev0, S->ev1));
+    st->solve_ms = ms;
+    st->launches = L->cx.launches + V->cx.launches + (Hz ? Hz->cx.launches : 0) - launches0;
+    return SOMAR_OK;
+}
+
+}  // extern "C"

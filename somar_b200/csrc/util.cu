@@ -83,6 +83,7 @@ __global__ void k_reduce(const Geom g, const double* __restrict__ x, const doubl
         else if (kind == 1) acc += fabs(v);
         else if (kind == 2) acc += v * v;
         else if (kind == 3) acc += v * yv[u];
+        else if (kind == 5) acc += v;                    // plain sum (LevelLepticSolver::setZeroAvg)
         else acc = fmax(acc, v);
     })
     acc = block_red(acc, isMax, ident);

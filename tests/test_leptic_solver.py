@@ -1,0 +1,162 @@
+"""The leptic ITERATION (SURVEY.md 8(a) LevelLepticSolver row): LevelLepticSolver::define + ::solve,
+src/calculus/LepticSolver/LevelLepticSolver.cpp:147-437,646-956.
+
+CPU: the oracle restatement (oracle/leptic_ref.py over the oracle's operator and oracle/leptic.cpp) is pinned to what the
+algorithm promises -- the reference ships no vectors and cannot be built here (PARITY UNPINNED against its output):
+  * Dirichlet top (no horizontal solve): on a thin domain every order cuts the residual norm (the leptic expansion);
+  * Neumann top and bottom: the excess bookkeeping makes every vertical problem solvable, the one horizontal solve of a
+    diagonal metric happens at O(1), the iteration then stalls on the column means and the multigrid fall-back
+    finishes the solve;
+  * the solution it returns satisfies the ORIGINAL equation L phi = rhs (with Jinv), not only the J-scaled one.
+GPU: the device driver (somar_leptic_create / somar_leptic_solve through the C ABI) against the oracle on the same
+inputs: vertically averaged metric bit-exact, residual norm of every order, exit status, solution."""
+import numpy as np
+import pytest
+
+from common import Problem
+
+NEUM, DIRI = 0, 1
+
+CASES = {
+    # name: (Problem kwargs, leptic kwargs)
+    "diri_top": (dict(n=(32, 24, 16), aniso=64.0, bc_type=[0, 0, 0, 0, NEUM, DIRI]), dict()),
+    "diri_bottom_2x2": (dict(n=(32, 32, 16), aniso=48.0, bc_type=[0, 0, 0, 0, DIRI, NEUM], parts=(2, 2, 1)), dict(max_order=3)),
+    "neum_o1": (dict(n=(32, 24, 16), aniso=64.0), dict(max_order=1)),
+    "neum_fallback": (dict(n=(32, 32, 16), aniso=64.0, parts=(2, 1, 1)), dict()),
+}
+
+
+def _oracle_solver(po, pb, **kw):
+    from oracle import leptic_ref as lr
+    prm = lr.LepticParams(**kw)
+    return lr.LevelLepticSolver(po, pb.n, pb.spec.dx, pb.jgup, pb.jinv, boxes=pb.boxes, bc_type=pb.bc_type, params=prm)
+
+
+def _rhs(pb):
+    return pb.rhs()
+
+
+def test_oracle_dirichlet_top_converges_order_by_order(oracle_lib):
+    pk, lk = CASES["diri_top"]
+    pb = Problem(**pk)
+    s = _oracle_solver(oracle_lib, pb, **lk)
+    rhs = _rhs(pb)
+    phi = s.solve(np.zeros_like(rhs), rhs, homogeneous=True)
+    nr = s.res_norms
+    assert len(nr) == 6 and s.horiz is None and s.horiz_solves == 0 and not s.krylov_used
+    assert all(nr[k + 1] < 0.5 * nr[k] for k in range(5)), nr
+    assert s.exit_status == 1                                   # ITER: the last order still converged
+    r = s.orig.residual(phi, rhs, homogeneous=True)
+    assert np.abs(r).max() < 1e-3 * np.abs(rhs).max()
+
+
+def test_oracle_neumann_excess_horizontal_and_fallback(oracle_lib):
+    pk, lk = CASES["neum_fallback"]
+    pb = Problem(**pk)
+    s = _oracle_solver(oracle_lib, pb, **lk)
+    rhs = _rhs(pb)
+    phi = s.solve(np.zeros_like(rhs), rhs, homogeneous=True)
+    nr = s.res_norms
+    assert s.horiz is not None and s.horiz_solves == 1          # diagonal metric: only the O(1) horizontal solve
+    assert nr[2] < 0.1 * nr[0]                                  # O(eps) vertical solve removes the top-layer defect
+    assert s.krylov_used and nr[-1] < 1e-5 * nr[0]              # stalled on the column means -> multigrid fall-back
+    r = s.orig.residual(phi, rhs, homogeneous=True)
+    assert np.abs(r).max() < 1e-5 * np.abs(rhs).max()
+
+
+def test_oracle_vertical_problems_are_solvable(oracle_lib):
+    """after the excess is moved into the upper BC, rhs and boundary fluxes of every column are compatible"""
+    pb = Problem(n=(16, 12, 16), aniso=32.0)
+    rhs = _rhs(pb)
+    rhs_v = rhs / pb.jinv
+    dz = pb.spec.dx[2]
+    lo = np.zeros(16 * 12)
+    hi = np.zeros(16 * 12)
+    ex = oracle_lib.leptic_vertical_excess(rhs_v.reshape(16, -1), lo, hi, dz)
+    hi = hi + ex * -1.0
+    ex2 = oracle_lib.leptic_vertical_excess(rhs_v.reshape(16, -1), lo, hi, dz)
+    assert np.abs(ex2).max() < 1e-12 * max(np.abs(ex).max(), 1.0)
+
+
+def test_oracle_horizontal_metric_is_the_vertical_average(oracle_lib):
+    from oracle import leptic_ref as lr
+    pb = Problem(n=(16, 12, 8), aniso=16.0)
+    avg = lr.vert_avg_faces(pb.jgup[0], 8)
+    assert np.allclose(avg, pb.jgup[0].mean(axis=0), rtol=1e-14, atol=0)
+
+
+def test_oracle_rejects_what_the_device_rejects(oracle_lib):
+    pb = Problem(n=(16, 16, 8), aniso=16.0, periodic=(1, 0, 0))
+    with pytest.raises(ValueError):
+        from oracle import leptic_ref as lr
+        lr.LevelLepticSolver(oracle_lib, pb.n, pb.spec.dx, pb.jgup, pb.jinv, periodic=pb.periodic)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", list(CASES))
+def test_leptic_solve_parity(name, oracle_lib, somar):
+    pk, lk = CASES[name]
+    pb = Problem(**pk)
+    rhs_h = _rhs(pb)
+    so = _oracle_solver(oracle_lib, pb, **lk)
+    want = so.solve(np.zeros_like(rhs_h), rhs_h, homogeneous=True)
+
+    lev = pb.level(somar)
+    ls = somar.LepticSolver(lev, somar.leptic_default_params(**lk))
+    if so.horiz is not None:                                    # createVertAvgFCJgupPtr on the device
+        j0, j1 = ls.horiz_metric()
+        assert np.array_equal(j0, so.hjg[0]) and np.array_equal(j1, so.hjg[1])
+    else:
+        assert ls.horiz_metric() is None
+    phi, rhs = lev.field(0), lev.field(0, rhs_h)
+    st = ls.solve(phi, rhs, homogeneous=True)
+    got = phi.get()
+    assert st["exit_status"] == so.exit_status and st["horiz_solves"] == so.horiz_solves
+    assert st["krylov_used"] == so.krylov_used and len(st["res_norms"]) == len(so.res_norms)
+    n_tight = len(so.res_norms) - (1 if so.krylov_used else 0)  # the fall-back multigrid stops on a tolerance
+    assert np.allclose(st["res_norms"][:n_tight], so.res_norms[:n_tight], rtol=1e-8, atol=0), (st["res_norms"], so.res_norms)
+    scale = np.abs(want).max()
+    if so.krylov_used:
+        assert st["res_norms"][-1] < 1e-5 * st["res_norms"][0]
+        assert np.abs(got - want).max() < 1e-4 * scale
+    elif so.horiz is None:
+        assert np.abs(got - want).max() <= 1e-13 * scale        # vertical solves and residuals only
+    else:
+        assert np.abs(got - want).max() < 1e-9 * scale          # one horizontal multigrid solve to 1e-12
+    # and the answer satisfies the original equation as well as the oracle's does
+    res = lev.field(0)
+    lev.residual(res, phi, rhs, homogeneous=True)
+    r_want = so.orig.residual(want, rhs_h, homogeneous=True)
+    assert np.abs(res.get()).max() <= 1.5 * np.abs(r_want).max() + 1e-12
+    assert st["launches"] > 0
+
+
+@pytest.mark.gpu
+def test_leptic_solve_accumulates_into_phi_and_is_repeatable(oracle_lib, somar):
+    """phi is an initial guess (the solver works on the residual, :698-716): a second call continues from the first"""
+    pk, lk = CASES["diri_top"]
+    pb = Problem(**pk)
+    rhs_h = _rhs(pb)
+    lev = pb.level(somar)
+    ls = somar.LepticSolver(lev, somar.leptic_default_params(max_order=2))
+    phi, rhs = lev.field(0), lev.field(0, rhs_h)
+    st1 = ls.solve(phi, rhs, homogeneous=True)
+    st2 = ls.solve(phi, rhs, homogeneous=True)
+    assert st2["res_norms"][0] == pytest.approx(st1["res_norms"][-1], rel=1e-12)
+    assert st2["res_norms"][-1] < st1["res_norms"][-1]
+    so = _oracle_solver(oracle_lib, pb, max_order=2)
+    w1 = so.solve(np.zeros_like(rhs_h), rhs_h, homogeneous=True)
+    w2 = so.solve(w1, rhs_h, homogeneous=True)
+    assert np.abs(phi.get() - w2).max() <= 1e-13 * np.abs(w2).max()
+
+
+@pytest.mark.gpu
+def test_leptic_create_rejects_out_of_scope_levels(somar):
+    for kw, msg in [(dict(n=(16, 16, 8), aniso=16.0, periodic=(1, 0, 0)), "non-periodic horizontal"),
+                    (dict(n=(16, 16, 8), aniso=16.0, periodic=(0, 0, 1)), "vertical direction is periodic"),
+                    (dict(n=(16, 12, 16), map_name="terrain", aniso=4.0), "diagonal metrics only")]:
+        pb = Problem(**kw)
+        lev = pb.level(somar)
+        with pytest.raises(somar.SomarError, match=msg):
+            somar.LepticSolver(lev)
