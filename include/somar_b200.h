@@ -264,12 +264,13 @@ int somar_leptic_level(SomarLeptic* s, int which, SomarLevel** out);
  * whalf_d (face fields, out): time-centred face states, times adv_vel_d when return_flux (the flux whose
  * somar_mac_divergence gives the advective update, AMRNavierStokesAdvancePPM.cpp:379-620).  w_old, source (may be NULL),
  * old_vel_d (cell-centred components) and cc_j (cell-centred J, LevelGeometry::fill_J) are cell fields, adv_vel_d face
- * fields.  Built for FULLY PERIODIC single-rank levels, normal_pred_order 2 (PPM), use_high_order_limiter 0; anything else
+ * fields.  Built for FULLY PERIODIC single-rank levels, normal_pred_order 2 (PPM), both limiter families; anything else
  * returns SOMAR_ERR_ARG (non-periodic sides need the physics BC holders, which are outside this library). */
 typedef struct SomarAdvectParams {
     int normal_pred_order;        /* ProblemContext normalPredOrder{Vel,Scal}: 2 = PPM */
     int use_limiting;             /* useLimiting{Vel,Scal}: van Leer + PPM limiters */
-    int use_high_order_limiter;   /* useHighOrderLimiter{Vel,Scal}: must be 0 */
+    int use_high_order_limiter;   /* useHighOrderLimiter{Vel,Scal}: FourthInterpFaces + CheckCubicLimiterF
+                                     (MappedGodunovUtilitiesF.ChF:517-566,611-745) instead of van Leer/PPMLimiterF */
     int use_upwinding;            /* useUpwinding{Vel,Scal}: 1 = RiemannSolver, 0 = AvgStates */
     int return_flux;              /* a_returnFlux */
 } SomarAdvectParams;

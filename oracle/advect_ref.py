@@ -3,12 +3,14 @@
 numpy restatement of SOMAR's PPM/CTU scalar predictor (SURVEY.md 8(a) "MappedAdvectionUtil::predictScalar" row,
 8(f)-3) for a FULLY PERIODIC level -- the TaylorGreen configuration of BASELINE.json.  Statement order follows
   MappedAdvectionUtil::predictScalar      src/advection/AdvectUtil.cpp:520-933   (the non-USE_OLD_METHOD version)
-  ::PPMNormalPred / ::PPMFaceValues       AdvectUtil.cpp:1158-1418               (m_useHighOrderLimiter = false branch)
+  ::PPMNormalPred / ::PPMFaceValues       AdvectUtil.cpp:1158-1418               (both m_useHighOrderLimiter branches)
   ::RiemannSolver / ::quasilinearUpdate   AdvectUtil.cpp:944-1037
   MappedGodunovUtilities::vanLeerSlopes   src/advection/MappedGodunovUtilities.cpp:49-102
   ::PPMLimiter / ::PPMNormalPred          MappedGodunovUtilities.cpp:373-500
   SecondSlopeDiffsF, VanLeerLimiterF, PPMLimiterF, PPMFaceValuesF, PPMNormalPredF
                                           src/advection/MappedGodunovUtilitiesF.ChF:35-95,151-186,315-468
+  GETSECONDDIFF, FourthInterpFaces, CheckCubicLimiterF (the extremum-preserving limiter, centre boxes)
+                                          MappedGodunovUtilitiesF.ChF:470-512,517-566,611-745
   RiemannSolver, AvgStates, QuasilinearUpdateF   src/advection/AdvectUtilF.ChF:28-159
 With every direction periodic the lo/hi one-sided boxes of PeriodicLoHiCenter are empty and no a_BCValues method runs,
 so each stage is one whole-domain array statement; numpy evaluates them elementwise in IEEE double without
@@ -16,7 +18,7 @@ contraction, in the Fortran's operation order.  A level of several boxes gives t
 pure stencil on exchanged ghosts), so the restatement works on global arrays with wrapped indices.
 
 NOT covered (the device path rejects them too): non-periodic sides (the physics BC holders scalarRiemannBC /
-scalarSlopeBC), normalPredOrder 0/1 (CTU/PLM), the high-order (Colella-Sekora) limiter.
+scalarSlopeBC), normalPredOrder 0/1 (CTU/PLM).
 PARITY UNPINNED against reference output (the reference cannot be built here and ships no vectors); pinned by
 tests/test_advect.py to exactness properties of the scheme (constants, uniform translation, conservation).
 
@@ -51,20 +53,66 @@ def _ppm_face(X, dX, d):
     return (w_left + w_right) * 0.5
 
 
-def ppm_face_values(W, J, d, use_limiting):
-    """MappedAdvectionUtil::PPMFaceValues: 4th-order face values of J W divided by those of J"""
-    edge_j = _ppm_face(J, van_leer_slopes(J, d, use_limiting), d)
+def _fourth_face(X, d):
+    """FourthInterpFaces, centre box (MappedGodunovUtilitiesF.ChF:559-566): face f between cells f-1 and f"""
+    return (7.0 * (_sh(X, d, -1) + X) - (_sh(X, d, -2) + _sh(X, d, 1))) / 12.0
+
+
+def ppm_face_values(W, J, d, use_limiting, high_order=False):
+    """MappedAdvectionUtil::PPMFaceValues: 4th-order face values of J W divided by those of J
+    (m_useHighOrderLimiter: FourthInterpFaces, AdvectUtil.cpp:1269-1292,1345-1368; else van Leer slopes + PPMFaceValuesF)"""
     JW = W * J
+    if high_order:
+        return _fourth_face(JW, d) / _fourth_face(J, d)
+    edge_j = _ppm_face(J, van_leer_slopes(J, d, use_limiting), d)
     w_face = _ppm_face(JW, van_leer_slopes(JW, d, use_limiting), d)
     return w_face / edge_j
 
 
-def ppm_normal_pred(W, J, vel_d, d, dtbydx, use_limiting):
+def check_cubic_limiter(dm, dp, W, d, limit_c=1.25, c3=0.1, eps=1.0e-12):
+    """MappedGodunovUtilities::PPMLimiter with m_highOrderLimiter (MappedGodunovUtilities.cpp:381-436):
+    GETSECONDDIFF (MappedGodunovUtilitiesF.ChF:470-512) + CheckCubicLimiterF, inner centre box (:611-745)"""
+    d2W = (_sh(W, d, 1) - W) - (W - _sh(W, d, -1))
+    atfcf = (dm + dp) * 6.0
+    big_m = np.abs(dm) > 2.0 * np.abs(dp)
+    big_p = np.abs(dp) > 2.0 * np.abs(dm)
+    dwavg_m = W - _sh(W, d, -2)
+    dwavg_p = _sh(W, d, 2) - W
+    prod_e1 = dm * dp
+    prod_e2 = dwavg_m * dwavg_p
+    extremum = (prod_e1 >= 0.0) | (prod_e2 <= 0.0)
+    d2l, d2c, d2r = _sh(d2W, d, -1), d2W, _sh(d2W, d, 1)
+    sl, sc, sr, sf = (np.copysign(1.0, x) for x in (d2l, d2c, d2r, atfcf))
+    same = (sl == sc) & (sr == sc) & (sf == sc) & (np.abs(atfcf) >= eps)
+    d2lim = sc * np.minimum(np.minimum(np.abs(atfcf), limit_c * np.abs(d2c)),
+                            np.minimum(limit_c * np.abs(d2l), limit_c * np.abs(d2r)))
+    with np.errstate(divide="ignore", invalid="ignore"):
+        rho = np.where(same, d2lim / atfcf, 0.0)
+    d2ll, d2rr = _sh(d2W, d, -2), _sh(d2W, d, 2)
+    d3 = [d2l - d2ll, d2c - d2l, d2r - d2c, d2rr - d2r]
+    d3min = np.minimum(np.minimum(d3[0], d3[1]), np.minimum(d3[2], d3[3]))
+    d3max = np.maximum(np.maximum(d3[0], d3[1]), np.maximum(d3[2], d3[3]))
+    prod_d3 = c3 * np.maximum(np.abs(d3max), np.abs(d3min)) - np.abs(d3max - d3min)
+    apply = extremum & (rho < (1.0 - eps)) & (prod_d3 <= 0.0)
+    case1 = apply & (prod_e1 > 0.0)
+    case2 = apply & ~(prod_e1 > 0.0) & big_m
+    case3 = apply & ~(prod_e1 > 0.0) & ~big_m & big_p
+    new_m = np.where(case1, dm * rho, np.where(case2, dm * rho - 2.0 * dp * (1.0 - rho), dm))
+    new_p = np.where(case1, dp * rho, np.where(case3, dp * rho - 2.0 * dm * (1.0 - rho), dp))
+    # not an extremum: the PPM limiter
+    new_m = np.where(~extremum & big_m, -2.0 * dp, new_m)
+    new_p = np.where(~extremum & big_p, -2.0 * dm, new_p)
+    return new_m, new_p
+
+
+def ppm_normal_pred(W, J, vel_d, d, dtbydx, use_limiting, high_order=False):
     """MappedAdvectionUtil::PPMNormalPred: returns (WMinus, WPlus) on cells"""
-    w_face = ppm_face_values(W, J, d, use_limiting)
+    w_face = ppm_face_values(W, J, d, use_limiting, high_order)
     dm = (0.0 - W) + w_face                   # low face of the cell
     dp = (0.0 - W) + _sh(w_face, d, 1)        # high face
-    if use_limiting:                          # PPMLimiterF
+    if use_limiting and high_order:
+        dm, dp = check_cubic_limiter(dm, dp, W, d)
+    elif use_limiting:                        # PPMLimiterF
         opp = dm * dp < 0.0
         dwc = (dp + dm) * 0.5
         d2w = dp - dm
@@ -102,13 +150,13 @@ def quasilinear_update(w_half_d, vel_d, scale, d):
 
 
 def predict_scalar(W, J, old_vel, adv_vel, dt, dx, dim, source=None, use_limiting=False, use_upwinding=True,
-                   return_flux=True):
+                   return_flux=True, high_order=False):
     """old_vel[d]: cell-centred velocity components; adv_vel[d]: face-centred advecting velocity of direction d.
     Returns the list of face-centred, time-centred states (times adv_vel when return_flux)."""
     dtondx = [dt / dx[d] for d in range(dim)]
     wm, wp, wh1 = [], [], []
     for d in range(dim):
-        m, p = ppm_normal_pred(W, J, old_vel[d], d, dt / dx[d], use_limiting)
+        m, p = ppm_normal_pred(W, J, old_vel[d], d, dt / dx[d], use_limiting, high_order)
         if source is not None:
             m = m + source * (0.5 * dt)
             p = p + source * (0.5 * dt)

@@ -1,9 +1,11 @@
 // advect.cu -- the PPM / corner-transport-upwind scalar predictor of SOMAR's advection step (SURVEY.md 8(a)
 // "MappedAdvectionUtil::predictScalar" row, 8(f)-3) on a FULLY PERIODIC level (BASELINE.json's TaylorGreen config):
-//   k_adv_face     MappedAdvectionUtil::PPMFaceValues   src/advection/AdvectUtil.cpp:1246-1418 (old-limiter branch)
+//   k_adv_face     MappedAdvectionUtil::PPMFaceValues   src/advection/AdvectUtil.cpp:1246-1418 (both branches:
+//                  m_useHighOrderLimiter -> FourthInterpFaces, MappedGodunovUtilitiesF.ChF:517-609; else)
 //                  -> vanLeerSlopes (MappedGodunovUtilities.cpp:49-102; SecondSlopeDiffsF, VanLeerLimiterF,
 //                  MappedGodunovUtilitiesF.ChF:35-95,151-186) + PPMFaceValuesF (:353-414), for J and J W, then W = JW / J
-//   k_adv_normal   MappedAdvectionUtil::PPMNormalPred   AdvectUtil.cpp:1158-1240 -> PPMLimiterF (:315-351),
+//   k_adv_normal   MappedAdvectionUtil::PPMNormalPred   AdvectUtil.cpp:1158-1240 -> PPMLimiterF (:315-351) or, with the
+//                  high-order limiter, GETSECONDDIFF + CheckCubicLimiterF (:470-512, 611-745),
 //                  PPMNormalPredF (:416-468), + the half-step source term (AdvectUtil.cpp:699-705)
 //   k_adv_riemann  RiemannSolver / AvgStates (AdvectUtilF.ChF:28-132) with the transverse corrections of
 //                  quasilinearUpdate (QuasilinearUpdateF, AdvectUtilF.ChF:134-159) applied on the fly to both states:
@@ -13,7 +15,7 @@
 // periodic image in the first ghost slot, where somar_mac_divergence expects the high face of the last cell.
 // The arithmetic is the Fortran's, statement for statement (-fmad=false): bit-identical to oracle/advect_ref.py.
 // Not built: non-periodic sides (they need the physics BC holders scalarRiemannBC / scalarSlopeBC), CTU / PLM normal
-// predictors, the high-order limiter, more than one rank -- the entry point rejects them.
+// predictors, more than one rank -- the entry point rejects them.
 // HBM-bound streaming passes (18 launches in 3-D); intermediate states live in scratch fields, not yet fused.
 #include "level.hpp"
 
@@ -69,7 +71,13 @@ __device__ __forceinline__ double ppm_face(double xm2, double xm1, double x0, do
     return (wl + wr) * 0.5;
 }
 
-template <bool LIM>
+// FourthInterpFaces (centre box, MappedGodunovUtilitiesF.ChF:559-566): the face between cells -1 and 0
+__device__ __forceinline__ double fourth_face(double xm2, double xm1, double x0, double xp1) {
+    return (7.0 * (xm1 + x0) - (xm2 + xp1)) / 12.0;
+}
+
+// HO = m_useHighOrderLimiter: FourthInterpFaces replaces van Leer slopes + PPMFaceValuesF (AdvectUtil.cpp:1269-1292,1345-1368)
+template <bool LIM, bool HO>
 __global__ void __launch_bounds__(ATPB) k_adv_face(const AGeom g, int d, const double* __restrict__ W,
                                                    const double* __restrict__ J, double* __restrict__ wface) {
     int i, j, k;
@@ -81,12 +89,69 @@ __global__ void __launch_bounds__(ATPB) k_adv_face(const AGeom g, int d, const d
         jj[o] = J[c];
         jw[o] = W[c] * jj[o];
     }
-    const double edgeJ = ppm_face<LIM>(jj[0], jj[1], jj[2], jj[3]);
-    const double fw = ppm_face<LIM>(jw[0], jw[1], jw[2], jw[3]);
+    const double edgeJ = HO ? fourth_face(jj[0], jj[1], jj[2], jj[3]) : ppm_face<LIM>(jj[0], jj[1], jj[2], jj[3]);
+    const double fw = HO ? fourth_face(jw[0], jw[1], jw[2], jw[3]) : ppm_face<LIM>(jw[0], jw[1], jw[2], jw[3]);
     wface[aidx(g, i, j, k)] = fw / edgeJ;
 }
 
-template <bool LIM>
+// CheckCubicLimiterF, inner centre box (MappedGodunovUtilitiesF.ChF:611-745) with limitC = 1.25, C3 = 0.1, eps = 1e-12
+// (MappedGodunovUtilities::PPMLimiter, MappedGodunovUtilities.cpp:381-436).  w[q] = W(i - 3 + q), q = 0..6;
+// d2W(i) = (W(i+1) - W(i)) - (W(i) - W(i-1)) is GETSECONDDIFF (:470-512); d2Wfcf = (dWM + dWP) * 6.
+__device__ __forceinline__ void cubic_limiter(const double w[7], double& dm, double& dp) {
+    const double limitC = 1.25, C3 = 0.1, eps = 1.0e-12;
+    const double dWM = dm, dWP = dp;
+    const bool bigM = fabs(dWM) > 2.0 * fabs(dWP);
+    const bool bigP = fabs(dWP) > 2.0 * fabs(dWM);
+    const double WLL = w[1], WC = w[3], WRR = w[5];
+    const double dWavgM = WC - WLL;
+    const double dWavgP = WRR - WC;
+    const double prodE1 = dWM * dWP;
+    const double prodE2 = dWavgM * dWavgP;
+    if (prodE1 >= 0.0 || prodE2 <= 0.0) {
+        double d2[5];                                  // d2W at i-2 .. i+2
+#pragma unroll
+        for (int q = 0; q < 5; ++q) d2[q] = (w[q + 2] - w[q + 1]) - (w[q + 1] - w[q]);
+        const double d2WL = d2[1], d2WC = d2[2], d2WR = d2[3];
+        double atfcf = dWM;
+        atfcf = atfcf + dWP;
+        atfcf = atfcf * 6.0;
+        double rho = 0.0;
+        if (fabs(atfcf) >= eps) {
+            const double sL = copysign(1.0, d2WL), sC = copysign(1.0, d2WC), sR = copysign(1.0, d2WR);
+            const double sF = copysign(1.0, atfcf);
+            if (sL == sC && sR == sC && sF == sC) {
+                const double d2Wlim = sC * fmin(fmin(fabs(atfcf), limitC * fabs(d2WC)),
+                                                fmin(limitC * fabs(d2WL), limitC * fabs(d2WR)));
+                rho = d2Wlim / atfcf;
+            }
+        }
+        if (rho < (1.0 - eps)) {
+            const double d2WLL = d2[0], d2WRR = d2[4];
+            const double d3WLL = d2WL - d2WLL;
+            const double d3WL = d2WC - d2WL;
+            const double d3WR = d2WR - d2WC;
+            const double d3WRR = d2WRR - d2WR;
+            const double d3Wmin = fmin(fmin(d3WLL, d3WL), fmin(d3WR, d3WRR));
+            const double d3Wmax = fmax(fmax(d3WLL, d3WL), fmax(d3WR, d3WRR));
+            const double prodD3 = C3 * fmax(fabs(d3Wmax), fabs(d3Wmin)) - fabs(d3Wmax - d3Wmin);
+            if (prodD3 <= 0.0) {
+                if (prodE1 > 0.0) {
+                    dm = dWM * rho;
+                    dp = dWP * rho;
+                } else if (bigM) {
+                    dm = dWM * rho - 2.0 * dWP * (1.0 - rho);
+                } else if (bigP) {
+                    dp = dWP * rho - 2.0 * dWM * (1.0 - rho);
+                }
+            }
+        }
+    } else {
+        if (bigM) dm = -2.0 * dWP;
+        if (bigP) dp = -2.0 * dWM;
+    }
+}
+
+template <bool LIM, bool HO>
 __global__ void __launch_bounds__(ATPB) k_adv_normal(const AGeom g, int d, const double* __restrict__ W,
                                                      const double* __restrict__ wface, const double* __restrict__ vel,
                                                      const double* __restrict__ src, double srcScale, double dtbydx,
@@ -97,7 +162,12 @@ __global__ void __launch_bounds__(ATPB) k_adv_normal(const AGeom g, int d, const
     const double w = W[c];
     double dm = (0.0 - w) + wface[c];
     double dp = (0.0 - w) + wface[aoff(g, i, j, k, d, 1)];
-    if (LIM) {   // PPMLimiterF
+    if (LIM && HO) {
+        double w7[7];
+#pragma unroll
+        for (int q = 0; q < 7; ++q) w7[q] = (q == 3) ? w : W[aoff(g, i, j, k, d, q - 3)];
+        cubic_limiter(w7, dm, dp);
+    } else if (LIM) {   // PPMLimiterF
         if (dm * dp < 0.0) {
             const double dwc = (dp + dm) * 0.5;
             const double d2w = dp - dm;
@@ -187,7 +257,9 @@ int advect_predict_scalar(SomarLevel* L, SomarField* const whalf[3], const Somar
             return SOMAR_ERR_ARG;
         }
     if (prm->normal_pred_order != 2) { set_error("predictScalar: only the PPM normal predictor (order 2) is built"); return SOMAR_ERR_ARG; }
-    if (prm->use_high_order_limiter) { set_error("predictScalar: the high-order limiter is not built"); return SOMAR_ERR_ARG; }
+    if (prm->use_high_order_limiter)
+        for (int d = 0; d < nd; ++d)
+            if (G.n[d] < 4) { set_error("predictScalar: the high-order limiter needs at least 4 cells per direction"); return SOMAR_ERR_ARG; }
     AGeom g;
     for (int d = 0; d < 3; ++d) g.n[d] = G.n[d];
     g.nd = nd;
@@ -211,17 +283,25 @@ int advect_predict_scalar(SomarLevel* L, SomarField* const whalf[3], const Somar
     const unsigned nb = (unsigned)((tot + ATPB - 1) / ATPB);
     cudaStream_t st = L->cx.stream;
     const bool lim = prm->use_limiting != 0;
+    const bool ho = prm->use_high_order_limiter != 0;
     const int up = prm->use_upwinding != 0;
     double dtondx[3];
     for (int d = 0; d < nd; ++d) dtondx[d] = dt / G.dx[d];
     const ACorr none = {{nullptr, nullptr}, {nullptr, nullptr}, {0.0, 0.0}, {0, 0}, 0};
     for (int d = 0; d < nd; ++d) {
         double* wface = whalf[d]->p;            // the output's memory holds the face values until they are consumed
-        if (lim) k_adv_face<true><<<nb, ATPB, 0, st>>>(g, d, wold->p, ccJ->p, wface);
-        else k_adv_face<false><<<nb, ATPB, 0, st>>>(g, d, wold->p, ccJ->p, wface);
         const double* src = source ? source->p : nullptr;
-        if (lim) k_adv_normal<true><<<nb, ATPB, 0, st>>>(g, d, wold->p, wface, oldVel[d]->p, src, 0.5 * dt, dtondx[d], wm[d], wp[d]);
-        else k_adv_normal<false><<<nb, ATPB, 0, st>>>(g, d, wold->p, wface, oldVel[d]->p, src, 0.5 * dt, dtondx[d], wm[d], wp[d]);
+#define ADV_STAGE(LIM_, HO_)                                                                                         \
+        do {                                                                                                         \
+            k_adv_face<LIM_, HO_><<<nb, ATPB, 0, st>>>(g, d, wold->p, ccJ->p, wface);                                \
+            k_adv_normal<LIM_, HO_><<<nb, ATPB, 0, st>>>(g, d, wold->p, wface, oldVel[d]->p, src, 0.5 * dt, dtondx[d], \
+                                                         wm[d], wp[d]);                                              \
+        } while (0)
+        if (lim && ho) ADV_STAGE(true, true);
+        else if (lim) ADV_STAGE(true, false);
+        else if (ho) ADV_STAGE(false, true);
+        else ADV_STAGE(false, false);
+#undef ADV_STAGE
         k_adv_riemann<<<nb, ATPB, 0, st>>>(g, d, wp[d], wm[d], advVel[d]->p, none, up, 0, 0, wh1[d]);
         L->cx.launches += 3;
     }

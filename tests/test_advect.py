@@ -3,7 +3,8 @@ fully periodic levels (BASELINE.json config "TaylorGreen 2D/3D periodic").
 
 CPU: the numpy restatement oracle/advect_ref.py is pinned to properties of the scheme (the reference ships no
 vectors): constants are preserved, a smooth profile carried by a uniform velocity is predicted to second order at
-t + dt/2, stagnant faces take the average state, the limiter keeps the face states inside the local data range.
+t + dt/2, stagnant faces take the average state, the limiter keeps the face states inside the local data range; the
+high-order (extremum-preserving) branch gives 4th-order faces and keeps a smooth extremum that PPMLimiterF flattens.
 GPU: the CUDA kernels through the C ABI against the oracle on seeded inputs -- BIT-EXACT (same statements, no FMA
 contraction) for every option combination, in 2-D and 3-D."""
 import itertools
@@ -41,11 +42,12 @@ def _inputs(shape, dim, seed=0):
 
 # ---------------------------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("dim", [2, 3])
-@pytest.mark.parametrize("lim", [False, True])
-def test_oracle_preserves_constants(dim, lim):
+@pytest.mark.parametrize("lim,ho", [(False, False), (True, False), (False, True), (True, True)])
+def test_oracle_preserves_constants(dim, lim, ho):
     shape = (6 if dim == 3 else 1, 10, 12)
     _, J, ov, av, _ = _inputs(shape, dim)
-    out = ar.predict_scalar(np.full(shape, 2.5), J, ov, av, 0.01, [0.1] * 3, dim, use_limiting=lim, return_flux=False)
+    out = ar.predict_scalar(np.full(shape, 2.5), J, ov, av, 0.01, [0.1] * 3, dim, use_limiting=lim, return_flux=False,
+                            high_order=ho)
     for o in out:
         assert np.abs(o - 2.5).max() <= 1e-14
 
@@ -84,6 +86,36 @@ def test_oracle_stagnant_faces_and_limiter_bounds():
     assert (m >= lo).all() and (m <= hi).all() and (p >= lo).all() and (p <= hi).all()
 
 
+def test_oracle_fourth_order_faces_and_extremum_preserving_limiter():
+    """m_useHighOrderLimiter: FourthInterpFaces is exact for cell averages of cubics (4th order in general); the
+    CheckCubicLimiterF limiter leaves a smooth extremum alone where PPMLimiterF flattens it, and still limits at a step."""
+    errs = []
+    for n in (16, 32):
+        xf = np.arange(n + 1) / n
+        F = -np.cos(2 * np.pi * xf) / (2 * np.pi)                     # antiderivative of sin(2 pi x)
+        avg = ((F[1:] - F[:-1]) * n).reshape(1, 1, n)                 # exact cell averages
+        face = ar.ppm_face_values(avg, np.ones_like(avg), 0, False, high_order=True)
+        errs.append(np.abs(face[0, 0] - np.sin(2 * np.pi * xf[:-1])).max())
+    assert errs[1] < errs[0] / 14.0, errs                              # 4th order
+    n = 32
+    x = (np.arange(n) + 0.5) / n
+    W = np.sin(2 * np.pi * x).reshape(1, 1, n)
+    one, zero = np.ones_like(W), np.zeros_like(W)
+    i_max = int(np.argmax(W))
+    m_un, p_un = ar.ppm_normal_pred(W, one, zero, 0, 0.0, False, high_order=True)
+    m_ho, p_ho = ar.ppm_normal_pred(W, one, zero, 0, 0.0, True, high_order=True)
+    m_lo, p_lo = ar.ppm_normal_pred(W, one, zero, 0, 0.0, True, high_order=False)
+    assert m_ho[0, 0, i_max] == m_un[0, 0, i_max] and p_ho[0, 0, i_max] == p_un[0, 0, i_max]   # extremum kept
+    assert m_lo[0, 0, i_max] == W[0, 0, i_max] and p_lo[0, 0, i_max] == W[0, 0, i_max]         # PPM flattens it
+    step = np.where(x < 0.5, 0.0, 1.0).reshape(1, 1, n)
+    m, p = ar.ppm_normal_pred(step, one, zero, 0, 0.0, True, high_order=True)
+    m_u, p_u = ar.ppm_normal_pred(step, one, zero, 0, 0.0, False, high_order=True)
+    # at the step the unlimited parabola of the last 0-cell reaches 1/2; the limiter pulls it back to 1/6 (rho = 0:
+    # dWP = -2 dWM) and never moves a state further out than the 1/12 under/overshoot of the 4th-order face value
+    assert p_u.max() > 1.0 + 1.0 / 13.0 and np.abs(p - p_u).max() > 0.3
+    assert m.min() >= -1.0 / 12.0 - 1e-12 and p.max() <= 1.0 + 1.0 / 12.0 + 1e-12
+
+
 # ---------------------------------------------------------------------------------------------------------------
 OPTS = list(itertools.product([False, True], [False, True], [False, True], [False, True]))   # lim, upwind, src, flux
 
@@ -99,18 +131,19 @@ def test_predict_scalar_parity(dim, n, somar):
     fov = [lev.field(0, v) for v in ov]
     fav = [lev.field(0, v) for v in av]
     out = [lev.field(0) for _ in range(dim)]
-    for lim, up, with_src, flux in OPTS:
+    for (lim, up, with_src, flux), ho in itertools.product(OPTS, [False, True]):
         lev.advect_predict_scalar(out, fW, fov, fav, fJ, dt, source=fS if with_src else None, use_limiting=lim,
-                                  use_upwinding=up, return_flux=flux)
+                                  use_upwinding=up, return_flux=flux, use_high_order_limiter=ho)
         want = ar.predict_scalar(W, J, ov, av, dt, pb.spec.dx, dim, source=src if with_src else None, use_limiting=lim,
-                                 use_upwinding=up, return_flux=flux)
+                                 use_upwinding=up, return_flux=flux, high_order=ho)
         for d in range(dim):
             got = out[d].get()
-            assert np.array_equal(got, want[d]), (dim, d, lim, up, with_src, flux, np.abs(got - want[d]).max())
+            assert np.array_equal(got, want[d]), (dim, d, lim, up, with_src, flux, ho, np.abs(got - want[d]).max())
     # the flux's periodic image is in place: the MAC divergence of the device equals the wrapped numpy divergence
     div = lev.field(0)
     lev.mac_divergence(div, out)
-    want = ar.predict_scalar(W, J, ov, av, dt, pb.spec.dx, dim, source=src, use_limiting=True, use_upwinding=True)
+    want = ar.predict_scalar(W, J, ov, av, dt, pb.spec.dx, dim, source=src, use_limiting=True, use_upwinding=True,
+                             high_order=True)      # the last combination of the loop
     s = (np.roll(want[0], -1, 2) - want[0]) * (1.0 / pb.spec.dx[0])
     s = s + (np.roll(want[1], -1, 1) - want[1]) * (1.0 / pb.spec.dx[1])
     if dim == 3:
@@ -134,8 +167,6 @@ def test_predict_scalar_rejects_what_is_not_built(somar):
     pb = Problem(n=(16, 16, 8), map_name="cartesian", aniso=1.0, periodic=(1, 1, 1))
     lev = pb.level(somar)
     f = [lev.field(0) for _ in range(12)]
-    with pytest.raises(somar.SomarError):
-        lev.advect_predict_scalar(f[0:3], f[3], f[4:7], f[7:10], f[10], 0.1, use_high_order_limiter=True)
     with pytest.raises(somar.SomarError):
         lev.advect_predict_scalar(f[0:3], f[3], f[4:7], f[7:10], f[10], 0.1, normal_pred_order=1)
     with pytest.raises(somar.SomarError):          # output aliases an input
