@@ -42,6 +42,7 @@ struct BicgArgs {
     double bottomMetric; // > 0: convergence metric set by the outer solver
     double eps, reps, small, one_minus_hang;
     int imax, normKind;
+    int tcx, tcy;        // core of the shared-memory tile of the fused preconditioner+operator pass (0: not used)
 };
 
 // ---- scalar state of the iteration and its steps (shared with the launch-per-step version in bicgstab.cu) ----
@@ -202,6 +203,92 @@ __device__ __forceinline__ void tree_barrier(unsigned long long* bar, unsigned& 
 
 #define BP_U 8
 
+// ---- fused "relaxations + operator" pass on shared-memory tiles ------------------------------------------------
+// preCond's nprecond red-black relaxations followed by L(.) are 2*nprecond + 1 dependent stencil passes, each a
+// grid barrier in the pass-per-barrier formulation.  Here a block loads a tile of the input with a halo of
+// h = 2*nprecond + 1 cells (all z-planes), relaxes it in shared memory -- every colour pass is valid on a region one
+// cell smaller, block barriers only -- and applies the operator on the core: ONE grid barrier instead of 2*nprecond+1.
+// Halo cells are relaxed redundantly by the neighbouring blocks with the statements, operands and order of the
+// owning block (gsrb_update_vals / apply_vals_ortho3 are the value forms of gsrb_cell_ortho / apply_cell_ortho), so
+// the result is bit-identical to the pass-per-barrier version.  Input and output are different arrays (a block
+// reads halo cells that another block owns).  3-D only; the tile must hold (tcx+2h) x (tcy+2h) x nz cells.
+#define BP_TILE_CAP 1872   // 26 x 18 x 4
+__device__ __forceinline__ void bp_tile_relax_apply(const Geom& g, const Metric& m, double* __restrict__ tile,
+                                                    const double* __restrict__ in, const double* __restrict__ rhs,
+                                                    double* __restrict__ outPhi, double* __restrict__ outL, int nrelax,
+                                                    int tcx, int tcy) {
+    const int h = 2 * nrelax + 1;
+    const int nx = g.n[0], ny = g.n[1], nz = g.n[2];
+    const int W = tcx + 2 * h, Hh = tcy + 2 * h;
+    const int tilesX = (nx + tcx - 1) / tcx, tilesY = (ny + tcy - 1) / tcy;
+    const int tid = threadIdx.x;
+    for (int t = blockIdx.x; t < tilesX * tilesY; t += gridDim.x) {
+        const int ty = t / tilesX, tx = t - ty * tilesX;
+        const int cx0 = tx * tcx, cy0 = ty * tcy;              // core origin
+        const int ox = cx0 - h, oy = cy0 - h;                  // tile origin (may lie outside the domain)
+        __syncthreads();                                       // the previous tile's readers are done
+        {   // load core + h, clipped to the domain
+            const int xa = max(0, ox), xb = min(nx, cx0 + tcx + h), ya = max(0, oy), yb = min(ny, cy0 + tcy + h);
+            const int wx = xb - xa, wy = yb - ya;
+            for (int q = tid; q < wx * wy * nz; q += BP_TPB) {
+                const int k = q / (wx * wy), r = q - k * wx * wy;
+                const int j = ya + r / wx, i = xa + (r - (r / wx) * wx);
+                tile[(i - ox) + W * ((j - oy) + Hh * k)] = in[g.idx(i, j, k)];
+            }
+        }
+        __syncthreads();
+        int sdone = 0;
+        for (int it = 0; it < nrelax; ++it)
+            for (int pass = 0; pass < 2; ++pass) {
+                ++sdone;
+                const int e = h - sdone;                       // this colour pass is valid on core + e
+                const int xa = max(0, cx0 - e), xb = min(nx, cx0 + tcx + e), ya = max(0, cy0 - e), yb = min(ny, cy0 + tcy + e);
+                const int half = (xb - xa + 1) >> 1, wy = yb - ya;
+                for (int q = tid; q < half * wy * nz; q += BP_TPB) {
+                    const int k = q / (half * wy), r = q - k * half * wy;
+                    const int j = ya + r / half;
+                    const int par = (g.g0[0] + g.g0[1] + j + g.g0[2] + k + pass) & 1;
+                    const int i = xa + ((xa ^ par) & 1) + 2 * (r - (r / half) * half);
+                    if (i < xb) {
+                        const int l = (i - ox) + W * ((j - oy) + Hh * k);
+                        double nb[3][2];
+                        nb[0][0] = tile[l - 1];
+                        nb[0][1] = tile[l + 1];
+                        nb[1][0] = tile[l - W];
+                        nb[1][1] = tile[l + W];
+                        nb[2][0] = (k > 0) ? tile[l - W * Hh] : 0.0;
+                        nb[2][1] = (k < nz - 1) ? tile[l + W * Hh] : 0.0;
+                        const GsrbCoef qc = gsrb_load_coef<3>(g, m, rhs, g.idx(i, j, k));
+                        tile[l] = gsrb_update_vals<3>(g, qc, i, j, k, tile[l], nb);
+                    }
+                }
+                __syncthreads();
+            }
+        {   // the operator on the core, and the relaxed values
+            const int xb = min(nx, cx0 + tcx), yb = min(ny, cy0 + tcy);
+            const int wx = xb - cx0, wy = yb - cy0;
+            for (int q = tid; q < wx * wy * nz; q += BP_TPB) {
+                const int k = q / (wx * wy), r = q - k * wx * wy;
+                const int j = cy0 + r / wx, i = cx0 + (r - (r / wx) * wx);
+                const int l = (i - ox) + W * ((j - oy) + Hh * k);
+                const long long c = g.idx(i, j, k);
+                const double pc = tile[l];
+                double nb[3][2];
+                nb[0][0] = tile[l - 1];
+                nb[0][1] = tile[l + 1];
+                nb[1][0] = tile[l - W];
+                nb[1][1] = tile[l + W];
+                nb[2][0] = (k > 0) ? tile[l - W * Hh] : 0.0;
+                nb[2][1] = (k < nz - 1) ? tile[l + W * Hh] : 0.0;
+                const double glo[3] = {m.jg[0][0][c], m.jg[1][1][c], m.jg[2][2][c]};
+                const double ghi[3] = {m.jg[0][0][c + 1], m.jg[1][1][c + g.sy], m.jg[2][2][c + g.sz]};
+                outL[c] = apply_vals_ortho3(g, side_mask(g, i, j, k), true, pc, nb, glo, ghi, m.jinv[c]);
+                outPhi[c] = pc;
+            }
+        }
+    }
+}
+
 template <int ND>
 __global__ void __launch_bounds__(BP_TPB, BP_MINBLOCKS)
     k_bicg_persistent(const Geom g, const Metric m, const BicgFields f, const BicgArgs a, double* part,
@@ -216,6 +303,10 @@ __global__ void __launch_bounds__(BP_TPB, BP_MINBLOCKS)
     };
     __shared__ BicgState s;
     __shared__ double rhoNext;   // <r_tilde, r> formed by the pass that wrote r
+    __shared__ double tile[(ND > 2) ? BP_TILE_CAP : 1];
+    // fused preconditioner + operator (bp_tile_relax_apply): the diagonally scaled input of preCond(p) is staged in
+    // stl's array and that of preCond(s) in pt's array -- each is free at that point of the iteration
+    const bool tiled = (ND > 2) && a.tcx > 0 && a.nprecond > 0;
     int buf = 0;
     const int tid = threadIdx.x;
     const int lane = tid & 31;
@@ -331,13 +422,17 @@ __global__ void __launch_bounds__(BP_TPB, BP_MINBLOCKS)
                     pn = t2 + 1.0 * pn;
                 }
                 f.pv[c] = pn;
-                f.pt[c] = a.nprecond ? pn / (g.alpha + g.beta * m.lapdiag[c]) : pn;
+                (tiled ? f.stl : f.pt)[c] = a.nprecond ? pn / (g.alpha + g.beta * m.lapdiag[c]) : pn;
             })
             gsync();
-            relax(f.pt, f.pv, a.nprecond);
+            if (!tiled) relax(f.pt, f.pv, a.nprecond);
         }
         {   // v = L p_tilde (spread over the grid), then <r_tilde, v> in the canonical order
-            BP_FOR_CELLS(g, c, { f.v[c] = apply_cell_ortho<ND>(g, m, f.pt, i, j, k, c, true); })
+            if (tiled) {
+                if (ND > 2) bp_tile_relax_apply(g, m, tile, f.stl, f.pv, f.pt, f.v, a.nprecond, a.tcx, a.tcy);
+            } else {
+                BP_FOR_CELLS(g, c, { f.v[c] = apply_cell_ortho<ND>(g, m, f.pt, i, j, k, c, true); })
+            }
             gsync();
             double acc = 0.0;
             double tv[BP_U], vv[BP_U];
@@ -356,7 +451,7 @@ __global__ void __launch_bounds__(BP_TPB, BP_MINBLOCKS)
                     f.e[c] = f.e[c] + al * f.pt[c];
                 }
                 f.r[c] = nv;
-                f.stl[c] = a.nprecond ? nv / (g.alpha + g.beta * m.lapdiag[c]) : nv;
+                (tiled ? f.pt : f.stl)[c] = a.nprecond ? nv / (g.alpha + g.beta * m.lapdiag[c]) : nv;
             })
             gsync();
             norm_and_rho();
@@ -364,9 +459,13 @@ __global__ void __launch_bounds__(BP_TPB, BP_MINBLOCKS)
         if (tid == 0) ctl3(&s);
         __syncthreads();
         if (s.doB) {
-            relax(f.stl, f.r, a.nprecond);
+            if (!tiled) relax(f.stl, f.r, a.nprecond);
             {   // t = L s_tilde (spread over the grid), then <t, r>, <t, t> in the canonical order
-                BP_FOR_CELLS(g, c, { f.t[c] = apply_cell_ortho<ND>(g, m, f.stl, i, j, k, c, true); })
+                if (tiled) {
+                    if (ND > 2) bp_tile_relax_apply(g, m, tile, f.pt, f.r, f.stl, f.t, a.nprecond, a.tcx, a.tcy);
+                } else {
+                    BP_FOR_CELLS(g, c, { f.t[c] = apply_cell_ortho<ND>(g, m, f.stl, i, j, k, c, true); })
+                }
                 gsync();
                 double a0 = 0.0, a1 = 0.0;
                 double tv[BP_U], rr[BP_U];

@@ -404,6 +404,20 @@ int launch_bottom_persistent(SomarLevel* L, const Geom& g_, const Metric& m_, do
     a.normKind = (p.bottom_normType == 0) ? 0 : (p.bottom_normType == 1 ? 1 : 2);
     Geom g = g_;
     Metric m = m_;
+    // tile of the fused preconditioner + operator pass (bp_tile_relax_apply): 16 x 8 core, shrunk until the tile with
+    // its halo of 2*nprecond+1 cells and every z-plane fits; SOMAR_B200_BOTTOM_TILED=0 keeps one pass per barrier
+    a.tcx = a.tcy = 0;
+    {
+        static const bool tiledOn = []() { const char* e = getenv("SOMAR_B200_BOTTOM_TILED"); return !(e && e[0] == '0'); }();
+        if (tiledOn && g.nd == 3 && a.nprecond > 0) {
+            const int h = 2 * a.nprecond + 1;
+            int cx = 16, cy = 8;
+            while ((cx + 2 * h) * (cy + 2 * h) * g.n[2] > BP_TILE_CAP && (cx > 4 || cy > 4)) {
+                if (cx > cy) cx /= 2; else cy /= 2;
+            }
+            if ((cx + 2 * h) * (cy + 2 * h) * g.n[2] <= BP_TILE_CAP) { a.tcx = cx; a.tcy = cy; }
+        }
+    }
     double* part = dv->part;
     int* itersAccum = &dv->iters;
     int cb = row_blocks(g, L->cx.sms);   // the blocks k_reduce would use: the canonical summation order

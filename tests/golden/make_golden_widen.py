@@ -19,6 +19,19 @@ PROJ = dict(n=(12, 8, 6), map_name="terrain", aniso=4.0, parts=(1, 2, 1))
 LOOSE = dict(n=(12, 8, 6), map_name="stretched", aniso=4.0, parts=(2, 2, 1))
 LEPTIC = dict(n=(8, 6, 10), map_name="stretched", aniso=4.0)
 ADV_N = (8, 6, 5)
+LEPTIC_SOLVE = {"diri": (dict(n=(16, 12, 8), aniso=32.0, bc_type=[0, 0, 0, 0, 0, 1]), dict(max_order=3)),
+                "neum": (dict(n=(16, 16, 8), aniso=32.0), dict(max_order=1))}
+
+
+def leptic_solve(name):
+    from oracle import leptic_ref as lr
+    pk, lk = LEPTIC_SOLVE[name]
+    pb = Problem(**pk)
+    rhs = pb.rhs()
+    s = lr.LevelLepticSolver(po, pb.n, pb.spec.dx, pb.jgup, pb.jinv, boxes=pb.boxes, bc_type=pb.bc_type,
+                             params=lr.LepticParams(**lk))
+    phi = s.solve(np.zeros_like(rhs), rhs, homogeneous=True)
+    return pb, rhs, phi, np.array(s.res_norms)
 
 
 def advect_inputs():
@@ -59,6 +72,11 @@ def main():
     for lim in (0, 1):
         for d, f in enumerate(ar.predict_scalar(W, J, ov, av, 0.02, dx, 3, source=src, use_limiting=bool(lim))):
             out[f"advect/flux{d}_lim{lim}"] = f
+    for d, f in enumerate(ar.predict_scalar(W, J, ov, av, 0.02, dx, 3, source=src, use_limiting=True, high_order=True)):
+        out[f"advect/flux{d}_ho"] = f
+    for name in LEPTIC_SOLVE:
+        _, rhs, phi, norms = leptic_solve(name)
+        out[f"leptic_solve/{name}_rhs"], out[f"leptic_solve/{name}_phi"], out[f"leptic_solve/{name}_norms"] = rhs, phi, norms
     np.savez_compressed(os.path.join(HERE, "widen_golden.npz"), **out)
     print({k: v.shape for k, v in out.items()})
 

@@ -36,6 +36,14 @@ def test_oracle_reproduces_fixtures(oracle_lib):
     for lim in (0, 1):
         for d, f in enumerate(ar.predict_scalar(W, J, ov, av, 0.02, dx, 3, source=src, use_limiting=bool(lim))):
             assert np.array_equal(f, G[f"advect/flux{d}_lim{lim}"])
+    for d, f in enumerate(ar.predict_scalar(W, J, ov, av, 0.02, dx, 3, source=src, use_limiting=True, high_order=True)):
+        assert np.array_equal(f, G[f"advect/flux{d}_ho"])
+    for name in mk.LEPTIC_SOLVE:
+        _, rhs, phi, norms = mk.leptic_solve(name)
+        assert np.array_equal(rhs, G[f"leptic_solve/{name}_rhs"])
+        tol = 0.0 if name == "diri" else 1e-9          # "neum" runs a multigrid solve (OpenMP reductions)
+        assert np.abs(phi - G[f"leptic_solve/{name}_phi"]).max() <= tol * np.abs(phi).max()
+        assert np.allclose(norms, G[f"leptic_solve/{name}_norms"], rtol=1e-9, atol=0)
 
 
 @pytest.mark.gpu
@@ -76,3 +84,17 @@ def test_cuda_reproduces_fixtures(somar):
                                   lev.field(0, J), 0.02, source=lev.field(0, src), use_limiting=bool(lim))
         for d in range(3):
             assert np.array_equal(fl[d].get(), G[f"advect/flux{d}_lim{lim}"])
+    lev.advect_predict_scalar(fl, lev.field(0, W), [lev.field(0, v) for v in ov], [lev.field(0, v) for v in av],
+                              lev.field(0, J), 0.02, source=lev.field(0, src), use_limiting=True, use_high_order_limiter=True)
+    for d in range(3):
+        assert np.array_equal(fl[d].get(), G[f"advect/flux{d}_ho"])
+    for name, (pk, lk) in mk.LEPTIC_SOLVE.items():
+        pb = Problem(**pk)
+        lev = pb.level(somar)
+        ls = somar.LepticSolver(lev, somar.leptic_default_params(**lk))
+        phi, rhs = lev.field(0), lev.field(0, G[f"leptic_solve/{name}_rhs"])
+        st = ls.solve(phi, rhs, homogeneous=True)
+        want = G[f"leptic_solve/{name}_phi"]
+        tol = 1e-13 if name == "diri" else 1e-9
+        assert np.abs(phi.get() - want).max() <= tol * np.abs(want).max()
+        assert np.allclose(st["res_norms"], G[f"leptic_solve/{name}_norms"], rtol=1e-8, atol=0)
