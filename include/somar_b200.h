@@ -228,7 +228,9 @@ int somar_leptic_accum_div(SomarLevel* lev, SomarField* flat_rhs, const SomarFie
  *      excess bookkeeping, the batched vertical solves, the horizontal right-hand side (computeHorizRHS, :981-1097) and
  *      multigrid solve, the new residual, the multigrid fall-back at the last order when the iteration hangs, and
  *      phi += sum of corrections.  `homogeneous` is setHomogeneous (:444).
- * Scope: one level without a coarser one, diagonal metric, one rank, vertical sides Neumann or Dirichlet; with a
+ * Scope: one level without a coarser one, diagonal metric, one rank or y-slab ranks (the vertical level shares the
+ * level's communicator, the small horizontal level is replicated and its rows all-gathered: destroy the solver BEFORE
+ * the level), vertical sides Neumann or Dirichlet; with a
  * horizontal solve the level must be 3-D with non-periodic horizontal directions (the reference leaves the boundary
  * faces of a periodic direction unset in computeHorizRHS).  Anything else is an error, never a CPU path. */
 typedef struct SomarLepticParams {

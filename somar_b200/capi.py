@@ -154,6 +154,7 @@ class LepticSolver:
         h = C.c_void_p()
         _ck(lib().somar_leptic_create(level.h, C.byref(self.params), C.byref(h)))
         self.h = h
+        level._leptics.add(self)       # destroyed before the level: the derived levels borrow its communicator
 
     def solve(self, phi: "Field", rhs: "Field", homogeneous=False) -> dict:
         st = LepticStats()
@@ -282,6 +283,7 @@ class Level:
         L = lib()
         self.h = None
         self._fields = weakref.WeakSet()
+        self._leptics = weakref.WeakSet()
         self.n = tuple(int(x) for x in n)
         self.dim = dim
         if boxes is None:
@@ -542,6 +544,8 @@ class Level:
 
     def destroy(self):
         if getattr(self, "h", None):
+            for s in list(self._leptics):
+                s.destroy()
             for f in list(self._fields):
                 f.destroy()
             lib().somar_level_destroy(self.h)

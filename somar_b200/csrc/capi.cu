@@ -68,11 +68,20 @@ int somar_comm_unique_id(unsigned char id[128]) {
 
 int somar_level_create(const SomarLevelDesc* desc, const SomarSolverParams* params, int device,
                        const unsigned char* comm_id, SomarLevel** out) {
+    return level_create_impl(desc, params, device, comm_id, nullptr, out);
+}
+
+}  // extern "C"
+
+// `borrowed`: a communicator owned by another level of the same ranks (the leptic solver's derived levels); the new
+// level uses it and does not destroy it.  The caller keeps the levels' NCCL work from overlapping (stream syncs).
+int somar::level_create_impl(const SomarLevelDesc* desc, const SomarSolverParams* params, int device,
+                             const unsigned char* comm_id, ncclComm_t borrowed, SomarLevel** out) {
     if (!desc || !params || !out) { set_error("null argument"); return SOMAR_ERR_ARG; }
     if (desc->dim != 2 && desc->dim != 3) { set_error("dim must be 2 or 3"); return SOMAR_ERR_ARG; }
     if (desc->dim == 2 && desc->n[2] != 1) { set_error("2-D problems need n[2] == 1"); return SOMAR_ERR_ARG; }
     if (desc->nboxes < 1 || !desc->box_lo || !desc->box_hi) { set_error("no boxes"); return SOMAR_ERR_ARG; }
-    if (desc->nranks > 1 && !comm_id) { set_error("nranks > 1 needs a communicator id"); return SOMAR_ERR_ARG; }
+    if (desc->nranks > 1 && !comm_id && !borrowed) { set_error("nranks > 1 needs a communicator id"); return SOMAR_ERR_ARG; }
     int ndev = 0;
     SOMAR_CUDA(cudaGetDeviceCount(&ndev));
     if (device < 0 || device >= ndev) { set_error("no such CUDA device (there is no CPU fallback)"); return SOMAR_ERR_CUDA; }
@@ -108,7 +117,10 @@ int somar_level_create(const SomarLevelDesc* desc, const SomarSolverParams* para
         delete L;
         return SOMAR_ERR_CUDA;
     }
-    if (desc->nranks > 1) {
+    if (desc->nranks > 1 && borrowed) {
+        L->comm = borrowed;
+        L->comm_borrowed = true;
+    } else if (desc->nranks > 1) {
         ncclUniqueId u;
         std::memcpy(&u, comm_id, 128);
         ncclResult_t ne = ncclCommInitRank(&L->comm, desc->nranks, u, desc->rank);
@@ -118,6 +130,8 @@ int somar_level_create(const SomarLevelDesc* desc, const SomarSolverParams* para
     *out = L;
     return SOMAR_OK;
 }
+
+extern "C" {
 
 int somar_level_destroy(SomarLevel* L) {
     if (!L) return SOMAR_OK;
@@ -136,7 +150,7 @@ int somar_level_destroy(SomarLevel* L) {
     if (L->pwork) { cudaFree(L->pwork->p); delete L->pwork; }
     for (auto* f : L->awork) if (f) { cudaFree(f->p); delete f; }
     halo_p2p_free(L);   // (collective: needs the communicator)
-    if (L->comm) ncclCommDestroy(L->comm);
+    if (L->comm && !L->comm_borrowed) ncclCommDestroy(L->comm);
     cudaFree(L->cx.scratch); cudaFree(L->cx.tickets); cudaFree(L->d_scal); cudaFreeHost(L->h_scal);
     if (L->d_bicg) cudaFree(L->d_bicg);
     if (L->h_bicg) cudaFreeHost(L->h_bicg);

@@ -15,12 +15,15 @@
 // Flat fields (excess, boundary data, horizontal right-hand side) are SomarFields of the vertical level that own only
 // the planes the flat kernels touch.  Each level has its own stream; the driver is host-sequenced (it reads a norm
 // back every order, as the reference does), so hand-overs between levels are stream synchronisations.
-// Scope: diagonal metric, one rank, one level; see include/somar_b200.h.
+// Scope: diagonal metric, one level, y-slab ranks (the vertical level borrows the level's communicator; the small
+// horizontal level is replicated on every rank, its rows all-gathered); see include/somar_b200.h.
 #include "level.hpp"
 #include "cells.cuh"
 #include <cmath>
 #include <cstring>
+#include <algorithm>
 #include <utility>
+#include <vector>
 
 struct SomarLeptic {
     SomarLevel* orig = nullptr;    // not owned
@@ -38,6 +41,11 @@ struct SomarLeptic {
     SomarField* res = nullptr;
     // horizontal level
     SomarField *hPhi = nullptr, *hRhs = nullptr;
+    // several ranks: the horizontal level is REPLICATED (every rank holds the whole flattened domain, like the
+    // gathered bottom depth of bottom_gather.cu); rows travel with one ncclAllGather on the vertical level's stream
+    std::vector<int> row0, rows;       // first row / number of rows of each rank at depth 0
+    int maxRows = 0;
+    double *gsend = nullptr, *gall = nullptr, *gdense = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 };
 
@@ -116,12 +124,10 @@ __global__ void k_fill_dense(double* __restrict__ x, long long n, double v) {
 }
 
 // x = x - a on the valid cells of a 2-D level (FArrayBox::operator-=, :1707)
-__global__ void __launch_bounds__(QTPB) k_sub_scalar(const Geom g, double* __restrict__ x, const double* __restrict__ sum,
-                                                     double count) {
+__global__ void __launch_bounds__(QTPB) k_sub_scalar(const Geom g, double* __restrict__ x, double avg) {
     const int i = blockIdx.x * QTPB + threadIdx.x;
     const int j = blockIdx.y;
     if (i >= g.n[0]) return;
-    const double avg = sum[0] / count;
     const long long c = g.idx(i, j, 0);
     x[c] = x[c] - avg;
 }
@@ -160,6 +166,25 @@ static int norm_of(SomarLevel* L, const SomarField* x, int ord, double* out) {
     return SOMAR_OK;
 }
 
+// Every rank's rows [0, rows_r) (+ one more row from the last rank when extraRow) of a row-pitched local array
+// -> the dense global array dst ((ny + extraRow) x width) on every rank.  Stream: the vertical level's.
+static int gather_rows(SomarLeptic* S, const double* src, size_t srcPitch, int width, int extraRow, double* dst) {
+    SomarLevel* V = S->vert;
+    const int me = V->desc.rank, nr = V->desc.nranks;
+    cudaStream_t st = V->cx.stream;
+    const size_t chunk = (size_t)(S->maxRows + 1) * (size_t)(S->orig->depths[0].g.n[0] + 1);
+    SOMAR_CUDA(cudaMemcpy2DAsync(S->gsend, width * sizeof(double), src, srcPitch * sizeof(double), width * sizeof(double),
+                                 S->rows[me] + extraRow, cudaMemcpyDeviceToDevice, st));
+    SOMAR_NCCL(ncclAllGather(S->gsend, S->gall, chunk, ncclDouble, V->comm, st));
+    for (int r = 0; r < nr; ++r) {
+        const bool last = S->row0[r] + S->rows[r] == V->depths[0].g.gn[1];
+        const size_t nrow = (size_t)S->rows[r] + ((extraRow && last) ? 1 : 0);
+        SOMAR_CUDA(cudaMemcpyAsync(dst + (size_t)S->row0[r] * width, S->gall + r * chunk, nrow * width * sizeof(double),
+                                   cudaMemcpyDeviceToDevice, st));
+    }
+    return SOMAR_OK;
+}
+
 }  // namespace somar
 
 using namespace somar;
@@ -192,6 +217,7 @@ int somar_leptic_destroy(SomarLeptic* S) {
     for (SomarField* f : {S->phiTotal, S->vertPhi, S->rhsA, S->rhsB, S->bdryLo, S->bdryHi, S->excess, S->flatRhs,
                           S->flatPhi, S->res, S->hPhi, S->hRhs})
         field_free(f);
+    cudaFree(S->gsend); cudaFree(S->gall); cudaFree(S->gdense);
     if (S->ev0) cudaEventDestroy(S->ev0);
     if (S->ev1) cudaEventDestroy(S->ev1);
     somar_level_destroy(S->horiz);
@@ -205,7 +231,6 @@ int somar_leptic_create(SomarLevel* L, const SomarLepticParams* prm, SomarLeptic
     if (!L->finalized) { set_error("leptic: the level is not finalized"); return SOMAR_ERR_ARG; }
     const SomarLevelDesc& D = L->desc;
     const int nd = D.dim, vd = nd - 1;
-    if (D.nranks > 1) { set_error("leptic solver: one rank only"); return SOMAR_ERR_ARG; }
     if (!D.is_diagonal) { set_error("leptic solver: diagonal metrics only (levelVertHorizGradient / MAPPEDMACGRAD not built)"); return SOMAR_ERR_ARG; }
     if (D.periodic[vd]) { set_error("leptic solver: the vertical direction is periodic (LevelLepticSolver.cpp:1316)"); return SOMAR_ERR_ARG; }
     if (prm->max_order < 0 || prm->max_order > 14) { set_error("leptic solver: max_order must be in 0..14"); return SOMAR_ERR_ARG; }
@@ -238,7 +263,7 @@ int somar_leptic_create(SomarLevel* L, const SomarLepticParams* prm, SomarLeptic
         dv.beta = 1.0;
         SomarSolverParams pv = prm->full;
         pv.bottom_normType = prm->norm_type;   // :274
-        if ((rc = somar_level_create(&dv, &pv, L->device, nullptr, &S->vert))) return fail(rc);
+        if ((rc = level_create_impl(&dv, &pv, L->device, nullptr, L->comm, &S->vert))) return fail(rc);
         Depth& src = L->depths[0];
         Depth& dst = S->vert->depths[0];
         if (src.g.total != dst.g.total) { set_error("leptic: vertical level layout differs"); return fail(SOMAR_ERR_ARG); }
@@ -286,27 +311,65 @@ int somar_leptic_create(SomarLevel* L, const SomarLepticParams* prm, SomarLeptic
         dh.nboxes = (int)(lo.size() / 3);
         dh.box_lo = lo.data();
         dh.box_hi = hi.data();
-        dh.box_rank = nullptr;
+        dh.box_rank = nullptr;                 // the whole flattened domain on this rank (replicated when nranks > 1)
+        dh.rank = 0;
+        dh.nranks = 1;
         SomarSolverParams ph = prm->horiz;
         ph.bottom_normType = prm->norm_type;   // :387
-        if ((rc = somar_level_create(&dh, &ph, L->device, nullptr, &S->horiz))) return fail(rc);
-        // vertically averaged J g^{00}, J g^{11}: scale = 1 / Nz (LevelGeometryBasics.cpp:545-568)
-        const long long n0 = (long long)(g.n[0] + 1) * g.n[1], n1 = (long long)g.n[0] * (g.n[1] + 1), nc = (long long)g.n[0] * g.n[1];
-        double* dense = nullptr;
-        if (cudaMalloc(&dense, sizeof(double) * (n0 + n1 + nc)) != cudaSuccess) { set_error("leptic: out of device memory"); return fail(SOMAR_ERR_CUDA); }
+        if ((rc = level_create_impl(&dh, &ph, L->device, nullptr, nullptr, &S->horiz))) return fail(rc);
+        const int nxg = g.gn[0], nyg = g.gn[1];
+        if (D.nranks > 1) {
+            S->row0.assign(D.nranks, 1 << 30);
+            S->rows.assign(D.nranks, 0);
+            std::vector<int> top(D.nranks, -1);
+            for (int b = 0; b < D.nboxes; ++b) {
+                const int r = L->box_rank[b];
+                S->row0[r] = std::min(S->row0[r], L->box_lo[3 * b + 1]);
+                top[r] = std::max(top[r], L->box_hi[3 * b + 1]);
+            }
+            for (int r = 0; r < D.nranks; ++r) {
+                if (top[r] < 0) { set_error("leptic: a rank owns no box"); return fail(SOMAR_ERR_ARG); }
+                S->rows[r] = top[r] - S->row0[r] + 1;
+                S->maxRows = std::max(S->maxRows, S->rows[r]);
+            }
+            const size_t chunk = (size_t)(S->maxRows + 1) * (size_t)(nxg + 1);
+            if (cudaMalloc(&S->gsend, chunk * sizeof(double)) != cudaSuccess ||
+                cudaMalloc(&S->gall, chunk * D.nranks * sizeof(double)) != cudaSuccess ||
+                cudaMalloc(&S->gdense, (size_t)(nyg + 1) * (nxg + 1) * sizeof(double)) != cudaSuccess) {
+                set_error("leptic: out of device memory (gather buffers)");
+                return fail(SOMAR_ERR_CUDA);
+            }
+        }
+        // vertically averaged J g^{00}, J g^{11}: scale = 1 / Nz (LevelGeometryBasics.cpp:545-568), on this rank's rows
+        const long long n0 = (long long)(g.n[0] + 1) * g.n[1], n1 = (long long)g.n[0] * (g.n[1] + 1);
+        const long long G0 = (long long)(nxg + 1) * nyg, G1 = (long long)nxg * (nyg + 1), GC = (long long)nxg * nyg;
+        double *dense = nullptr, *glob = nullptr;
+        if (cudaMalloc(&dense, sizeof(double) * (n0 + n1)) != cudaSuccess || cudaMalloc(&glob, sizeof(double) * (G0 + G1 + GC)) != cudaSuccess) {
+            cudaFree(dense);
+            set_error("leptic: out of device memory");
+            return fail(SOMAR_ERR_CUDA);
+        }
         cudaStream_t st = S->vert->cx.stream;
         const double scale = 1.0 / (double)g.n[2];
         const Depth& dv = S->vert->depths[0];
         k_vert_avg_dense<<<plane_grid(g, 1, 0), QTPB, 0, st>>>(g, dense, dv.jg[0][0], 1, 0, scale);
         k_vert_avg_dense<<<plane_grid(g, 0, 1), QTPB, 0, st>>>(g, dense + n0, dv.jg[1][1], 0, 1, scale);
-        k_fill_dense<<<64, 256, 0, st>>>(dense + n0 + n1, nc, 1.0);   // "because we are solving L[phi] = J*rhs" (:428-430)
+        k_fill_dense<<<64, 256, 0, st>>>(glob + G0 + G1, GC, 1.0);   // "because we are solving L[phi] = J*rhs" (:428-430)
         S->vert->cx.launches += 3;
+        rc = SOMAR_OK;
+        if (D.nranks > 1) {
+            rc = gather_rows(S, dense, g.n[0] + 1, nxg + 1, 0, glob);
+            if (!rc) rc = gather_rows(S, dense + n0, g.n[0], nxg, 1, glob + G0);
+        } else {
+            cudaMemcpyAsync(glob, dense, sizeof(double) * (n0 + n1), cudaMemcpyDeviceToDevice, st);
+        }
         cudaError_t ce = cudaStreamSynchronize(st);
-        if (ce == cudaSuccess) {
-            rc = somar_level_set_metric_device(S->horiz, 1, dense, dense + n0, nullptr, dense + n0 + n1);
+        if (!rc && ce == cudaSuccess) {
+            rc = somar_level_set_metric_device(S->horiz, 1, glob, glob + G0, nullptr, glob + G0 + G1);
             if (!rc) rc = somar_level_finalize(S->horiz);
         }
         cudaFree(dense);
+        cudaFree(glob);
         if (ce != cudaSuccess) { set_error(std::string("leptic: ") + cudaGetErrorString(ce)); return fail(SOMAR_ERR_CUDA); }
         if (rc) return fail(rc);
         if ((rc = field_alloc(S->horiz, 0, &S->hPhi)) || (rc = field_alloc(S->horiz, 0, &S->hRhs))) return fail(rc);
@@ -390,14 +453,21 @@ int somar_leptic_solve(SomarLeptic* S, SomarField* phi, const SomarField* rhs, i
         if ((rc = leptic_vertical_solve(V, S->vertPhi, rhsP, S->vertBC[0], S->vertBC[1], dz, S->bdryLo, S->bdryHi))) return rc;
 
         if (useHoriz) {
-            // flatRhs = computeHorizRHS [- excess / H] (:800-808)
+            // flatRhs = computeHorizRHS [- excess / H] (:800-808); "this exchanges vertPhi" (:1006)
+            if ((rc = exchange(V, 0, S->vertPhi->p, 1))) return rc;
             k_horiz_rhs<<<plane_grid(g), QTPB, 0, vs>>>(g, S->flatRhs->p, S->vertPhi->p, dv.jg[0][0], dv.jg[1][1],
                                                         useExcess ? S->excess->p : nullptr, -1.0 / H, 1.0 / (double)g.n[2]);
             V->cx.launches++;
             // to the horizontal grids (:811-812)
             const Geom& gh = Hz->depths[0].g;
-            SOMAR_CUDA(cudaMemcpy2DAsync(S->hRhs->p + gh.idx(0, 0, 0), gh.sy * sizeof(double), S->flatRhs->p + g.idx(0, 0, 0),
-                                         g.sy * sizeof(double), g.n[0] * sizeof(double), g.n[1], cudaMemcpyDeviceToDevice, vs));
+            if (V->desc.nranks > 1) {
+                if ((rc = gather_rows(S, S->flatRhs->p + g.idx(0, 0, 0), g.sy, gh.n[0], 0, S->gdense))) return rc;
+                SOMAR_CUDA(cudaMemcpy2DAsync(S->hRhs->p + gh.idx(0, 0, 0), gh.sy * sizeof(double), S->gdense,
+                                             gh.n[0] * sizeof(double), gh.n[0] * sizeof(double), gh.n[1], cudaMemcpyDeviceToDevice, vs));
+            } else {
+                SOMAR_CUDA(cudaMemcpy2DAsync(S->hRhs->p + gh.idx(0, 0, 0), gh.sy * sizeof(double), S->flatRhs->p + g.idx(0, 0, 0),
+                                             g.sy * sizeof(double), g.n[0] * sizeof(double), g.n[1], cudaMemcpyDeviceToDevice, vs));
+            }
             if ((rc = sync(V))) return rc;
             double hnorm = 0.0;
             if ((rc = norm_of(Hz, S->hRhs, P.norm_type, &hnorm))) return rc;
@@ -411,10 +481,11 @@ int somar_leptic_solve(SomarLeptic* S, SomarField* phi, const SomarField* rhs, i
             st->horiz_iters_total += hs.iters;
             st->horiz_solves++;
             // setZeroAvg: the flattened boxes cover the horizontal domain (:410-433)
-            launch_reduce(Hz->cx, gh, S->hPhi->p, nullptr, 5, Hz->d_scal + 5);
-            k_sub_scalar<<<plane_grid(gh), QTPB, 0, Hz->cx.stream>>>(gh, S->hPhi->p, Hz->d_scal + 5, (double)gh.cells());
+            double hsum = 0.0;
+            if ((rc = reduce_global(Hz, 0, S->hPhi->p, nullptr, 5, &hsum))) return rc;   // (the whole horizontal domain is here)
+            k_sub_scalar<<<plane_grid(gh), QTPB, 0, Hz->cx.stream>>>(gh, S->hPhi->p, hsum / ((double)gh.gn[0] * (double)gh.gn[1]));
             Hz->cx.launches++;
-            SOMAR_CUDA(cudaMemcpy2DAsync(S->flatPhi->p + g.idx(0, 0, 0), g.sy * sizeof(double), S->hPhi->p + gh.idx(0, 0, 0),
+            SOMAR_CUDA(cudaMemcpy2DAsync(S->flatPhi->p + g.idx(0, 0, 0), g.sy * sizeof(double), S->hPhi->p + gh.idx(0, g.g0[1], 0),
                                          gh.sy * sizeof(double), g.n[0] * sizeof(double), g.n[1], cudaMemcpyDeviceToDevice,
                                          Hz->cx.stream));
             if ((rc = sync(Hz))) return rc;

@@ -77,6 +77,7 @@ struct SomarLevel {
     int box_size[3];                   // uniform tiling size at depth 0 (0 = not uniform)
     // communication
     ncclComm_t comm = nullptr;
+    bool comm_borrowed = false;        // the communicator belongs to another level (leptic solver's derived levels)
     // scalars
     double* d_scal = nullptr;          // 8 doubles on device
     double* h_scal = nullptr;          // pinned mirror
@@ -154,6 +155,9 @@ void set_error(const std::string& s);
         }                                                                                                   \
     } while (0)
 
+// capi.cu
+int level_create_impl(const SomarLevelDesc* desc, const SomarSolverParams* params, int device,
+                      const unsigned char* comm_id, ncclComm_t borrowed, SomarLevel** out);
 // level.cu
 int level_build(SomarLevel* L);                      // schedule + allocation
 int level_finalize(SomarLevel* L);                   // coarse metrics, lapDiag, null-space probe

@@ -85,8 +85,8 @@ def main():
     diag = spec.is_diagonal
     per = (0, int(periodic_y), 0)
 
-    def make(nranks, rk, cid, yr, **extra):
-        lev = capi.Level(n, spec.dx, dim=3, periodic=per, is_diagonal=diag, boxes=boxes,
+    def make(nranks, rk, cid, yr, bc_type=None, **extra):
+        lev = capi.Level(n, spec.dx, dim=3, periodic=per, is_diagonal=diag, boxes=boxes, bc_type=bc_type,
                          box_rank=(box_rank if nranks > 1 else [0] * NB),
                          params=capi.default_params(**{**SOLVE, **extra}),
                          device=local, rank=rk, nranks=nranks, comm_id=cid)
@@ -157,6 +157,22 @@ def main():
         return {"relax_loose": fp.get()}
     if diag:
         mine.update(loose(make(world, rank, new_comm_id(), (j0, j1), relaxMode=2), (j0, j1)))
+    # the leptic solver across ranks (diagonal metric, non-periodic): vertical solves are rank-local, the flattened
+    # horizontal level and the fall-back level are partitioned like the level and borrow its communicator
+    def leptic(nranks, rk, sl):
+        out = {}
+        for tag, bc, kw in [("diri", [0, 0, 0, 0, 0, 1], dict(max_order=2)), ("neum", [0] * 6, dict(max_order=1))]:
+            lv = make(nranks, rk, new_comm_id() if nranks > 1 else None, sl, bc_type=bc)
+            ls = capi.LepticSolver(lv, capi.leptic_default_params(**kw))
+            fphi, frhs = lv.field(0), lv.field(0, np.ascontiguousarray(rhs_g.numpy()[:, sl[0]:sl[1]]))
+            st = ls.solve(fphi, frhs, homogeneous=True)
+            out["leptic_" + tag] = fphi.get()
+            out["norms_leptic_" + tag] = np.array(st["res_norms"] + [st["exit_status"], st["horiz_solves"]])
+            lv.destroy()
+        return out
+    do_leptic = diag and not periodic_y
+    if do_leptic:
+        mine.update(leptic(world, rank, (j0, j1)))
     # gather the slabs on rank 0
     gathered = [None] * world
     dist.gather_object(mine, gathered if rank == 0 else None, dst=0)
@@ -167,6 +183,8 @@ def main():
         ref.update(solve(make(1, 0, None, (0, n[1]), **STRICT), (0, n[1]), "_strict"))
         if diag:
             ref.update(loose(make(1, 0, None, (0, n[1]), relaxMode=2), (0, n[1])))
+        if do_leptic:
+            ref.update(leptic(1, 0, (0, n[1])))
         for key in ref:
             if key.startswith(("norm", "iters", "history")):
                 got = gathered[0][key]
@@ -179,6 +197,10 @@ def main():
                 good = np.array_equal(got, want)            # bit-exact: same arithmetic, halos instead of neighbours
             elif key.startswith("iters"):
                 good = abs(int(got[0]) - int(want[0])) <= 1
+            elif key.startswith("norms_leptic"):
+                good = bool(np.allclose(got, want, rtol=1e-8, atol=1e-12 * np.abs(want).max()))
+            elif key == "leptic_neum":                      # one horizontal multigrid solve to 1e-12
+                good = np.abs(got - want).max() <= 1e-8 * np.abs(want).max()
             elif key == "history":
                 # same tolerance as the single-rank history test (tests/test_gpu_solve.py): the unconverged
                 # BiCGStab bottom amplifies summation-order differences (measured on the terrain case: the residual
