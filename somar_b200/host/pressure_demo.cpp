@@ -55,13 +55,16 @@ int main(int argc, char** argv) {
     if (argc >= 4)
         for (int d = 0; d < 3; ++d) n[d] = std::atoi(argv[1 + d]);
     const int relaxMode = (argc >= 5) ? std::atoi(argv[4]) : SOMAR_RELAX_LEVEL_GSRB;
-    const double aniso = 4.0;
+    // "leptic": a thin domain (dx / H = 4) with a Dirichlet top, solved by LevelLepticSolver instead of multigrid
+    const bool leptic = argc >= 6 && std::string(argv[5]) == "leptic";
+    const double aniso = leptic ? 4.0 * n[2] : 4.0;
     try {
         // ---- geometry: 2 x 2 x 1 boxes, all on this rank -------------------------------------------------------
         LevelGeometryDesc geo;
         geo.n = n;
         geo.dx = {{1.0 / n[0], 1.0 / n[0], 1.0 / (aniso * n[0])}};
         const double Hc = geo.dx[2] * n[2];   // computational depth
+        if (leptic) geo.bcType[5] = SOMAR_BC_DIRI;
         for (int by = 0; by < 2; ++by)
             for (int bx = 0; bx < 2; ++bx) {
                 geo.boxLo.push_back({{bx * n[0] / 2, by * n[1] / 2, 0}});
@@ -117,6 +120,25 @@ int main(int argc, char** argv) {
         op.applyOp(dRhs, dStar, true);
         dRhs.copyTo(vRhs);
 
+        if (leptic) {
+            // ---- LevelLepticSolver::define(op) + solve(phi, rhs) on device fields (LevelLepticSolver.cpp:147,646) ----
+            LevelLepticSolver ls;
+            ls.define(lev, true);
+            Field dPhi(lev, 0);
+            op.setToZero(dPhi);
+            const SomarLepticStats ls_st = ls.solve(dPhi, dRhs);
+            const std::vector<double> nr = ls.resNorms();
+            bool falling = nr.size() >= 2;
+            for (size_t q = 1; q < nr.size(); ++q) falling = falling && nr[q] < 0.5 * nr[q - 1];
+            op.incr(dPhi, dStar, -1.0);
+            const double err = op.norm(dPhi, 0), ref = op.norm(dStar, 0);
+            std::printf("leptic solver %dx%dx%d: %d orders, exit status %s, |r|/|r0| = %.3e, max |phi - phi*| / max |phi*| = %.3e, "
+                        "%.2f ms, %lld launches\n", n[0], n[1], n[2], ls_st.orders, ls.exitStatusStr(), nr.back() / nr.front(),
+                        err / ref, ls_st.solve_ms, ls_st.launches);
+            const bool ok = falling && ls_st.exit_status != 4 && nr.back() <= 1e-3 * nr.front() && err <= 1e-2 * ref;
+            std::printf(ok ? "DEMO-OK\n" : "DEMO-FAILED\n");
+            return ok ? 0 : 1;
+        }
         // ---- the projector's call ---------------------------------------------------------------------------
         const SomarSolveStats st = solver.levelSolve(vPhi, vRhs, true, false);
 

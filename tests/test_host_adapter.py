@@ -30,7 +30,8 @@ def test_adapter_builds_and_has_no_cpu_fallback():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("args", [["64", "64", "32", "1"], ["64", "64", "32", "3"], ["48", "96", "16", "1"]])
+@pytest.mark.parametrize("args", [["64", "64", "32", "1"], ["64", "64", "32", "3"], ["48", "96", "16", "1"],
+                                  ["64", "64", "16", "1", "leptic"]])      # adapter's LevelLepticSolver on a thin domain
 def test_pressure_demo_recovers_manufactured_solution(args):
     if not os.path.exists(DEMO):
         _build()
