@@ -148,6 +148,7 @@ int somar_level_destroy(SomarLevel* L) {
     for (auto* f : L->bwork) if (f) { cudaFree(f->p); delete f; }
     for (auto* f : L->swork) if (f) { cudaFree(f->p); delete f; }
     if (L->pwork) { cudaFree(L->pwork->p); delete L->pwork; }
+    cudaFree(L->zeroPlane);
     for (auto* f : L->awork) if (f) { cudaFree(f->p); delete f; }
     halo_p2p_free(L);   // (collective: needs the communicator)
     if (L->comm && !L->comm_borrowed) ncclCommDestroy(L->comm);

@@ -111,6 +111,7 @@ struct Lane {
     int x0, y;              // local x of column 0, local y of my row
     int k0, k1;             // z chunk [k0, k1)
     int isz;                // plane stride of the brick (elements)
+    int psz, cb;            // plane stride of the phi INPUT (0: every plane is the level's zero plane), my pair in plane 0
     int own, cown;          // my pair in a phi plane / in a coefficient plane (element index)
     int ctr;                // start of my row in a phi plane
     int redMask, coreMask;  // bit p: column 2t+p takes part in red updates / is a core cell
@@ -203,13 +204,14 @@ __device__ __forceinline__ void sweep_step(const Geom& g, const Metric& m, const
     }
     if (k + 3 <= L.k1 + 1) {
         const long long o = s.gk + 3 * L.isz;
+        const long long po = L.cb + (long long)(k + 3) * L.psz;
         const uint32_t d = L.sRow + OFF_PHI + wrap(s.i5 + 4, NPHI) * PHI_BYTES + ROWB;
         if (L.rowOk) {
-            copy16(d, phi + o);
+            copy16(d, phi + po);
             copy16(L.sRow + OFF_ZF + wrap(s.i4 + 3, NZF) * ZF_BYTES, m.jg[2][2] + o);
         }
-        if (L.r == 0 && L.y - 1 >= -g.gh[1]) copy16(d - ROWB, phi + o - g.sy);
-        if (L.r == EY - 1 && L.rowUp) copy16(d + ROWB, phi + o + g.sy);
+        if (L.r == 0 && L.y - 1 >= -g.gh[1]) copy16(d - ROWB, phi + po - g.sy);
+        if (L.r == EY - 1 && L.rowUp) copy16(d + ROWB, phi + po + g.sy);
     }
     copy_commit();
     copy_wait<1>();            // my copies of the previous group (data of step k+1) have landed
@@ -268,7 +270,7 @@ __device__ __forceinline__ void sweep_step(const Geom& g, const Metric& m, const
 
 __global__ void __launch_bounds__(NTHREADS, 1)
 k_gsrb_async(const Geom g, const Metric m, double* __restrict__ phiOut, const double* __restrict__ phi,
-             const double* __restrict__ rhs, int kc) {
+             const double* __restrict__ rhs, int kc, int phiPlaneStride) {
     extern __shared__ __align__(1024) unsigned char smem[];
     uint64_t* const redDone = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
     uint64_t* const empty = redDone + 1;
@@ -283,6 +285,7 @@ k_gsrb_async(const Geom g, const Metric m, double* __restrict__ phiOut, const do
     L.k0 = blockIdx.z * kc;
     L.k1 = min(L.k0 + kc, g.n[2]);
     L.isz = (int)g.sz;
+    L.psz = phiPlaneStride;
     const int k0 = L.k0;
 
     if (tid == 0) {
@@ -296,11 +299,12 @@ k_gsrb_async(const Geom g, const Metric m, double* __restrict__ phiOut, const do
     L.rowOk = (L.y >= -g.gh[1]) && (L.y < g.n[1] + g.gh[1]);
     L.rowUp = (L.y + 1 < g.n[1] + g.gh[1]);                     // row y+1 exists (y+1 >= -gh always)
     const int cbase = (int)g.idx(L.x0 + 2 * L.t, L.y, 0);       // my pair in plane 0 (brick index)
+    L.cb = cbase;
     L.sRow = smem_u32(smem) + L.r * ROWB + 16 * L.t;
     // planes k0-2 .. k1+1 exist in the brick (two ghost planes: gsrb_async_usable)
     auto load_phi = [&](int p) {        // phi rows y0-1 .. y0+16: mine is r+1; warps 0 and 15 add the outer rows
         const uint32_t d = L.sRow + OFF_PHI + ((p - (k0 - 2)) % NPHI) * PHI_BYTES + ROWB;
-        const double* s = phi + cbase + (long long)p * L.isz;
+        const double* s = phi + cbase + (long long)p * L.psz;
         if (L.rowOk) copy16(d, s);
         if (L.r == 0 && L.y - 1 >= -g.gh[1]) copy16(d - ROWB, s - g.sy);
         if (L.r == EY - 1 && L.rowUp) copy16(d + ROWB, s + g.sy);
@@ -392,8 +396,10 @@ bool gsrb_async_usable(const Geom& g, const Metric& m) {
     return true;
 }
 
+// zeroPlane != nullptr: the input is identically zero and is not read from phiIn at all -- every input plane is
+// the level's (L2-resident) zero plane, plane stride 0 (the first relaxation of a V-cycle visit)
 bool launch_gsrb_async(Ctx& cx, const Geom& g, const Metric& m, double* phiOut, const double* phiIn,
-                       const double* rhs) {
+                       const double* rhs, const double* zeroPlane) {
     static bool attr = false;
     if (!attr) {
         if (cudaFuncSetAttribute(k_gsrb_async, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES) != cudaSuccess) {
@@ -421,7 +427,8 @@ bool launch_gsrb_async(Ctx& cx, const Geom& g, const Metric& m, double* phiOut, 
         if (best < 0) kc = 64;
     }
     dim3 grid((g.n[0] + CX - 1) / CX, (g.n[1] + CY - 1) / CY, (g.n[2] + kc - 1) / kc);
-    k_gsrb_async<<<grid, NTHREADS, SMEM_BYTES, cx.stream>>>(g, m, phiOut, phiIn, rhs, kc);
+    k_gsrb_async<<<grid, NTHREADS, SMEM_BYTES, cx.stream>>>(g, m, phiOut, zeroPlane ? zeroPlane : phiIn, rhs, kc,
+                                                            zeroPlane ? 0 : (int)g.sz);
     cx.launches++;
     return true;
 }

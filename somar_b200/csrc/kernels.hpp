@@ -34,7 +34,7 @@ void launch_gsrb_fused(Ctx& cx, const Geom& g, const Metric& m, double* phiOut, 
 // Returns false (nothing launched) if the kernel cannot get its shared memory.
 bool gsrb_async_usable(const Geom& g, const Metric& m);
 bool launch_gsrb_async(Ctx& cx, const Geom& g, const Metric& m, double* phiOut, const double* phiIn,
-                       const double* rhs);
+                       const double* rhs, const double* zeroPlane = nullptr);
 // full metric: out-of-place pass, phiOut gets the updated colour AND a copy of the other colour
 void launch_gsrb_full(Ctx& cx, const Geom& g, const Metric& m, double* phiOut, const double* phiIn,
                       const double* rhs, int pass);

@@ -301,10 +301,29 @@ static int ensure_line(SomarLevel* L, Depth& dp) {
 }
 
 // MappedAMRPoissonOp::relax -- MappedAMRPoissonOp.cpp:1733-1743 -> RelaxationMethod::relax
-int op_relax(SomarLevel* L, int depth, SomarField* phi, const SomarField* rhs, int iters, int modeOverride) {
+int op_relax(SomarLevel* L, int depth, SomarField* phi, const SomarField* rhs, int iters, int modeOverride, bool phiIsZero) {
     Depth& dp = L->depths[depth];
     const int mode = (modeOverride != -100) ? modeOverride : L->prm.relaxMode;
     int rc;
+    // phiIsZero: the caller skipped "set the correction to zero".  The pipelined smoother then takes every input plane
+    // of its first iteration from the level's zero plane (no DRAM read of phi, no fill pass, no halo exchange: every
+    // rank's phi is zero); any other smoother gets the fill it would have had.
+    bool zeroIn = false;
+    if (phiIsZero) {
+        zeroIn = iters > 0 && mode == SOMAR_RELAX_LEVEL_GSRB && L->use_fused == 2 && gsrb_async_usable(dp.g, dp.m);
+        if (zeroIn && !L->zeroPlane) {
+            const Geom& g0 = L->depths[0].g;
+            const size_t nz = (size_t)(g0.off0 + g0.sz);
+            if (cudaMalloc(&L->zeroPlane, nz * sizeof(double)) != cudaSuccess ||
+                cudaMemsetAsync(L->zeroPlane, 0, nz * sizeof(double), L->cx.stream) != cudaSuccess) {
+                (void)cudaGetLastError();
+                cudaFree(L->zeroPlane);
+                L->zeroPlane = nullptr;
+                zeroIn = false;
+            }
+        }
+        if (!zeroIn) launch_fill(L->cx, dp.g, phi->p, 0.0);
+    }
     const bool coarse = depth > 0 && depth < L->ndepths() - 1;
     ProfScope psCoarse(L, coarse ? PH_SMOOTH_COARSE : -1);
     for (int it = 0; it < iters; ++it) {
@@ -315,9 +334,10 @@ int op_relax(SomarLevel* L, int depth, SomarField* phi, const SomarField* rhs, i
             // metric's ghost rows were filled at finalize, the right-hand side's are filled here once.
             const bool ranks = dp.g.nbr[0] >= 0 || dp.g.nbr[1] >= 0;
             if (ranks && it == 0 && (rc = exchange(L, depth, const_cast<double*>(rhs->p), 1)) != SOMAR_OK) return rc;
-            if (ranks && (rc = exchange(L, depth, phi->p, 2)) != SOMAR_OK) return rc;
+            const bool fromZero = zeroIn && it == 0;
+            if (ranks && !fromZero && (rc = exchange(L, depth, phi->p, 2)) != SOMAR_OK) return rc;
             ProfScope psK(L, depth == 0 ? PH_SMOOTH0_KERNEL : -1);
-            if (!launch_gsrb_async(L->cx, dp.g, dp.m, dp.tmp, phi->p, rhs->p)) {
+            if (!launch_gsrb_async(L->cx, dp.g, dp.m, dp.tmp, phi->p, rhs->p, fromZero ? L->zeroPlane : nullptr)) {
                 set_error("relax: k_gsrb_async could not reserve its shared memory");
                 return SOMAR_ERR_CUDA;
             }

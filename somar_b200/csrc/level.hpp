@@ -97,6 +97,7 @@ struct SomarLevel {
     // outer-solve work fields (depth 0)
     std::vector<SomarField*> swork;
     std::vector<SomarField*> awork;    // advection: WMinus/WPlus/WHalf scratch (depth 0, allocated on first use)
+    double* zeroPlane = nullptr;       // off0 + sz zeros of depth 0: the input of a relaxation that starts from phi = 0
     SomarField* pwork = nullptr;       // projector: the divergence / right-hand side (depth 0)
     double bottomMetric = 0.0, bottomEps = 1e-6;
     int bottom_iters_total = 0;
@@ -164,13 +165,14 @@ int level_finalize(SomarLevel* L);                   // coarse metrics, lapDiag,
 int field_alloc(SomarLevel* L, int depth, SomarField** out);
 int exchange(SomarLevel* L, int depth, double* x, int width);
 int op_apply(SomarLevel* L, int depth, double* out, SomarField* phi, const double* rhs, int mode, bool homog);
-int op_relax(SomarLevel* L, int depth, SomarField* phi, const SomarField* rhs, int iters, int modeOverride = -100);
+int op_relax(SomarLevel* L, int depth, SomarField* phi, const SomarField* rhs, int iters, int modeOverride = -100,
+             bool phiIsZero = false);   // phiIsZero: phi is logically zero and its memory has NOT been cleared
 int op_precond(SomarLevel* L, int depth, SomarField* cor, const SomarField* res);
 int op_restrict(SomarLevel* L, int depth, SomarField* crse, SomarField* phi, const SomarField* rhs);
 int op_prolong(SomarLevel* L, int depth, SomarField* phi, const SomarField* crse);
 int reduce_global(SomarLevel* L, int depth, const double* x, const double* y, int kind, double* out);
 // solver.cu
-int mg_cycle(SomarLevel* L, int depth, SomarField* e, const SomarField* r);
+int mg_cycle(SomarLevel* L, int depth, SomarField* e, const SomarField* r, bool eIsZero = false);
 int bottom_solve(SomarLevel* L, SomarField* e, const SomarField* r, int* iters);
 bool bottom_persistent_usable(SomarLevel* L);
 int bottom_persistent(SomarLevel* L, SomarField* e, const SomarField* r);

@@ -11,13 +11,14 @@ namespace somar {
 
 static inline Geom& G(SomarLevel* L, int d) { return L->depths[d].g; }
 
-int mg_cycle(SomarLevel* L, int depth, SomarField* e, const SomarField* r) {
+int mg_cycle(SomarLevel* L, int depth, SomarField* e, const SomarField* r, bool eIsZero) {
     const SomarSolverParams& p = L->prm;
     int rc;
     if (depth == L->ndepths() - 1) {
         const Geom& g = G(L, depth);
         const long long bottomCells = (long long)g.gn[0] * g.gn[1] * g.gn[2];
         ProfScope ps(L, PH_BOTTOM);
+        if (eIsZero) launch_fill(L->cx, g, e->p, 0.0);
         if (bottomCells == 1) return op_relax(L, depth, e, r, 1);                       // :566-568
         if (bottom_persistent_usable(L)) return bottom_persistent(L, e, r);             // both steps, one launch
         if (bottom_gathered_usable(L)) return bottom_gathered(L, e, r);                 // the same on the replicated depth
@@ -31,6 +32,7 @@ int mg_cycle(SomarLevel* L, int depth, SomarField* e, const SomarField* r) {
     int cycles = p.numMG;
     if (cycles < 0) {   // F-cycle branch :578-619
         cycles = -cycles;
+        if (eIsZero) launch_fill(L->cx, G(L, depth), e->p, 0.0);
         if ((rc = op_restrict(L, depth, nx.res, e, r))) return rc;
         launch_fill(L->cx, nx.g, nx.cor->p, 0.0);
         if ((rc = mg_cycle(L, depth + 1, nx.cor, nx.res))) return rc;
@@ -48,14 +50,15 @@ int mg_cycle(SomarLevel* L, int depth, SomarField* e, const SomarField* r) {
         }
         return op_relax(L, depth, e, r, p.num_smooth_up);
     }
-    if ((rc = op_relax(L, depth, e, r, p.num_smooth_down))) return rc;                 // :622
+    if ((rc = op_relax(L, depth, e, r, p.num_smooth_down, -100, eIsZero))) return rc;  // :622
     {
         ProfScope ps(L, PH_RESTRICT);
         if ((rc = op_restrict(L, depth, nx.res, e, r))) return rc;                     // :628
-        launch_fill(L->cx, nx.g, nx.cor->p, 0.0);                                       // :629
     }
+    // "set the coarse correction to zero" (:629) is handed down: the first consumer clears it, or -- the pipelined
+    // smoother -- never reads it
     for (int img = 0; img < cycles; ++img)
-        if ((rc = mg_cycle(L, depth + 1, nx.cor, nx.res))) return rc;                   // :631-633
+        if ((rc = mg_cycle(L, depth + 1, nx.cor, nx.res, img == 0))) return rc;         // :631-633
     {
         ProfScope ps(L, PH_PROLONG);
         if ((rc = op_prolong(L, depth, e, nx.cor))) return rc;                         // :638
@@ -78,7 +81,7 @@ int mg_solve(SomarLevel* L, SomarField* phi, const SomarField* rhs, bool zeroPhi
     SomarField *corr = L->swork[0], *resid = L->swork[1], *best = L->swork[2];
     const long long launches0 = cx.launches;
     SOMAR_CUDA(cudaEventRecord(L->ev0, cx.stream));
-    launch_fill(cx, g, corr->p, 0.0);
+    // (the correction's "set to zero" before every V-cycle, MappedAMRMultiGrid.H:1064,1215, is handed to mg_cycle)
     if (zeroPhi) launch_fill(cx, g, phi->p, 0.0);
     launch_copy(cx, g, best->p, phi->p);
     auto computeResidual = [&](double* out) {
@@ -103,11 +106,10 @@ int mg_solve(SomarLevel* L, SomarField* phi, const SomarField* rhs, bool zeroPhi
     bool goHang = iter < p.imin || rnorm < (1 - p.hang) * norm_last;
     while (goIter && goRedu && goHang && goNorm) {
         norm_last = rnorm;
-        if ((rc = mg_cycle(L, 0, corr, resid))) return rc;       // AMRVCycle, single level
+        if ((rc = mg_cycle(L, 0, corr, resid, true))) return rc; // AMRVCycle, single level; corr = 0 on entry
         {
             ProfScope ps(L, PH_OUTER);
             launch_axpy(cx, g, phi->p, corr->p, 1.0);             // postVCycleOps
-            launch_fill(cx, g, corr->p, 0.0);
             if ((rc = computeResidual(&rnorm))) return rc;
             ++iter;
             if (hl < 128) st->history[hl++] = rnorm;
