@@ -74,16 +74,19 @@ int mg_solve(SomarLevel* L, SomarField* phi, const SomarField* rhs, bool zeroPhi
     Ctx& cx = L->cx;
     int rc;
     if (L->swork.empty()) {
-        L->swork.resize(3, nullptr);
+        L->swork.resize(4, nullptr);
         for (auto& f : L->swork)
             if ((rc = field_alloc(L, 0, &f))) return rc;
     }
-    SomarField *corr = L->swork[0], *resid = L->swork[1], *best = L->swork[2];
+    SomarField *corr = L->swork[0], *resid = L->swork[1], *best = L->swork[2], *spare = L->swork[3];
+    // Best-phi bookkeeping (MappedAMRMultiGrid.H:1105-1117) without copies: phi += corr is written out of place into
+    // `spare` and the buffers trade places, so the previous iterate survives for free.  While the newest iterate is
+    // the best one nothing is kept; when an iterate gets worse the previous one (still in `spare`) becomes `best`.
+    bool bestIsCurrent = true;
     const long long launches0 = cx.launches;
     SOMAR_CUDA(cudaEventRecord(L->ev0, cx.stream));
     // (the correction's "set to zero" before every V-cycle, MappedAMRMultiGrid.H:1064,1215, is handed to mg_cycle)
     if (zeroPhi) launch_fill(cx, g, phi->p, 0.0);
-    launch_copy(cx, g, best->p, phi->p);
     auto computeResidual = [&](double* out) {
         int r2 = op_apply(L, 0, resid->p, phi, rhs->p, 1, forceHomog);
         if (r2) return r2;
@@ -109,15 +112,18 @@ int mg_solve(SomarLevel* L, SomarField* phi, const SomarField* rhs, bool zeroPhi
         if ((rc = mg_cycle(L, 0, corr, resid, true))) return rc; // AMRVCycle, single level; corr = 0 on entry
         {
             ProfScope ps(L, PH_OUTER);
-            launch_axpy(cx, g, phi->p, corr->p, 1.0);             // postVCycleOps
+            launch_axby(cx, g, spare->p, phi->p, corr->p, 1.0, 1.0);   // postVCycleOps: phi + corr (1.0 * x is exact)
+            std::swap(spare->p, phi->p);                               // phi = the new iterate, spare = the previous one
             if ((rc = computeResidual(&rnorm))) return rc;
             ++iter;
             if (hl < 128) st->history[hl++] = rnorm;
             if (rnorm <= best_rnorm) {
                 best_rnorm = rnorm;
-                launch_copy(cx, g, best->p, phi->p);
+                bestIsCurrent = true;
                 useBest = false;
             } else {
+                if (bestIsCurrent) std::swap(best->p, spare->p);   // the previous iterate was the best one: keep it
+                bestIsCurrent = false;
                 useBest = true;
             }
         }
@@ -131,7 +137,7 @@ int mg_solve(SomarLevel* L, SomarField* phi, const SomarField* rhs, bool zeroPhi
     }
     if (useBest) {
         rnorm = best_rnorm;
-        launch_copy(cx, g, phi->p, best->p);
+        std::swap(phi->p, best->p);
     }
     SOMAR_CUDA(cudaEventRecord(L->ev1, cx.stream));
     SOMAR_CUDA(cudaEventSynchronize(L->ev1));
