@@ -17,6 +17,8 @@ struct Ctx {
 
 // ---- operator (stencil_ortho.cuh / stencil_full.cuh) ----
 // mode 0: out = (alpha + beta L) phi;  mode 1: out = rhs - (alpha + beta L) phi
+bool launch_residual_maxnorm(Ctx& cx, const Geom& g, const Metric& m, double* out, const double* phi, const double* rhs,
+                             bool homog, double* maxOut);
 void launch_apply(Ctx& cx, const Geom& g, const Metric& m, double* out, const double* phi, const double* rhs,
                   int mode, bool homog);
 // one colour pass of point Gauss-Seidel (pass 0 = red: (i+j+k) even in global indices)

@@ -290,6 +290,26 @@ int op_apply(SomarLevel* L, int depth, double* out, SomarField* phi, const doubl
     return SOMAR_OK;
 }
 
+// residual at depth 0 and its max-norm over all ranks (MappedAMRMultiGrid::computeAMRResidual + the norm of
+// solveNoInitResid, MappedAMRMultiGrid.H:793-839): one pass where k_march runs, else residual then k_reduce
+int residual_maxnorm(SomarLevel* L, SomarField* res, SomarField* phi, const SomarField* rhs, bool homog, double* out) {
+    Depth& dp = L->depths[0];
+    if (res->p == phi->p) { set_error("residual: lhs must not alias phi (MappedAMRPoissonOp.cpp:653)"); return SOMAR_ERR_ARG; }
+    int rc = exchange(L, 0, phi->p, 1);
+    if (rc != SOMAR_OK) return rc;
+    SOMAR_CUDA(cudaMemsetAsync(L->d_scal, 0, sizeof(double), L->cx.stream));
+    if (!launch_residual_maxnorm(L->cx, dp.g, dp.m, res->p, phi->p, rhs->p, homog, L->d_scal)) {
+        launch_apply(L->cx, dp.g, dp.m, res->p, phi->p, rhs->p, 1, homog);
+        return reduce_global(L, 0, res->p, nullptr, 0, out);
+    }
+    if (L->desc.nranks > 1)
+        SOMAR_NCCL(ncclAllReduce(L->d_scal, L->d_scal, 1, ncclDouble, ncclMax, L->comm, L->cx.stream));
+    SOMAR_CUDA(cudaMemcpyAsync(L->h_scal, L->d_scal, sizeof(double), cudaMemcpyDeviceToHost, L->cx.stream));
+    SOMAR_CUDA(cudaStreamSynchronize(L->cx.stream));
+    *out = L->h_scal[0];
+    return SOMAR_OK;
+}
+
 static int ensure_line(SomarLevel* L, Depth& dp) {
     if (dp.line_valid) return SOMAR_OK;
     int rc;

@@ -171,6 +171,7 @@ int op_precond(SomarLevel* L, int depth, SomarField* cor, const SomarField* res)
 int op_restrict(SomarLevel* L, int depth, SomarField* crse, SomarField* phi, const SomarField* rhs);
 int op_prolong(SomarLevel* L, int depth, SomarField* phi, const SomarField* crse);
 int reduce_global(SomarLevel* L, int depth, const double* x, const double* y, int kind, double* out);
+int residual_maxnorm(SomarLevel* L, SomarField* res, SomarField* phi, const SomarField* rhs, bool homog, double* out);
 // solver.cu
 int mg_cycle(SomarLevel* L, int depth, SomarField* e, const SomarField* r, bool eIsZero = false);
 int bottom_solve(SomarLevel* L, SomarField* e, const SomarField* r, int* iters);

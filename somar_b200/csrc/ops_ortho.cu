@@ -10,7 +10,7 @@ namespace somar {
 #define BY 4
 // k_march tuning, measured at 1024x1024x256 (unroll x CTAs/SM sweep): occupancy beats register comfort.
 // residual (modes 0/1): unroll 4, 4 CTAs/SM (64 regs): 3.91 -> 2.86 ms; restrict (mode 2): no unroll, 5 CTAs/SM: 4.21 -> 3.36 ms
-#define MARCH_UNROLL(MODE) ((MODE) == 2 ? 1 : 4)
+#define MARCH_UNROLL(MODE) ((MODE) == 2 ? 1 : 4)   // (MODE 3 = residual + max-norm: as MODE 1)
 #define MARCH_MINB(MODE) ((MODE) == 2 ? 5 : 4)
 
 // ---------------------------------------------------------------------------------------------------------
@@ -45,10 +45,15 @@ __global__ void __launch_bounds__(BX* BY) k_apply(const Geom g, const Metric m, 
 template <int MODE>
 __global__ void __launch_bounds__(BX* BY, MARCH_MINB(MODE)) k_march(const Geom g, const Metric m, const Geom gc, double* __restrict__ out,
                                                    const double* __restrict__ phi, const double* __restrict__ rhs,
-                                                   bool homog, int kz) {
+                                                   bool homog, int kz, unsigned long long* __restrict__ maxBits = nullptr) {
+    // MODE 3 = MODE 1 + max |residual| folded into *maxBits (the bit pattern of a non-negative double orders like the
+    // integer; a maximum does not depend on the order it is taken in, so this equals k_reduce's result bit for bit)
     const int i = blockIdx.x * BX + threadIdx.x;
     const int j = blockIdx.y * BY + threadIdx.y;
-    if (i >= g.n[0] || j >= g.n[1]) return;
+    const bool act = i < g.n[0] && j < g.n[1];
+    if (MODE != 3 && !act) return;
+    double rmax = 0.0;
+    if (act) {
     const int k0 = blockIdx.z * kz;
     const int k1 = min(k0 + kz, g.n[2]);
     const double* __restrict__ jg0 = m.jg[0][0];
@@ -90,6 +95,10 @@ __global__ void __launch_bounds__(BX* BY, MARCH_MINB(MODE)) k_march(const Geom g
             out[c] = v;
         } else if (MODE == 1) {
             out[c] = rhs[c] - v;
+        } else if (MODE == 3) {
+            const double res = rhs[c] - v;
+            out[c] = res;
+            rmax = fmax(rmax, fabs(res));
         } else {
             const double res = rhs[c] - v;
             s = s + res / ji;
@@ -104,9 +113,35 @@ __global__ void __launch_bounds__(BX* BY, MARCH_MINB(MODE)) k_march(const Geom g
         pc = pn;
         zlo = zhi;
     }
+    }
+    if (MODE == 3) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) rmax = fmax(rmax, __shfl_xor_sync(0xffffffffu, rmax, o));
+        __shared__ double wmax[BX * BY / 32];
+        const int t = threadIdx.y * BX + threadIdx.x;
+        if ((t & 31) == 0) wmax[t >> 5] = rmax;
+        __syncthreads();
+        if (t == 0) {
+#pragma unroll
+            for (int w = 1; w < BX * BY / 32; ++w) rmax = fmax(rmax, wmax[w]);
+            if (rmax > 0.0) atomicMax(maxBits, (unsigned long long)__double_as_longlong(rmax));   // one per block
+        }
+    }
 }
 
 static int march_kz(const Geom& g) { return (g.n[2] >= 32) ? 16 : ((g.n[2] + 1) / 2) * 2; }
+
+// residual and its max-norm in one pass (the outer loop's "residual, then norm"); false when this geometry does not
+// run k_march (the caller then takes the two-pass route).  *maxBits must be zero on the stream before the launch.
+bool launch_residual_maxnorm(Ctx& cx, const Geom& g, const Metric& m, double* out, const double* phi, const double* rhs,
+                             bool homog, double* maxOut) {
+    if (!(m.diagonal && g.nd == 3)) return false;
+    const int kzm = march_kz(g);
+    dim3 gridm((g.n[0] + BX - 1) / BX, (g.n[1] + BY - 1) / BY, (g.n[2] + kzm - 1) / kzm), blockm(BX, BY);
+    k_march<3><<<gridm, blockm, 0, cx.stream>>>(g, m, g, out, phi, rhs, homog, kzm, reinterpret_cast<unsigned long long*>(maxOut));
+    cx.launches++;
+    return true;
+}
 
 void launch_apply(Ctx& cx, const Geom& g, const Metric& m, double* out, const double* phi, const double* rhs,
                   int mode, bool homog) {

@@ -88,9 +88,7 @@ int mg_solve(SomarLevel* L, SomarField* phi, const SomarField* rhs, bool zeroPhi
     // (the correction's "set to zero" before every V-cycle, MappedAMRMultiGrid.H:1064,1215, is handed to mg_cycle)
     if (zeroPhi) launch_fill(cx, g, phi->p, 0.0);
     auto computeResidual = [&](double* out) {
-        int r2 = op_apply(L, 0, resid->p, phi, rhs->p, 1, forceHomog);
-        if (r2) return r2;
-        return reduce_global(L, 0, resid->p, nullptr, 0, out);
+        return residual_maxnorm(L, resid, phi, rhs, forceHomog, out);
     };
     double initial_rnorm;
     if ((rc = computeResidual(&initial_rnorm))) return rc;
