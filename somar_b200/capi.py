@@ -205,6 +205,11 @@ def _ptr(a):
         return None, 0
     if hasattr(a, "data_ptr"):
         assert a.is_contiguous() and str(a.dtype) == "torch.float64"
+        if a.is_cuda:
+            # the library works on its own (non-blocking) stream: whatever produced this tensor on torch's current
+            # stream must have finished before the library reads it (and before it overwrites it)
+            import torch
+            torch.cuda.current_stream(a.device).synchronize()
         return C.c_void_p(a.data_ptr()), int(a.is_cuda)
     assert isinstance(a, np.ndarray) and a.dtype == np.float64 and a.flags["C_CONTIGUOUS"]
     return C.c_void_p(a.ctypes.data), 0
