@@ -95,9 +95,10 @@ def horiz_rhs(phi, jgup, dx, nz):
 class LevelLepticSolver:
     """define(op) + solve(phi, rhs) of the reference class, over the CPU oracle"""
 
-    def __init__(self, po, n, dx, jgup, jinv, *, periodic=(0, 0, 0), boxes=None, bc_type=None, bc_value=None,
+    def __init__(self, po, n, dx, jgup, jinv, *, dim=3, periodic=(0, 0, 0), boxes=None, bc_type=None, bc_value=None,
                  params: LepticParams = None):
         self.po = po
+        self.dim = dim                                          # 2: arrays (1, ny, nx), y is the vertical
         self.n = tuple(int(x) for x in n)
         self.dx = tuple(float(x) for x in dx)
         self.prm = params or LepticParams()
@@ -106,13 +107,16 @@ class LevelLepticSolver:
         nx, ny, nz = self.n
         bt = list(bc_type) if bc_type is not None else [NEUM] * 6
         bv = list(bc_value) if bc_value is not None else [0.0] * 6
-        if periodic[2]:
+        vd = dim - 1
+        if periodic[vd]:
             raise ValueError("periodic vertical direction: unforeseen BC type in verticalLineSolver (:1316)")
-        self.vert_bc = (bt[4], bt[5])
+        self.vert_bc = (bt[2 * vd], bt[2 * vd + 1])
         if any(t not in (NEUM, DIRI) for t in self.vert_bc):
             raise ValueError("vertical BCs must be Neumann or Dirichlet")
         self.do_horiz = self.vert_bc == (NEUM, NEUM)            # gatherVerticalBCTypes :1615-1628
-        kw = dict(dim=3, periodic=periodic, boxes=boxes, alpha=0.0, beta=1.0, is_diagonal=True, bc_type=bt, bc_value=bv)
+        if self.do_horiz and dim != 3:
+            raise ValueError("horizontal solves need a 3-D level")
+        kw = dict(dim=dim, periodic=periodic, boxes=boxes, alpha=0.0, beta=1.0, is_diagonal=True, bc_type=bt, bc_value=bv)
         # the operator handed to define() (m_origOpPtr)
         self.orig = po.Oracle(self.n, self.dx, self.jgup, self.jinv, params=po.default_params(), **kw)
         # m_opPtr and m_mgSolverPtr share the vertical grids' metric: Jgup copied, Jinv = 1 (:197-205)
@@ -146,7 +150,9 @@ class LevelLepticSolver:
     def solve(self, phi, rhs, homogeneous=False):
         po, prm = self.po, self.prm
         nx, ny, nz = self.n
-        dz = self.dx[2]
+        if self.dim == 2:                                       # columns run along y: nv = ny, flat arrays are (1, nx)
+            nz, ny = ny, 1
+        dz = self.dx[self.dim - 1]
         H = dz * nz
         max_order = prm.max_order
         # J * residual to the vertical grids (:698-716)
@@ -162,7 +168,7 @@ class LevelLepticSolver:
         use_excess = use_horiz = self.do_horiz
         self.horiz_solves = 0
         self.krylov_used = False
-        jgzz = self.jgup[2].reshape(nz + 1, -1)
+        jgzz = self.jgup[self.dim - 1].reshape(nz + 1, -1)
         for order in range(max_order + 1):
             if self.do_horiz:
                 if order >= 1:
@@ -182,8 +188,8 @@ class LevelLepticSolver:
                                                             bdry_hi=bdry_hi.ravel())
             if info != 0:
                 raise RuntimeError("LepticLapackVerticalSolver: INFO = %d" % info)
-            vert_phi = sol.reshape(nz, ny, nx)
-            rhs_v = rhs_after.reshape(nz, ny, nx)
+            vert_phi = sol.reshape(phi_total.shape)
+            rhs_v = rhs_after.reshape(phi_total.shape)
             if use_horiz:
                 flat_rhs = horiz_rhs(vert_phi, self.jgup, self.dx, nz)
                 if use_excess:

@@ -21,6 +21,7 @@ CASES = {
     # name: (Problem kwargs, leptic kwargs)
     "diri_top": (dict(n=(32, 24, 16), aniso=64.0, bc_type=[0, 0, 0, 0, NEUM, DIRI]), dict()),
     "diri_bottom_2x2": (dict(n=(32, 32, 16), aniso=48.0, bc_type=[0, 0, 0, 0, DIRI, NEUM], parts=(2, 2, 1)), dict(max_order=3)),
+    "diri_top_2d": (dict(n=(48, 16, 1), dim=2, aniso=64.0, bc_type=[0, 0, NEUM, DIRI, 0, 0]), dict(max_order=3)),
     "neum_o1": (dict(n=(32, 24, 16), aniso=64.0), dict(max_order=1)),
     "neum_fallback": (dict(n=(32, 32, 16), aniso=64.0, parts=(2, 1, 1)), dict()),
 }
@@ -29,7 +30,8 @@ CASES = {
 def _oracle_solver(po, pb, **kw):
     from oracle import leptic_ref as lr
     prm = lr.LepticParams(**kw)
-    return lr.LevelLepticSolver(po, pb.n, pb.spec.dx, pb.jgup, pb.jinv, boxes=pb.boxes, bc_type=pb.bc_type, params=prm)
+    return lr.LevelLepticSolver(po, pb.n, pb.spec.dx, pb.jgup, pb.jinv, dim=pb.dim, boxes=pb.boxes, bc_type=pb.bc_type,
+                                params=prm)
 
 
 def _rhs(pb):
