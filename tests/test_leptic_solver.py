@@ -135,6 +135,27 @@ def test_leptic_solve_parity(name, oracle_lib, somar):
 
 
 @pytest.mark.gpu
+def test_leptic_solve_inhomogeneous_bcs_and_initial_guess(oracle_lib, somar):
+    """setHomogeneous(false): the boundary VALUES enter through the first residual (m_origOpPtr->residual, :702) and a
+    non-zero initial guess is kept (phi += corrections)"""
+    pb = Problem(n=(24, 16, 16), aniso=64.0, bc_type=[0, 0, 0, 0, NEUM, DIRI], bc_value=[0.3, -0.2, 0.1, 0.0, 0.05, 0.7])
+    rhs_h = _rhs(pb)
+    phi0 = pb.rand() * 0.1
+    from oracle import leptic_ref as lr
+    so = lr.LevelLepticSolver(oracle_lib, pb.n, pb.spec.dx, pb.jgup, pb.jinv, boxes=pb.boxes, bc_type=pb.bc_type,
+                              bc_value=pb.bc_value, params=lr.LepticParams(max_order=3))
+    want = so.solve(phi0, rhs_h, homogeneous=False)
+    lev = pb.level(somar)
+    ls = somar.LepticSolver(lev, somar.leptic_default_params(max_order=3))
+    phi, rhs = lev.field(0, phi0), lev.field(0, rhs_h)
+    st = ls.solve(phi, rhs, homogeneous=False)
+    assert st["exit_status"] == so.exit_status
+    assert np.allclose(st["res_norms"], so.res_norms, rtol=1e-9, atol=0)
+    assert np.abs(phi.get() - want).max() <= 1e-13 * np.abs(want).max()
+    assert so.res_norms[-1] < 1e-2 * so.res_norms[0]
+
+
+@pytest.mark.gpu
 def test_leptic_solve_accumulates_into_phi_and_is_repeatable(oracle_lib, somar):
     """phi is an initial guess (the solver works on the residual, :698-716): a second call continues from the first"""
     pk, lk = CASES["diri_top"]
