@@ -98,6 +98,8 @@ void launch_reduce(Ctx& cx, const Geom& g, const double* x, const double* y, int
 // ---- prolongation -----------------------------------------------------------------------------------------
 // ConstInterpPS / ConstInterpWithAvgPS -- ProlongationStrategyF.ChF:37-160:  fine += coarse[i/m];
 // optionally sums[0] += sum(dV*fine), sums[1] += sum(dV), dV = dxProduct / Jinv.
+// SH: every refinement ratio is 1 or 2 (the semicoarsening schedule produces nothing else), so i / r is a shift
+template <bool SH>
 __global__ void k_prolong(const Geom gf, const double* __restrict__ jinv, const Geom gc, double* __restrict__ fine,
                           const double* __restrict__ crse, int r0, int r1, int r2, double dxProduct, bool withAvg,
                           double* __restrict__ scratch, unsigned int* __restrict__ tickets,
@@ -109,7 +111,7 @@ __global__ void k_prolong(const Geom gf, const double* __restrict__ jinv, const 
     double aS = 0.0, aV = 0.0;
     double fv[4], cv[4], jv[4] = {1.0, 1.0, 1.0, 1.0};
     FOR_VALID_CELLS4(gf, c, u,
-                     { fv[u] = fine[c]; cv[u] = crse[gc.idx(i / r0, j / r1, k / r2)]; if (withAvg) jv[u] = jinv[c]; },
+                     { fv[u] = fine[c]; cv[u] = crse[SH ? gc.idx(i >> (r0 - 1), j >> (r1 - 1), k >> (r2 - 1)) : gc.idx(i / r0, j / r1, k / r2)]; if (withAvg) jv[u] = jinv[c]; },
                      {
                          const double v = fv[u] + cv[u];
                          if (withAvg) {
@@ -131,22 +133,27 @@ __global__ void k_prolong(const Geom gf, const double* __restrict__ jinv, const 
 
 void launch_prolong(Ctx& cx, const Geom& gf, const Metric& mf, const Geom& gc, double* fine, const double* crse,
                     const int r[3], double dxProduct, double* sums) {
-    k_prolong<<<row_blocks(gf, cx.sms), TPB, 0, cx.stream>>>(gf, mf.jinv, gc, fine, crse, r[0], r[1], r[2], dxProduct,
-                                                             sums != nullptr, cx.scratch, cx.tickets, sums);
+    const bool sh = r[0] <= 2 && r[1] <= 2 && r[2] <= 2;
+    if (sh) k_prolong<true><<<row_blocks(gf, cx.sms), TPB, 0, cx.stream>>>(gf, mf.jinv, gc, fine, crse, r[0], r[1], r[2], dxProduct,
+                                                                           sums != nullptr, cx.scratch, cx.tickets, sums);
+    else k_prolong<false><<<row_blocks(gf, cx.sms), TPB, 0, cx.stream>>>(gf, mf.jinv, gc, fine, crse, r[0], r[1], r[2], dxProduct,
+                                                                         sums != nullptr, cx.scratch, cx.tickets, sums);
     cx.launches++;
 }
 
 // fine = (fine + coarse[i/m]) - sums[0]/sums[1]     (ZeroAvgConstInterpPS::prolongIncrement, ProlongationStrategy.cpp:163)
+template <bool SH>
 __global__ void k_prolong_finish(const Geom gf, const Geom gc, double* __restrict__ fine, const double* __restrict__ crse,
                                  int r0, int r1, int r2, const double* __restrict__ sums) {
     const double avg = sums[0] / sums[1];
     double fv[4], cv[4];
-    FOR_VALID_CELLS4(gf, c, u, { fv[u] = fine[c]; cv[u] = crse[gc.idx(i / r0, j / r1, k / r2)]; },
+    FOR_VALID_CELLS4(gf, c, u, { fv[u] = fine[c]; cv[u] = crse[SH ? gc.idx(i >> (r0 - 1), j >> (r1 - 1), k >> (r2 - 1)) : gc.idx(i / r0, j / r1, k / r2)]; },
                      { fine[c] = (fv[u] + cv[u]) - avg; })
 }
 void launch_prolong_finish(Ctx& cx, const Geom& gf, const Geom& gc, double* fine, const double* crse, const int r[3],
                            const double* sums) {
-    k_prolong_finish<<<row_blocks(gf, cx.sms), TPB, 0, cx.stream>>>(gf, gc, fine, crse, r[0], r[1], r[2], sums);
+    if (r[0] <= 2 && r[1] <= 2 && r[2] <= 2) k_prolong_finish<true><<<row_blocks(gf, cx.sms), TPB, 0, cx.stream>>>(gf, gc, fine, crse, r[0], r[1], r[2], sums);
+    else k_prolong_finish<false><<<row_blocks(gf, cx.sms), TPB, 0, cx.stream>>>(gf, gc, fine, crse, r[0], r[1], r[2], sums);
     cx.launches++;
 }
 
