@@ -21,7 +21,7 @@
 
 namespace somar {
 
-#define ATPB 256
+#define ATPB 128
 
 struct AGeom {
     int n[3];
@@ -37,15 +37,13 @@ __device__ __forceinline__ long long aidx(const AGeom& g, int i, int j, int k) {
 __device__ __forceinline__ long long aoff(const AGeom& g, int i, int j, int k, int d, int o) {
     return aidx(g, i + (d == 0 ? o : 0), j + (d == 1 ? o : 0), k + (d == 2 ? o : 0));
 }
+// thread -> cell: x from the block and thread index, y and z from the grid (no per-cell integer division: the
+// 64-bit div/mod of a flattened index cost more issue slots than the stencil arithmetic, cf. k_prolong)
 __device__ __forceinline__ bool acell(const AGeom& g, int& i, int& j, int& k) {
-    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    const long long tot = (long long)g.n[0] * g.n[1] * g.n[2];
-    if (t >= tot) return false;
-    i = (int)(t % g.n[0]);
-    const long long r = t / g.n[0];
-    j = (int)(r % g.n[1]);
-    k = (int)(r / g.n[1]);
-    return true;
+    i = blockIdx.x * blockDim.x + threadIdx.x;
+    j = blockIdx.y;
+    k = blockIdx.z;
+    return i < g.n[0];
 }
 
 // vanLeerSlopes at one cell from its neighbours along the direction
@@ -279,8 +277,7 @@ int advect_predict_scalar(SomarLevel* L, SomarField* const whalf[3], const Somar
             for (int d2 = 0; d2 < 3; ++d2)
                 if (d2 != d1) wh2[d1][d2] = L->awork[q++]->p;
     }
-    const long long tot = (long long)g.n[0] * g.n[1] * g.n[2];
-    const unsigned nb = (unsigned)((tot + ATPB - 1) / ATPB);
+    const dim3 nb((g.n[0] + ATPB - 1) / ATPB, g.n[1], g.n[2]);
     cudaStream_t st = L->cx.stream;
     const bool lim = prm->use_limiting != 0;
     const bool ho = prm->use_high_order_limiter != 0;
