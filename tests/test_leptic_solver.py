@@ -52,6 +52,19 @@ def test_oracle_dirichlet_top_converges_order_by_order(oracle_lib):
     assert np.abs(r).max() < 1e-3 * np.abs(rhs).max()
 
 
+def test_oracle_two_dimensional_level_columns_along_y(oracle_lib):
+    pk, lk = CASES["diri_top_2d"]
+    pb = Problem(**pk)
+    s = _oracle_solver(oracle_lib, pb, **lk)
+    rhs = _rhs(pb)
+    phi = s.solve(np.zeros_like(rhs), rhs, homogeneous=True)
+    nr = s.res_norms
+    assert len(nr) == 5 and s.horiz is None
+    assert all(nr[k + 1] < 0.5 * nr[k] for k in range(4)), nr
+    r = s.orig.residual(phi, rhs, homogeneous=True)
+    assert np.abs(r).max() < 1e-3 * np.abs(rhs).max()
+
+
 def test_oracle_neumann_excess_horizontal_and_fallback(oracle_lib):
     pk, lk = CASES["neum_fallback"]
     pb = Problem(**pk)
