@@ -337,6 +337,28 @@ void orc_mac_gradient(void* hv, int depth, double* g0, double* g1, double* g2, c
     gather_faces(op, gr, g);
 }
 
+// LevelLepticSolver::computeHorizRHS / ::levelVertHorizGradient on depth 0 (flat outputs: one value per column)
+void orc_leptic_horiz_rhs(void* hv, double* flatRhs, const double* phi) {
+    Op& op = *((OrcHandle*)hv)->mg->ops[0];
+    LevelData p;
+    op.create(p, 1);
+    scatter(op, p, phi);
+    op.lepticHorizRHS(flatRhs, p);
+}
+
+void orc_leptic_vert_horiz_grad(void* hv, double* flatLo, double* flatHi, const double* phi, double scale) {
+    Op& op = *((OrcHandle*)hv)->mg->ops[0];
+    LevelData p;
+    op.create(p, 1);
+    scatter(op, p, phi);
+    // the reference makes no exchange here: it finds the ghosts as the residual evaluation that closed the previous
+    // order left them (LevelLepticSolver.cpp:839: exchange + homogeneous BC ghosts) -- reproduce that state
+    LevelData tmp;
+    op.create(tmp, 0);
+    op.applyOp(tmp, p, true);
+    op.lepticVertHorizGradient(flatLo, flatHi, p, scale);
+}
+
 void orc_mac_divergence(void* hv, int depth, double* div, const double* f0, const double* f1, const double* f2) {
     Op& op = *((OrcHandle*)hv)->mg->ops[depth];
     FluxLevelData fl;

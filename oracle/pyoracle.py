@@ -256,6 +256,26 @@ class Oracle:
                            int(zero_pressure), int(force_homogeneous), C.byref(st))
         return v[:self.dim], p, _stats(st)
 
+    # -- leptic solver pieces with per-box ghosts (either metric) ---------------------------------
+    def _flat_shape(self):
+        return (self.n[1], self.n[0]) if self.dim == 3 else (self.n[0],)
+
+    def leptic_horiz_rhs(self, phi):
+        """LevelLepticSolver::computeHorizRHS: -d_m avg_z(J g^{mj} d_j phi), boundary faces zero"""
+        phi = _f64(phi)
+        out = np.zeros(self._flat_shape())
+        self.L.orc_leptic_horiz_rhs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        self.L.orc_leptic_horiz_rhs(self.h, _ptr(out), _ptr(phi))
+        return out
+
+    def leptic_vert_horiz_grad(self, phi, scale):
+        """LevelLepticSolver::levelVertHorizGradient: scale * J g^{zm} d_m phi on the lower / upper boundary faces"""
+        phi = _f64(phi)
+        lo, hi = np.zeros(self._flat_shape()), np.zeros(self._flat_shape())
+        self.L.orc_leptic_vert_horiz_grad.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double]
+        self.L.orc_leptic_vert_horiz_grad(self.h, _ptr(lo), _ptr(hi), _ptr(phi), float(scale))
+        return lo, hi
+
     def timed_solve(self, rhs, ncycles_cap=0):
         rhs = _f64(rhs)
         st = OrcStats()

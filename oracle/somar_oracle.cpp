@@ -535,6 +535,117 @@ void Op::macGradient(FluxLevelData& grad, LevelData& phi, bool homog) const {
     }
 }
 
+// ----------------------------------------------------------------------------------------------
+// Leptic solver pieces that depend on per-box ghost cells (full metrics; the diagonal case reduces to
+// oracle/leptic_ref.py's global-array statements and is tested against them).
+// ----------------------------------------------------------------------------------------------
+// extrapAllGhosts -- src/calculus/extrapolation/ExtrapolationUtils.cpp:388-421: per box, before any exchange;
+// direction by direction, the valid box growing so that edges and corners are reached.
+void Op::lepticExtrapAllGhosts(LevelData& phi, int order) const {
+    int numghosts = phi.ghost[0];
+    for (int d = 1; d < nd; ++d) numghosts = std::min(numghosts, phi.ghost[d]);
+    for (size_t b = 0; b < grids.size(); ++b) {
+        Box valid = grids[b];
+        for (int ghost = 0; ghost < numghosts; ++ghost)
+            for (int dir = 0; dir < nd; ++dir) {
+                ExtrapolateFaceNoEV(phi[b], phi[b], valid, dir, Lo, order);
+                ExtrapolateFaceNoEV(phi[b], phi[b], valid, dir, Hi, order);
+                valid.grow(dir, 1);
+            }
+    }
+}
+
+// LevelLepticSolver::computeHorizRHS -- LevelLepticSolver.cpp:981-1097: every ghost extrapolated (order 2), exchange
+// (+ corners for a full metric), MAPPEDMACGRAD[ORTHO] of the horizontal directions on the faces interior to the DOMAIN
+// (boundary faces take the BoundaryData values: zero in the horizontal directions), vertical average
+// (UNMAPPEDVERTINTEGRAL, scale 1/Nz), -divergence (LEPTICACCUMDIV).  Boxes span the vertical (columns are whole).
+void Op::lepticHorizRHS(double* flatRhs, LevelData& phi) const {
+    const int vd = nd - 1;
+    const Box& dom = domain.box;
+    const int Nz = dom.size(vd);
+    const long nx = dom.size(0);
+    lepticExtrapAllGhosts(phi, 2);                                         // :1004
+    exchange(phi, false);                                                  // :1006
+    if (!isDiagonal) exchange(phi, true);                                  // :1008-1014 (no CF region on one level)
+    for (size_t b = 0; b < grids.size(); ++b) {
+        const Box& valid = grids[b];
+        if (valid.lo[vd] != dom.lo[vd] || valid.hi[vd] != dom.hi[vd]) { fprintf(stderr, "lepticHorizRHS: box does not span the vertical\n"); abort(); }
+        Box flat = valid;
+        flat.hi[vd] = flat.lo[vd];
+        FAB rhs(flat, 1);                                                  // setValLevel(a_rhs, 0) :1017
+        for (int FCdir = 0; FCdir < vd; ++FCdir) {
+            Box domInterior = surroundingNodes(dom, FCdir);
+            domInterior.grow(FCdir, -1);                                   // :997-1001
+            const Box faceBox = surroundingNodes(valid, FCdir);
+            const Box interiorFaceBox = faceBox & domInterior;
+            FAB grad(faceBox, 1);                                          // boundary faces: bdryData = 0 (:1063-1069)
+            if (!interiorFaceBox.isEmpty()) {
+                if (isDiagonal) macgrad_ortho(grad, phi[b], Jgup.fabs[b][FCdir], interiorFaceBox, dx[FCdir], FCdir);
+                else macgrad_full(grad, phi[b], phi[b], Jgup.fabs[b][FCdir], interiorFaceBox, dx, FCdir, nd);
+            }
+            const Box flatFace = surroundingNodes(flat, FCdir);
+            FAB avg(flatFace, 1);
+            const double dzScale = 1.0 / double(Nz);
+            const int k0 = flat.lo[vd];
+            ORC_LOOP(faceBox, i, j, k) {                                   // the vertical index ascends for every column
+                int a[3] = {i, j, k};
+                a[vd] = k0;
+                avg(a[0], a[1], a[2]) = avg(a[0], a[1], a[2]) + grad(i, j, k) * dzScale;
+            }
+            const double dxScale = -1.0 / dx[FCdir];
+            const int ei = FCdir == 0, ej = FCdir == 1;
+            ORC_LOOP(flat, i, j, k) rhs(i, j, k) = rhs(i, j, k) + (avg(i + ei, j + ej, k) - avg(i, j, k)) * dxScale;
+        }
+        ORC_LOOP(flat, i, j, k) {
+            const long col = (nd > 2) ? (i - dom.lo[0]) + nx * (j - dom.lo[1]) : (i - dom.lo[0]);
+            flatRhs[col] = rhs(i, j, k);
+        }
+    }
+}
+
+// LevelLepticSolver::levelVertHorizGradient -- LevelLepticSolver.cpp:1107-1176 + LEPTICVERTHORIZGRAD,
+// LevelLepticSolverF.ChF:74-122: scale * sum_m J g^{z m} d_m phi on the lower / upper DOMAIN faces, from phi with
+// its vertical domain ghosts extrapolated in place (order 2, ExtrapolateFaceAndCopy: faces, then the edges of the
+// ghost layer).  Zero for a diagonal metric (:1125).  No exchange is made ("non-blocking, fast, and seems to work").
+void Op::lepticVertHorizGradient(double* flatLo, double* flatHi, LevelData& phi, double scale) const {
+    const int vd = nd - 1;
+    const Box& dom = domain.box;
+    const long nx = dom.size(0);
+    const long ncol = (nd > 2) ? nx * dom.size(1) : nx;
+    for (long c = 0; c < ncol; ++c) flatLo[c] = flatHi[c] = 0.0;           // a_vertBdryData.setVal(0.0) :1122
+    if (isDiagonal) return;
+    for (int side = 0; side < 2; ++side) {
+        const int isign = side == Lo ? -1 : 1;
+        double* out = side == Lo ? flatLo : flatHi;
+        for (size_t b = 0; b < grids.size(); ++b) {
+            const Box& valid = grids[b];
+            if (valid.sideEnd(side, vd) != dom.sideEnd(side, vd)) continue;
+            FAB& p = phi[b];
+            const Box domValid = p.box() & dom;                             // :1147-1148
+            ExtrapolateFaceAndCopy(p, p, domValid, vd, side, 2, nd);       // :1149
+            Box dest = valid;                                               // bdryBox(valid, vd, side, 1): FC faces
+            dest.surroundingNodes(vd);
+            if (side == Lo) dest.hi[vd] = dest.lo[vd]; else dest.lo[vd] = dest.hi[vd];
+            const FAB& Jgz = Jgup.fabs[b][vd];
+            const double dxinv0 = scale * 0.25 / dx[0];
+            const double dxinv1 = (nd > 2) ? scale * 0.25 / dx[1] : 0.0;
+            // offsets from the face index to the ghost-side and valid-side cells (CHF_AUTOID[gi; ...; -(1-isign)/2])
+            const int go = -(1 - isign) / 2, vo = -(1 + isign) / 2;
+            ORC_LOOP(dest, i, j, k) {
+                double v;
+                if (nd > 2) {
+                    v = Jgz(i, j, k, 0) * dxinv0 * (p(i + 1, j, k + go) - p(i - 1, j, k + go) + p(i + 1, j, k + vo) - p(i - 1, j, k + vo)) +
+                        Jgz(i, j, k, 1) * dxinv1 * (p(i, j + 1, k + go) - p(i, j - 1, k + go) + p(i, j + 1, k + vo) - p(i, j - 1, k + vo));
+                    out[(i - dom.lo[0]) + nx * (j - dom.lo[1])] = v;
+                } else {
+                    v = Jgz(i, j, k, 0) * dxinv0 * (p(i + 1, j + go, k) - p(i - 1, j + go, k) + p(i + 1, j + vo, k) - p(i - 1, j + vo, k));
+                    out[i - dom.lo[0]] = v;
+                }
+            }
+        }
+    }
+}
+
 // Divergence::levelDivergenceMAC with a_fluxBC == NULL (the caller's fluxes carry their boundary values)
 // -- Divergence.cpp:44-127 -> MAPPEDFLUXDIVERGENCE{2,3}D, DivCurlGradF.ChF:1034-1214.
 void Op::macDivergence(LevelData& div, const FluxLevelData& flux) const {

@@ -126,6 +126,11 @@ struct Op {
     void applyOp(LevelData& lhs, LevelData& phi, bool homog) const;
     void residual(LevelData& lhs, LevelData& phi, const LevelData& rhs, bool homog) const;
     void fillGhostsAndExtrapolate(LevelData& phi);
+    // leptic solver pieces that need per-box ghosts (either metric): LevelLepticSolver::computeHorizRHS and
+    // ::levelVertHorizGradient.  flat*: one value per (i, j), global x-fastest arrays.
+    void lepticExtrapAllGhosts(LevelData& phi, int order) const;
+    void lepticHorizRHS(double* flatRhs, LevelData& phi) const;
+    void lepticVertHorizGradient(double* flatLo, double* flatHi, LevelData& phi, double scale) const;
     void relax(LevelData& phi, const LevelData& rhs, int iters);
     void relaxOnce(LevelData& phi, const LevelData& rhs);
     void fullStencilGSRB(FAB& phi, const FAB& rhs, const Box& region, size_t bi, int pass) const;

@@ -196,3 +196,49 @@ def test_leptic_create_rejects_out_of_scope_levels(somar):
         lev = pb.level(somar)
         with pytest.raises(somar.SomarError, match=msg):
             somar.LepticSolver(lev)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Pieces of the leptic iteration that need per-box ghost cells (oracle/somar_oracle.cpp Op::lepticHorizRHS /
+# ::lepticVertHorizGradient, written for either metric; the device has the diagonal case only so far).
+@pytest.mark.parametrize("parts", [(1, 1, 1), (2, 2, 1)])
+def test_oracle_horiz_rhs_diagonal_equals_the_global_restatement(parts, oracle_lib):
+    from oracle import leptic_ref as lr
+    pb = Problem(n=(16, 12, 8), aniso=16.0, parts=parts)
+    orc = pb.oracle(oracle_lib)
+    phi = pb.rand()
+    assert np.array_equal(orc.leptic_horiz_rhs(phi), lr.horiz_rhs(phi, pb.jgup, pb.spec.dx, 8))
+    lo, hi = orc.leptic_vert_horiz_grad(phi, -1.0)
+    assert not lo.any() and not hi.any()                        # diagonal metric: levelVertHorizGradient returns zeros
+
+
+@pytest.mark.parametrize("parts", [(1, 1, 1), (2, 1, 1)])
+def test_oracle_full_metric_pieces_are_exact_for_linear_fields(parts, oracle_lib):
+    """order-2 extrapolation reproduces a linear phi in every ghost cell, so the gradients are the analytic ones:
+    computeHorizRHS = -d_x avg_z(J g^{xx} a) with zero boundary faces, levelVertHorizGradient = scale J g^{zx} a"""
+    n = (16, 12, 8)
+    pb = Problem(n=n, map_name="terrain", aniso=4.0, parts=parts)
+    orc = pb.oracle(oracle_lib)
+    dx = pb.spec.dx
+    a = 0.37
+    x = (np.arange(n[0]) + 0.5) * dx[0]
+    phi = np.broadcast_to(a * x, pb.shape).copy()
+    assert not orc.leptic_horiz_rhs(np.full(pb.shape, 2.5)).any()           # constants: no gradient at all
+    jg00 = pb.jgup[0][0]                                                      # (nz, ny, nx+1): J g^{xx} on x faces
+    flux = (jg00 * a).mean(axis=0)
+    flux[:, 0] = 0.0
+    flux[:, -1] = 0.0
+    want = -(flux[:, 1:] - flux[:, :-1]) / dx[0]
+    jg10 = pb.jgup[1][0]                                                      # J g^{yx} on y faces: d_x phi there is a
+    fy = (jg10 * a).mean(axis=0)
+    fy[0, :] = 0.0
+    fy[-1, :] = 0.0
+    want = want - (fy[1:, :] - fy[:-1, :]) / dx[1]
+    got = orc.leptic_horiz_rhs(phi)
+    assert np.abs(got - want).max() <= 1e-12 * np.abs(want).max()
+    lo, hi = orc.leptic_vert_horiz_grad(phi, -1.0)
+    jgzx = pb.jgup[2][0]                                                      # (nz+1, ny, nx): J g^{zx} on z faces
+    # (columns next to the side walls see the Neumann ghosts the preceding residual evaluation leaves, not linear ones)
+    inner = (slice(1, -1), slice(1, -1))
+    assert np.abs(lo - (-1.0) * jgzx[0] * a)[inner].max() <= 1e-12 * np.abs(jgzx).max()
+    assert np.abs(hi - (-1.0) * jgzx[-1] * a)[inner].max() <= 1e-12 * np.abs(jgzx).max()
