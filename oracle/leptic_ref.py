@@ -14,7 +14,8 @@ The leptic ITERATION of SOMAR (SURVEY.md 8(a) "LevelLepticSolver" row, 8(f)-2) r
                                         :1183-1240, :1247-1425, :1427-1462, :1489-1515, :1665-1709
   ::gatherVerticalBCTypes               :1522-1644
 
-Scope (the device driver has the same one): one level, no coarser level (m_crsePhiPtr == NULL), DIAGONAL metric,
+Scope: one level, no coarser level (m_crsePhiPtr == NULL); diagonal metrics (the device driver's scope) and, through
+Op::lepticHorizRHS / Op::lepticVertHorizGradient of oracle/somar_oracle.cpp, full metrics in 3-D (oracle only so far);
 non-periodic vertical direction with Neumann or Dirichlet sides; when a horizontal solve is needed the problem must be
 3-D with non-periodic horizontal directions (the reference leaves the domain-boundary faces of a periodic direction
 unset in computeHorizRHS, :997-1001 + :1064-1069, BoundaryData.cpp:103-104).  The horizontal grids are the flattened
@@ -116,7 +117,10 @@ class LevelLepticSolver:
         self.do_horiz = self.vert_bc == (NEUM, NEUM)            # gatherVerticalBCTypes :1615-1628
         if self.do_horiz and dim != 3:
             raise ValueError("horizontal solves need a 3-D level")
-        kw = dict(dim=dim, periodic=periodic, boxes=boxes, alpha=0.0, beta=1.0, is_diagonal=True, bc_type=bt, bc_value=bv)
+        self.diag = all(j.ndim == 3 for j in self.jgup)         # full metric: jgup[d] is (dim, nz, ny, nx) with +1 in d
+        if not self.diag and dim != 3:
+            raise ValueError("the full-metric iteration is restated for 3-D levels")
+        kw = dict(dim=dim, periodic=periodic, boxes=boxes, alpha=0.0, beta=1.0, is_diagonal=self.diag, bc_type=bt, bc_value=bv)
         # the operator handed to define() (m_origOpPtr)
         self.orig = po.Oracle(self.n, self.dx, self.jgup, self.jinv, params=po.default_params(), **kw)
         # m_opPtr and m_mgSolverPtr share the vertical grids' metric: Jgup copied, Jinv = 1 (:197-205)
@@ -136,10 +140,15 @@ class LevelLepticSolver:
                     if b not in seen:
                         seen.append(b)
                 flat_boxes = seen
-            self.hjg = [vert_avg_faces(self.jgup[0], nz), vert_avg_faces(self.jgup[1], nz)]
-            self.horiz = po.Oracle((nx, ny, 1), (self.dx[0], self.dx[1], 1.0), [h[None] for h in self.hjg],
+            if self.diag:
+                self.hjg = [vert_avg_faces(self.jgup[0], nz), vert_avg_faces(self.jgup[1], nz)]
+                hmetric = [h[None] for h in self.hjg]
+            else:                                               # J g^{ab}, a, b horizontal (LevelGeometryBasics.cpp:545-568)
+                self.hjg = [np.stack([vert_avg_faces(self.jgup[a][b], nz) for b in range(2)]) for a in range(2)]
+                hmetric = [h[:, None] for h in self.hjg]
+            self.horiz = po.Oracle((nx, ny, 1), (self.dx[0], self.dx[1], 1.0), hmetric,
                                    np.ones((1, ny, nx)), dim=2, periodic=(periodic[0], periodic[1], 0),
-                                   boxes=flat_boxes, alpha=0.0, beta=1.0, is_diagonal=True,
+                                   boxes=flat_boxes, alpha=0.0, beta=1.0, is_diagonal=self.diag,
                                    bc_type=[NEUM] * 6, bc_value=[0.0] * 6, params=po.default_params(**hor))
         self.horiz_remove_avg = True                            # the flattened boxes cover the domain (:410-433)
         self.res_norms = []
@@ -168,12 +177,15 @@ class LevelLepticSolver:
         use_excess = use_horiz = self.do_horiz
         self.horiz_solves = 0
         self.krylov_used = False
-        jgzz = self.jgup[self.dim - 1].reshape(nz + 1, -1)
+        jzz = self.jgup[self.dim - 1] if self.diag else self.jgup[self.dim - 1][self.dim - 1]
+        jgzz = np.ascontiguousarray(jzz).reshape(nz + 1, -1)
         for order in range(max_order + 1):
             if self.do_horiz:
-                if order >= 1:
+                if order >= 1 and self.diag:
                     bdry_lo = np.zeros((ny, nx))     # levelVertHorizGradient: diagonal metric -> zero (:1122-1125)
                     bdry_hi = np.zeros((ny, nx))
+                elif order >= 1:                     # -Grad[phi_{order-1}]^z on the boundary faces (:760-762)
+                    bdry_lo, bdry_hi = self.vert.leptic_vert_horiz_grad(vert_phi, -1.0)
                 if order >= 1 and use_excess:
                     bdry_hi = bdry_hi + excess * 1.0                      # vertPlus (:766)
                 if use_excess:
@@ -191,7 +203,7 @@ class LevelLepticSolver:
             vert_phi = sol.reshape(phi_total.shape)
             rhs_v = rhs_after.reshape(phi_total.shape)
             if use_horiz:
-                flat_rhs = horiz_rhs(vert_phi, self.jgup, self.dx, nz)
+                flat_rhs = horiz_rhs(vert_phi, self.jgup, self.dx, nz) if self.diag else self.vert.leptic_horiz_rhs(vert_phi)
                 if use_excess:
                     flat_rhs = flat_rhs + excess * (-1.0 / H)
                 horiz_rhs_f = np.zeros((ny, nx)) + flat_rhs                 # setVal(0) + addTo (:811-812)
@@ -228,7 +240,8 @@ class LevelLepticSolver:
             else:
                 self.exit_status = EXIT["KABOOM"] if order == 0 else EXIT["HANG"]
                 break
-            use_horiz = False                                               # LevelGeometry::isDiagonal() (:924-926)
+            if self.diag:
+                use_horiz = False                                           # LevelGeometry::isDiagonal() (:924-926)
         if self.exit_status != EXIT["KABOOM"]:
             return phi + phi_total * 1.0
         return phi.copy()
