@@ -14,6 +14,9 @@
  *   - Fields are opaque device-resident objects created per multigrid depth.  Host data crosses the boundary in the
  *     CHF_FRA convention: `const double* fab, lo[3], hi[3]` = a Fortran-ordered array over the box [lo,hi]
  *     (ghost cells included), absolute (global) cell indices.  2-D problems use n[2] == 1.
+ *   - Lifetime of sources: somar_field_set / set_face / somar_level_set_metric_device with a DEVICE (or pinned host)
+ *     source only enqueue the copy on the level stream and return.  The caller keeps the source alive and unmodified
+ *     until somar_level_sync() (or an event recorded on somar_level_stream()) says the copy has run.
  *   - There is no CPU fallback: every call fails with SOMAR_ERR_CUDA when no sm_100 device is usable.
  */
 #ifndef SOMAR_B200_H
@@ -28,7 +31,8 @@ extern "C" {
 #define SOMAR_ERR_CUDA (-2)
 #define SOMAR_ERR_LAYOUT (-3)
 #define SOMAR_ERR_COMM (-4)
-#define SOMAR_ERR_DIVERGED (-5) /* residual grew 10x: MappedAMRMultiGrid.H:1134-1145 "kaboom" */
+#define SOMAR_ERR_DIVERGED (-5) /* residual grew 10x ("kaboom", MappedAMRMultiGrid.H:1134-1138), or no V-cycle improved
+                                   on the initial guess ("solver blew up", :1140-1144) */
 
 /* BCType codes: src/calculus/BCInterface/BCDescriptor.H:33-38 */
 #define SOMAR_BC_NONE (-1)
@@ -120,6 +124,12 @@ int somar_level_set_metric_device(SomarLevel* lev, int jgup_ncomp, const double*
                                   const double* d_jgup2, const double* d_jinv);
 int somar_level_finalize(SomarLevel* lev);
 int somar_level_set_alpha_beta(SomarLevel* lev, double alpha, double beta); /* MappedAMRPoissonOp::setAlphaAndBeta */
+/* MappedAMRMultiGrid<T>::m_convergenceMetric (MappedAMRMultiGrid.H:1036-1038): when non-zero it replaces the initial
+ * residual norm in the relative stopping test of somar_solve and as the bottom solver's metric; 0 restores the default. */
+int somar_level_set_convergence_metric(SomarLevel* lev, double metric);
+/* AMRPressureSolver::setAMRMGParameters / setBottomParameters (src/projection/AMRPressureSolver.cpp:46-81) on an
+ * existing level: every AMRMG.* / bottom.* knob except maxDepth (it fixes the schedule built at create time). */
+int somar_level_set_solver_params(SomarLevel* lev, const SomarSolverParams* params);
 int somar_level_num_depths(const SomarLevel* lev, int* ndepths);
 /* n = domain cells at that depth, ratio = mgCrseRefRatio to the next coarser depth, local_lo/hi = this rank's region */
 int somar_level_depth_info(const SomarLevel* lev, int depth, int n[3], int ratio[3], double dx[3], int* zero_avg,

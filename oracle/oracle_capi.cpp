@@ -282,6 +282,10 @@ void orc_solve(void* hv, double* phi, const double* rhs, int zeroPhi, int forceH
     for (int i = 0; i < out->history_len; ++i) out->history[i] = st.history[i];
 }
 
+// m_convergenceMetric of the next solves (0: the initial residual norm); did the last solve hit the "blew up" abort?
+void orc_set_convergence_metric(void* hv, double metric) { ((OrcHandle*)hv)->mg->convergenceMetric = metric; }
+int orc_blew_up(void* hv) { return ((OrcHandle*)hv)->mg->blewUp ? 1 : 0; }
+
 // Solve used by the CPU-baseline timer: keeps fields inside the handle so that the timed region is the
 // solve only.  Returns seconds spent in mg.solve().
 double orc_timed_solve(void* hv, const double* rhs, int ncycles_cap, OrcStats* out) {

@@ -222,6 +222,15 @@ class Oracle:
         it = self.L.orc_bottom_solve(self.h, _ptr(e), _ptr(r), float(metric), float(eps))
         return e, it
 
+    def set_convergence_metric(self, metric: float):
+        self.L.orc_set_convergence_metric.argtypes = [C.c_void_p, C.c_double]
+        self.L.orc_set_convergence_metric(self.h, float(metric))
+
+    def blew_up(self) -> bool:
+        """did the last solve end in the reference's "solver blew up" abort (MappedAMRMultiGrid.H:1140-1144)?"""
+        self.L.orc_blew_up.argtypes = [C.c_void_p]
+        return bool(self.L.orc_blew_up(self.h))
+
     def solve(self, rhs, phi0=None, zero_phi=True, force_homogeneous=True):
         rhs = _f64(rhs)
         phi = np.zeros_like(rhs) if phi0 is None else _f64(phi0).copy()

@@ -264,6 +264,7 @@ void Op::applyOp(LevelData& lhs, LevelData& phi, bool homog) const {
 // MappedAMRPoissonOp::residualI -- MappedAMRPoissonOp.cpp:646-677
 void Op::residual(LevelData& lhs, LevelData& phi, const LevelData& rhs, bool homog) const {
     applyOp(lhs, phi, homog);
+#pragma omp parallel for schedule(dynamic)
     for (size_t b = 0; b < grids.size(); ++b) subtractop(lhs[b], rhs[b], lhs[b], grids[b]);
 }
 
@@ -305,6 +306,8 @@ void Op::fullStencilGSRB(FAB& phi, const FAB& rhs, const Box& region, size_t bi,
 // BaseGSRB::boundaryGSRB -- GSRB.cpp:489-653
 void Op::boundaryGSRB(LevelData& phi, const LevelData& rhs, int pass, bool all) const {
     const std::vector<BoundaryBoxData>& ref = all ? simpleBoundaryBoxData : boundaryBoxData;
+    // (the slabs are disjoint and a colour pass reads only the other colour: any order gives the same bits)
+#pragma omp parallel for schedule(dynamic)
     for (size_t idx = 0; idx < ref.size(); ++idx) {
         const BoundaryBoxData& data = ref[idx];
         const size_t bi = (size_t)data.index;
@@ -367,6 +370,7 @@ void Op::relaxOnce(LevelData& phi, const LevelData& rhs) {
         LevelData res;
         res.define(grids, phi.nc, IntVect::Zero());
         residual(res, phi, rhs, true);
+#pragma omp parallel for schedule(dynamic)
         for (size_t b = 0; b < grids.size(); ++b) jacobi_iter(phi[b], res[b], lapDiag[b], grids[b], alpha, beta);
     } else {
         fprintf(stderr, "orc::Op::relaxOnce: bad relaxMode %d\n", relaxMode);
@@ -385,6 +389,7 @@ void Op::preCond(LevelData& phi, const LevelData& rhs) {
         assign(phi, rhs);
         return;
     }
+#pragma omp parallel for schedule(dynamic)
     for (size_t b = 0; b < grids.size(); ++b) diagprecond(phi[b], rhs[b], lapDiag[b], grids[b], alpha, beta);
     const int saveMode = relaxMode;
     if (precondMode == 2) relaxMode = RELAX_LINE_GSRB;  // PrecondMode::DiagLineRelax
@@ -412,6 +417,7 @@ void Op::restrictResidual(LevelData& resCoarse, LevelData& phiFine, const LevelD
 void Op::prolongIncrement(LevelData& phiFine, const LevelData& corrCoarse) const {
     const IntVect r = mgCrseRefRatio;
     if (!zeroAvgProlong) {
+#pragma omp parallel for schedule(dynamic)
         for (size_t b = 0; b < grids.size(); ++b) const_interp(phiFine[b], corrCoarse[b], grids[b], r);
         return;
     }
@@ -419,6 +425,7 @@ void Op::prolongIncrement(LevelData& phiFine, const LevelData& corrCoarse) const
     for (size_t b = 0; b < grids.size(); ++b)
         const_interp_with_avg(phiFine[b], corrCoarse[b], grids[b], r, Jinv[b], dxProduct, localVol, localSum);
     const double avgPhi = localSum / localVol;
+#pragma omp parallel for schedule(dynamic)
     for (size_t b = 0; b < grids.size(); ++b)
         for (double& v : phiFine[b].d) v -= avgPhi;  // a_phiThisLevel[dit] -= avgPhi (whole FAB, :163)
 }
@@ -428,6 +435,14 @@ void Op::prolongIncrement(LevelData& phiFine, const LevelData& corrCoarse) const
 // ----------------------------------------------------------------------------------------------
 double Op::norm(const LevelData& x, int ord) const {
     double r = 0.0;
+    if (ord == 0) {   // a maximum does not depend on the order it is taken in: boxes in parallel
+#pragma omp parallel for schedule(dynamic) reduction(max : r)
+        for (size_t b = 0; b < grids.size(); ++b) {
+            const FAB& f = x[b];
+            ORC_LOOP(grids[b], i, j, k) r = std::max(r, std::fabs(f(i, j, k)));
+        }
+        return r;
+    }
     for (size_t b = 0; b < grids.size(); ++b) {
         const FAB& f = x[b];
         ORC_LOOP(grids[b], i, j, k) {
@@ -449,6 +464,7 @@ double Op::dot(const LevelData& a, const LevelData& b2) const {
     return r;
 }
 void Op::incr(LevelData& y, const LevelData& x, double s) const {
+#pragma omp parallel for schedule(dynamic)
     for (size_t b = 0; b < grids.size(); ++b) {
         FAB& fy = y[b];
         const FAB& fx = x[b];
@@ -456,9 +472,11 @@ void Op::incr(LevelData& y, const LevelData& x, double s) const {
     }
 }
 void Op::assign(LevelData& y, const LevelData& x) const {
+#pragma omp parallel for schedule(dynamic)
     for (size_t b = 0; b < grids.size(); ++b) y[b].copy(x[b]);  // whole FAB (MappedAMRPoissonOp.H:577-581)
 }
 void Op::scale(LevelData& y, double s) const {
+#pragma omp parallel for schedule(dynamic)
     for (size_t b = 0; b < grids.size(); ++b) {
         FAB& fy = y[b];
         ORC_LOOP(grids[b], i, j, k) fy(i, j, k) *= s;
@@ -957,7 +975,9 @@ void MG::solve(LevelData& phi, const LevelData& rhs, bool zeroPhi, bool forceHom
         op.residual(uberResidual, phi, rhs, forceHomogeneous);
         return op.norm(uberResidual, 0);
     };
-    const double initial_rnorm = computeResidual();
+    double initial_rnorm = computeResidual();
+    if (convergenceMetric != 0.0) initial_rnorm = convergenceMetric;   // :1036-1038
+    bool somethingConverged = false;                                   // :1043
     double rnorm = initial_rnorm, norm_last = 2 * initial_rnorm, best_rnorm = rnorm;
     bool useBestPhi = false;
     bottomMetric = initial_rnorm;   // setConvergenceMetrics(initial_rnorm, cushion(=1) * eps) :1047
@@ -982,6 +1002,7 @@ void MG::solve(LevelData& phi, const LevelData& rhs, bool zeroPhi, bool forceHom
             best_rnorm = rnorm;
             op.assign(bestPhi, phi);
             useBestPhi = false;
+            somethingConverged = true;
         } else {
             useBestPhi = true;
         }
@@ -997,6 +1018,7 @@ void MG::solve(LevelData& phi, const LevelData& rhs, bool zeroPhi, bool forceHom
         rnorm = best_rnorm;
         op.assign(phi, bestPhi);
     }
+    blewUp = (!somethingConverged && rnorm >= initial_rnorm && rnorm >= p.eps);   // :1140-1144
     st.iters = iter;
     st.initial_rnorm = initial_rnorm;
     st.final_rnorm = rnorm;

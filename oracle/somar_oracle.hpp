@@ -159,6 +159,8 @@ struct MG {
     // bottom solver convergence metrics (BiCGStabSolver::setConvergenceMetrics)
     double bottomMetric = 0.0, bottomEps = 1e-6;
     int bottom_iters_total = 0;
+    double convergenceMetric = 0.0;   // MappedAMRMultiGrid::m_convergenceMetric (MappedAMRMultiGrid.H:1036-1038)
+    bool blewUp = false;              // "solver blew up" abort of :1140-1144 (the reference calls MayDay::Error)
     int depth() const { return (int)ops.size(); }
     void cycle(int depth, LevelData& e, const LevelData& r);
     int bottomSolve(LevelData& e, const LevelData& r);

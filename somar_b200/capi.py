@@ -23,7 +23,8 @@ RELAX_JACOBI, RELAX_LEVEL_GSRB, RELAX_LOOSE_GSRB, RELAX_LINE_GSRB = 0, 1, 2, 3
 SYMBOLS = [
     "somar_last_error", "somar_version", "somar_default_params", "somar_device_count", "somar_comm_unique_id",
     "somar_level_create", "somar_level_destroy", "somar_level_set_metric_fab", "somar_level_set_metric_device",
-    "somar_level_finalize", "somar_level_set_alpha_beta", "somar_level_num_depths", "somar_level_depth_info",
+    "somar_level_finalize", "somar_level_set_alpha_beta", "somar_level_set_convergence_metric",
+    "somar_level_set_solver_params", "somar_level_num_depths", "somar_level_depth_info",
     "somar_level_sync", "somar_level_stream", "somar_level_launch_count", "somar_level_get_metric",
     "somar_level_profile_enable", "somar_level_profile_read", "somar_level_relax_kernel", "somar_level_halo_path",
     "somar_field_create", "somar_field_destroy", "somar_field_set_fab", "somar_field_get_fab", "somar_field_set",
@@ -230,6 +231,10 @@ class Field:
         p, dev = _ptr(data)
         assert tuple(data.shape) == self.shape(), (tuple(data.shape), self.shape())
         _ck(lib().somar_field_set(self.h, p, dev))
+        if hasattr(data, "data_ptr"):
+            # the copy is only ENQUEUED on the library's stream; torch's caching allocator does not know that stream,
+            # so a torch source (device, or pinned host) must not be recycled before the copy has run
+            self.level.sync()
         return self
 
     def get(self, out=None):
@@ -245,6 +250,8 @@ class Field:
         """dense rank-local face array of direction dir: shape = cell shape with +1 point in that direction"""
         p, dev = _ptr(data)
         _ck(lib().somar_field_set_face(self.h, p, int(dir), dev))
+        if hasattr(data, "data_ptr"):
+            self.level.sync()
         return self
 
     def get_face(self, dir: int, out=None):
@@ -350,6 +357,7 @@ class Level:
         """torch CUDA tensors over the rank-local region (faces: +1 point in their direction)."""
         ps = [_ptr(j)[0] for j in list(jgup) + [None] * (3 - len(jgup))]
         _ck(lib().somar_level_set_metric_device(self.h, int(ncomp), ps[0], ps[1], ps[2], _ptr(jinv)[0]))
+        self.sync()   # the sources are torch tensors the caller may free right away (see Field.set)
 
     def finalize(self):
         _ck(lib().somar_level_finalize(self.h))
@@ -357,6 +365,14 @@ class Level:
 
     def set_alpha_beta(self, alpha, beta):
         _ck(lib().somar_level_set_alpha_beta(self.h, C.c_double(alpha), C.c_double(beta)))
+
+    def set_convergence_metric(self, metric: float):
+        _ck(lib().somar_level_set_convergence_metric(self.h, C.c_double(metric)))
+
+    def set_params(self, params: "SolverParams"):
+        """AMRPressureSolver::setAMRMGParameters / setBottomParameters on an existing level (not maxDepth)."""
+        _ck(lib().somar_level_set_solver_params(self.h, C.byref(params)))
+        self.params = params
 
     def depth_info(self, depth: int):
         n, r, lo, hi = (C.c_int * 3)(), (C.c_int * 3)(), (C.c_int * 3)(), (C.c_int * 3)()

@@ -235,6 +235,24 @@ int somar_level_set_alpha_beta(SomarLevel* L, double alpha, double beta) {
     return SOMAR_OK;   // lapDiag does not depend on alpha/beta (FILLMAPPEDLAPDIAG); the smoothers apply them
 }
 
+int somar_level_set_convergence_metric(SomarLevel* L, double metric) {
+    CHECK_LEVEL(L);
+    L->convergenceMetric = metric;
+    return SOMAR_OK;
+}
+
+int somar_level_set_solver_params(SomarLevel* L, const SomarSolverParams* p) {
+    CHECK_LEVEL(L);
+    if (!p) { set_error("null params"); return SOMAR_ERR_ARG; }
+    if (p->maxDepth != L->prm.maxDepth) {
+        set_error("maxDepth fixes the multigrid schedule and cannot change after somar_level_create");
+        return SOMAR_ERR_ARG;
+    }
+    L->prm = *p;
+    for (auto& dp : L->depths) dp.line_valid = false;
+    return SOMAR_OK;
+}
+
 int somar_level_num_depths(const SomarLevel* L, int* n) {
     CHECK_LEVEL(L);
     *n = L->ndepths();

@@ -100,6 +100,7 @@ struct SomarLevel {
     double* zeroPlane = nullptr;       // off0 + sz zeros of depth 0: the input of a relaxation that starts from phi = 0
     SomarField* pwork = nullptr;       // projector: the divergence / right-hand side (depth 0)
     double bottomMetric = 0.0, bottomEps = 1e-6;
+    double convergenceMetric = 0.0;    // MappedAMRMultiGrid::m_convergenceMetric (0: the initial residual norm)
     int bottom_iters_total = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     // phase profiler (CUDA events on the level stream; off by default)

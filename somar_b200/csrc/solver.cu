@@ -92,8 +92,10 @@ int mg_solve(SomarLevel* L, SomarField* phi, const SomarField* rhs, bool zeroPhi
     };
     double initial_rnorm;
     if ((rc = computeResidual(&initial_rnorm))) return rc;
+    if (L->convergenceMetric != 0.0) initial_rnorm = L->convergenceMetric;   // m_convergenceMetric :1036-1038
     double rnorm = initial_rnorm, norm_last = 2 * initial_rnorm, best_rnorm = rnorm;
     bool useBest = false;
+    bool somethingConverged = false;       // stays false while no V-cycle improves on what we were given :1043
     L->bottomMetric = initial_rnorm;       // setConvergenceMetrics(initial_rnorm, cushion * eps) :1047
     L->bottomEps = 1.0 * p.eps;
     if ((rc = bottom_collect_iters(L))) return rc;    // counts left by direct mg_cycle calls
@@ -119,6 +121,7 @@ int mg_solve(SomarLevel* L, SomarField* phi, const SomarField* rhs, bool zeroPhi
                 best_rnorm = rnorm;
                 bestIsCurrent = true;
                 useBest = false;
+                somethingConverged = true;
             } else {
                 if (bestIsCurrent) std::swap(best->p, spare->p);   // the previous iterate was the best one: keep it
                 bestIsCurrent = false;
@@ -152,6 +155,10 @@ int mg_solve(SomarLevel* L, SomarField* phi, const SomarField* rhs, bool zeroPhi
     st->launches = cx.launches - launches0;
     if (rnorm > 10.0 * initial_rnorm && rnorm > 10.0 * p.eps) {   // :1133-1138 "kaboom"
         set_error("solver diverged (residual > 10 x initial)");
+        return SOMAR_ERR_DIVERGED;
+    }
+    if (!somethingConverged && rnorm >= initial_rnorm && rnorm >= p.eps) {   // :1140-1144 "solver blew up"
+        set_error("MappedAMRMultiGrid solver blew up (no V-cycle improved on the initial guess)");
         return SOMAR_ERR_DIVERGED;
     }
     return SOMAR_OK;
