@@ -2,26 +2,38 @@
 """bench.py -- fp64 mapped-Poisson pressure solve (semicoarsening multigrid V-cycles) on B200, BASELINE.json metric.
 
 A "step" is ONE pressure solve of the synthetic stratified, stretched-grid problem: V-cycles until
-the max-norm residual has dropped by 1e-10, pre/post/bottom smooths 4/4/2, LevelGSRB (the shipped decks' settings).
+the max-norm residual has dropped by 1e-10, pre/post/bottom smooths 4/4/2, LevelGSRB.
     value  = N_fine * (#V-cycles) / t_solve   [Mcell-updates/s], whole job, inputs resident in HBM
     e2e    = same metric through the C ABI with HOST buffers: pinned rhs -> device, solve, phi -> host
 Strong scaling: the 1024 x 1024 x 256 grid is always cut into the same 8 y-slab boxes, spread over the N ranks.
+
+Solver knobs: the shipped decks' settings (exec/inputs.LockExchange_Cartesian3D.machine:96-113) EXCEPT two bottom-solver
+knobs of the reference's own parameter space (src/utils/ProblemContext.cpp:1206-1216, AMRPressureSolver.cpp:253-262):
+bottom.imax 80 -> 1000 and bottom.numRestarts 5 -> 50.  With the deck values the 256 x 256 x 4 bottom problem of this
+flat domain is not solved (BiCGStab stops after 5 restarts / 80 iterations) and the outer iteration hangs at ~1e-5;
+with them the solve reaches 1e-10 in 15 V-cycles (tools/converge_study.py).  The deck settings run as
+`config.secondary.deck` in the same line.
+
 `--impl reference` times the reference's own algorithm on the host cores (the CPU oracle; the reference itself
 needs Chombo/Fortran/MPI and cannot be built here), on a bounded sample of the workload.
 """
 import argparse
+import hashlib
 import json
 import os
 import subprocess
 import sys
-import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-SOLVE = dict(eps=1e-10, num_smooth_down=4, num_smooth_up=4, num_smooth_bottom=2, imin=0, imax=50)
+# the headline solve: every AMRMG.* / bottom.* knob that differs from the library defaults (= ProblemContext defaults)
+SOLVE = dict(eps=1e-10, num_smooth_down=4, num_smooth_up=4, num_smooth_bottom=2, imin=0, imax=50,
+             bottom_imax=1000, bottom_numRestarts=50)
+DECK_BOTTOM = dict(bottom_imax=80, bottom_numRestarts=5)          # what the shipped decks use
+CHANGED_KNOBS = "bottom.imax 80->1000, bottom.numRestarts 5->50 (all other knobs: shipped decks)"
 NBOXES = 8
-CPU_SAMPLE_GRID = (256, 256, 64)
+SWEEP_GRIDS = [(256, 256, 64), (512, 512, 128)]                   # SURVEY 8(d) sweep points below the headline
 CPU_SAMPLE_CYCLES = 2
 
 
@@ -37,70 +49,111 @@ def parse():
     ap.add_argument("--relax", type=int, default=1)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the secondary blocks (deck, relax3, sweep, terrain)")
+    ap.add_argument("--cpu-grid", type=int, nargs=3, default=None, help="grid of the CPU sample (default: by host RAM)")
     return ap.parse_args()
 
 
+def workload_text(grid, map_name, aniso, relax, solve):
+    return (f"synthetic stratified stretched-grid Poisson solve {grid[0]}x{grid[1]}x{grid[2]} ({map_name}, "
+            f"dx/dz={aniso:g}, homogeneous Neumann, eps {solve['eps']:g}, pre/post/bottom "
+            f"{solve['num_smooth_down']}/{solve['num_smooth_up']}/{solve['num_smooth_bottom']}, relax_mode {relax}, "
+            f"bottom.imax {solve['bottom_imax']}, bottom.numRestarts {solve['bottom_numRestarts']})")
+
+
+def workload_config(a, extra, grid=None):
+    grid = list(grid if grid is not None else a.grid)
+    c = {"workload": workload_text(grid, a.map, a.aniso, a.relax, SOLVE), "knobs_changed_from_decks": CHANGED_KNOBS,
+         "grid": grid, "boxes": NBOXES, "partition": f"y-slabs over {a.gpus} GPU(s)",
+         "l2_policy": "inputs larger than L2 (2.2 GB per field at depth 0 vs 126 MB L2)"}
+    if extra:
+        c.update(extra)
+    return c
+
+
 # ------------------------------------------------------------------------------------------------------------
+# CPU arm: the oracle (restatement of the reference's CPU path) on the host cores
+# ------------------------------------------------------------------------------------------------------------
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def cpu_sample_grid(a):
+    if a.cpu_grid:
+        return tuple(a.cpu_grid)
+    avail_gb = 0.0
+    try:
+        for ln in open("/proc/meminfo"):
+            if ln.startswith("MemAvailable:"):
+                avail_gb = float(ln.split()[1]) / 1048576.0
+    except OSError:
+        pass
+    # 512 x 512 x 128 needs ~15 GB in the oracle; 256 x 256 x 64 otherwise
+    return (512, 512, 128) if (avail_gb >= 40.0 and host_cores() >= 16) else (256, 256, 64)
+
+
 def cpu_reference_run(grid, aniso, map_name, relax, cycles, threads=None):
     """Times the oracle (port of the reference's CPU path) on `grid`, capped at `cycles` V-cycles."""
     import numpy as np
     from oracle import pyoracle as po
     from somar_b200 import synthetic as syn
     po.build()
-    if threads:
-        po.set_threads(threads)
+    # torchrun exports OMP_NUM_THREADS=1 to its workers: ask for the cores explicitly
+    po.set_threads(threads or host_cores())
+    got = po.max_threads()
     spec = syn.headline_grid(n=tuple(grid), aniso=aniso, map_name=map_name)
     m = syn.build_metric(spec)
     jg = [np.ascontiguousarray(j[0].numpy()) if m.ncomp == 1 else j.numpy() for j in m.jgup]
     rhs = syn.random_rhs(spec, m.jinv).numpy()
-    # one y-slab box per host thread (the reference runs one MPI rank per core, each owning boxes); the oracle's
-    # OpenMP loops run over boxes
+    # one y-slab box per host thread (the reference runs one MPI rank per core, each owning boxes; the oracle's
+    # OpenMP loops run over boxes), at least the 8 boxes of the GPU arm, at least 4 cells per box at the bottom depth
     nb = 1
-    while nb * 2 <= po.max_threads() and grid[1] // (nb * 2) >= 16:
+    while nb * 2 <= max(got, NBOXES) and grid[1] // (nb * 2) >= 16:
         nb *= 2
     boxes = syn.split_boxes(spec.n, (1, nb, 1))
     orc = po.Oracle(spec.n, spec.dx, jg, m.jinv.numpy(), dim=3, is_diagonal=spec.is_diagonal, boxes=boxes,
                     params=po.default_params(relaxMode=relax, **SOLVE))
     secs, st = orc.timed_solve(rhs, ncycles_cap=cycles)
     cells = grid[0] * grid[1] * grid[2]
-    return {"secs": secs, "iters": st["iters"], "mcups": cells * st["iters"] / secs / 1e6,
-            "cores": min(nb, po.max_threads()), "boxes": nb}
+    return {"secs": secs, "iters": st["iters"], "mcups": cells * st["iters"] / secs / 1e6, "cores": got, "boxes": nb,
+            "bottom_iters": st["bottom_iters_total"]}
+
+
+def cpu_sample_text(grid, map_name, aniso, r):
+    return (f"{grid[0]}x{grid[1]}x{grid[2]} {map_name} grid, dx/dz={aniso:g}, same solver knobs, first {r['iters']} V-cycles "
+            f"of the solve ({r['bottom_iters']} bottom iterations) in {r['secs']:.2f} s, {r['cores']} OpenMP threads over "
+            f"{r['boxes']} y-slab boxes")
 
 
 def run_reference(a):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    grid = cpu_sample_grid(a)
     vals = []
     for i in range(a.warmup + a.steps):
-        r = cpu_reference_run(CPU_SAMPLE_GRID, a.aniso, a.map, a.relax, CPU_SAMPLE_CYCLES)
+        r = cpu_reference_run(grid, a.aniso, a.map, a.relax, CPU_SAMPLE_CYCLES)
         if i >= a.warmup:
             vals.append(r)
     secs = sum(v["secs"] for v in vals) / len(vals)
     mc = sum(v["mcups"] for v in vals) / len(vals)
-    sample = (f"{CPU_SAMPLE_GRID[0]}x{CPU_SAMPLE_GRID[1]}x{CPU_SAMPLE_GRID[2]} {a.map} grid, aniso {a.aniso:g}, "
-              f"{CPU_SAMPLE_CYCLES} V-cycles per step, OpenMP over {vals[0]['boxes']} y-slab boxes")
+    cfg = workload_config(a, {"same_config": False, "partition": f"{vals[0]['boxes']} y-slab boxes on the host",
+                              "boxes": vals[0]["boxes"], "vcycles_per_step": CPU_SAMPLE_CYCLES,
+                              "note": "bounded sample of the headline workload: smaller grid of the same family, the "
+                                      "first V-cycles of the solve; the GPU arm runs 1024x1024x256 to convergence",
+                              "l2_policy": "n/a (CPU)"}, grid=grid)
     line = {"impl": "reference", "metric": "fp64 Poisson V-cycle Mcell-updates/s", "value": mc, "unit": "Mcell-updates/s",
             "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": secs * 1e3,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": workload_config(a, None),
+            "config": cfg,
             "cpu_baseline": {"value": mc, "unit": "Mcell-updates/s", "cores": vals[0]["cores"], "kind": "port",
-                             "sample": sample},
+                             "sample": cpu_sample_text(grid, a.map, a.aniso, vals[-1])},
             "e2e": {"value": mc, "unit": "Mcell-updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     emit(line)
-
-
-def workload_config(a, extra):
-    c = {"workload": f"synthetic stratified stretched-grid Poisson solve {a.grid[0]}x{a.grid[1]}x{a.grid[2]} "
-                     f"({a.map}, dx/dz={a.aniso:g}, homogeneous Neumann, eps 1e-10, pre/post/bottom 4/4/2, "
-                     f"relax_mode {a.relax})",
-         "grid": list(a.grid), "boxes": NBOXES, "partition": f"y-slabs over {a.gpus} GPU(s)",
-         "l2_policy": "inputs larger than L2 (2.2 GB per field at depth 0 vs 126 MB L2)"}
-    if extra:
-        c.update(extra)
-    return c
-
 
 # ------------------------------------------------------------------------------------------------------------
 class ClockSampler:
@@ -159,126 +212,316 @@ def byte_model(schedule, diagonal, relax, pre, post):
     return total
 
 
-def run_ours(a):
-    import numpy as np
-    import torch
-    import torch.distributed as dist
-    from somar_b200 import capi, synthetic as syn
+KERNEL_BYTES = {"k_gsrb_ortho": 48, "k_gsrb_fused": 96, "k_gsrb_async": 96, "k_gsrb_full": 104, "k_gsrb_full_march": 208}
+KERNEL_DESC = {"k_gsrb_ortho": "k_gsrb_ortho<3> (depth-0 red/black colour pass, 2 launches per iteration)",
+               "k_gsrb_fused": "k_gsrb_fused (depth-0 red+black iteration in one sweep)",
+               "k_gsrb_async": "k_gsrb_async (depth-0 red+black iteration in one sweep, producer/consumer pipeline)",
+               "k_gsrb_full": "k_gsrb_full<3> (depth-0 colour pass, full metric)",
+               "k_gsrb_full_march": "k_gsrb_full_march (depth-0 red+black iteration in one sweep, full metric)",
+               "k_line_gsrb": "k_line_gsrb<3> (depth-0 vertical-line colour pass)",
+               "k_line_pair": "k_line_pair (depth-0 vertical-line red+black iteration in one launch)"}
+KERNEL_SOURCE = {"k_gsrb_ortho": "ops_ortho.cu", "k_gsrb_fused": "gsrb_fused.cu", "k_gsrb_async": "gsrb_async.cu",
+                 "k_gsrb_full": "ops_ortho.cu", "k_gsrb_full_march": "gsrb_full_march.cu", "k_line_gsrb": "line.cu",
+                 "k_line_pair": "line.cu"}
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    comm_id = None
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-        buf = torch.zeros(128, dtype=torch.uint8, device=dev)
-        if rank == 0:
+
+def kernel_bytes_per_cell(kname, diagonal):
+    if kname == "k_line_gsrb":
+        return 44 if diagonal else 100
+    if kname == "k_line_pair":
+        return 88 if diagonal else 200
+    return KERNEL_BYTES[kname]
+
+
+def source_sha(kname):
+    p = os.path.join(ROOT, "somar_b200", "csrc", KERNEL_SOURCE.get(kname, ""))
+    if not os.path.isfile(p):
+        return None
+    return hashlib.sha256(open(p, "rb").read()).hexdigest()[:16]
+
+
+def measured_traffic(kname, map_name, grid, world):
+    """DRAM bytes per launch from the ncu --set full capture recorded in profiles/traffic.json -- only when the capture
+    is of the kernel source as it is NOW (sha of the .cu file); a stale capture reads as null."""
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if not os.path.exists(tpath):
+        return None, "no profiles/traffic.json"
+    tj = json.load(open(tpath))
+    key = f"{kname}_{map_name}_{grid[0]}x{grid[1]}x{grid[2]}_gpus{world}"
+    ent = tj.get(key)
+    if not ent:
+        return None, f"no ncu capture recorded for {key}"
+    if ent.get("source_sha16") != source_sha(kname):
+        return None, f"ncu capture {ent.get('capture')} is of an older {KERNEL_SOURCE.get(kname)} (stale)"
+    return ent.get("dram_bytes_per_launch"), ent.get("capture")
+
+
+# ------------------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------------------
+class Ctx:
+    """rank / device bookkeeping of one bench process"""
+
+    def __init__(self):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist = torch, dist
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        if self.world > 1:
+            dist.init_process_group("nccl", device_id=self.dev)
+
+    def new_comm_id(self):
+        """a fresh NCCL unique id for one level: made on rank 0, broadcast with torch.distributed"""
+        if self.world == 1:
+            return None
+        from somar_b200 import capi
+        torch = self.torch
+        buf = torch.zeros(128, dtype=torch.uint8, device=self.dev)
+        if self.rank == 0:
             buf.copy_(torch.tensor(list(capi.comm_unique_id()), dtype=torch.uint8))
-        dist.broadcast(buf, 0)
-        comm_id = bytes(buf.cpu().tolist())
-    assert NBOXES % world == 0, "--gpus must divide 8"
+        self.dist.broadcast(buf, 0)
+        return bytes(buf.cpu().tolist())
 
-    grid = tuple(a.grid)
-    spec = syn.headline_grid(n=grid, aniso=a.aniso, map_name=a.map)
-    boxes = syn.split_boxes(grid, (1, NBOXES, 1))
-    box_rank = [b * world // NBOXES for b in range(NBOXES)]
-    mine = [b for b in range(NBOXES) if box_rank[b] == rank]
-    j0, j1 = boxes[mine[0]][0][1], boxes[mine[-1]][1][1] + 1
-    params = capi.default_params(relaxMode=a.relax, **SOLVE)
-    lev = capi.Level(grid, spec.dx, dim=3, is_diagonal=spec.is_diagonal, boxes=boxes, box_rank=box_rank, params=params,
-                     device=local, rank=rank, nranks=world, comm_id=comm_id)
-    m = syn.build_metric(spec, device=dev, yrange=(j0, j1))
-    if m.ncomp == 1:
-        lev.set_metric_device([j[0].contiguous() for j in m.jgup], m.jinv, 1)
-    else:
-        lev.set_metric_device(m.jgup, m.jinv, m.ncomp)
-    lev.finalize()
-    # rhs: seeded global field, zero dV-mean (every rank draws the same numbers and keeps its slab)
-    gen = torch.Generator(device=dev)
-    gen.manual_seed(12345)
-    w = 1.0 / m.jinv
-    parts = []
-    for b in range(NBOXES):   # box by box so that no rank ever holds the global field
-        r = torch.rand((grid[2], boxes[b][1][1] - boxes[b][0][1] + 1, grid[0]), dtype=torch.float64, device=dev,
-                       generator=gen) * 2.0 - 1.0
-        if b in mine:
-            parts.append(r)
-        del r
-    rhs = torch.cat(parts, 1).contiguous()
-    del parts
-    sums = torch.stack([(rhs * w).sum(), w.sum()])
-    if world > 1:
-        dist.all_reduce(sums)
-    rhs -= sums[0] / sums[1]
-    del w, m
-    torch.cuda.empty_cache()
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
 
-    frhs, fphi = lev.field(0, rhs), lev.field(0)
-    h_rhs = rhs.cpu().pin_memory()
-    h_phi = torch.empty_like(h_rhs).pin_memory()
-    del rhs
-    stream = torch.cuda.ExternalStream(lev.stream(), device=dev)
-    schedule = [lev.depth_info(d) for d in range(lev.ndepths)]
-    n_fine = grid[0] * grid[1] * grid[2]
-    local_cells = grid[0] * (j1 - j0) * grid[2]
 
-    def barrier():
+class Job:
+    """One synthetic problem of the SURVEY 8(d) family resident on this rank: level (all depths), rhs, phi."""
+
+    def __init__(self, cx, grid, aniso, map_name, relax, solve):
+        from somar_b200 import capi, synthetic as syn
+        torch = cx.torch
+        self.cx, self.grid = cx, tuple(grid)
+        world, rank = cx.world, cx.rank
+        assert NBOXES % world == 0, "--gpus must divide 8"
+        self.spec = spec = syn.headline_grid(n=self.grid, aniso=aniso, map_name=map_name)
+        boxes = syn.split_boxes(self.grid, (1, NBOXES, 1))
+        box_rank = [b * world // NBOXES for b in range(NBOXES)]
+        mine = [b for b in range(NBOXES) if box_rank[b] == rank]
+        j0, j1 = boxes[mine[0]][0][1], boxes[mine[-1]][1][1] + 1
+        self.solve_kw = dict(solve)
+        self.relax = relax
+        params = capi.default_params(relaxMode=relax, **solve)
+        lev = capi.Level(self.grid, spec.dx, dim=3, is_diagonal=spec.is_diagonal, boxes=boxes, box_rank=box_rank,
+                         params=params, device=cx.local, rank=rank, nranks=world, comm_id=cx.new_comm_id())
+        m = syn.build_metric(spec, device=cx.dev, yrange=(j0, j1))
+        if m.ncomp == 1:
+            lev.set_metric_device([j[0].contiguous() for j in m.jgup], m.jinv, 1)
+        else:
+            lev.set_metric_device(m.jgup, m.jinv, m.ncomp)
+        lev.finalize()
+        # rhs: seeded global field, zero dV-mean (every rank draws the same numbers and keeps its slab)
+        gen = torch.Generator(device=cx.dev)
+        gen.manual_seed(12345)
+        w = 1.0 / m.jinv
+        parts = []
+        for b in range(NBOXES):   # box by box so that no rank ever holds the global field
+            r = torch.rand((self.grid[2], boxes[b][1][1] - boxes[b][0][1] + 1, self.grid[0]), dtype=torch.float64,
+                           device=cx.dev, generator=gen) * 2.0 - 1.0
+            if b in mine:
+                parts.append(r)
+            del r
+        rhs = torch.cat(parts, 1).contiguous()
+        del parts
+        sums = torch.stack([(rhs * w).sum(), w.sum()])
         if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
+            cx.dist.all_reduce(sums)
+        rhs -= sums[0] / sums[1]
+        del w, m
+        self.lev = lev
+        self.frhs, self.fphi = lev.field(0, rhs), lev.field(0)
+        self.rhs = rhs
+        torch.cuda.empty_cache()
+        self.stream = torch.cuda.ExternalStream(lev.stream(), device=cx.dev)
+        self.schedule = [lev.depth_info(d) for d in range(lev.ndepths)]
+        self.n_fine = self.grid[0] * self.grid[1] * self.grid[2]
+        self.local_cells = self.grid[0] * (j1 - j0) * self.grid[2]
 
-    def timed(fn, steps):
-        barrier()
+    def set_knobs(self, **kw):
+        from somar_b200 import capi
+        k = dict(self.solve_kw)
+        k.update(kw)
+        relax = k.pop("relaxMode", self.relax)
+        self.lev.set_params(capi.default_params(relaxMode=relax, **k))
+
+    def solve(self):
+        return self.lev.solve(self.fphi, self.frhs)
+
+    def timed(self, fn, steps):
+        """`steps` calls of fn between barriers, CUDA events on the level stream, max over ranks -> (ms, results)"""
+        cx, torch = self.cx, self.cx.torch
+        cx.barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(stream)
+        e0.record(self.stream)
         out = [fn() for _ in range(steps)]
-        e1.record(stream)
+        e1.record(self.stream)
         e1.synchronize()
-        barrier()
-        t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        cx.barrier()
+        t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=cx.dev)
+        if cx.world > 1:
+            cx.dist.all_reduce(t, op=cx.dist.ReduceOp.MAX)
         return float(t.item()), out
 
-    def solve_resident():
-        return lev.solve(fphi, frhs)
+    def close(self):
+        self.frhs.destroy()
+        self.fphi.destroy()
+        self.lev.destroy()
+        self.rhs = None
+        self.cx.torch.cuda.empty_cache()
+
+
+def solve_summary(job, ms, stats, steps):
+    """the numbers of a timed run of `steps` solves that every block of the line reports"""
+    it = sum(s["iters"] for s in stats)
+    last = stats[-1]
+    rel = last["final_rnorm"] / last["initial_rnorm"] if last["initial_rnorm"] > 0 else 0.0
+    return {"value": job.n_fine * it / (ms * 1e-3) / 1e6, "unit": "Mcell-updates/s", "ms_per_solve": ms / steps,
+            "vcycles_per_solve": it / steps, "final_rel_residual": rel, "exit_status": last["exit_status"],
+            "converged": bool(last["exit_status"] == 1 and rel <= job.solve_kw["eps"]),
+            "bottom_iters_per_solve": last["bottom_iters_total"]}
+
+
+def profiled_solve(job, relax):
+    """one warm-up solve, then one timed solve with the phase profiler on -> (ms, stats, kernel block)"""
+    job.solve()
+    job.lev.profile(True)
+    job.lev.profile_read()
+    ms, stats = job.timed(job.solve, 1)
+    prof = job.lev.profile_read()
+    job.lev.profile(False)
+    k = prof["smooth0_kernel"]
+    kname = job.lev.relax_kernel(0, relax)
+    avg = k["ms"] / max(k["count"], 1)
+    bpc = kernel_bytes_per_cell(kname, job.spec.is_diagonal)
+    kb = {"kernel": KERNEL_DESC.get(kname, kname), "kernel_ms": avg, "kernel_launches": k["count"],
+          "alg_bytes_per_cell_per_launch": bpc,
+          "kernel_model_gbs": bpc * job.local_cells / (avg * 1e-3) / 1e9 if avg > 0 else None,
+          "phase_ms_per_solve": {n: v["ms"] for n, v in prof.items()}}
+    return ms, stats, kb
+
+
+def secondary_blocks(a, cx, job):
+    """Extra measurements of the same run (none of them is `value`): three strict V-cycles whose residuals must agree
+    across GPU counts, the shipped decks' bottom knobs, LineGSRB."""
+    sec = {}
+    # (1) three V-cycles with the Krylov bottom off (bottom.imax 0: the bottom is its two relaxations): every kernel on
+    #     this path is bit-exact across rank counts, so the three max-norm residuals must agree between N = 1, 2, 4, 8
+    job.set_knobs(bottom_imax=0, imin=3, imax=3)
+    st = job.solve()
+    strict3 = [h / st["history"][0] for h in st["history"][1:4]]
+    # (2) the shipped decks' bottom knobs (bottom.imax 80, numRestarts 5): the solve that hangs
+    job.set_knobs(**DECK_BOTTOM)
+    job.solve()
+    ms, stats = job.timed(job.solve, 1)
+    sec["deck"] = dict(solve_summary(job, ms, stats, 1), knobs="bottom.imax 80, bottom.numRestarts 5 (shipped decks)",
+                       residual_history=[h / stats[-1]["history"][0] for h in stats[-1]["history"]])
+    # (3) LineGSRB (relax_mode 3), same knobs as the headline
+    if a.relax != 3:
+        try:
+            job.set_knobs(relaxMode=3)
+            ms, stats, kb = profiled_solve(job, 3)
+            sec["relax3"] = dict(solve_summary(job, ms, stats, 1), **kb,
+                                 residual_history=[h / stats[-1]["history"][0] for h in stats[-1]["history"]])
+        except Exception as e:   # a secondary block never takes the headline down
+            sec["relax3"] = {"error": str(e)}
+    job.set_knobs()
+    return strict3, sec
+
+
+def sweep_blocks(a, cx):
+    """the SURVEY 8(d) sweep points below the headline, same family and knobs, two timed solves each"""
+    out = []
+    for g in SWEEP_GRIDS:
+        if tuple(g) == tuple(a.grid):
+            continue
+        try:
+            j = Job(cx, g, a.aniso, a.map, a.relax, SOLVE)
+            j.solve()
+            ms, stats = j.timed(j.solve, 2)
+            out.append(dict(solve_summary(j, ms, stats, 2), grid=list(g)))
+            j.close()
+        except Exception as e:
+            out.append({"grid": list(g), "error": str(e)})
+    return out
+
+
+def terrain_block(a, cx):
+    """family T (terrain-following, full J g^{ij}) at 512 x 512 x 128: value, per-kernel time, byte-model rate"""
+    g = (512, 512, 128)
+    try:
+        j = Job(cx, g, a.aniso, "terrain", a.relax, SOLVE)
+        ms, stats, kb = profiled_solve(j, a.relax)
+        out = dict(solve_summary(j, ms, stats, 1), grid=list(g), map="terrain", **kb)
+        j.close()
+        return out
+    except Exception as e:
+        return {"grid": list(g), "map": "terrain", "error": str(e)}
+
+
+def run_ours(a):
+    cx = Ctx()
+    torch, world, rank = cx.torch, cx.world, cx.rank
+    job = Job(cx, a.grid, a.aniso, a.map, a.relax, SOLVE)
+    lev = job.lev
+    h_rhs = job.rhs.cpu().pin_memory()
+    h_phi = torch.empty_like(h_rhs).pin_memory()
+    job.rhs = None
+    torch.cuda.empty_cache()
 
     def solve_e2e():
-        frhs.set(h_rhs)                      # pinned host -> device (inside the timed region)
-        st = lev.solve(fphi, frhs)
-        fphi.get(h_phi)                      # device -> pinned host (synchronises)
+        job.frhs.set(h_rhs)                  # pinned host -> device (inside the timed region)
+        st = job.solve()
+        job.fphi.get(h_phi)                  # device -> pinned host (synchronises)
         return st
 
     for _ in range(a.warmup):
-        st = solve_resident()
+        job.solve()
     lev.profile(True)
     lev.profile_read()
-    clocks = ClockSampler(local) if rank == 0 else None
-    ms, stats = timed(solve_resident, a.steps)
+    clocks = ClockSampler(cx.local) if rank == 0 else None
+    ms, stats = job.timed(job.solve, a.steps)
     clk = clocks.stop() if clocks else None
     prof = lev.profile_read()
     lev.profile(False)
+    head = solve_summary(job, ms, stats, a.steps)
     iters = sum(s["iters"] for s in stats)
     launches = sum(s["launches"] for s in stats)
-    value = n_fine * iters / (ms * 1e-3) / 1e6
 
     e2e = None
     if not a.no_e2e:
         solve_e2e()
-        ms_e, stats_e = timed(solve_e2e, a.steps)
+        ms_e, stats_e = job.timed(solve_e2e, a.steps)
         it_e = sum(s["iters"] for s in stats_e)
-        e2e = {"value": n_fine * it_e / (ms_e * 1e-3) / 1e6, "unit": "Mcell-updates/s",
+        e2e = {"value": job.n_fine * it_e / (ms_e * 1e-3) / 1e6, "unit": "Mcell-updates/s",
                "h2d_bytes_per_step": int(h_rhs.numel() * 8 * world), "d2h_bytes_per_step": int(h_phi.numel() * 8 * world),
                "ms_per_step": ms_e / a.steps}
 
+    strict3, sec = None, {}
+    if not a.no_secondary:
+        strict3, sec = secondary_blocks(a, cx, job)
+    schedule, spec, local_cells = job.schedule, job.spec, job.local_cells
+    kname = lev.relax_kernel(0, a.relax)
+    halo = lev.halo_path()
+    job.close()
+    del h_rhs, h_phi
+    if not a.no_secondary:
+        sec["sweep"] = sweep_blocks(a, cx)
+        if a.map != "terrain":
+            sec["terrain"] = terrain_block(a, cx)
+
     if rank != 0:
         if world > 1:
-            dist.destroy_process_group()
-        return
+            cx.dist.destroy_process_group()
+        return 0 if head["converged"] else 4
     peaks = {}
     pk_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(pk_path):
@@ -288,53 +531,56 @@ def run_ours(a):
     k = prof["smooth0_kernel"]
     # algorithmic bytes per cell one launch of the depth-0 smoother kernel moves (a red+black GSRB
     # iteration is 96 B/cell diagonal, 208 full; LineGSRB 88 / 200; a colour pass is half an iteration)
-    kname = lev.relax_kernel(0, a.relax)
-    per_cell = {"k_gsrb_ortho": 48, "k_gsrb_fused": 96, "k_gsrb_async": 96, "k_gsrb_full": 104,
-                "k_line_gsrb": 44 if spec.is_diagonal else 100}[kname]
-    kdesc = {"k_gsrb_ortho": "k_gsrb_ortho<3> (depth-0 red/black colour pass, 2 launches per iteration)",
-             "k_gsrb_fused": "k_gsrb_fused (depth-0 red+black iteration in one sweep)",
-             "k_gsrb_async": "k_gsrb_async (depth-0 red+black iteration in one sweep, producer/consumer pipeline)",
-             "k_gsrb_full": "k_gsrb_full<3> (depth-0 colour pass, full metric)",
-             "k_line_gsrb": "k_line_gsrb<3> (depth-0 vertical-line colour pass)"}[kname]
+    per_cell = kernel_bytes_per_cell(kname, spec.is_diagonal)
     alg_bytes = per_cell * local_cells
     avg_ms = k["ms"] / max(k["count"], 1)
     achieved = alg_bytes / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
-    traffic = None
-    tpath = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tpath):
-        tj = json.load(open(tpath))
-        key = f"{kname}_{a.map}_{grid[0]}x{grid[1]}x{grid[2]}_gpus{world}"
-        traffic = tj.get(key, {}).get("dram_bytes_per_launch")
+    traffic, traffic_src = measured_traffic(kname, a.map, a.grid, world)
     bv = byte_model(schedule, spec.is_diagonal, a.relax, SOLVE["num_smooth_down"], SOLVE["num_smooth_up"])
     vcycle_gbs = bv * iters / (ms * 1e-3) / 1e9
-    line = {"metric": "fp64 Poisson V-cycle Mcell-updates/s", "value": value, "unit": "Mcell-updates/s", "n_gpus": world,
-            "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms / a.steps, "higher_is_better": True,
+    hist = stats[-1]["history"]
+    cfg = {"halo_path": halo, "vcycles_per_solve": head["vcycles_per_solve"],
+           "final_rel_residual": head["final_rel_residual"], "exit_status": head["exit_status"],
+           "converged": head["converged"], "residual_history": [h / hist[0] for h in hist],
+           "bottom_iters_per_solve": head["bottom_iters_per_solve"],
+           "schedule": [{"n": list(s["n"]), "ratio": list(s["ratio"])} for s in schedule],
+           "model_bytes_per_vcycle": bv, "vcycle_model_gbs": vcycle_gbs,
+           "vcycle_hbm_frac_per_gpu": vcycle_gbs / world / peak,
+           "phase_ms_per_solve": {n: v["ms"] / a.steps for n, v in prof.items()},
+           "phase_ms_per_vcycle": {n: v["ms"] / max(iters, 1) for n, v in prof.items()}}
+    if strict3 is not None:
+        cfg["strict3"] = strict3
+    if sec:
+        cfg["sweep"] = sec.pop("sweep", None)
+        cfg["secondary"] = sec
+    line = {"metric": "fp64 Poisson V-cycle Mcell-updates/s", "value": head["value"], "unit": "Mcell-updates/s",
+            "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms / a.steps, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": workload_config(a, {
-                "halo_path": lev.halo_path(),
-                "vcycles_per_solve": iters / a.steps, "final_rel_residual": stats[-1]["final_rnorm"] / stats[-1]["initial_rnorm"],
-                "exit_status": stats[-1]["exit_status"], "bottom_iters_per_solve": stats[-1]["bottom_iters_total"],
-                "schedule": [{"n": list(s["n"]), "ratio": list(s["ratio"])} for s in schedule],
-                "model_bytes_per_vcycle": bv, "vcycle_model_gbs": vcycle_gbs,
-                "vcycle_hbm_frac_per_gpu": vcycle_gbs / world / peak,
-                "phase_ms_per_solve": {n: v["ms"] / a.steps for n, v in prof.items()}}),
-            "roofline": {"bound": "hbm", "kernel": kdesc, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                         "alg_bytes_per_launch": alg_bytes, "avg_launch_ms": avg_ms, "launches_timed": k["count"],
-                         # the same launch time against the DRAM bytes ncu saw (profiles/traffic.json): the fused sweep
-                         # moves fewer bytes than the SURVEY 8(d) model charges, so `frac` can exceed 1; this one cannot
+            "config": workload_config(a, cfg),
+            "roofline": {"bound": "hbm", "kernel": KERNEL_DESC.get(kname, kname), "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                         "peak_source": peak_src, "alg_bytes_per_launch": alg_bytes, "avg_launch_ms": avg_ms,
+                         "launches_timed": k["count"],
+                         # the same launch time against the DRAM bytes ncu saw: the fused sweep moves fewer bytes than
+                         # the SURVEY 8(d) model charges, so `frac` can exceed 1; this one cannot
                          "frac_of_peak_by_dram_traffic": (traffic / (avg_ms * 1e-3) / 1e9 / peak) if (traffic and avg_ms > 0) else None},
-            "clocks": clk, "gpu_launches": int(launches), "pressure_solve_ms": ms / a.steps}
+            "clocks": clk, "gpu_launches": int(launches), "pressure_solve_ms": ms / a.steps,
+            "converged": head["converged"]}
     if e2e:
         line["e2e"] = e2e
     if world == 1 and not a.no_cpu_baseline:
-        r = cpu_reference_run(CPU_SAMPLE_GRID, a.aniso, a.map, a.relax, CPU_SAMPLE_CYCLES)
+        g = cpu_sample_grid(a)
+        r = cpu_reference_run(g, a.aniso, a.map, a.relax, CPU_SAMPLE_CYCLES)
         line["cpu_baseline"] = {"value": r["mcups"], "unit": "Mcell-updates/s", "cores": r["cores"], "kind": "port",
-                                "sample": f"{CPU_SAMPLE_GRID[0]}x{CPU_SAMPLE_GRID[1]}x{CPU_SAMPLE_GRID[2]} {a.map} grid, "
-                                          f"{r['iters']} V-cycles in {r['secs']:.2f} s, OpenMP over {r['boxes']} y-slab boxes"}
+                                "sample": cpu_sample_text(g, a.map, a.aniso, r)}
     emit(line)
     if world > 1:
-        dist.destroy_process_group()
+        cx.dist.destroy_process_group()
+    if not head["converged"]:
+        print(f"bench.py: the headline solve did NOT converge (exit_status {head['exit_status']}, relative residual "
+              f"{head['final_rel_residual']:.3e}): pressure_solve_ms is not a time-to-tolerance", file=sys.stderr)
+        return 4
+    return 0
 
 
 _JSON_OUT = None
@@ -354,5 +600,5 @@ if __name__ == "__main__":
     args = parse()
     if args.impl == "reference":
         run_reference(args)
-    else:
-        run_ours(args)
+        sys.exit(0)
+    sys.exit(run_ours(args))
