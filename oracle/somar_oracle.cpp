@@ -372,6 +372,9 @@ void Op::relaxOnce(LevelData& phi, const LevelData& rhs) {
         residual(res, phi, rhs, true);
 #pragma omp parallel for schedule(dynamic)
         for (size_t b = 0; b < grids.size(); ++b) jacobi_iter(phi[b], res[b], lapDiag[b], grids[b], alpha, beta);
+    } else if (relaxMode == -1) {
+        // ProblemContext::RelaxMode::NORELAX: the factory installs no relaxation method and relax() returns at once
+        // (MappedAMRPoissonOp.cpp:1733-1743, m_relaxPtr == NULL)
     } else {
         fprintf(stderr, "orc::Op::relaxOnce: bad relaxMode %d\n", relaxMode);
         abort();
