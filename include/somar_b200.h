@@ -181,6 +181,18 @@ int somar_norm(SomarLevel* lev, const SomarField* x, int ord, double* out);     
 int somar_local_max_norm(SomarLevel* lev, const SomarField* x, double* out);      /* localMaxNorm */
 int somar_dot(SomarLevel* lev, const SomarField* a, const SomarField* b, double* out);
 
+/* ---- allocation-free norm ---------------------------------------------------------------------------------
+ * somar_norm_noalloc has NO counterpart in the reference: it was added for
+ * callers that cannot call cudaMalloc (CUDA-graph capture, tight serving loops, harnesses that forbid allocation).
+ * It is the reduction behind somar_norm (ord 0: max |x|, 1: sum |x|, 2: sqrt(sum x^2)) over a DENSE device array of
+ * n doubles, with the result written to the device address d_out, enqueued on `cuda_stream` (NULL = the default
+ * stream) of the CURRENT device; it does not synchronise.  Its scratch (per-block partials + ticket) is a file-scope
+ * static __device__ array of 128 KiB + 256 B that every GPU loading the library holds until exit, so
+ * n <= SOMAR_NOALLOC_MAX_N; larger n returns SOMAR_ERR_ARG.  No cudaMalloc / cudaFree / allocating routine is called.
+ * All calls share that array: calls that overlap on one GPU (several streams or host threads) race -- serialise them. */
+#define SOMAR_NOALLOC_MAX_N 67108864LL /* 16384 blocks x 4096 doubles */
+int somar_norm_noalloc(const double* d_x, long long n, int ord, double* d_out, void* cuda_stream);
+
 /* ---- MappedMGLevelOp<T> (MappedMultiGrid.H:43-114) -------------------------------------------------------- */
 int somar_relax(SomarLevel* lev, int depth, SomarField* phi, const SomarField* rhs, int iters);     /* relax :1733 */
 int somar_restrict_residual(SomarLevel* lev, int depth, SomarField* res_coarse, SomarField* phi_fine,

@@ -36,7 +36,7 @@ SYMBOLS = [
     "somar_leptic_vertical_excess", "somar_leptic_add_extrusion", "somar_leptic_accum_div",
     "somar_advect_predict_scalar", "somar_advect_update",
     "somar_leptic_default_params", "somar_leptic_create", "somar_leptic_destroy", "somar_leptic_solve",
-    "somar_leptic_level",
+    "somar_leptic_level", "somar_norm_noalloc",
 ]
 
 
@@ -188,6 +188,17 @@ class LepticSolver:
             self.destroy()
         except Exception:
             pass
+
+
+NOALLOC_MAX_N = 67108864
+
+
+def norm_noalloc(x, ord: int, out, stream: int = 0):
+    """somar_norm_noalloc: x, out are contiguous float64 CUDA tensors (n values, 1 value); nothing is allocated and
+    nothing synchronised -- the result is in `out` once `stream` (a cudaStream_t as int, 0 = default) has run."""
+    assert x.is_cuda and out.is_cuda and x.is_contiguous() and str(x.dtype) == "torch.float64"
+    _ck(lib().somar_norm_noalloc(C.c_void_p(x.data_ptr()), C.c_longlong(x.numel()), int(ord),
+                                 C.c_void_p(out.data_ptr()), C.c_void_p(stream)))
 
 
 def comm_unique_id() -> bytes:
