@@ -332,7 +332,7 @@ static int ensure_state(SomarLevel* L) {
 }
 
 bool bottom_persistent_usable(SomarLevel* L) {
-    if (L->bottom_mode != 2) return false;
+    if (L->bottom_mode < 2) return false;
     const Depth& dp = L->depths[L->ndepths() - 1];
     const Geom& g = dp.g;
     if (!dp.m.diagonal || L->desc.nranks > 1 || g.nbr[0] >= 0 || g.nbr[1] >= 0) return false;
@@ -390,6 +390,8 @@ int launch_bottom_persistent(SomarLevel* L, const Geom& g_, const Metric& m_, do
     int rc;
     if ((rc = ensure_state(L))) return rc;
     BicgDev* dv = static_cast<BicgDev*>(L->d_bicg);
+    if (bottom_resident_usable(L, g_, m_))   // mode 3: the whole bottom problem resident on chip (bicg_resident.cu)
+        return launch_bottom_resident(L, g_, m_, phi, rhs, work, dv, dv->part, &dv->iters);
     BicgFields f;
     f.phi = phi; f.rhs = rhs;
     f.r = work[0]; f.rt = work[1]; f.e = work[2]; f.pv = work[3]; f.pt = work[4];

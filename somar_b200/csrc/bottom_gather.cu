@@ -68,7 +68,7 @@ static int gather_arrays(SomarLevel* L, double* const* local, double* const* ful
 int gathered_bottom_build(SomarLevel* L) {
     gathered_bottom_free(L);
     const SomarLevelDesc& D = L->desc;
-    if (D.nranks <= 1 || L->bottom_mode != 2 || L->ndepths() < 1) return SOMAR_OK;
+    if (D.nranks <= 1 || L->bottom_mode < 2 || L->ndepths() < 1) return SOMAR_OK;
     const int bd = L->ndepths() - 1;
     const Depth& dp = L->depths[bd];
     const Geom& gl = dp.g;
@@ -126,7 +126,7 @@ int gathered_bottom_build(SomarLevel* L) {
 }
 
 bool bottom_gathered_usable(SomarLevel* L) {
-    if (!L->gb || L->bottom_mode != 2) return false;
+    if (!L->gb || L->bottom_mode < 2) return false;
     return bottom_persistent_params_ok(L, L->gb->g);
 }
 

@@ -102,7 +102,7 @@ int somar::level_create_impl(const SomarLevelDesc* desc, const SomarSolverParams
     L->desc.box_rank = L->box_rank.data();
     L->cx.sms = prop.multiProcessorCount;
     if (const char* e = getenv("SOMAR_B200_FUSED")) L->use_fused = (e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 2;
-    if (const char* e = getenv("SOMAR_B200_BOTTOM")) L->bottom_mode = (e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 2;
+    if (const char* e = getenv("SOMAR_B200_BOTTOM")) L->bottom_mode = (e[0] >= '0' && e[0] <= '3') ? e[0] - '0' : 3;
     int rc;
     cudaError_t ce;
     if ((ce = cudaStreamCreateWithFlags(&L->cx.stream, cudaStreamNonBlocking)) != cudaSuccess ||

@@ -83,8 +83,10 @@ struct SomarLevel {
     double* h_scal = nullptr;          // pinned mirror
     void* d_bicg = nullptr;            // BicgState of the bottom solver (bicgstab.cu) and its pinned mirror
     void* h_bicg = nullptr;
-    int bottom_mode = 2;               // SOMAR_B200_BOTTOM: 0 host-sequenced BiCGStab, 1 scalars on the device,
-                                       // 2 one persistent kernel per bottom visit where usable (else 1)
+    int bottom_mode = 3;               // SOMAR_B200_BOTTOM: 0 host-sequenced BiCGStab, 1 scalars on the device,
+                                       // 2 one persistent kernel per bottom visit where usable (else 1),
+                                       // 3 (default) the on-chip-resident kernel where usable (else as 2)
+    int bottom_resident_blocks = -1;   // co-resident blocks of k_bicg_resident (-1: not yet queried)
     int bottom_coop_blocks = -1;       // co-resident blocks of the persistent kernel (-1: not yet queried)
     bool bottom_iters_pending = false; // the device-side iteration counter holds uncollected counts
     somar::GatheredBottom* gb = nullptr; // multi-rank: replicated bottom depth (built at finalize when usable)
@@ -182,6 +184,10 @@ int bottom_collect_iters(SomarLevel* L);
 bool bottom_persistent_params_ok(SomarLevel* L, const Geom& g);
 int launch_bottom_persistent(SomarLevel* L, const Geom& g, const Metric& m, double* phi, double* rhs,
                              double* const work[8]);
+// bicg_resident.cu
+bool bottom_resident_usable(SomarLevel* L, const Geom& g, const Metric& m);
+int launch_bottom_resident(SomarLevel* L, const Geom& g, const Metric& m, double* phi, double* rhs, double* const work[8],
+                           void* bicgDev, double* part, int* itersAccum);
 // projector.cu
 int op_mac_gradient(SomarLevel* L, SomarField* const grad[3], SomarField* phi, bool homog, double scale, bool accumulate);
 int op_mac_divergence(SomarLevel* L, SomarField* div, const SomarField* const flux[3], double divideBy);

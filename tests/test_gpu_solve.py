@@ -64,8 +64,14 @@ def test_w_and_f_cycles_match_oracle(case, numMG, oracle_lib, somar):
     assert rel_err(f1.get(), want) > 1e-6
 
 
+# bottom.imax / numRestarts of bench.py: the bottom problem is actually solved.  With the decks' 80 / 5 the (64,64,16)
+# dx/dz = 16 case leaves its 64 x 64 x 4 bottom unsolved and the V-cycle count then depends on the ORDER of the bottom
+# solver's dot-product sums: oracle 12, bottom modes 0-2 13, mode 3 15 (profiles/r2_diag_resident.log)
+SOLVED_BOTTOM = dict(bottom_imax=1000, bottom_numRestarts=50)
+
+
 @pytest.mark.parametrize("case,mode", [
-    (dict(n=(64, 64, 16), map_name="stretched", aniso=16.0), 1),
+    (dict(n=(64, 64, 16), map_name="stretched", aniso=16.0, knobs=SOLVED_BOTTOM), 1),
     (dict(n=(64, 64, 16), map_name="stretched", aniso=16.0), 3),
     (dict(n=(48, 32, 16), map_name="stretched", aniso=4.0, periodic=(0, 1, 0)), 1),
     (dict(n=(64, 32, 1), dim=2, map_name="stretched", aniso=4.0), 1),
@@ -73,9 +79,11 @@ def test_w_and_f_cycles_match_oracle(case, numMG, oracle_lib, somar):
     (dict(n=(32, 32, 32), map_name="stretched", aniso=4.0, parts=(1, 2, 1)), 2),      # LooseGSRB, two boxes
 ])
 def test_solve_history_matches_oracle(case, mode, oracle_lib, somar):
+    case = dict(case)
+    kw = dict(SOLVE, **case.pop("knobs", {}))
     pb = Problem(**case)
-    orc = pb.oracle(oracle_lib, relaxMode=mode, **SOLVE)
-    lev = pb.level(somar, relaxMode=mode, **SOLVE)
+    orc = pb.oracle(oracle_lib, relaxMode=mode, **kw)
+    lev = pb.level(somar, relaxMode=mode, **kw)
     rhs = pb.rhs()
     phi_o, st_o = orc.solve(rhs)
     fphi, frhs = lev.field(0), lev.field(0, rhs)
@@ -273,3 +281,75 @@ def test_convergence_metric_and_blow_up_abort(oracle_lib, somar):
     assert orc2.blew_up()
     with pytest.raises(somar.SomarError, match="blew up"):
         lev2.solve(lev2.field(0), lev2.field(0, rhs2))
+
+
+# ---- the on-chip-resident bottom kernel (bicg_resident.cu, SOMAR_B200_BOTTOM=3, the default) ------------------------
+RESIDENT_CASES = [
+    dict(n=(64, 64, 16), map_name="stretched", aniso=16.0),                                   # 2 x 4 whole tiles
+    dict(n=(48, 40, 16), map_name="stretched", aniso=16.0, parts=(1, 2, 1)),                  # ragged tiles
+    dict(n=(96, 48, 16), map_name="stretched", aniso=16.0, bc_type=[0, 0, 0, 0, 0, 1]),       # Dirichlet top
+]
+
+
+@pytest.mark.parametrize("case", RESIDENT_CASES)
+@pytest.mark.parametrize("bottom_imax", [0, 1, 3, -6])
+def test_resident_bottom_visit_matches_device_bicgstab(case, bottom_imax, somar, monkeypatch):
+    """One bottom visit (num_smooth_bottom relaxations + at most bottom_imax BiCGStab iterations) on the bottom depth
+    itself.  The relaxations, preCond and L are the same statements in both modes (bit-exact: bottom_imax = 0); with
+    Krylov iterations only the order of the dot-product sums differs, so a few iterations agree to rounding."""
+    pb = Problem(**case)
+    out = {}
+    extra = {}
+    if bottom_imax < 0:   # six iterations with a generous hang criterion: every second iteration restarts (fold e into
+        bottom_imax, extra = -bottom_imax, dict(bottom_hang=0.9, bottom_numRestarts=50)   # phi, true residual, r~ = r)
+    for variant in ("1", "3"):
+        monkeypatch.setenv("SOMAR_B200_BOTTOM", variant)
+        lev = pb.level(somar, bottom_imax=bottom_imax, **dict(SOLVE, **extra))
+        bd = lev.ndepths - 1
+        assert lev.depth_info(bd)["n"][2] <= 4
+        rng = np.random.default_rng(3)
+        r = rng.uniform(-1.0, 1.0, size=lev.local_shape(bd))
+        e0 = rng.uniform(-1.0, 1.0, size=lev.local_shape(bd))
+        fe, fr = lev.field(bd, e0), lev.field(bd, r)
+        n0 = lev.launches()
+        lev.mg_cycle(fe, fr)
+        out[variant] = (fe.get(), lev.launches() - n0)
+        lev.destroy()
+    a, b = out["3"][0], out["1"][0]
+    assert out["3"][1] == 1, out["3"][1]                    # the whole visit was ONE launch (the resident kernel ran)
+    if bottom_imax == 0:
+        assert np.array_equal(a, b)
+    else:
+        assert rel_err(a, b) <= (1e-11 if not extra else 1e-9), rel_err(a, b)
+
+
+@pytest.mark.parametrize("case", RESIDENT_CASES[:2])
+@pytest.mark.parametrize("extra", [dict(bottom_imax=1000, bottom_numRestarts=50)])
+def test_resident_bottom_matches_the_other_modes(case, extra, oracle_lib, somar, monkeypatch):
+    """Whole solves: mode 3 against mode 1 (and the oracle): same V-cycle count (+-1), same exit status, histories
+    within 2 % over the first cycles, converged fields to the solver tolerance.  The bottom solver is given the
+    iterations it needs (bench.py's knobs): with the decks' bottom.imax 80 / numRestarts 5 the bottom problem is NOT
+    solved and the outer history depends on the order of the dot-product sums -- no two summation
+    orders, the oracle's included, agree on a V-cycle count there."""
+    pb = Problem(**case)
+    prm = dict(SOLVE, **extra)
+    rhs = pb.rhs()
+    got = {}
+    for variant in ("1", "3"):
+        monkeypatch.setenv("SOMAR_B200_BOTTOM", variant)
+        lev = pb.level(somar, **prm)
+        fphi, frhs = lev.field(0), lev.field(0, rhs)
+        got[variant] = (lev.solve(fphi, frhs), fphi.get())
+        lev.destroy()
+    (s1, p1), (s3, p3) = got["1"], got["3"]
+    phi_o, st_o = pb.oracle(oracle_lib, **prm).solve(rhs)
+    assert s3["launches"] < 0.5 * s1["launches"]
+    for s in (s1, st_o):
+        assert abs(s3["iters"] - s["iters"]) <= 1, (s3["iters"], s["iters"])
+        assert s3["exit_status"] == s["exit_status"] or abs(s3["iters"] - s["iters"]) == 1
+        for x, y in zip(s3["history"][:4], s["history"][:4]):
+            assert abs(x - y) <= 0.02 * y, (s3["history"], s["history"])
+    if s3["exit_status"] == 1:
+        assert s3["final_rnorm"] <= SOLVE["eps"] * s3["initial_rnorm"]
+        for p in (p1, phi_o):
+            assert np.abs((p3 - p3.mean()) - (p - p.mean())).max() <= 1e-6 * np.abs(p).max()
