@@ -8,11 +8,13 @@ from somar_b200 import synthetic as syn
 
 class Problem:
     def __init__(self, n, *, dim=3, map_name="stretched", aniso=4.0, periodic=(0, 0, 0), parts=(1, 1, 1), bc_type=None,
-                 bc_value=None, alpha=0.0, beta=1.0, map_params=None, seed=7):
+                 bc_value=None, alpha=0.0, beta=1.0, map_params=None, seed=7, L=None):
         self.n = tuple(n)
         self.dim = dim
         self.periodic = tuple(int(x) for x in periodic)
-        if dim == 3:
+        if L is not None:   # explicit computational extent (the shipped decks' amr.length)
+            L = tuple(float(x) for x in L) + (1.0,) * (3 - len(L))
+        elif dim == 3:
             L = (float(n[0]), float(n[1]), float(n[2]) / aniso)
         else:
             L = (float(n[0]), float(n[1]) / aniso, 1.0)
