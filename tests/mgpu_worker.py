@@ -19,7 +19,10 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 from somar_b200 import synthetic as syn  # noqa: E402
 
 NB = 8
-SOLVE = dict(eps=1e-10, num_smooth_down=4, num_smooth_up=4, num_smooth_bottom=2, imin=0, imax=30)
+# bottom.imax / numRestarts as in bench.py: the bottom problem is solved, so V-cycle counts and histories are defined
+# quantities (with the decks' 80 / 5 they depend on the order of the dot-product sums)
+SOLVE = dict(eps=1e-10, num_smooth_down=4, num_smooth_up=4, num_smooth_bottom=2, imin=0, imax=30, bottom_imax=1000,
+             bottom_numRestarts=50)
 
 
 def partition(n, world):
@@ -206,8 +209,12 @@ def main():
                 # BiCGStab bottom amplifies summation-order differences (measured on the terrain case: the residual
                 # after a cycle moves by up to 20 % between 1 and 2 ranks while the strict fields below agree to
                 # 1e-10 and the V-cycle counts are equal)
-                rel = 0.02 if diag else 0.5
-                good = bool(np.all(np.abs(got - want) <= rel * np.abs(want) + 1e-8 * abs(want[0])))
+                # terrain: the outer iteration of this full-metric problem slows down below ~1e-5 (it stalls on the
+                # oracle too, tests/test_baseline_configs.py); from there on a cycle's residual is rounding noise
+                # amplified (measured 7 % at the fourth cycle, 75 % at the fifth), so the first three cycles are compared
+                rel = 0.02
+                m_ = len(want) if diag else 4
+                good = bool(np.all(np.abs(got[:m_] - want[:m_]) <= rel * np.abs(want[:m_]) + 1e-8 * abs(want[0])))
             else:
                 den = max(np.abs(want).max(), 1e-300)
                 tol = (1e-6 if diag else 1e-4) if key == "solution" else (1e-10 if "strict" in key else 1e-12)
@@ -215,6 +222,8 @@ def main():
             if not good:
                 ok = False
                 print(f"MGPU-FAIL {key}: max diff {np.abs(np.asarray(got, float) - np.asarray(want, float)).max():.3e}")
+                if np.asarray(got).size <= 8:
+                    print(f"   got {np.asarray(got).tolist()}\n   want {np.asarray(want).tolist()}")
         print("MGPU-OK nccl" if ok else "MGPU-FAILED")
     dist.barrier()
     dist.destroy_process_group()

@@ -31,10 +31,13 @@ def test_partition_plumbing_gloo_world2():
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("nproc", [2, 4, 8])
 @pytest.mark.parametrize("args", [["nccl", "stretched"], ["nccl", "stretched", "periodic"], ["nccl", "terrain"]])
-def test_two_ranks_match_one_rank_nccl(args):
+def test_n_ranks_match_one_rank_nccl(args, nproc):
+    """2 ranks: every rank has ONE neighbour (and, periodic, the same neighbour on both sides); 4 and 8 ranks: interior
+    ranks with two distinct peers -- two IPC mappings, independent ready/ack counters per side (halo_p2p.cu)."""
     import torch
-    if torch.cuda.device_count() < 2:
-        pytest.skip("needs 2 GPUs")
-    rc, out = _launch(2, args)
+    if torch.cuda.device_count() < nproc:
+        pytest.skip(f"needs {nproc} GPUs")
+    rc, out = _launch(nproc, args)
     assert rc == 0 and "MGPU-OK nccl" in out, out[-4000:]
