@@ -296,7 +296,7 @@ int somar_level_relax_kernel(const SomarLevel* L, int depth, int mode, int* id) 
     if (depth < 0 || depth >= L->ndepths() || !id) { set_error("bad depth"); return SOMAR_ERR_ARG; }
     const Depth& dp = L->depths[depth];
     if (mode == SOMAR_RELAX_LEVEL_GSRB)
-        *id = (L->use_fused == 2 && gsrb_async_usable(dp.g, dp.m)) ? 5
+        *id = (L->use_fused == 2 && gsrb_async_usable(dp.g, dp.m)) ? (gsrb_tma_usable(dp.g, dp.m) ? 7 : 5)
               : (L->use_fused && gsrb_fused_usable(dp.g, dp.m))     ? 1
                                                                     : (dp.m.diagonal ? 0 : 2);
     else if (mode == SOMAR_RELAX_LINE_GSRB) *id = 3;

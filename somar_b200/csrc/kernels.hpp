@@ -37,6 +37,11 @@ void launch_gsrb_fused(Ctx& cx, const Geom& g, const Metric& m, double* phiOut, 
 bool gsrb_async_usable(const Geom& g, const Metric& m);
 bool launch_gsrb_async(Ctx& cx, const Geom& g, const Metric& m, double* phiOut, const double* phiIn,
                        const double* rhs, const double* zeroPlane = nullptr);
+// k_gsrb_async with its rings fed by TMA tensor-map loads issued by one thread (gsrb_tma.cu); SOMAR_B200_TMA=0 turns
+// it off.  Same contract and the same bits as launch_gsrb_async.
+bool gsrb_tma_usable(const Geom& g, const Metric& m);
+bool launch_gsrb_tma(Ctx& cx, const Geom& g, const Metric& m, double* phiOut, const double* phiIn, const double* rhs,
+                     const double* zeroPlane = nullptr);
 // full metric: out-of-place pass, phiOut gets the updated colour AND a copy of the other colour
 void launch_gsrb_full(Ctx& cx, const Geom& g, const Metric& m, double* phiOut, const double* phiIn,
                       const double* rhs, int pass);

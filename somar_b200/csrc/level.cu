@@ -357,7 +357,10 @@ int op_relax(SomarLevel* L, int depth, SomarField* phi, const SomarField* rhs, i
             const bool fromZero = zeroIn && it == 0;
             if (ranks && !fromZero && (rc = exchange(L, depth, phi->p, 2)) != SOMAR_OK) return rc;
             ProfScope psK(L, depth == 0 ? PH_SMOOTH0_KERNEL : -1);
-            if (!launch_gsrb_async(L->cx, dp.g, dp.m, dp.tmp, phi->p, rhs->p, fromZero ? L->zeroPlane : nullptr)) {
+            const double* zp = fromZero ? L->zeroPlane : nullptr;
+            const bool launched = gsrb_tma_usable(dp.g, dp.m) ? launch_gsrb_tma(L->cx, dp.g, dp.m, dp.tmp, phi->p, rhs->p, zp)
+                                                              : launch_gsrb_async(L->cx, dp.g, dp.m, dp.tmp, phi->p, rhs->p, zp);
+            if (!launched) {
                 set_error("relax: k_gsrb_async could not reserve its shared memory");
                 return SOMAR_ERR_CUDA;
             }

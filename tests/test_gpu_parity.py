@@ -215,8 +215,10 @@ def test_gsrb_kernel_variants_bit_identical(name, oracle_lib, somar, monkeypatch
     pb = Problem(**VARIANT_CASES[name])
     phi, rhs = pb.rand(), pb.rand()
     out = {}
-    for variant, kernel in (("0", "k_gsrb_ortho"), ("1", "k_gsrb_fused"), ("2", "k_gsrb_async")):
-        monkeypatch.setenv("SOMAR_B200_FUSED", variant)
+    # "2": the pipelined sweep fed by TMA tensor-map loads (gsrb_tma.cu, the default), "2c": by cp.async (gsrb_async.cu)
+    for variant, kernel in (("0", "k_gsrb_ortho"), ("1", "k_gsrb_fused"), ("2", "k_gsrb_tma"), ("2c", "k_gsrb_async")):
+        monkeypatch.setenv("SOMAR_B200_FUSED", variant[0])
+        monkeypatch.setenv("SOMAR_B200_TMA", "0" if variant == "2c" else "1")
         lev = pb.level(somar, relaxMode=1, maxDepth=0)
         assert lev.relax_kernel(0, 1) == kernel
         fphi, frhs = lev.field(0, phi), lev.field(0, rhs)
