@@ -337,7 +337,8 @@ k_gsrb_async(const Geom g, const Metric m, double* __restrict__ phiOut, const do
     // rank (its phi, metric and right-hand side were exchanged; relaxing its red cells here, exactly as the
     // owner does, spares the exchange between the colour passes).
     const bool yown = (L.y >= 0) && (L.y < g.n[1]);
-    const bool yred = (L.y >= (g.nbr[0] >= 0 ? -1 : 0)) && (L.y < g.n[1] + (g.nbr[1] >= 0 ? 1 : 0));
+    const bool yred = (L.y >= ((g.nbr[0] >= 0 || g.periodic[1]) ? -1 : 0)) &&
+                      (L.y < g.n[1] + ((g.nbr[1] >= 0 || g.periodic[1]) ? 1 : 0));   // periodic y: the image row
     const bool ycore = (L.r >= 1) && (L.r <= CY);
     L.redMask = 0;
     L.coreMask = 0;
@@ -389,7 +390,9 @@ k_gsrb_async(const Geom g, const Metric m, double* __restrict__ phiOut, const do
 
 bool gsrb_async_usable(const Geom& g, const Metric& m) {
     if (!m.diagonal || g.nd != 3) return false;
-    if (g.periodic[0] || g.periodic[1] || g.periodic[2]) return false;   // periodic images need a fill between passes
+    // periodic y is a neighbour like any other (the image rows are filled by the exchange before each iteration and
+    // their red cells relaxed here); periodic x / z images would need a fill between the colour passes
+    if (g.periodic[0] || g.periodic[2]) return false;
     if (g.total >= (1LL << 31)) return false;                             // 32-bit brick indices
     if (g.gh[0] < 2 || (g.gh[0] & 1) || g.gh[1] < 2 || g.gh[2] < 2) return false;   // rows start 16-byte aligned
     if ((g.sy & 1) || (g.off0 & 1)) return false;

@@ -319,7 +319,8 @@ k_gsrb_async(const Geom g, const __grid_constant__ TmaMaps tm, double* __restric
     // rank (its phi, metric and right-hand side were exchanged; relaxing its red cells here, exactly as the
     // owner does, spares the exchange between the colour passes).
     const bool yown = (L.y >= 0) && (L.y < g.n[1]);
-    const bool yred = (L.y >= (g.nbr[0] >= 0 ? -1 : 0)) && (L.y < g.n[1] + (g.nbr[1] >= 0 ? 1 : 0));
+    const bool yred = (L.y >= ((g.nbr[0] >= 0 || g.periodic[1]) ? -1 : 0)) &&
+                      (L.y < g.n[1] + ((g.nbr[1] >= 0 || g.periodic[1]) ? 1 : 0));   // periodic y: the image row
     const bool ycore = (L.r >= 1) && (L.r <= CY);
     L.redMask = 0;
     L.coreMask = 0;

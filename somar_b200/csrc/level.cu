@@ -352,7 +352,7 @@ int op_relax(SomarLevel* L, int depth, SomarField* phi, const SomarField* rhs, i
             // first ghost row on each side (same inputs, same arithmetic as their owner), so ONE exchange of two
             // ghost rows of phi per iteration replaces the reference's exchange before each colour pass; the
             // metric's ghost rows were filled at finalize, the right-hand side's are filled here once.
-            const bool ranks = dp.g.nbr[0] >= 0 || dp.g.nbr[1] >= 0;
+            const bool ranks = dp.g.nbr[0] >= 0 || dp.g.nbr[1] >= 0 || dp.g.periodic[1];
             if (ranks && it == 0 && (rc = exchange(L, depth, const_cast<double*>(rhs->p), 1)) != SOMAR_OK) return rc;
             const bool fromZero = zeroIn && it == 0;
             if (ranks && !fromZero && (rc = exchange(L, depth, phi->p, 2)) != SOMAR_OK) return rc;
@@ -477,7 +477,7 @@ int level_finalize(SomarLevel* L) {
         dp.line_valid = false;
         // The fused smoother also relaxes the red cells of the first ghost row towards a neighbour rank
         // (op_relax), so the diagonal metric gets two ghost rows from the neighbours, once.
-        if (L->desc.nranks > 1 && dp.m.diagonal) {
+        if ((L->desc.nranks > 1 || dp.g.periodic[1]) && dp.m.diagonal) {
             double* arr[5] = {dp.jg[0][0], dp.jg[1][1], nd > 2 ? dp.jg[2][2] : nullptr, dp.jinv, dp.lapdiag};
             for (double* a : arr)
                 if (a && (rc = exchange(L, k, a, SOMAR_GHOST)) != SOMAR_OK) return rc;

@@ -115,7 +115,11 @@ __device__ __forceinline__ double apply_vals_ortho3(const Geom& g, unsigned sm, 
 // boundary kernels of the reference (BaseGSRB::boundaryGSRB, GSRB.cpp:489-653; domInterior = grow(domain,-1)).
 template <int ND>
 __device__ __forceinline__ bool on_domain_rim(const Geom& g, int i, int j, int k) {
-    const int gi = i + g.g0[0], gj = j + g.g0[1], gk = k + g.g0[2];
+    const int gi = i + g.g0[0], gk = k + g.g0[2];
+    int gj = j + g.g0[1];
+    // a ghost row beyond a periodic y side is the image of a row at the other end of the domain (the fused smoother
+    // relaxes the red cells of the first ghost row exactly as their owner does)
+    if (g.periodic[1]) gj = (gj < 0) ? gj + g.gn[1] : (gj >= g.gn[1] ? gj - g.gn[1] : gj);
     bool r = (gi == 0) | (gi == g.gn[0] - 1) | (gj == 0) | (gj == g.gn[1] - 1);
     if (ND > 2) r = r | (gk == 0) | (gk == g.gn[2] - 1);
     return r;
