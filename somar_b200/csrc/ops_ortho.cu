@@ -13,6 +13,13 @@ namespace somar {
 #define MARCH_UNROLL(MODE) ((MODE) == 2 ? 1 : 4)   // (MODE 3 = residual + max-norm: as MODE 1)
 #define MARCH_MINB(MODE) ((MODE) == 2 ? 5 : 4)
 
+// Full metric: is cell (i, j, k) strictly inside its box of the uniform tiling?  Then every `extrap` value its stencil
+// reads is phi itself and the branch-free *_inner statement applies (same expressions, same bits as the general one).
+template <int ND>
+__device__ __forceinline__ bool full_inner_xy(const Geom& g, int i, int j) {
+    return box_inner_dir<ND>(g, i, 0) && box_inner_dir<ND>(g, j, 1);
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // apply / residual: one thread per cell of an (BX x BY) tile, marching KZ planes in z.
 // ---------------------------------------------------------------------------------------------------------
@@ -25,11 +32,16 @@ __global__ void __launch_bounds__(BX* BY) k_apply(const Geom g, const Metric m, 
     if (i >= g.n[0] || j >= g.n[1]) return;
     const int k0 = blockIdx.z * kz;
     const int k1 = min(k0 + kz, g.n[2]);
+    const bool innerXY = FULL && full_inner_xy<ND>(g, i, j);
     for (int k = k0; k < k1; ++k) {
         const long long c = g.idx(i, j, k);
         double v;
-        if (FULL) v = apply_cell_full<ND>(g, m, phi, i, j, k, c, homog);
-        else v = apply_cell_ortho<ND>(g, m, phi, i, j, k, c, homog);
+        if (FULL) {
+            if (innerXY && (ND < 3 || box_inner_dir<ND>(g, k, 2))) v = apply_cell_full_inner<ND>(g, m, phi, i, j, k, c, homog);
+            else v = apply_cell_full<ND>(g, m, phi, i, j, k, c, homog);
+        } else {
+            v = apply_cell_ortho<ND>(g, m, phi, i, j, k, c, homog);
+        }
         out[c] = mode ? (rhs[c] - v) : v;
     }
 }
@@ -255,26 +267,48 @@ void launch_gsrb_loose(Ctx& cx, const Geom& g, const Metric& m, double* phi, con
 
 // full metric: out of place (cross terms read same-colour cells of the pre-pass state = the `extrap` snapshot,
 // RelaxationMethod.cpp:411).  Every cell is written: updated colour gets the new value, the other a copy.
+// A thread owns the x-adjacent PAIR (2t, 2t+1) of a row: exactly one of the two cells is of the pass's colour in any
+// plane, so every lane computes (a thread per cell idles the lanes of the other colour) and the pair leaves as one
+// 16-byte store.  Box-interior cells take the branch-free statement.
 template <int ND>
 __global__ void __launch_bounds__(BX* BY) k_gsrb_full(const Geom g, const Metric m, double* __restrict__ phiOut,
                                                        const double* __restrict__ phiIn,
                                                        const double* __restrict__ rhs, int pass, int kz) {
-    const int i = blockIdx.x * BX + threadIdx.x;
+    const int t = blockIdx.x * BX + threadIdx.x;
     const int j = blockIdx.y * BY + threadIdx.y;
-    if (i >= g.n[0] || j >= g.n[1]) return;
+    const int ia = 2 * t;
+    if (ia >= g.n[0] || j >= g.n[1]) return;
+    const bool two = ia + 1 < g.n[0];
     const int k0 = blockIdx.z * kz;
     const int k1 = min(k0 + kz, g.n[2]);
+    const bool innerY = box_inner_dir<ND>(g, j, 1);
+    const bool inner0 = innerY && box_inner_dir<ND>(g, ia, 0), inner1 = innerY && two && box_inner_dir<ND>(g, ia + 1, 0);
     for (int k = k0; k < k1; ++k) {
-        const long long c = g.idx(i, j, k);
-        const int par = (g.g0[0] + i + g.g0[1] + j + ((ND > 2) ? (g.g0[2] + k) : 0) + pass) & 1;
-        phiOut[c] = par ? phiIn[c] : gsrb_cell_full<ND>(g, m, phiIn, rhs, i, j, k, c);
+        const long long c = g.idx(ia, j, k);
+        // cell ia is of this pass's colour iff par == 0
+        const int par = (g.g0[0] + ia + g.g0[1] + j + ((ND > 2) ? (g.g0[2] + k) : 0) + pass) & 1;
+        const int i = ia + par;
+        double va = phiIn[c], vb = two ? phiIn[c + 1] : 0.0;
+        if (i < g.n[0]) {
+            const bool inner = (par ? inner1 : inner0) && (ND < 3 || box_inner_dir<ND>(g, k, 2));
+            const double v = inner ? gsrb_cell_full_inner<ND>(g, m, phiIn, rhs, i, j, k, c + par)
+                                   : gsrb_cell_full<ND>(g, m, phiIn, rhs, i, j, k, c + par);
+            if (par) vb = v; else va = v;
+        }
+        if (two && ((c & 1) == 0)) {
+            *reinterpret_cast<double2*>(phiOut + c) = make_double2(va, vb);
+        } else {
+            phiOut[c] = va;
+            if (two) phiOut[c + 1] = vb;
+        }
     }
 }
 
 void launch_gsrb_full(Ctx& cx, const Geom& g, const Metric& m, double* phiOut, const double* phiIn,
                       const double* rhs, int pass) {
     const int kz = (g.n[2] >= 64) ? 8 : 1;
-    dim3 grid((g.n[0] + BX - 1) / BX, (g.n[1] + BY - 1) / BY, (g.n[2] + kz - 1) / kz), block(BX, BY);
+    const int half = (g.n[0] + 1) / 2;
+    dim3 grid((half + BX - 1) / BX, (g.n[1] + BY - 1) / BY, (g.n[2] + kz - 1) / kz), block(BX, BY);
     if (g.nd == 3) k_gsrb_full<3><<<grid, block, 0, cx.stream>>>(g, m, phiOut, phiIn, rhs, pass, kz);
     else k_gsrb_full<2><<<grid, block, 0, cx.stream>>>(g, m, phiOut, phiIn, rhs, pass, kz);
     cx.launches++;
@@ -351,8 +385,14 @@ __global__ void __launch_bounds__(BX* BY) k_restrict(const Geom gf, const Metric
                 const int i = ic * r0 + ii, j = jc * r1 + jj, k = kc * r2 + kk;
                 const long long c = gf.idx(i, j, k);
                 double v;
-                if (FULL) v = apply_cell_full<ND>(gf, mf, phi, i, j, k, c, true);
-                else v = apply_cell_ortho<ND>(gf, mf, phi, i, j, k, c, true);
+                if (FULL) {
+                    const bool inner = box_inner_dir<ND>(gf, i, 0) && box_inner_dir<ND>(gf, j, 1) &&
+                                       (ND < 3 || box_inner_dir<ND>(gf, k, 2));
+                    v = inner ? apply_cell_full_inner<ND>(gf, mf, phi, i, j, k, c, true)
+                              : apply_cell_full<ND>(gf, mf, phi, i, j, k, c, true);
+                } else {
+                    v = apply_cell_ortho<ND>(gf, mf, phi, i, j, k, c, true);
+                }
                 const double res = rhs[c] - v;
                 const double ji = mf.jinv[c];
                 s = s + res / ji;

@@ -129,11 +129,32 @@ struct ExView {
     }
 };
 
+// The same accessor for a cell that is INTERIOR TO ITS BOX (no side of the box, hence no side of the domain, within
+// one cell): every ex() is phi itself, addressed by a compile-time offset from the cell -- no box search, no branches.
+// The expressions instantiated with it are the ones ExView takes when b.rim is false, so the bits are the same.
+template <int ND>
+struct FastView {
+    const double* __restrict__ p;   // phi + index of the cell (i0, j0, k0)
+    int i0, j0, k0;
+    long long sy, sz;
+    __device__ __forceinline__ double ex(int i, int j, int k) const {
+        return p[(i - i0) + sy * (j - j0) + sz * (k - k0)];
+    }
+};
+
+// Is local cell (q0, q1, q2) strictly inside its box of the level's uniform tiling (not touching any box side)?
+// x/y part and z part separately, so that a z-marching thread tests x/y once.
+template <int ND>
+__device__ __forceinline__ bool box_inner_dir(const Geom& g, int q, int d) {
+    const int r = (q + g.g0[d]) % g.bs[d];
+    return r != 0 && r != g.bs[d] - 1;
+}
+
 // 4-point transverse difference used by every cross term: around the face between cell A=(a0,a1,a2) and
 // cell B = A - e_n (n = face normal), difference taken in direction t:
 //    ex(A+t) - ex(A-t) + ex(B+t) - ex(B-t)
-template <int ND>
-__device__ __forceinline__ double cross4(const ExView<ND>& v, int a0, int a1, int a2, int n, int t) {
+template <int ND, class V>
+__device__ __forceinline__ double cross4(const V& v, int a0, int a1, int a2, int n, int t) {
     const int e0 = (n == 0), e1 = (n == 1), e2 = (n == 2);
     const int t0 = (t == 0), t1 = (t == 1), t2 = (t == 2);
     return v.ex(a0 + t0, a1 + t1, a2 + t2) - v.ex(a0 - t0, a1 - t1, a2 - t2) +
@@ -141,8 +162,8 @@ __device__ __forceinline__ double cross4(const ExView<ND>& v, int a0, int a1, in
 }
 
 // beta * flux through the low (S=0) / high (S=1) face of cell q=(i,j,k) in direction A (MAPPEDGETFLUX + BCs).
-template <int ND, int A, int S>
-__device__ __forceinline__ double face_flux_full(const Geom& g, const Metric& m, const ExView<ND>& v,
+template <int ND, int A, int S, class V>
+__device__ __forceinline__ double face_flux_full(const Geom& g, const Metric& m, const V& v,
                                                  const double* __restrict__ phi, int i, int j, int k, long long c,
                                                  bool atBdry, bool homog, double pc) {
     constexpr int B = (A + 1) % ND;
@@ -171,11 +192,10 @@ __device__ __forceinline__ double face_flux_full(const Geom& g, const Metric& m,
 }
 
 // (alpha I + beta L) phi at one cell, full metric (applyOpI, MappedAMRPoissonOp.cpp:772-898).
-template <int ND>
-__device__ __forceinline__ double apply_cell_full(const Geom& g, const Metric& m, const double* __restrict__ phi,
-                                                  int i, int j, int k, long long c, bool homog) {
-    const unsigned sm = side_mask(g, i, j, k);
-    const ExView<ND> v(g, phi, i, j, k, EXMODE_OP);
+template <int ND, class V>
+__device__ __forceinline__ double apply_cell_full_v(const Geom& g, const Metric& m, const V& v,
+                                                    const double* __restrict__ phi, int i, int j, int k, long long c,
+                                                    bool homog, unsigned sm) {
     const double pc = phi[c];
     const double f0l = face_flux_full<ND, 0, 0>(g, m, v, phi, i, j, k, c, sm & 1u, homog, pc);
     const double f0h = face_flux_full<ND, 0, 1>(g, m, v, phi, i, j, k, c, sm & 2u, homog, pc);
@@ -192,10 +212,23 @@ __device__ __forceinline__ double apply_cell_full(const Geom& g, const Metric& m
     if (g.alpha != 0.0) r = g.alpha * pc + 1.0 * r;
     return r;
 }
+template <int ND>
+__device__ __forceinline__ double apply_cell_full(const Geom& g, const Metric& m, const double* __restrict__ phi,
+                                                  int i, int j, int k, long long c, bool homog) {
+    const ExView<ND> v(g, phi, i, j, k, EXMODE_OP);
+    return apply_cell_full_v<ND>(g, m, v, phi, i, j, k, c, homog, side_mask(g, i, j, k));
+}
+// box-interior cell: no boundary side, no extrapolated value
+template <int ND>
+__device__ __forceinline__ double apply_cell_full_inner(const Geom& g, const Metric& m, const double* __restrict__ phi,
+                                                        int i, int j, int k, long long c, bool homog) {
+    const FastView<ND> v{phi + c, i, j, k, g.sy, g.sz};
+    return apply_cell_full_v<ND>(g, m, v, phi, i, j, k, c, homog, 0u);
+}
 
 // d_a ( J g^{ab} d_b ex ) without the 1/(4 dx_a dx_b) factor: high-face term minus low-face term.
-template <int ND>
-__device__ __forceinline__ double cross_ab(const Metric& m, const ExView<ND>& v, int i, int j, int k, long long c,
+template <int ND, class V>
+__device__ __forceinline__ double cross_ab(const Metric& m, const V& v, int i, int j, int k, long long c,
                                            long long sta, int a, int b) {
     const int e0 = (a == 0), e1 = (a == 1), e2 = (a == 2);
     const double up = m.jg[a][b][c + sta] * cross4<ND>(v, i + e0, j + e1, k + e2, a, b);
@@ -205,13 +238,13 @@ __device__ __forceinline__ double cross_ab(const Metric& m, const ExView<ND>& v,
 
 // One red-black update of one cell, full metric: phi = pre-pass state (normal terms read the other colour,
 // cross terms the frozen snapshot).  GSRBITER{2,3}D / GSRBBOUNDARYITER{2,3}D.
-template <int ND>
-__device__ __forceinline__ double gsrb_cell_full(const Geom& g, const Metric& m, const double* __restrict__ phi,
-                                                 const double* __restrict__ rhs, int i, int j, int k, long long c) {
-    const ExView<ND> v(g, phi, i, j, k, EXMODE_SMOOTHER);
-    const long long st[3] = {1, g.sy, g.sz};
+// interior statement (GSRBITER{2,3}D) on any accessor
+template <int ND, class V>
+__device__ __forceinline__ double gsrb_interior_full(const Geom& g, const Metric& m, const V& v,
+                                                     const double* __restrict__ phi, const double* __restrict__ rhs,
+                                                     int i, int j, int k, long long c) {
     const double ji = m.jinv[c];
-    if (!on_domain_rim<ND>(g, i, j, k)) {
+    {
         const double xx = 1.0 / (g.dx[0] * g.dx[0]), yy = 1.0 / (g.dx[1] * g.dx[1]);
         const double xy = 0.25 / (g.dx[0] * g.dx[1]);
         const double JDxx = m.jg[0][0][c + 1] * phi[c + 1] + m.jg[0][0][c] * phi[c - 1];
@@ -235,6 +268,22 @@ __device__ __forceinline__ double gsrb_cell_full(const Geom& g, const Metric& m,
         }
         return (rhs[c] - lphi) / (g.alpha + g.beta * m.lapdiag[c]);
     }
+}
+// box-interior cell: every ex() is phi
+template <int ND>
+__device__ __forceinline__ double gsrb_cell_full_inner(const Geom& g, const Metric& m, const double* __restrict__ phi,
+                                                       const double* __restrict__ rhs, int i, int j, int k, long long c) {
+    const FastView<ND> v{phi + c, i, j, k, g.sy, g.sz};
+    return gsrb_interior_full<ND>(g, m, v, phi, rhs, i, j, k, c);
+}
+
+template <int ND>
+__device__ __forceinline__ double gsrb_cell_full(const Geom& g, const Metric& m, const double* __restrict__ phi,
+                                                 const double* __restrict__ rhs, int i, int j, int k, long long c) {
+    const ExView<ND> v(g, phi, i, j, k, EXMODE_SMOOTHER);
+    if (!on_domain_rim<ND>(g, i, j, k)) return gsrb_interior_full<ND>(g, m, v, phi, rhs, i, j, k, c);
+    const long long st[3] = {1, g.sy, g.sz};
+    const double ji = m.jinv[c];
     // rim cell (GSRBBOUNDARYITER*): every non-Neumann face contributes its whole flux, Neumann faces nothing
     const unsigned sm = side_mask(g, i, j, k);
     const double pc = phi[c];
