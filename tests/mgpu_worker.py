@@ -189,6 +189,14 @@ def main():
         if do_leptic:
             ref.update(leptic(1, 0, (0, n[1])))
         for key in ref:
+            if key.startswith("apply_mac") and not diag and world == NB:
+                # Full metric, one box per rank: the reference's MAC gradient is per BOX (each box computes the faces of
+                # its surroundingNodes box from its own box-relative extrap copy, Gradient.cpp:137-149), so a face shared
+                # by two boxes has two values when the two extrapolated views differ (8-row boxes of this layout: up to
+                # 0.11, tools/diag_macdiv.py).  The brick stores ONE value per face (the high-side box's), except at a rank
+                # boundary, where each rank holds its own box's value -- the per-box semantics.  With one box per rank the
+                # two representations are not comparable; the solver path (apply, relax, restrict, solve) is, and is.
+                continue
             if key.startswith(("norm", "iters", "history")):
                 got = gathered[0][key]
                 for g in gathered[1:]:
