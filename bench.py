@@ -220,14 +220,15 @@ KERNEL_DESC = {"k_gsrb_ortho": "k_gsrb_ortho<3> (depth-0 red/black colour pass, 
                "k_gsrb_full": "k_gsrb_full<3> (depth-0 colour pass, full metric)",
                "k_gsrb_full_march": "k_gsrb_full_march (depth-0 red+black iteration in one sweep, full metric)",
                "k_line_gsrb": "k_line_gsrb<3> (depth-0 vertical-line colour pass)",
+               "k_line_pass_c": "k_line_pass_c (depth-0 vertical-line colour pass, colour-split layout)",
                "k_line_pair": "k_line_pair (depth-0 vertical-line red+black iteration in one launch)"}
 KERNEL_SOURCE = {"k_gsrb_ortho": "ops_ortho.cu", "k_gsrb_fused": "gsrb_fused.cu", "k_gsrb_async": "gsrb_async.cu", "k_gsrb_tma": "gsrb_tma.cu",
-                 "k_gsrb_full": "ops_ortho.cu", "k_gsrb_full_march": "gsrb_full_march.cu", "k_line_gsrb": "line.cu",
+                 "k_gsrb_full": "ops_ortho.cu", "k_gsrb_full_march": "gsrb_full_march.cu", "k_line_gsrb": "line.cu", "k_line_pass_c": "line_compact.cu",
                  "k_line_pair": "line.cu"}
 
 
 def kernel_bytes_per_cell(kname, diagonal):
-    if kname == "k_line_gsrb":
+    if kname in ("k_line_gsrb", "k_line_pass_c"):
         return 44 if diagonal else 100
     if kname == "k_line_pair":
         return 88 if diagonal else 200

@@ -140,7 +140,8 @@ int somar_level_launch_count(const SomarLevel* lev, long long* launches);
 /* Which kernel does relax(mode) run at `depth` (benchmark bookkeeping): 0 = k_gsrb_ortho, one launch per colour
  * pass; 1 = k_gsrb_fused, one launch per red+black iteration; 2 = k_gsrb_full (colour pass, full metric);
  * 3 = k_line_gsrb (colour pass); 4 = apply + k_jacobi; 5 = k_gsrb_async (as 1, pipelined); 6 = k_gsrb_loose (four
- * stage launches per iteration, diagonal metric); 7 = k_gsrb_tma (as 5, rings fed by TMA tensor-map loads); -1 = none. */
+ * stage launches per iteration, diagonal metric); 7 = k_gsrb_tma (as 5, rings fed by TMA tensor-map loads);
+ * 8 = k_line_pass_c (colour pass of the line smoother in the colour-split layout); -1 = none. */
 int somar_level_relax_kernel(const SomarLevel* lev, int depth, int relax_mode, int* kernel_id);
 /* Which path do y-halo exchanges take on this level: 0 = none needed (one rank), 1 = pack + ncclSend/Recv + unpack,
  * 2 = peer-memory push/pull kernels over CUDA IPC (halo_p2p.cu); valid after somar_level_finalize. */

@@ -423,7 +423,7 @@ class Level:
         names = ["smooth0_kernel", "smooth_coarse", "restrict", "prolong", "bottom", "outer"]
         return {n: {"count": cnt[i], "ms": ms[i]} for i, n in enumerate(names)}
 
-    RELAX_KERNELS = {0: "k_gsrb_ortho", 1: "k_gsrb_fused", 2: "k_gsrb_full", 3: "k_line_gsrb", 4: "k_jacobi", 5: "k_gsrb_async", 6: "k_gsrb_loose", 7: "k_gsrb_tma", -1: "none"}
+    RELAX_KERNELS = {0: "k_gsrb_ortho", 1: "k_gsrb_fused", 2: "k_gsrb_full", 3: "k_line_gsrb", 4: "k_jacobi", 5: "k_gsrb_async", 6: "k_gsrb_loose", 7: "k_gsrb_tma", 8: "k_line_pass_c", -1: "none"}
 
     def relax_kernel(self, depth=0, mode=RELAX_LEVEL_GSRB) -> str:
         v = C.c_int()

@@ -141,6 +141,7 @@ int somar_level_destroy(SomarLevel* L) {
         for (int d = 0; d < 3; ++d)
             for (int c = 0; c < 3; ++c) cudaFree(dp.jg[d][c]);
         cudaFree(dp.jinv); cudaFree(dp.lapdiag); cudaFree(dp.tmp); cudaFree(dp.line_fact); cudaFree(dp.line_dmod);
+        line_compact_free(dp);
         for (int s = 0; s < 2; ++s) { cudaFree(dp.sendbuf[s]); cudaFree(dp.recvbuf[s]); }
         if (dp.res) { cudaFree(dp.res->p); delete dp.res; }
         if (dp.cor) { cudaFree(dp.cor->p); delete dp.cor; }
@@ -299,7 +300,7 @@ int somar_level_relax_kernel(const SomarLevel* L, int depth, int mode, int* id) 
         *id = (L->use_fused == 2 && gsrb_async_usable(dp.g, dp.m)) ? (gsrb_tma_usable(dp.g, dp.m) ? 7 : 5)
               : (L->use_fused && gsrb_fused_usable(dp.g, dp.m))     ? 1
                                                                     : (dp.m.diagonal ? 0 : 2);
-    else if (mode == SOMAR_RELAX_LINE_GSRB) *id = 3;
+    else if (mode == SOMAR_RELAX_LINE_GSRB) *id = line_compact_usable(L, dp) ? 8 : 3;
     else if (mode == SOMAR_RELAX_LOOSE_GSRB) *id = dp.m.diagonal ? 6 : -1;
     else if (mode == SOMAR_RELAX_JACOBI) *id = 4;
     else *id = -1;

@@ -381,6 +381,13 @@ int op_relax(SomarLevel* L, int depth, SomarField* phi, const SomarField* rhs, i
                     std::swap(dp.tmp, phi->p);
                 }
             }
+        } else if (mode == SOMAR_RELAX_LINE_GSRB && line_compact_usable(L, dp)) {
+            // all the iterations of the call in the colour-split layout (line_compact.cu): same statements, same bits
+            const bool stale = !dp.line_valid;
+            if ((rc = ensure_line(L, dp)) != SOMAR_OK) return rc;
+            if ((rc = line_compact_relax(L, dp, phi->p, rhs->p, iters, stale, depth == 0 ? PH_SMOOTH0_KERNEL : -1)) != SOMAR_OK)
+                return rc;
+            break;
         } else if (mode == SOMAR_RELAX_LINE_GSRB) {    // LineGSRB::relax, GSRB.cpp:148-330
             if ((rc = ensure_line(L, dp)) != SOMAR_OK) return rc;
             for (int pass = 0; pass < 2; ++pass) {

@@ -27,6 +27,7 @@ struct Depth {
     double* line_fact = nullptr;       // lazily built by line relaxation
     double* line_dmod = nullptr;
     bool line_valid = false;
+    void* line_compact = nullptr;      // colour-split arrays of the line smoother (line_compact.cu), built on first use
     double* tmp = nullptr;             // ping-pong partner for out-of-place passes / Jacobi residual
     bool zeroAvg = false;
     double dxProduct = 1.0;
@@ -188,6 +189,10 @@ int launch_bottom_persistent(SomarLevel* L, const Geom& g, const Metric& m, doub
 bool bottom_resident_usable(SomarLevel* L, const Geom& g, const Metric& m);
 int launch_bottom_resident(SomarLevel* L, const Geom& g, const Metric& m, double* phi, double* rhs, double* const work[8],
                            void* bicgDev, double* part, int* itersAccum);
+// line_compact.cu
+bool line_compact_usable(const SomarLevel* L, const Depth& dp);
+int line_compact_relax(SomarLevel* L, Depth& dp, double* phi, const double* rhs, int iters, bool coefStale, int profPhase);
+void line_compact_free(Depth& dp);
 // projector.cu
 int op_mac_gradient(SomarLevel* L, SomarField* const grad[3], SomarField* phi, bool homog, double scale, bool accumulate);
 int op_mac_divergence(SomarLevel* L, SomarField* div, const SomarField* const flux[3], double divideBy);

@@ -233,3 +233,37 @@ def test_gsrb_kernel_variants_bit_identical(name, oracle_lib, somar, monkeypatch
     want = pb.oracle(oracle_lib, relaxMode=1, maxDepth=0).relax(phi, rhs, iters=3, depth=0)
     for variant in out:
         assert np.array_equal(out[variant], want), f"variant {variant}: rel err {rel_err(out[variant], want):.3e}"
+
+
+LINE_CASES = {
+    "odd_nx_dirichlet": dict(n=(67, 30, 20), map_name="stretched", aniso=4.0, bc_type=[1, 0, 0, 1, 0, 1],
+                             bc_value=[0, 0, 0, 0, 0, 0.5]),
+    "boxes": dict(n=(64, 48, 32), map_name="stretched", aniso=16.0, parts=(1, 4, 1)),
+    "helmholtz": dict(n=(34, 18, 16), map_name="stretched", aniso=4.0, alpha=1.0, beta=-0.05),
+    "thin": dict(n=(128, 30, 4), map_name="stretched", aniso=1.0),
+}
+
+
+@pytest.mark.parametrize("name", list(LINE_CASES))
+def test_line_gsrb_colour_split_layout_bit_identical(name, oracle_lib, somar, monkeypatch):
+    """LineGSRB in the colour-split layout (line_compact.cu) against the brick kernel (line.cu) and the oracle: the same
+    statements on the same operands, so the same bits -- odd row lengths, Dirichlet x / y sides, alpha != 0 included."""
+    pb = Problem(**LINE_CASES[name])
+    phi, rhs = pb.rand(), pb.rand()
+    out = {}
+    for variant, kernel in (("2", "k_line_pass_c"), ("0", "k_line_gsrb")):   # "2": the compact path at every size
+        monkeypatch.setenv("SOMAR_B200_LINE_COMPACT", variant)
+        lev = pb.level(somar, relaxMode=3, maxDepth=0)
+        assert lev.relax_kernel(0, 3) == kernel
+        fphi, frhs = lev.field(0, phi), lev.field(0, rhs)
+        lev.relax(fphi, frhs, iters=3)
+        lev.relax(fphi, frhs, iters=1)            # a second call: phi is packed again, the coefficients are reused
+        if name == "helmholtz":
+            lev.set_alpha_beta(0.5, -0.1)          # the column matrix changes: coefficients rebuilt
+            lev.relax(fphi, frhs, iters=1)
+        out[variant] = fphi.get()
+        lev.destroy()
+    assert np.array_equal(out["2"], out["0"])
+    if name != "helmholtz":
+        want = pb.oracle(oracle_lib, relaxMode=3, maxDepth=0).relax(phi, rhs, iters=4, depth=0)
+        assert np.array_equal(out["2"], want), rel_err(out["2"], want)
