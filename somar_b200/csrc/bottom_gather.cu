@@ -18,6 +18,7 @@ namespace somar {
 static int dalloc0(double** p, long long n) {
     SOMAR_CUDA(cudaMalloc(p, sizeof(double) * (size_t)n));
     SOMAR_CUDA(cudaMemset(*p, 0, sizeof(double) * (size_t)n));
+    SOMAR_CUDA(cudaStreamSynchronize(nullptr));   // the level's stream is non-blocking: see dalloc in level.cu
     return SOMAR_OK;
 }
 

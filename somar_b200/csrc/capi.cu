@@ -111,6 +111,7 @@ int somar::level_create_impl(const SomarLevelDesc* desc, const SomarSolverParams
         (ce = cudaMemset(L->cx.tickets, 0, sizeof(unsigned) * 8)) != cudaSuccess ||
         (ce = cudaMalloc(&L->d_scal, sizeof(double) * 8)) != cudaSuccess ||
         (ce = cudaMemset(L->d_scal, 0, sizeof(double) * 8)) != cudaSuccess ||
+        (ce = cudaStreamSynchronize(nullptr)) != cudaSuccess ||   // default-stream memsets vs the non-blocking stream
         (ce = cudaMallocHost(&L->h_scal, sizeof(double) * 8)) != cudaSuccess ||
         (ce = cudaEventCreate(&L->ev0)) != cudaSuccess || (ce = cudaEventCreate(&L->ev1)) != cudaSuccess) {
         set_error(std::string("level_create: ") + cudaGetErrorString(ce));

@@ -121,6 +121,9 @@ static void make_geom(const SomarLevel* L, const int coarsening[3], const double
 static int dalloc(double** p, long long n) {
     SOMAR_CUDA(cudaMalloc(p, sizeof(double) * (size_t)n));
     SOMAR_CUDA(cudaMemset(*p, 0, sizeof(double) * (size_t)n));
+    // cudaMemset of device memory runs on the legacy default stream, asynchronously to the host; the level's stream is
+    // non-blocking and would not wait for it: a kernel launched next on that stream could be overtaken by the zeros
+    SOMAR_CUDA(cudaStreamSynchronize(nullptr));
     return SOMAR_OK;
 }
 

@@ -201,13 +201,22 @@ int line_compact_relax(SomarLevel* L, Depth& dp, double* phi, const double* rhs,
         C->lc.plane = C->lc.pitch * g.n[1];
         C->lc.total = C->lc.plane * g.n[2];
         const size_t bytes = sizeof(double) * (size_t)C->lc.total;
+        // every array starts at zero: the pad columns of a row and, with an odd row length, the last column of one
+        // colour are never written, and a value selected away must not be a NaN that a 0 * x would keep
+        auto zalloc = [&](double*& x) {
+            if (cudaMalloc(&x, bytes) != cudaSuccess) return false;
+            return cudaMemsetAsync(x, 0, bytes, L->cx.stream) == cudaSuccess;
+        };
+        bool ok = true;
         for (int p = 0; p < 2; ++p) {
-            for (double*& x : C->coef[p]) SOMAR_CUDA(cudaMalloc(&x, bytes));
-            SOMAR_CUDA(cudaMalloc(&C->rj[p], bytes));
-            SOMAR_CUDA(cudaMalloc(&C->phi[p], bytes));
-            SOMAR_CUDA(cudaMemsetAsync(C->phi[p], 0, bytes, L->cx.stream));
+            for (double*& x : C->coef[p]) ok = ok && zalloc(x);
+            ok = ok && zalloc(C->rj[p]) && zalloc(C->phi[p]);
         }
-        SOMAR_CUDA(cudaMalloc(&C->bp, bytes));
+        ok = ok && zalloc(C->bp);
+        if (!ok) {
+            set_error(std::string("line_compact: ") + cudaGetErrorString(cudaGetLastError()));
+            return SOMAR_ERR_CUDA;
+        }
     }
     const LineC lc = C->lc;
     const dim3 pb(64, 4), pg((lc.nxh + 63) / 64, (g.n[1] + 3) / 4, g.n[2]);
