@@ -150,8 +150,34 @@ __device__ __forceinline__ void rb_tile_pass(const Geom& g, const Metric& m, dou
 // One CTA per tile, cooperative launch (grid barriers).  `part`: 4 * MAX_RED_BLOCKS doubles of reduction partials.
 __global__ void __launch_bounds__(RB_TPB, 1)
 k_bicg_resident(const Geom g, const Metric m, const BicgFields f, const BicgArgs a, double* part, int* itersAccum,
-                const int tilesX) {
+                const int tilesX, unsigned long long* gbar) {
     cg::grid_group grid = cg::this_grid();
+    // Grid-wide barrier.  gbar == nullptr: cooperative groups' grid barrier (every CTA's thread 0 adds to ONE word and
+    // polls it: ~128 serialised atomics).  gbar != nullptr (the launch has thread-block clusters): the hardware cluster
+    // barrier inside each cluster, one atomic per CLUSTER on a counter that only grows (zeroed before the launch), the
+    // cluster barrier again.  Visibility: barrier.cluster is release/acquire at cluster scope, the leader's
+    // __threadfence() at gpu scope is cumulative over what it observed through the cluster barrier.
+    unsigned bepoch = 0;
+    auto gsync = [&]() {
+        if (gbar == nullptr) {
+            grid.sync();
+            return;
+        }
+        cg::cluster_group cl = cg::this_cluster();
+        cl.sync();
+        if (cl.block_rank() == 0 && threadIdx.x == 0) {
+            ++bepoch;
+            const unsigned long long want = (unsigned long long)bepoch * (gridDim.x / cl.num_blocks());
+            __threadfence();
+            atomicAdd(gbar, 1ULL);
+            const long long t0 = clock64();
+            while (*((volatile unsigned long long*)gbar) < want) {
+                if (clock64() - t0 > (20ll << 30)) __trap();   // ~10 s: a bug must not hang the GPU
+            }
+            __threadfence();
+        }
+        cl.sync();
+    };
     extern __shared__ __align__(16) double sm[];
     __shared__ BicgState s;
     __shared__ double rhoNext;
@@ -203,7 +229,7 @@ k_bicg_resident(const Geom g, const Metric m, const BicgFields f, const BicgArgs
             pb[blockIdx.x] = p0;
             if (n > 1) pb[MAX_RED_BLOCKS + blockIdx.x] = p1;
         }
-        grid.sync();
+        gsync();
         for (int q = 0; q < n; ++q) {
             const bool isMax = isMax0 && q == 0;
             double v = 0.0;
@@ -297,7 +323,7 @@ k_bicg_resident(const Geom g, const Metric m, const BicgFields f, const BicgArgs
                     pv[k] = pn;
                     f.pv[cidx[k]] = pn;
                 }
-            grid.sync();
+            gsync();
         }
         // p~ = preCond(p) (diagonal scaling + relaxations), v = L p~
         rb_tile_pass(g, m, sm, T, f.pv, f.pv, pre, a.nprecond, pc, lp);
@@ -370,7 +396,7 @@ k_bicg_resident(const Geom g, const Metric m, const BicgFields f, const BicgArgs
 #pragma unroll
             for (int k = 0; k < RB_NZ; ++k)
                 if (cidx[k] >= 0) f.pt[cidx[k]] = phi[k];   // staged in p~'s array (not otherwise used by this kernel)
-            grid.sync();
+            gsync();
             rb_tile_pass(g, m, sm, T, f.pt, f.rhs, false, 0, pc, lp);
             residual_from_lp();
             norm_and_rho();
@@ -420,8 +446,7 @@ bool bottom_resident_usable(SomarLevel* L, const Geom& g, const Metric& m) {
 }
 
 int launch_bottom_resident(SomarLevel* L, const Geom& g_, const Metric& m_, double* phi, double* rhs,
-                           double* const work[8], void* bicgDev, double* part, int* itersAccum) {
-    (void)bicgDev;
+                           double* const work[8], void* bicgBar, double* part, int* itersAccum) {
     const SomarSolverParams& p = L->prm;
     BicgFields f;
     f.phi = phi; f.rhs = rhs;
@@ -440,9 +465,46 @@ int launch_bottom_resident(SomarLevel* L, const Geom& g_, const Metric& m_, doub
     Metric m = m_;
     int tilesX = (g.n[0] + RB_CX - 1) / RB_CX;
     const int tiles = tilesX * ((g.n[1] + RB_CY - 1) / RB_CY);
-    void* args[] = {&g, &m, &f, &a, &part, &itersAccum, &tilesX};
-    SOMAR_CUDA(cudaLaunchCooperativeKernel((const void*)k_bicg_resident, dim3(tiles), dim3(RB_TPB), args, RB_SMEM_BYTES,
-                                           L->cx.stream));
+    // SOMAR_B200_BOTTOM_CLUSTER=8|4|2: thread-block clusters for the grid barrier (gsync in the kernel) -- the largest
+    // cluster size <= the request that divides the tile count and whose clusters are all co-resident.  OFF by default:
+    // measured on B200 at 256x256x4 (2059 iterations per solve) 75.6 us per iteration with clusters of 8 or 4 against
+    // 70.8 with cooperative groups' barrier -- as with round 1's counter tree, the barrier itself is not what the
+    // iteration waits for.
+    int csize = 0;
+    {
+        const char* e = getenv("SOMAR_B200_BOTTOM_CLUSTER");
+        const int want = e ? atoi(e) : 0;
+        for (int c = want; c >= 2 && !csize; c >>= 1) {
+            if (tiles % c) continue;
+            cudaLaunchConfig_t q = {};
+            q.gridDim = dim3(tiles); q.blockDim = dim3(RB_TPB); q.dynamicSmemBytes = RB_SMEM_BYTES;
+            cudaLaunchAttribute at[1];
+            at[0].id = cudaLaunchAttributeClusterDimension;
+            at[0].val.clusterDim.x = c; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+            q.attrs = at; q.numAttrs = 1;
+            int nclusters = 0;
+            if (cudaOccupancyMaxActiveClusters(&nclusters, k_bicg_resident, &q) == cudaSuccess && nclusters * c >= tiles) csize = c;
+            else (void)cudaGetLastError();
+        }
+    }
+    unsigned long long* gbar = nullptr;
+    if (csize) {
+        gbar = static_cast<unsigned long long*>(bicgBar);
+        SOMAR_CUDA(cudaMemsetAsync(gbar, 0, sizeof(unsigned long long), L->cx.stream));
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(tiles); cfg.blockDim = dim3(RB_TPB); cfg.dynamicSmemBytes = RB_SMEM_BYTES; cfg.stream = L->cx.stream;
+        cudaLaunchAttribute at[2];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = csize; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        at[1].id = cudaLaunchAttributeCooperative;
+        at[1].val.cooperative = 1;
+        cfg.attrs = at; cfg.numAttrs = 2;
+        SOMAR_CUDA(cudaLaunchKernelEx(&cfg, k_bicg_resident, g, m, f, a, part, itersAccum, tilesX, gbar));
+    } else {
+        void* args[] = {&g, &m, &f, &a, &part, &itersAccum, &tilesX, &gbar};
+        SOMAR_CUDA(cudaLaunchCooperativeKernel((const void*)k_bicg_resident, dim3(tiles), dim3(RB_TPB), args, RB_SMEM_BYTES,
+                                               L->cx.stream));
+    }
     L->cx.launches++;
     L->bottom_iters_pending = true;
     return SOMAR_OK;

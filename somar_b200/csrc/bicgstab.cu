@@ -391,7 +391,7 @@ int launch_bottom_persistent(SomarLevel* L, const Geom& g_, const Metric& m_, do
     if ((rc = ensure_state(L))) return rc;
     BicgDev* dv = static_cast<BicgDev*>(L->d_bicg);
     if (bottom_resident_usable(L, g_, m_))   // mode 3: the whole bottom problem resident on chip (bicg_resident.cu)
-        return launch_bottom_resident(L, g_, m_, phi, rhs, work, dv, dv->part, &dv->iters);
+        return launch_bottom_resident(L, g_, m_, phi, rhs, work, dv->bar, dv->part, &dv->iters);
     BicgFields f;
     f.phi = phi; f.rhs = rhs;
     f.r = work[0]; f.rt = work[1]; f.e = work[2]; f.pv = work[3]; f.pt = work[4];

@@ -188,7 +188,7 @@ int launch_bottom_persistent(SomarLevel* L, const Geom& g, const Metric& m, doub
 // bicg_resident.cu
 bool bottom_resident_usable(SomarLevel* L, const Geom& g, const Metric& m);
 int launch_bottom_resident(SomarLevel* L, const Geom& g, const Metric& m, double* phi, double* rhs, double* const work[8],
-                           void* bicgDev, double* part, int* itersAccum);
+                           void* bicgBar, double* part, int* itersAccum);
 // line_compact.cu
 bool line_compact_usable(const SomarLevel* L, const Depth& dp);
 int line_compact_relax(SomarLevel* L, Depth& dp, double* phi, const double* rhs, int iters, bool coefStale, int profPhase);
