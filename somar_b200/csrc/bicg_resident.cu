@@ -27,6 +27,7 @@
 #include "bicg_persistent.cuh"
 #include "level.hpp"
 
+#include <cstdio>
 #include <cstdlib>
 
 namespace somar {
@@ -45,6 +46,16 @@ constexpr int RB_OFF_JX = 0, RB_OFF_JY = RB_OFF_JX + RB_CELLS, RB_OFF_JI = RB_OF
 constexpr int RB_SMEM_BYTES = RB_SMEM_DOUBLES * 8;               // 218 400 B
 static_assert(RB_SMEM_BYTES <= 227 * 1024, "shared memory budget");
 
+// development probe (SOMAR_B200_BOTTOM_PROF=1): nanoseconds block 0 spends in [0] tile-pass load, [1] colour passes,
+// [2] apply, [3] grid barriers incl. waiting, [4] everything else; [5] iterations
+__device__ unsigned long long g_rb_prof[8];
+__device__ __forceinline__ unsigned long long rb_now() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define RB_PROF(slot, t0) do { if (prof && blockIdx.x == 0 && threadIdx.x == 0) { const unsigned long long t1_ = rb_now(); g_rb_prof[slot] += t1_ - (t0); (t0) = t1_; } } while (0)
+
 struct RbTile {
     int cx0, cy0, ox, oy;   // core origin, region origin (local cell indices; the region may stick out of the domain)
     int x, y;               // my core column
@@ -58,7 +69,7 @@ struct RbTile {
 //   out: pc[k] = relaxed value, lp[k] = L(relaxed) of my column's cells (garbage where !own or k >= nz)
 __device__ __forceinline__ void rb_tile_pass(const Geom& g, const Metric& m, double* __restrict__ sm, const RbTile& T,
                                              const double* src, const double* rhsSrc, bool scaled, int nrelax,
-                                             double (&pc)[RB_NZ], double (&lp)[RB_NZ]) {
+                                             double (&pc)[RB_NZ], double (&lp)[RB_NZ], bool prof, unsigned long long& tp) {
     const int nx = g.n[0], ny = g.n[1], nz = g.n[2];
     const int h = 2 * nrelax + 1;
     const int tid = threadIdx.x;
@@ -69,6 +80,7 @@ __device__ __forceinline__ void rb_tile_pass(const Geom& g, const Metric& m, dou
     const double* const JZ = sm + RB_OFF_JZ;
     const double* const JI = sm + RB_OFF_JI;
     __syncthreads();   // the previous pass's readers are done with G and R
+    RB_PROF(4, tp);
     {
         const int xa = max(0, T.cx0 - h), xb = min(nx, T.cx0 + RB_CX + h), ya = max(0, T.cy0 - h), yb = min(ny, T.cy0 + RB_CY + h);
         const int wx = xb - xa, wy = yb - ya;
@@ -89,6 +101,7 @@ __device__ __forceinline__ void rb_tile_pass(const Geom& g, const Metric& m, dou
         }
     }
     __syncthreads();
+    RB_PROF(0, tp);
     int sdone = 0;
     for (int it = 0; it < nrelax; ++it)
         for (int pass = 0; pass < 2; ++pass) {
@@ -123,6 +136,7 @@ __device__ __forceinline__ void rb_tile_pass(const Geom& g, const Metric& m, dou
             }
             __syncthreads();
         }
+    RB_PROF(1, tp);
     if (T.own) {
 #pragma unroll
         for (int k = 0; k < RB_NZ; ++k) {
@@ -143,6 +157,7 @@ __device__ __forceinline__ void rb_tile_pass(const Geom& g, const Metric& m, dou
             }
         }
     }
+    RB_PROF(2, tp);
 }
 
 }  // namespace
@@ -158,9 +173,13 @@ k_bicg_resident(const Geom g, const Metric m, const BicgFields f, const BicgArgs
     // cluster barrier again.  Visibility: barrier.cluster is release/acquire at cluster scope, the leader's
     // __threadfence() at gpu scope is cumulative over what it observed through the cluster barrier.
     unsigned bepoch = 0;
+    const bool prof = a.tcx == 1234;   // (tcx / tcy belong to the persistent kernel's tile pass; 1234 = probe on)
+    unsigned long long tp = prof ? rb_now() : 0ull;
     auto gsync = [&]() {
         if (gbar == nullptr) {
+            RB_PROF(4, tp);
             grid.sync();
+            RB_PROF(3, tp);
             return;
         }
         cg::cluster_group cl = cg::this_cluster();
@@ -281,7 +300,7 @@ k_bicg_resident(const Geom g, const Metric m, const BicgFields f, const BicgArgs
     };
 
     // ---- num_smooth_bottom relaxations and the true residual: one tile pass straight from the multigrid fields
-    rb_tile_pass(g, m, sm, T, f.phi, f.rhs, false, a.presmooth, pc, lp);
+    rb_tile_pass(g, m, sm, T, f.phi, f.rhs, false, a.presmooth, pc, lp, prof, tp);
 #pragma unroll
     for (int k = 0; k < RB_NZ; ++k) phi[k] = pc[k];
     residual_from_lp();
@@ -326,7 +345,7 @@ k_bicg_resident(const Geom g, const Metric m, const BicgFields f, const BicgArgs
             gsync();
         }
         // p~ = preCond(p) (diagonal scaling + relaxations), v = L p~
-        rb_tile_pass(g, m, sm, T, f.pv, f.pv, pre, a.nprecond, pc, lp);
+        rb_tile_pass(g, m, sm, T, f.pv, f.pv, pre, a.nprecond, pc, lp, prof, tp);
         {
             double acc = 0.0;
 #pragma unroll
@@ -359,7 +378,7 @@ k_bicg_resident(const Geom g, const Metric m, const BicgFields f, const BicgArgs
         __syncthreads();
         if (s.doB) {
             // s~ = preCond(r), t = L s~
-            rb_tile_pass(g, m, sm, T, f.r, f.r, pre, a.nprecond, pc, lp);
+            rb_tile_pass(g, m, sm, T, f.r, f.r, pre, a.nprecond, pc, lp, prof, tp);
             {
                 double a0 = 0.0, a1 = 0.0;
 #pragma unroll
@@ -397,7 +416,7 @@ k_bicg_resident(const Geom g, const Metric m, const BicgFields f, const BicgArgs
             for (int k = 0; k < RB_NZ; ++k)
                 if (cidx[k] >= 0) f.pt[cidx[k]] = phi[k];   // staged in p~'s array (not otherwise used by this kernel)
             gsync();
-            rb_tile_pass(g, m, sm, T, f.pt, f.rhs, false, 0, pc, lp);
+            rb_tile_pass(g, m, sm, T, f.pt, f.rhs, false, 0, pc, lp, prof, tp);
             residual_from_lp();
             norm_and_rho();
             if (tid == 0) {
@@ -415,6 +434,8 @@ k_bicg_resident(const Geom g, const Metric m, const BicgFields f, const BicgArgs
 #pragma unroll
     for (int k = 0; k < RB_NZ; ++k)
         if (cidx[k] >= 0) f.phi[cidx[k]] = phi[k] + 1.0 * e[k];
+    RB_PROF(4, tp);
+    if (prof && blockIdx.x == 0 && tid == 0) g_rb_prof[5] += s.i;
     if (blockIdx.x == 0 && tid == 0) *itersAccum += s.i;
 }
 
@@ -461,6 +482,8 @@ int launch_bottom_resident(SomarLevel* L, const Geom& g_, const Metric& m_, doub
     a.imax = p.bottom_imax;
     a.normKind = (p.bottom_normType == 0) ? 0 : (p.bottom_normType == 1 ? 1 : 2);
     a.tcx = a.tcy = 0;
+    static const bool profOn = []() { const char* e = getenv("SOMAR_B200_BOTTOM_PROF"); return e && e[0] == '1'; }();
+    if (profOn) a.tcx = 1234;
     Geom g = g_;
     Metric m = m_;
     int tilesX = (g.n[0] + RB_CX - 1) / RB_CX;
@@ -507,6 +530,18 @@ int launch_bottom_resident(SomarLevel* L, const Geom& g_, const Metric& m_, doub
     }
     L->cx.launches++;
     L->bottom_iters_pending = true;
+    if (profOn) {   // development probe: synchronises
+        static int visits = 0;
+        if (++visits % 5 == 0) {
+            unsigned long long h[8];
+            cudaStreamSynchronize(L->cx.stream);
+            cudaMemcpyFromSymbol(h, g_rb_prof, sizeof(h));
+            const double it = h[5] ? (double)h[5] : 1.0;
+            fprintf(stderr, "k_bicg_resident probe (block 0, per iteration, us): load %.2f  colour passes %.2f  apply %.2f  "
+                            "grid barriers %.2f  rest %.2f  (%llu iterations)\n",
+                    h[0] / it * 1e-3, h[1] / it * 1e-3, h[2] / it * 1e-3, h[3] / it * 1e-3, h[4] / it * 1e-3, h[5]);
+        }
+    }
     return SOMAR_OK;
 }
 
