@@ -108,14 +108,24 @@ __device__ __forceinline__ void rb_tile_pass(const Geom& g, const Metric& m, dou
             ++sdone;
             const int e = h - sdone;   // this colour pass is valid on core + e
             const int xa = max(0, T.cx0 - e), xb = min(nx, T.cx0 + RB_CX + e), ya = max(0, T.cy0 - e), yb = min(ny, T.cy0 + RB_CY + e);
-            const int half = (xb - xa + 1) >> 1, wy = yb - ya;
-            for (int q = tid; q < half * wy * nz; q += RB_TPB) {
-                const int k = q / (half * wy), r = q - k * half * wy;
-                const int jj = r / half;
-                const int j = ya + jj;
-                const int par = (g.g0[0] + g.g0[1] + j + g.g0[2] + k + pass) & 1;
-                const int i = xa + ((xa ^ par) & 1) + 2 * (r - jj * half);
-                if (i < xb) {
+            // Cell mapping of a colour pass: a warp takes 32 CONSECUTIVE columns of a PAIR of rows, lane by lane
+            // alternating between the two rows (the cell of the pass's colour in each column).  Shared-memory words of
+            // adjacent lanes then differ by 1 or by 1 + RB_W (= 43: odd), so a half-warp's 16 eight-byte accesses hit 16
+            // different banks -- a row-wise mapping strides by 2 cells and is a 2-way conflict on every access (the
+            // passes were LDS-bound at 3.4 us each).  The decode uses float reciprocals (exact for these small integers)
+            // instead of two runtime integer divisions per cell.
+            const int wx = xb - xa, wy = yb - ya;
+            const int npair = (wy + 1) >> 1;
+            const int perPlane = wx * npair, total = perPlane * nz;
+            const float rPlane = 1.0f / (float)perPlane, rWx = 1.0f / (float)wx;
+            for (int q = tid; q < total; q += RB_TPB) {
+                const int k = (int)(((float)q + 0.5f) * rPlane);
+                const int r = q - k * perPlane;
+                const int rp = (int)(((float)r + 0.5f) * rWx);
+                const int i = xa + (r - rp * wx);
+                // the row of the pair whose cell in column i has this pass's colour: (g0 + i + j + k + pass) even
+                const int j = ya + 2 * rp + ((g.g0[0] + i + g.g0[1] + ya + g.g0[2] + k + pass) & 1);
+                if (j < yb) {
                     const int l = (i - T.ox) + RB_W * (j - T.oy) + RB_PL * k;
                     double nb[3][2];
                     nb[0][0] = G[l - 1];
