@@ -219,6 +219,36 @@ int somar_mac_gradient(SomarLevel* lev, SomarField* gx, SomarField* gy, SomarFie
 int somar_mac_divergence(SomarLevel* lev, SomarField* div, const SomarField* fx, const SomarField* fy,
                          const SomarField* fz, double divide_by);
 int somar_mac_apply_correction(SomarLevel* lev, SomarField* vx, SomarField* vy, SomarField* vz, SomarField* phi, double dt);
+/* The reference projectors' own BC holders (LevelMACProjector.cpp:99-101, LevelCCProjector.cpp:103-105):
+ *   m_divBC  = PhysBCUtil::uStarFuncBC: on solid walls the normal face value is set to zero IN PLACE
+ *              (BasicVelocityBCGhostClass -> setSideDiriBC face-centred branch, EllipticBCUtils.cpp:41-118; inflow /
+ *              outflow / tidal sides are not built)                                  -> somar_mac_wall_flux_bc
+ *   m_gradBC = PhysBCUtil::basicGradPressureFuncBC: EllipticExtrapBCGhostClass(2), ghost = 3 (p1 - p2) + p3 and no
+ *              flux method (ELLIPTICEXTRAPBCGHOST, EllipticBCUtilsF.ChF:165-173)    -> grad_bc = 1
+ * somar_mac_gradient keeps the operator's BC holder (grad_bc = 0: with homogeneous Neumann pressure BCs a wall face gets
+ * no correction, which is what the reference's velocity BCs restore right after the projection,
+ * AMRNavierStokesAdvancePPM.cpp:287-294).  somar_level_set_projector_bc(lev, 1) makes somar_project apply both holders
+ * itself, as LevelMACProjector::computeDiv / computeGrad do; 0 (default) is the round-1 behaviour. */
+int somar_level_set_projector_bc(SomarLevel* lev, int mode);
+int somar_mac_gradient_bc(SomarLevel* lev, SomarField* gx, SomarField* gy, SomarField* gz, SomarField* phi, int homogeneous,
+                          int grad_bc);
+int somar_mac_wall_flux_bc(SomarLevel* lev, SomarField* fx, SomarField* fy, SomarField* fz);
+
+/* ---- cell-centred projector: LevelCCProjector (src/projection/LevelCCProjector.cpp:156-255), the second projection of
+ * the reference's time step (AMRNavierStokes::doCCProjection, AMRNavierStokesAdvancePPM.cpp:1513-1573) ----------------
+ * u* are CELL fields holding the velocity components; J is the cell-centred Jacobian field the reference caches
+ * (LevelGeometry::getCCJ) or NULL when the velocity is already a flux (a_velIsFlux = true).  The library exchanges the
+ * halos of u* and J itself; ghosts beyond solid walls are not read.
+ * somar_cc_divergence: Divergence::levelDivergenceCC (Divergence.cpp:359-396): [multByJ,] CellToEdge, m_divBC,
+ *                      MAPPEDFLUXDIVERGENCE, then / divide_by unless that is 0 -- one pass, no face arrays
+ * somar_cc_gradient:   Gradient::levelGradientCC (Gradient.cpp:469-494): levelGradientMAC with m_gradBC, EdgeToCell
+ * somar_project_cc:    BaseProjector<FArrayBox>::project on one level (BaseProjectorI.H:176-300):
+ *                      [u *= J;] rhs = Div[u]/dt; solve; u -= dt Grad[p]; [u *= Jinv]  -- two sweeps around the solve */
+int somar_cc_divergence(SomarLevel* lev, SomarField* div, SomarField* ux, SomarField* uy, SomarField* uz, SomarField* J,
+                        double divide_by);
+int somar_cc_gradient(SomarLevel* lev, SomarField* gx, SomarField* gy, SomarField* gz, SomarField* phi);
+int somar_project_cc(SomarLevel* lev, SomarField* ux, SomarField* uy, SomarField* uz, SomarField* J, SomarField* pressure,
+                     double dt, int zero_pressure, int force_homogeneous, SomarSolveStats* stats);
 
 /* ---- leptic-solver sweeps (SURVEY 8(a) LevelLepticSolver row; the iteration that drives them is somar_leptic_solve below) --
  * "Flat" arguments are depth-0 fields whose vertical index 0 holds a horizontal array (the reference's VertShifter,

@@ -341,6 +341,85 @@ void orc_mac_gradient(void* hv, int depth, double* g0, double* g1, double* g2, c
     gather_faces(op, gr, g);
 }
 
+// the same with the BC holder named: 0 the operator's, 1 order-2 extrapolated ghosts (the projectors' m_gradBC)
+void orc_mac_gradient_bc(void* hv, int depth, double* g0, double* g1, double* g2, const double* phi, int homog, int gradBC) {
+    Op& op = *((OrcHandle*)hv)->mg->ops[depth];
+    LevelData p;
+    op.create(p, 1);
+    scatter(op, p, phi);
+    FluxLevelData gr;
+    gr.define(op.grids, 1, op.nd);
+    op.macGradient(gr, p, homog != 0, gradBC);
+    double* g[3] = {g0, g1, g2};
+    gather_faces(op, gr, g);
+}
+
+// Divergence::levelDivergenceCC (Divergence.cpp:359-396) with the projector's wall BC, and Gradient::levelGradientCC
+// (Gradient.cpp:469-494) with the projector's gradient BC, on depth 0.  u*, c*: cell arrays.
+void orc_cc_divergence(void* hv, double* div, const double* u0, const double* u1, const double* u2) {
+    Op& op = *((OrcHandle*)hv)->mg->ops[0];
+    const double* u[3] = {u0, u1, u2};
+    std::array<LevelData, 3> vel;
+    for (int d = 0; d < op.nd; ++d) {
+        op.create(vel[d], 1);
+        scatter(op, vel[d], u[d]);
+        op.exchange(vel[d], false);
+    }
+    FluxLevelData edge;
+    edge.define(op.grids, 1, op.nd);
+    op.cellToEdge(edge, vel);
+    op.wallFluxBC(edge);
+    LevelData d;
+    op.create(d, 0);
+    op.macDivergence(d, edge);
+    gather(op, d, div);
+}
+
+void orc_cc_gradient(void* hv, double* c0, double* c1, double* c2, const double* phi) {
+    Op& op = *((OrcHandle*)hv)->mg->ops[0];
+    LevelData p;
+    op.create(p, 1);
+    scatter(op, p, phi);
+    FluxLevelData eg;
+    eg.define(op.grids, 1, op.nd);
+    op.macGradient(eg, p, false, 1);
+    std::array<LevelData, 3> cc;
+    for (int d = 0; d < op.nd; ++d) op.create(cc[d], 0);
+    op.edgeToCell(cc, eg);
+    double* c[3] = {c0, c1, c2};
+    for (int d = 0; d < op.nd; ++d) gather(op, cc[d], c[d]);
+}
+
+// BaseProjector<FArrayBox>::project via LevelCCProjector on depth 0.  J may be NULL (a_velIsFlux = true).
+void orc_project_cc(void* hv, double* u0, double* u1, double* u2, const double* J, double* pressure, double dt,
+                    int zeroPressure, int forceHomogeneous, OrcStats* out) {
+    MG& mg = *((OrcHandle*)hv)->mg;
+    Op& op = *mg.ops[0];
+    double* u[3] = {u0, u1, u2};
+    std::array<LevelData, 3> vel;
+    for (int d = 0; d < op.nd; ++d) {
+        op.create(vel[d], 1);
+        scatter(op, vel[d], u[d]);
+    }
+    LevelData Jl;
+    if (J) {
+        op.create(Jl, 0);
+        scatter(op, Jl, J);
+    }
+    LevelData p;
+    op.create(p, 1);
+    scatter(op, p, pressure);
+    SolveStats st;
+    mg.projectCC(vel, J ? &Jl : nullptr, p, dt, zeroPressure != 0, forceHomogeneous != 0, st);
+    gather(op, p, pressure);
+    for (int d = 0; d < op.nd; ++d) gather(op, vel[d], u[d]);
+    out->iters = st.iters; out->exitStatus = st.exitStatus;
+    out->initial_rnorm = st.initial_rnorm; out->final_rnorm = st.final_rnorm;
+    out->bottom_iters_total = st.bottom_iters_total;
+    out->history_len = (int)std::min<size_t>(128, st.history.size());
+    for (int i = 0; i < out->history_len; ++i) out->history[i] = st.history[i];
+}
+
 // LevelLepticSolver::computeHorizRHS / ::levelVertHorizGradient on depth 0 (flat outputs: one value per column)
 void orc_leptic_horiz_rhs(void* hv, double* flatRhs, const double* phi) {
     Op& op = *((OrcHandle*)hv)->mg->ops[0];

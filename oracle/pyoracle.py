@@ -265,6 +265,41 @@ class Oracle:
                            int(zero_pressure), int(force_homogeneous), C.byref(st))
         return v[:self.dim], p, _stats(st)
 
+    def mac_gradient_bc(self, phi, grad_bc, depth=0, homogeneous=False):
+        """grad_bc 0: the operator's BC holder; 1: order-2 extrapolated ghosts (the reference projectors' m_gradBC)"""
+        phi = _f64(phi)
+        g = [np.zeros(sh) for sh in self.face_shapes(depth)] + [None] * (3 - self.dim)
+        self.L.orc_mac_gradient_bc.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 4 + [C.c_int, C.c_int]
+        self.L.orc_mac_gradient_bc(self.h, depth, *[(_ptr(x) if x is not None else None) for x in g], _ptr(phi),
+                                   int(homogeneous), int(grad_bc))
+        return g[:self.dim]
+
+    # -- cell-centred projector (LevelCCProjector) ------------------------------------------------
+    def cc_divergence(self, vel):
+        u = [_f64(x) for x in vel] + [None] * (3 - self.dim)
+        out = np.zeros(self.shape(0))
+        self.L.orc_cc_divergence.argtypes = [C.c_void_p] * 5
+        self.L.orc_cc_divergence(self.h, _ptr(out), *[(_ptr(x) if x is not None else None) for x in u])
+        return out
+
+    def cc_gradient(self, phi):
+        phi = _f64(phi)
+        g = [np.zeros(self.shape(0)) for _ in range(self.dim)] + [None] * (3 - self.dim)
+        self.L.orc_cc_gradient.argtypes = [C.c_void_p] * 5
+        self.L.orc_cc_gradient(self.h, *[(_ptr(x) if x is not None else None) for x in g], _ptr(phi))
+        return g[:self.dim]
+
+    def project_cc(self, vel, dt, J=None, pressure0=None, zero_pressure=True, force_homogeneous=False):
+        v = [_f64(x).copy() for x in vel] + [None] * (3 - self.dim)
+        p = np.zeros(self.shape(0)) if pressure0 is None else _f64(pressure0).copy()
+        Jp = None if J is None else _f64(J)
+        st = OrcStats()
+        self.L.orc_project_cc.argtypes = [C.c_void_p] * 6 + [C.c_double, C.c_int, C.c_int, C.POINTER(OrcStats)]
+        self.L.orc_project_cc(self.h, *[(_ptr(x) if x is not None else None) for x in v],
+                              None if Jp is None else _ptr(Jp), _ptr(p), float(dt), int(zero_pressure),
+                              int(force_homogeneous), C.byref(st))
+        return v[:self.dim], p, _stats(st)
+
     # -- leptic solver pieces with per-box ghosts (either metric) ---------------------------------
     def _flat_shape(self):
         return (self.n[1], self.n[0]) if self.dim == 3 else (self.n[0],)

@@ -527,7 +527,27 @@ static void macgrad_full(FAB& grad, const FAB& phi, const FAB& ex, const FAB& Jg
 // extrapolation of the transverse-derivative copy past the DOMAIN (validPhi = FAB box & validDomain),
 // BC ghosts (a_fluxBC->setGhosts, non-homogeneous unless asked), MAPPEDMACGRAD[ORTHO], BC fluxes.
 // LevelMACProjector::computeGrad -- LevelMACProjector.cpp:186-218 calls it with the pressure BC.
-void Op::macGradient(FluxLevelData& grad, LevelData& phi, bool homog) const {
+// EllipticExtrapBCGhostClass(order 2) -- EllipticBCUtils.cpp (operator() -> setSideExtrapBC :224-310, cell-centred
+// branch) -> ELLIPTICEXTRAPBCGHOST, EllipticBCUtilsF.ChF:115-173: ghost = 3 (s1 - s2) + s3 counted inward.
+static void extrapGhostBC(FAB& phi, const Box& valid, const Domain& domain, int nd) {
+    for (int idir = 0; idir < nd; ++idir) {
+        if (domain.periodic[idir]) continue;
+        for (int iside = 0; iside < 2; ++iside) {
+            const int isign = sign(iside);
+            Box destBox = bdryBox(domain.box, idir, iside, 1) & surroundingNodes(valid, idir);
+            if (destBox.isEmpty()) continue;
+            destBox.shiftHalf(idir, isign);
+            destBox &= phi.box();
+            if (destBox.isEmpty()) continue;
+            const int e0 = (idir == 0) ? -isign : 0, e1 = (idir == 1) ? -isign : 0, e2 = (idir == 2) ? -isign : 0;
+            ORC_LOOP(destBox, i, j, k)
+                phi(i, j, k) = 3.0 * (phi(i + e0, j + e1, k + e2) - phi(i + 2 * e0, j + 2 * e1, k + 2 * e2)) +
+                               phi(i + 3 * e0, j + 3 * e1, k + 3 * e2);
+        }
+    }
+}
+
+void Op::macGradient(FluxLevelData& grad, LevelData& phi, bool homog, int gradBC) const {
     exchange(phi, true);                                               // Gradient.cpp:120-121
     Box vdom = domain.box;                                             // :117,123-127
     for (int d = 0; d < nd; ++d)
@@ -548,11 +568,12 @@ void Op::macGradient(FluxLevelData& grad, LevelData& phi, bool homog) const {
                     valid.grow(fdir, 1);
                 }
             }
-            setGhosts(phiFAB, &ex, grids[b], b, homog);                // :1004-1020
+            if (gradBC == 1) extrapGhostBC(phiFAB, grids[b], domain, nd);
+            else setGhosts(phiFAB, &ex, grids[b], b, homog);           // :1004-1020
             if (isDiagonal) macgrad_ortho(g, phiFAB, Jgup.fabs[b][dir], edgeBox, dx[dir], dir);        // :1070-1078
             else macgrad_full(g, phiFAB, ex, Jgup.fabs[b][dir], edgeBox, dx, dir, nd);                 // :1060-1067
         }
-        setFluxes(grad.fabs[b], grids[b], homog);                      // :1082-1096 (each direction touches its own FAB)
+        if (gradBC != 1) setFluxes(grad.fabs[b], grids[b], homog);     // :1082-1096 (each direction touches its own FAB)
     }
 }
 
@@ -671,6 +692,90 @@ void Op::lepticVertHorizGradient(double* flatLo, double* flatHi, LevelData& phi,
 // -- Divergence.cpp:44-127 -> MAPPEDFLUXDIVERGENCE{2,3}D, DivCurlGradF.ChF:1034-1214.
 void Op::macDivergence(LevelData& div, const FluxLevelData& flux) const {
     for (size_t b = 0; b < grids.size(); ++b) flux_divergence(div[b], flux.fabs[b].data(), Jinv[b], grids[b], dx, nd);
+}
+
+void Op::wallFluxBC(FluxLevelData& flux) const {
+    for (size_t b = 0; b < grids.size(); ++b)
+        for (int d = 0; d < nd; ++d) {
+            if (domain.periodic[d]) continue;
+            for (int iside = 0; iside < 2; ++iside) {
+                Box thisDom = domain.box;
+                thisDom.surroundingNodes(d);
+                const Box destBox = bdryBox(thisDom, d, iside, 1) & surroundingNodes(grids[b], d);
+                if (destBox.isEmpty()) continue;
+                flux.fabs[b][d].setVal(0.0, destBox, 0, 1);
+            }
+        }
+}
+
+// CellToEdge(LevelData<FArrayBox>, LevelData<FluxBox>) with SpaceDim cell components per face component -- Chombo 3.2
+// lib/src/AMRTools/CellToEdge.cpp + CellToEdgeF.ChF (third party, not under /root/reference; published algorithm):
+//   edge_d(i) = half * (cell_d(i) + cell_d(i - e_d))   on the faces of the valid box; one ghost cell of cell_d is read.
+void Op::cellToEdge(FluxLevelData& edge, std::array<LevelData, 3>& cell) const {
+    for (size_t b = 0; b < grids.size(); ++b)
+        for (int d = 0; d < nd; ++d) {
+            const FAB& c = cell[d][b];
+            FAB& e = edge.fabs[b][d];
+            const int e0 = (d == 0), e1 = (d == 1), e2 = (d == 2);
+            ORC_LOOP(surroundingNodes(grids[b], d), i, j, k) e(i, j, k) = 0.5 * (c(i, j, k) + c(i - e0, j - e1, k - e2));
+        }
+}
+
+// EdgeToCell -- Chombo 3.2 lib/src/AMRTools/EdgeToCell.cpp + EdgeToCellF.ChF:
+//   cell_d(i) = half * (edge_d(i) + edge_d(i + e_d))
+void Op::edgeToCell(std::array<LevelData, 3>& cell, const FluxLevelData& edge) const {
+    for (size_t b = 0; b < grids.size(); ++b)
+        for (int d = 0; d < nd; ++d) {
+            FAB& c = cell[d][b];
+            const FAB& e = edge.fabs[b][d];
+            const int e0 = (d == 0), e1 = (d == 1), e2 = (d == 2);
+            ORC_LOOP(grids[b], i, j, k) c(i, j, k) = 0.5 * (e(i, j, k) + e(i + e0, j + e1, k + e2));
+        }
+}
+
+// BaseProjector<FArrayBox>::project on one level (BaseProjectorI.H:176-300) with LevelCCProjector's virtuals
+// (LevelCCProjector.cpp:156-255):
+//   [vel *= J]                                           LevelGeometry::multByJ, LevelGeometryUtil.cpp:302-340 (cached CCJ)
+//   rhs = levelDivergenceCC(vel) / dt                    Divergence.cpp:359-396 (USE_SIMPLE_STENCIL is off):
+//                                                        CellToEdge, then levelDivergenceMAC with m_divBC = uStarFuncBC
+//   solve L[p] = rhs                                     m_solverBC = LevelPressureFuncBC
+//   corr = levelGradientCC(p)                            Gradient.cpp:469-494: levelGradientMAC with m_gradBC =
+//                                                        gradPiFuncBC (order-2 extrapolated ghosts), then EdgeToCell
+//   vel += corr * dtScale                                LevelCCProjector::applyCorrection :236-254
+//   [vel *= Jinv]                                        LevelGeometry::divByJ :464-500
+// The caller has filled the ghosts of vel (AMRNavierStokes::doCCProjection sets BCs and exchanges first,
+// AMRNavierStokesAdvancePPM.cpp:1513-1530); here box-interface and periodic ghosts come from an exchange and the
+// ghosts beyond solid walls are never used (the wall faces are overwritten by m_divBC).
+void MG::projectCC(std::array<LevelData, 3>& vel, const LevelData* J, LevelData& pressure, double dt, bool zeroPressure,
+                   bool forceHomogeneous, SolveStats& st) {
+    Op& op = *ops[0];
+    const int nd = op.nd;
+    if (J)
+        for (int d = 0; d < nd; ++d)
+            for (size_t b = 0; b < op.grids.size(); ++b) ORC_LOOP(op.grids[b], i, j, k) vel[d][b](i, j, k) *= (*J)[b](i, j, k);
+    for (int d = 0; d < nd; ++d) op.exchange(vel[d], false);
+    FluxLevelData edge;
+    edge.define(op.grids, 1, nd);
+    op.cellToEdge(edge, vel);
+    op.wallFluxBC(edge);
+    LevelData rhs;
+    op.create(rhs, 0);
+    op.macDivergence(rhs, edge);
+    if (dt != 0.0)
+        for (size_t b = 0; b < op.grids.size(); ++b) ORC_LOOP(op.grids[b], i, j, k) rhs[b](i, j, k) /= dt;
+    solve(pressure, rhs, zeroPressure, forceHomogeneous, st);
+    FluxLevelData eg;
+    eg.define(op.grids, 1, nd);
+    op.macGradient(eg, pressure, false, 1);
+    std::array<LevelData, 3> corr;
+    for (int d = 0; d < nd; ++d) op.create(corr[d], 0);
+    op.edgeToCell(corr, eg);
+    const double dtScale = (dt == 0.0) ? -1.0 : -dt;
+    for (int d = 0; d < nd; ++d)
+        for (size_t b = 0; b < op.grids.size(); ++b) {
+            ORC_LOOP(op.grids[b], i, j, k) vel[d][b](i, j, k) += corr[d][b](i, j, k) * dtScale;
+            if (J) ORC_LOOP(op.grids[b], i, j, k) vel[d][b](i, j, k) *= op.Jinv[b](i, j, k);
+        }
 }
 
 // BaseProjector::project with a_velIsFlux = true on one level -- BaseProjectorI.H:176-300:

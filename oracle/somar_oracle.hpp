@@ -146,8 +146,16 @@ struct Op {
     void scale(LevelData& y, double s) const;
     void create(LevelData& y, int ghosts) const;
     // projector calculus (Gradient::levelGradientMAC, Divergence::levelDivergenceMAC)
-    void macGradient(FluxLevelData& grad, LevelData& phi, bool homog) const;
+    // gradBC 0: the operator's BC holder (ghosts + boundary fluxes); 1: order-2 extrapolated ghosts and no flux
+    // method -- PhysBCUtil::basicGradPressureFuncBC (PhysBCUtil.cpp), the m_gradBC of both reference projectors
+    void macGradient(FluxLevelData& grad, LevelData& phi, bool homog, int gradBC = 0) const;
     void macDivergence(LevelData& div, const FluxLevelData& flux) const;
+    // the projectors' m_divBC on solid walls (PhysBCUtil::uStarFuncBC -> BasicVelocityBCGhostClass, normal component,
+    // face-centred branch of setSideDiriBC, EllipticBCUtils.cpp:41-118): boundary faces of direction d of flux[d] <- 0
+    void wallFluxBC(FluxLevelData& flux) const;
+    // Chombo AMRTools CellToEdge / EdgeToCell (component d of the cell data <-> faces of direction d)
+    void cellToEdge(FluxLevelData& edge, std::array<LevelData, 3>& cell) const;
+    void edgeToCell(std::array<LevelData, 3>& cell, const FluxLevelData& edge) const;
 };
 
 struct MG {
@@ -167,6 +175,10 @@ struct MG {
     void solve(LevelData& phi, const LevelData& rhs, bool zeroPhi, bool forceHomogeneous, SolveStats& st);
     void project(FluxLevelData& vel, LevelData& pressure, double dt, bool zeroPressure, bool forceHomogeneous,
                  SolveStats& st);   // BaseProjector::project, a_velIsFlux = true
+    // BaseProjector<FArrayBox>::project through LevelCCProjector (LevelCCProjector.cpp:156-255); J == nullptr means
+    // a_velIsFlux = true
+    void projectCC(std::array<LevelData, 3>& vel, const LevelData* J, LevelData& pressure, double dt, bool zeroPressure,
+                   bool forceHomogeneous, SolveStats& st);
 };
 
 // Factory: builds all depths (MGnewOp schedule + coarse metrics).

@@ -37,6 +37,8 @@ SYMBOLS = [
     "somar_advect_predict_scalar", "somar_advect_update",
     "somar_leptic_default_params", "somar_leptic_create", "somar_leptic_destroy", "somar_leptic_solve",
     "somar_leptic_level", "somar_norm_noalloc",
+    "somar_level_set_projector_bc", "somar_mac_gradient_bc", "somar_mac_wall_flux_bc", "somar_cc_divergence",
+    "somar_cc_gradient", "somar_project_cc",
 ]
 
 
@@ -530,6 +532,48 @@ class Level:
                 "final_rnorm": st.final_rnorm, "bottom_iters_total": st.bottom_iters_total,
                 "history": [st.history[i] for i in range(st.history_len)], "solve_ms": st.solve_ms,
                 "launches": st.launches}
+
+    @staticmethod
+    def _stats(st):
+        return {"iters": st.iters, "exit_status": st.exitStatus, "initial_rnorm": st.initial_rnorm,
+                "final_rnorm": st.final_rnorm, "bottom_iters_total": st.bottom_iters_total,
+                "history": [st.history[i] for i in range(st.history_len)], "solve_ms": st.solve_ms,
+                "launches": st.launches}
+
+    def set_projector_bc(self, mode: int):
+        """0: the fluxes carry their wall values, gradient with the operator's BCs; 1: the reference projectors' own
+        m_divBC / m_gradBC inside project()"""
+        _ck(lib().somar_level_set_projector_bc(self.h, int(mode)))
+
+    def mac_gradient_bc(self, grad, phi: Field, grad_bc: int, homogeneous=False):
+        L = lib()
+        L.somar_mac_gradient_bc.argtypes = [C.c_void_p] * 5 + [C.c_int, C.c_int]
+        _ck(L.somar_mac_gradient_bc(self.h, *self._h3(grad), phi.h, int(homogeneous), int(grad_bc)))
+
+    def mac_wall_flux_bc(self, flux):
+        L = lib()
+        L.somar_mac_wall_flux_bc.argtypes = [C.c_void_p] * 4
+        _ck(L.somar_mac_wall_flux_bc(self.h, *self._h3(flux)))
+
+    # -- cell-centred projector (LevelCCProjector) ---------------------------------------------------------------
+    def cc_divergence(self, div: Field, vel, J: Field = None, divide_by=0.0):
+        L = lib()
+        L.somar_cc_divergence.argtypes = [C.c_void_p] * 6 + [C.c_double]
+        _ck(L.somar_cc_divergence(self.h, div.h, *self._h3(vel), J.h if J is not None else None, float(divide_by)))
+
+    def cc_gradient(self, grad, phi: Field):
+        L = lib()
+        L.somar_cc_gradient.argtypes = [C.c_void_p] * 5
+        _ck(L.somar_cc_gradient(self.h, *self._h3(grad), phi.h))
+
+    def project_cc(self, vel, pressure: Field, dt: float, J: Field = None, zero_pressure=True,
+                   force_homogeneous=False) -> dict:
+        st = SolveStats()
+        L = lib()
+        L.somar_project_cc.argtypes = [C.c_void_p] * 6 + [C.c_double, C.c_int, C.c_int, C.POINTER(SolveStats)]
+        _ck(L.somar_project_cc(self.h, *self._h3(vel), J.h if J is not None else None, pressure.h, float(dt),
+                               int(zero_pressure), int(force_homogeneous), C.byref(st)))
+        return self._stats(st)
 
     # -- leptic-solver sweeps ---------------------------------------------------------------------------------
     def leptic_vertical_solve(self, phi: Field, rhs: Field, lo_bc: int, hi_bc: int, dz_crse=None, bdry_lo=None,

@@ -165,6 +165,64 @@ int somar_project(SomarLevel* L, SomarField* vx, SomarField* vy, SomarField* vz,
     return project(L, v, pressure, dt, zero_pressure != 0, force_homogeneous != 0, stats);
 }
 
+int somar_level_set_projector_bc(SomarLevel* L, int mode) {
+    if (!L) { set_error("null level"); return SOMAR_ERR_ARG; }
+    if (mode != 0 && mode != 1) { set_error("projector BC mode must be 0 or 1"); return SOMAR_ERR_ARG; }
+    L->projector_bc = mode;
+    return SOMAR_OK;
+}
+int somar_mac_gradient_bc(SomarLevel* L, SomarField* gx, SomarField* gy, SomarField* gz, SomarField* phi, int homogeneous,
+                          int grad_bc) {
+    CHECK_FINAL(L); CHECK_F(phi, L, 0);
+    if (grad_bc != 0 && grad_bc != 1) { set_error("grad_bc must be 0 or 1"); return SOMAR_ERR_ARG; }
+    SomarField* g[3] = {gx, gy, gz};
+    int rc = check_faces(L, g);
+    if (rc) return rc;
+    for (int d = 0; d < L->desc.dim; ++d) if (g[d] == phi) { set_error("macGradient: output aliases phi"); return SOMAR_ERR_ARG; }
+    return op_mac_gradient(L, g, phi, homogeneous != 0, 1.0, false, grad_bc);
+}
+int somar_mac_wall_flux_bc(SomarLevel* L, SomarField* fx, SomarField* fy, SomarField* fz) {
+    CHECK_FINAL(L);
+    SomarField* f[3] = {fx, fy, fz};
+    int rc = check_faces(L, f);
+    if (rc) return rc;
+    return op_wall_flux_bc(L, f);
+}
+// ---- cell-centred projector (LevelCCProjector) -----------------------------------------------------------
+int somar_cc_divergence(SomarLevel* L, SomarField* div, SomarField* ux, SomarField* uy, SomarField* uz, SomarField* J,
+                        double divide_by) {
+    CHECK_FINAL(L); CHECK_F(div, L, 0);
+    if (J) CHECK_F(J, L, 0);
+    SomarField* u[3] = {ux, uy, uz};
+    int rc = check_faces(L, u);
+    if (rc) return rc;
+    for (int d = 0; d < L->desc.dim; ++d)
+        if (u[d] == div || u[d] == J) { set_error("ccDivergence: a velocity component aliases div or J"); return SOMAR_ERR_ARG; }
+    if (J == div) { set_error("ccDivergence: J aliases div"); return SOMAR_ERR_ARG; }
+    return op_cc_divergence(L, div, u, J, divide_by);
+}
+int somar_cc_gradient(SomarLevel* L, SomarField* gx, SomarField* gy, SomarField* gz, SomarField* phi) {
+    CHECK_FINAL(L); CHECK_F(phi, L, 0);
+    SomarField* g[3] = {gx, gy, gz};
+    int rc = check_faces(L, g);
+    if (rc) return rc;
+    for (int d = 0; d < L->desc.dim; ++d) if (g[d] == phi) { set_error("ccGradient: output aliases phi"); return SOMAR_ERR_ARG; }
+    return op_cc_gradient(L, g, phi);
+}
+int somar_project_cc(SomarLevel* L, SomarField* ux, SomarField* uy, SomarField* uz, SomarField* J, SomarField* pressure,
+                     double dt, int zero_pressure, int force_homogeneous, SomarSolveStats* stats) {
+    CHECK_FINAL(L); CHECK_F(pressure, L, 0);
+    if (J) CHECK_F(J, L, 0);
+    if (!stats) { set_error("null stats"); return SOMAR_ERR_ARG; }
+    SomarField* u[3] = {ux, uy, uz};
+    int rc = check_faces(L, u);
+    if (rc) return rc;
+    for (int d = 0; d < L->desc.dim; ++d)
+        if (u[d] == pressure || u[d] == J) { set_error("projectCC: a velocity component aliases the pressure or J"); return SOMAR_ERR_ARG; }
+    if (J == pressure) { set_error("projectCC: J aliases the pressure"); return SOMAR_ERR_ARG; }
+    return project_cc(L, u, J, pressure, dt, zero_pressure != 0, force_homogeneous != 0, stats);
+}
+
 // ---- leptic-solver sweeps (SURVEY 8(a) LevelLepticSolver row) ---------------------------------------------
 #define CHECK_F0(f, L) do { if (!(f) || (f)->lev != (L) || (f)->depth != 0) { set_error("field does not belong to depth 0 of this level"); return SOMAR_ERR_ARG; } } while (0)
 int somar_leptic_vertical_solve(SomarLevel* L, SomarField* phi, SomarField* rhs, int lo_bc, int hi_bc, double dz_crse,

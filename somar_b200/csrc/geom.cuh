@@ -16,7 +16,10 @@
 
 namespace somar {
 
-enum { BC_NONE = -1, BC_NEUM = 0, BC_DIRI = 1, BC_PERIODIC = 2 };
+enum { BC_NONE = -1, BC_NEUM = 0, BC_DIRI = 1, BC_PERIODIC = 2,
+       // order-2 extrapolated ghost, no flux method: EllipticExtrapBCGhostClass(2), the reference projectors' gradient BC
+       // (PhysBCUtil::basicGradPressureFuncBC).  Only the gradient kernels of projector.cu run with it.
+       BC_EXTRAP2 = 4 };
 
 struct Geom {
     int n[3];        // rank-local valid cells

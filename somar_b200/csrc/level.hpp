@@ -102,6 +102,7 @@ struct SomarLevel {
     std::vector<SomarField*> awork;    // advection: WMinus/WPlus/WHalf scratch (depth 0, allocated on first use)
     double* zeroPlane = nullptr;       // off0 + sz zeros of depth 0: the input of a relaxation that starts from phi = 0
     SomarField* pwork = nullptr;       // projector: the divergence / right-hand side (depth 0)
+    int projector_bc = 0;              // somar_level_set_projector_bc: 0 operator BCs (round 1), 1 the reference projectors' m_divBC / m_gradBC
     double bottomMetric = 0.0, bottomEps = 1e-6;
     double convergenceMetric = 0.0;    // MappedAMRMultiGrid::m_convergenceMetric (0: the initial residual norm)
     int bottom_iters_total = 0;
@@ -194,7 +195,13 @@ bool line_compact_usable(const SomarLevel* L, const Depth& dp);
 int line_compact_relax(SomarLevel* L, Depth& dp, double* phi, const double* rhs, int iters, bool coefStale, int profPhase);
 void line_compact_free(Depth& dp);
 // projector.cu
-int op_mac_gradient(SomarLevel* L, SomarField* const grad[3], SomarField* phi, bool homog, double scale, bool accumulate);
+int op_mac_gradient(SomarLevel* L, SomarField* const grad[3], SomarField* phi, bool homog, double scale, bool accumulate,
+                    int gradBC = 0);
+int op_wall_flux_bc(SomarLevel* L, SomarField* const flux[3]);
+int op_cc_divergence(SomarLevel* L, SomarField* div, SomarField* const vel[3], SomarField* J, double divideBy);
+int op_cc_gradient(SomarLevel* L, SomarField* const grad[3], SomarField* phi);
+int project_cc(SomarLevel* L, SomarField* const vel[3], SomarField* J, SomarField* pressure, double dt, bool zeroPressure,
+               bool forceHomog, SomarSolveStats* st);
 int op_mac_divergence(SomarLevel* L, SomarField* div, const SomarField* const flux[3], double divideBy);
 int project(SomarLevel* L, SomarField* const vel[3], SomarField* pressure, double dt, bool zeroPressure, bool forceHomog,
             SomarSolveStats* st);

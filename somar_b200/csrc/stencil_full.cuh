@@ -173,7 +173,12 @@ __device__ __forceinline__ double face_flux_full(const Geom& g, const Metric& m,
     double nb;
     if (atBdry) {  // Dirichlet ghost
         const double farV = S ? phi[c - st] : phi[c + st];
-        nb = diri_ghost_val(pc, farV, homog ? 0.0 : g.bcval[A][S], g.diriOrder);
+        if (g.bc[A][S] == BC_EXTRAP2) {   // ELLIPTICEXTRAPBCGHOST order 2 (projector gradients only)
+            const double far2 = S ? phi[c - 2 * st] : phi[c + 2 * st];
+            nb = 3.0 * (pc - farV) + far2;
+        } else {
+            nb = diri_ghost_val(pc, farV, homog ? 0.0 : g.bcval[A][S], g.diriOrder);
+        }
     } else {
         nb = S ? phi[c + st] : phi[c - st];
     }

@@ -47,7 +47,12 @@ __device__ __forceinline__ double face_flux_ortho(const Geom& g, const double* _
         if (bct == BC_NEUM) return (homog ? 0.0 : g.bcval[d][S]) * g.beta;
         // Dirichlet: ghost from the interior values
         const double farV = S ? phi[c - st] : phi[c + st];
-        nb = diri_ghost_val(pc, farV, homog ? 0.0 : g.bcval[d][S], g.diriOrder);
+        if (bct == BC_EXTRAP2) {   // ELLIPTICEXTRAPBCGHOST order 2, EllipticBCUtilsF.ChF:165-173
+            const double far2 = S ? phi[c - 2 * st] : phi[c + 2 * st];
+            nb = 3.0 * (pc - farV) + far2;
+        } else {
+            nb = diri_ghost_val(pc, farV, homog ? 0.0 : g.bcval[d][S], g.diriOrder);
+        }
     } else {
         nb = S ? phi[c + st] : phi[c - st];
     }
