@@ -281,9 +281,11 @@ int somar_leptic_accum_div(SomarLevel* lev, SomarField* flat_rhs, const SomarFie
  *      excess bookkeeping, the batched vertical solves, the horizontal right-hand side (computeHorizRHS, :981-1097) and
  *      multigrid solve, the new residual, the multigrid fall-back at the last order when the iteration hangs, and
  *      phi += sum of corrections.  `homogeneous` is setHomogeneous (:444).
- * Scope: one level without a coarser one, diagonal metric, one rank or y-slab ranks (the vertical level shares the
+ * Scope: one level without a coarser one; a diagonal metric on one rank or y-slab ranks (the vertical level shares the
  * level's communicator, the small horizontal level is replicated and its rows all-gathered: destroy the solver BEFORE
- * the level), vertical sides Neumann or Dirichlet; with a
+ * the level), a full (terrain-following) metric on one rank (3-D: levelVertHorizGradient :1107-1176, MAPPEDMACGRAD in
+ * computeHorizRHS, a 2-D full-metric horizontal level, a horizontal solve at every order); vertical sides Neumann or
+ * Dirichlet; with a
  * horizontal solve the level must be 3-D with non-periodic horizontal directions (the reference leaves the boundary
  * faces of a periodic direction unset in computeHorizRHS).  Anything else is an error, never a CPU path. */
 typedef struct SomarLepticParams {
@@ -319,15 +321,18 @@ int somar_leptic_level(SomarLeptic* s, int which, SomarLevel** out);
  * whalf_d (face fields, out): time-centred face states, times adv_vel_d when return_flux (the flux whose
  * somar_mac_divergence gives the advective update, AMRNavierStokesAdvancePPM.cpp:379-620).  w_old, source (may be NULL),
  * old_vel_d (cell-centred components) and cc_j (cell-centred J, LevelGeometry::fill_J) are cell fields, adv_vel_d face
- * fields.  Built for FULLY PERIODIC single-rank levels, normal_pred_order 2 (PPM), both limiter families; anything else
- * returns SOMAR_ERR_ARG (non-periodic sides need the physics BC holders, which are outside this library). */
+ * fields.  Built for FULLY PERIODIC single-rank levels, the three normal predictors (CTU, PLM, PPM) and both limiter
+ * families; anything else returns SOMAR_ERR_ARG (non-periodic sides need the physics BC holders, which are outside this
+ * library). */
 typedef struct SomarAdvectParams {
-    int normal_pred_order;        /* ProblemContext normalPredOrder{Vel,Scal}: 2 = PPM */
+    int normal_pred_order;        /* ProblemContext normalPredOrder{Vel,Scal}: 0 = CTU, 1 = PLM, 2 = PPM */
     int use_limiting;             /* useLimiting{Vel,Scal}: van Leer + PPM limiters */
     int use_high_order_limiter;   /* useHighOrderLimiter{Vel,Scal}: FourthInterpFaces + CheckCubicLimiterF
                                      (MappedGodunovUtilitiesF.ChF:517-566,611-745) instead of van Leer/PPMLimiterF */
     int use_upwinding;            /* useUpwinding{Vel,Scal}: 1 = RiemannSolver, 0 = AvgStates */
     int return_flux;              /* a_returnFlux */
+    int use_fourth_order_slopes;  /* useFourthOrderSlopes{Vel,Scal}: PLM only (FourthSlopeDiffsF + the van Leer limiter on
+                                     one-sided differences, AdvectUtil.cpp:1094-1128) */
 } SomarAdvectParams;
 int somar_advect_predict_scalar(SomarLevel* lev, SomarField* whalf_x, SomarField* whalf_y, SomarField* whalf_z,
                                 const SomarField* w_old, const SomarField* source, const SomarField* old_vel_x,

@@ -17,8 +17,9 @@ so each stage is one whole-domain array statement; numpy evaluates them elementw
 contraction, in the Fortran's operation order.  A level of several boxes gives the same numbers (every stage is a
 pure stencil on exchanged ghosts), so the restatement works on global arrays with wrapped indices.
 
+All three normal predictors (normalPredOrder 0 CTU, 1 PLM with or without fourth-order slopes, 2 PPM).
 NOT covered (the device path rejects them too): non-periodic sides (the physics BC holders scalarRiemannBC /
-scalarSlopeBC), normalPredOrder 0/1 (CTU/PLM).
+scalarSlopeBC; the reference itself carries TODO() markers there, AdvectUtil.cpp:713,780,874,905).
 PARITY UNPINNED against reference output (the reference cannot be built here and ships no vectors); pinned by
 tests/test_advect.py to exactness properties of the scheme (constants, uniform translation, conservation).
 
@@ -135,6 +136,56 @@ def ppm_normal_pred(W, J, vel_d, d, dtbydx, use_limiting, high_order=False):
     return new_m + W, new_p + W
 
 
+TWO3RD = 2.0 / 3.0     # Chombo CONSTANTS.H "two3rd" (BaseTools; third party, not under /root/reference)
+
+
+def van_leer_limiter(dWc, dWl, dWr):
+    """VanLeerLimiterF, MappedGodunovUtilitiesF.ChF:151-186"""
+    lim = np.minimum(2.0 * np.abs(dWl), 2.0 * np.abs(dWr))
+    lim = np.minimum(lim, np.abs(dWc))
+    return np.where(dWl * dWr < 0.0, 0.0, lim * np.copysign(1.0, dWl))
+
+
+def plm_normal_pred(W, vel_d, d, dtbydx, use_limiting, fourth_order_slopes=False):
+    """MappedAdvectionUtil::PLMNormalPred, AdvectUtil.cpp:1066-1152 -> FourthSlopeDiffsF (MappedGodunovUtilitiesF.ChF:
+    96-146), oneSidedDifferences / slopeLimiter (MappedGodunovUtilities.cpp:143-171,240-262), PLMNormalPredF (:266-311).
+    The second limiter pass is the reference's, quirk included: WITHOUT fourth-order slopes it is handed the zeroed
+    a_WMinus / a_WPlus as one-sided differences (AdvectUtil.cpp:1116-1128), so `use_limiting` alone flattens every slope
+    and the predictor degenerates to CTU.  m_util's own m_highOrderLimiter is never set (MappedGodunovUtilities.cpp:15)."""
+    if fourth_order_slopes:
+        dWvL = van_leer_slopes(W, d, use_limiting)
+        dWR = _sh(W, d, 1) - _sh(dWvL, d, 1) * 0.25
+        dWL = _sh(W, d, -1) + _sh(dWvL, d, -1) * 0.25
+        dW = TWO3RD * (dWR - dWL)
+        dWm = W - _sh(W, d, -1)
+        dWp = _sh(W, d, 1) - W
+    else:
+        dW = van_leer_slopes(W, d, use_limiting)
+        dWm = np.zeros_like(W)
+        dWp = np.zeros_like(W)
+    if use_limiting or fourth_order_slopes:
+        dW = van_leer_limiter(dW, dWm, dWp)
+    lam = vel_d
+    lmin = np.minimum(lam, 0.0)
+    lmax = np.maximum(lam, 0.0)
+    lo_fac = np.where(lam < 0.0, lam, lmin)     # lambdaK < 0: lambdaK, else lmin
+    hi_fac = np.where(lam > 0.0, lam, lmax)     # lambdaK > 0: lambdaK, else lmax
+    dm = dW * (-0.5) * (1.0 + dtbydx * lo_fac)
+    dp = dW * 0.5 * (1.0 - dtbydx * hi_fac)
+    return dm + W, dp + W
+
+
+def normal_pred(W, J, vel_d, d, dtbydx, use_limiting, high_order, order, fourth_order_slopes):
+    """the switch on m_normalPredOrder, AdvectUtil.cpp:660-692"""
+    if order == 0:      # CTUNormalPred, AdvectUtil.cpp:1043-1057: straight copies
+        return W.copy(), W.copy()
+    if order == 1:
+        return plm_normal_pred(W, vel_d, d, dtbydx, use_limiting, fourth_order_slopes)
+    if order == 2:
+        return ppm_normal_pred(W, J, vel_d, d, dtbydx, use_limiting, high_order)
+    raise ValueError("normal predictor order must be 0 (CTU), 1 (PLM) or 2 (PPM)")
+
+
 def riemann(w_plus, w_minus, adv_vel_d, d, upwind):
     """RiemannSolver / AvgStates at face f: left state = WPlus of cell f-1, right state = WMinus of cell f"""
     wl = _sh(w_plus, d, -1)
@@ -150,13 +201,14 @@ def quasilinear_update(w_half_d, vel_d, scale, d):
 
 
 def predict_scalar(W, J, old_vel, adv_vel, dt, dx, dim, source=None, use_limiting=False, use_upwinding=True,
-                   return_flux=True, high_order=False):
+                   return_flux=True, high_order=False, normal_pred_order=2, fourth_order_slopes=False):
     """old_vel[d]: cell-centred velocity components; adv_vel[d]: face-centred advecting velocity of direction d.
     Returns the list of face-centred, time-centred states (times adv_vel when return_flux)."""
     dtondx = [dt / dx[d] for d in range(dim)]
     wm, wp, wh1 = [], [], []
     for d in range(dim):
-        m, p = ppm_normal_pred(W, J, old_vel[d], d, dt / dx[d], use_limiting, high_order)
+        m, p = normal_pred(W, J, old_vel[d], d, dt / dx[d], use_limiting, high_order, normal_pred_order,
+                           fourth_order_slopes)
         if source is not None:
             m = m + source * (0.5 * dt)
             p = p + source * (0.5 * dt)

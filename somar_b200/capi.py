@@ -66,7 +66,7 @@ class SolveStats(C.Structure):
 
 class AdvectParams(C.Structure):
     _fields_ = [("normal_pred_order", C.c_int), ("use_limiting", C.c_int), ("use_high_order_limiter", C.c_int),
-                ("use_upwinding", C.c_int), ("return_flux", C.c_int)]
+                ("use_upwinding", C.c_int), ("return_flux", C.c_int), ("use_fourth_order_slopes", C.c_int)]
 
 
 class LepticParams(C.Structure):
@@ -167,8 +167,9 @@ class LepticSolver:
                 "res_norms": [st.res_norms[i] for i in range(st.num_res_norms)], "solve_ms": st.solve_ms,
                 "launches": st.launches}
 
-    def horiz_metric(self):
-        """(J g^00, J g^11) of the flattened level, as (ny, nx+1) and (ny+1, nx) arrays (None without one)"""
+    def horiz_metric(self, full=False):
+        """(J g^00, J g^11) of the flattened level, as (ny, nx+1) and (ny+1, nx) arrays (None without one); full=True:
+        both components per face direction"""
         hv = C.c_void_p()
         _ck(lib().somar_leptic_level(self.h, 1, C.byref(hv)))
         if not hv.value:
@@ -178,6 +179,8 @@ class LepticSolver:
         j1 = np.zeros((2, ny + 1, nx))
         _ck(lib().somar_level_get_metric(hv, 0, j0.ctypes.data_as(C.c_void_p), j1.ctypes.data_as(C.c_void_p), None, None,
                                          None))
+        if full:
+            return j0, j1           # j0[b] = J g^{0b} on x faces, j1[b] = J g^{1b} on y faces
         return j0[0], j1[1]
 
     def destroy(self):
@@ -605,9 +608,9 @@ class Level:
     # -- advection predictor --------------------------------------------------------------------------------
     def advect_predict_scalar(self, whalf, w_old: Field, old_vel, adv_vel, cc_j: Field, dt: float, source=None,
                               normal_pred_order=2, use_limiting=False, use_high_order_limiter=False, use_upwinding=True,
-                              return_flux=True):
+                              return_flux=True, use_fourth_order_slopes=False):
         prm = AdvectParams(int(normal_pred_order), int(use_limiting), int(use_high_order_limiter), int(use_upwinding),
-                           int(return_flux))
+                           int(return_flux), int(use_fourth_order_slopes))
         L = lib()
         L.somar_advect_predict_scalar.argtypes = [C.c_void_p] * 13 + [C.c_double, C.POINTER(AdvectParams)]
         _ck(L.somar_advect_predict_scalar(self.h, *self._h3(whalf), w_old.h, source.h if source is not None else None,

@@ -14,8 +14,9 @@
 // index the rank's brick with wrapped indices (no ghost cells are read); the final states are also written to the
 // periodic image in the first ghost slot, where somar_mac_divergence expects the high face of the last cell.
 // The arithmetic is the Fortran's, statement for statement (-fmad=false): bit-identical to oracle/advect_ref.py.
-// Not built: non-periodic sides (they need the physics BC holders scalarRiemannBC / scalarSlopeBC), CTU / PLM normal
-// predictors, more than one rank -- the entry point rejects them.
+//   k_adv_normal_low   the other two normal predictors: CTUNormalPred (:1043-1057) and PLMNormalPred (:1066-1152)
+// Not built: non-periodic sides (they need the physics BC holders scalarRiemannBC / scalarSlopeBC), more than one rank
+// -- the entry point rejects them.
 // HBM-bound streaming passes (18 launches in 3-D); intermediate states live in scratch fields, not yet fused.
 #include "level.hpp"
 
@@ -200,6 +201,59 @@ __global__ void __launch_bounds__(ATPB) k_adv_normal(const AGeom g, int d, const
     wplus[c] = np;
 }
 
+// MappedAdvectionUtil::PLMNormalPred (AdvectUtil.cpp:1066-1152) on a periodic level: van Leer slopes, or FOURTH:
+// FourthSlopeDiffsF (MappedGodunovUtilitiesF.ChF:96-146) from the van Leer slopes of the two neighbours with the one-sided
+// differences as limiter inputs; the second limiter pass of :1126-1128 (quirk included: without FOURTH it is handed
+// zeros as one-sided differences, so use_limiting alone flattens every slope); PLMNormalPredF (:266-311), one slope;
+// "+= W"; the half-step source.  ORDER 0 is CTUNormalPred (:1043-1057): both states are W.
+template <bool LIM, bool FOURTH, int ORDER>
+__global__ void __launch_bounds__(ATPB) k_adv_normal_low(const AGeom g, int d, const double* __restrict__ W,
+                                                         const double* __restrict__ vel,
+                                                         const double* __restrict__ src, double srcScale, double dtbydx,
+                                                         double* __restrict__ wminus, double* __restrict__ wplus) {
+    int i, j, k;
+    if (!acell(g, i, j, k)) return;
+    const long long c = aidx(g, i, j, k);
+    const double w = W[c];
+    double nm = w, np = w;
+    if (ORDER == 1) {
+        const double wm1 = W[aoff(g, i, j, k, d, -1)], wp1 = W[aoff(g, i, j, k, d, 1)];
+        double dW, dWm = 0.0, dWp = 0.0;
+        if (FOURTH) {
+            const double wm2 = W[aoff(g, i, j, k, d, -2)], wp2 = W[aoff(g, i, j, k, d, 2)];
+            const double vlP = vl_slope<LIM>(w, wp1, wp2);
+            const double vlM = vl_slope<LIM>(wm2, wm1, w);
+            const double dWR = wp1 - vlP * 0.25;
+            const double dWL = wm1 + vlM * 0.25;
+            dW = (2.0 / 3.0) * (dWR - dWL);
+            dWm = w - wm1;
+            dWp = wp1 - w;
+        } else {
+            dW = vl_slope<LIM>(wm1, w, wp1);
+        }
+        if (LIM || FOURTH) {   // VanLeerLimiterF
+            double lim = fmin(2.0 * fabs(dWm), 2.0 * fabs(dWp));
+            lim = fmin(lim, fabs(dW));
+            dW = (dWm * dWp < 0.0) ? 0.0 : lim * copysign(1.0, dWm);
+        }
+        const double lam = vel[c];
+        const double lmin = fmin(lam, 0.0), lmax = fmax(lam, 0.0);
+        const double loFac = (lam < 0.0) ? lam : lmin;
+        const double hiFac = (lam > 0.0) ? lam : lmax;
+        const double dm = dW * (-0.5) * (1.0 + dtbydx * loFac);
+        const double dp = dW * 0.5 * (1.0 - dtbydx * hiFac);
+        nm = dm + w;
+        np = dp + w;
+    }
+    if (src) {
+        const double s = src[c] * srcScale;
+        nm = nm + s;
+        np = np + s;
+    }
+    wminus[c] = nm;
+    wplus[c] = np;
+}
+
 // up to two transverse corrections  A = scale * u_d2 * (WHalf(i + e_d2) - WHalf(i))  added to both states, in order
 struct ACorr {
     const double* wh[2];
@@ -254,8 +308,9 @@ int advect_predict_scalar(SomarLevel* L, SomarField* const whalf[3], const Somar
                       "scalarRiemannBC / scalarSlopeBC, AdvectUtil.cpp:715-740)");
             return SOMAR_ERR_ARG;
         }
-    if (prm->normal_pred_order != 2) { set_error("predictScalar: only the PPM normal predictor (order 2) is built"); return SOMAR_ERR_ARG; }
-    if (prm->use_high_order_limiter)
+    const int order = prm->normal_pred_order;
+    if (order < 0 || order > 2) { set_error("predictScalar: the normal predictor order must be 0 (CTU), 1 (PLM) or 2 (PPM)"); return SOMAR_ERR_ARG; }
+    if (order == 2 && prm->use_high_order_limiter)
         for (int d = 0; d < nd; ++d)
             if (G.n[d] < 4) { set_error("predictScalar: the high-order limiter needs at least 4 cells per direction"); return SOMAR_ERR_ARG; }
     AGeom g;
@@ -281,6 +336,7 @@ int advect_predict_scalar(SomarLevel* L, SomarField* const whalf[3], const Somar
     cudaStream_t st = L->cx.stream;
     const bool lim = prm->use_limiting != 0;
     const bool ho = prm->use_high_order_limiter != 0;
+    const bool fourth = prm->use_fourth_order_slopes != 0;
     const int up = prm->use_upwinding != 0;
     double dtondx[3];
     for (int d = 0; d < nd; ++d) dtondx[d] = dt / G.dx[d];
@@ -294,13 +350,22 @@ int advect_predict_scalar(SomarLevel* L, SomarField* const whalf[3], const Somar
             k_adv_normal<LIM_, HO_><<<nb, ATPB, 0, st>>>(g, d, wold->p, wface, oldVel[d]->p, src, 0.5 * dt, dtondx[d], \
                                                          wm[d], wp[d]);                                              \
         } while (0)
-        if (lim && ho) ADV_STAGE(true, true);
+#define ADV_LOW(LIM_, FOURTH_, ORDER_)                                                                               \
+        k_adv_normal_low<LIM_, FOURTH_, ORDER_><<<nb, ATPB, 0, st>>>(g, d, wold->p, oldVel[d]->p, src, 0.5 * dt,      \
+                                                                     dtondx[d], wm[d], wp[d])
+        if (order == 0) ADV_LOW(false, false, 0);
+        else if (order == 1 && lim && fourth) ADV_LOW(true, true, 1);
+        else if (order == 1 && lim) ADV_LOW(true, false, 1);
+        else if (order == 1 && fourth) ADV_LOW(false, true, 1);
+        else if (order == 1) ADV_LOW(false, false, 1);
+        else if (lim && ho) ADV_STAGE(true, true);
         else if (lim) ADV_STAGE(true, false);
         else if (ho) ADV_STAGE(false, true);
         else ADV_STAGE(false, false);
 #undef ADV_STAGE
+#undef ADV_LOW
         k_adv_riemann<<<nb, ATPB, 0, st>>>(g, d, wp[d], wm[d], advVel[d]->p, none, up, 0, 0, wh1[d]);
-        L->cx.launches += 3;
+        L->cx.launches += (order == 2) ? 3 : 2;
     }
     if (nd == 3) {
         for (int d1 = 0; d1 < 3; ++d1)

@@ -15,10 +15,13 @@
 // Flat fields (excess, boundary data, horizontal right-hand side) are SomarFields of the vertical level that own only
 // the planes the flat kernels touch.  Each level has its own stream; the driver is host-sequenced (it reads a norm
 // back every order, as the reference does), so hand-overs between levels are stream synchronisations.
-// Scope: diagonal metric, one level, y-slab ranks (the vertical level borrows the level's communicator; the small
-// horizontal level is replicated on every rank, its rows all-gathered); see include/somar_b200.h.
+// Scope: one level; diagonal metric on one rank or y-slab ranks (the vertical level borrows the level's communicator; the
+// small horizontal level is replicated on every rank, its rows all-gathered); full (terrain-following) metric on one
+// rank: k_horiz_rhs_full, k_vert_horiz_grad, a 2-D full-metric horizontal level, a horizontal solve at every order; see
+// include/somar_b200.h.
 #include "level.hpp"
 #include "cells.cuh"
+#include "stencil_full.cuh"
 #include <cmath>
 #include <cstring>
 #include <algorithm>
@@ -105,6 +108,110 @@ __global__ void __launch_bounds__(QTPB) k_horiz_rhs(const Geom g, double* __rest
     r = r + (fyh - fyl) * (-1.0 / g.dx[1]);
     if (excess) r = r + excess[c0] * exScale;
     rhs[c0] = r;
+}
+
+// ---- full (terrain-following) metric ------------------------------------------------------------------------
+// phi as computeHorizRHS sees it from the box of the column being processed (:1004-1014): extrapAllGhosts
+// (ExtrapolationUtils.cpp:388-421) extrapolates EVERY ghost of every box with order 2, direction by direction on a
+// growing box (x innermost), BEFORE the exchange; the exchange (faces, then corners) overwrites the ghosts that lie
+// inside the domain with the neighbours' cells; what lies outside the domain keeps the per-box extrapolation -- in
+// every direction in which it is outside the BOX, so an edge ghost next to a box interface depends on the box layout.
+template <int ND>
+struct LepticView {
+    const Geom& g;
+    const double* __restrict__ phi;
+    BoxOf b;
+    __device__ LepticView(const Geom& g_, const double* __restrict__ phi_, int i, int j, int k)
+        : g(g_), phi(phi_), b(box_of<ND>(g_, i, j, k)) {}
+    __device__ double ex(int p0, int p1, int p2) const {
+        const int p[3] = {p0, p1, p2};
+        int o[3] = {0, 0, 0}, ord[3] = {0, 0, 0};
+        bool outBox = false, outDom = false;
+#pragma unroll
+        for (int d = 0; d < ND; ++d) {
+            if (p[d] < b.lo[d]) o[d] = -1;
+            else if (p[d] > b.hi[d]) o[d] = 1;
+            if (o[d] != 0) {
+                outBox = true;
+                ord[d] = 2;
+            }
+            const int gq = p[d] + g.g0[d];
+            if (gq < 0 || gq >= g.gn[d]) outDom = true;
+        }
+        if (!outBox || !outDom) return phi[g.idx(p0, p1, p2)];
+        return ExRec<ND - 1>::eval(g, phi, p0, p1, p2, o, ord);
+    }
+};
+
+// computeHorizRHS, full metric, one thread per column: the statements of k_horiz_rhs with MAPPEDMACGRAD
+// (DivCurlGradF.ChF:87-147: normal difference + the four-point transverse differences in the other two directions) for the
+// face gradients.  Both faces of a column are formed with the column's own box view, as the reference forms every face
+// once per box.
+__global__ void __launch_bounds__(QTPB) k_horiz_rhs_full(const Geom g, const Metric m, double* __restrict__ rhs,
+                                                         const double* __restrict__ phi,
+                                                         const double* __restrict__ excess, double exScale,
+                                                         double dzScale) {
+    const int i = blockIdx.x * QTPB + threadIdx.x;
+    const int j = blockIdx.y;
+    if (i >= g.n[0]) return;
+    const int gi = g.g0[0] + i, gj = g.g0[1] + j;
+    const bool xl = gi >= 1, xh = gi + 1 <= g.gn[0] - 1, yl = gj >= 1, yh = gj + 1 <= g.gn[1] - 1;
+    double fxl = 0.0, fxh = 0.0, fyl = 0.0, fyh = 0.0;
+    const long long c0 = g.idx(i, j, 0);
+    const int nz = g.n[2];
+    const LepticView<3> v(g, phi, i, j, 0);
+    for (int k = 0; k < nz; ++k) {
+        const long long c = c0 + g.sz * k;
+        const double p = phi[c];
+        if (xl) fxl = fxl + face_flux_full<3, 0, 0>(g, m, v, phi, i, j, k, c, false, true, p) * dzScale;
+        if (xh) fxh = fxh + face_flux_full<3, 0, 1>(g, m, v, phi, i, j, k, c, false, true, p) * dzScale;
+        if (yl) fyl = fyl + face_flux_full<3, 1, 0>(g, m, v, phi, i, j, k, c, false, true, p) * dzScale;
+        if (yh) fyh = fyh + face_flux_full<3, 1, 1>(g, m, v, phi, i, j, k, c, false, true, p) * dzScale;
+    }
+    double r = 0.0;
+    r = r + (fxh - fxl) * (-1.0 / g.dx[0]);
+    r = r + (fyh - fyl) * (-1.0 / g.dx[1]);
+    if (excess) r = r + excess[c0] * exScale;
+    rhs[c0] = r;
+}
+
+// levelVertHorizGradient (:1107-1176) + LEPTICVERTHORIZGRAD (LevelLepticSolverF.ChF:74-122): on the lower and the upper
+// domain face of every column,  scale * sum_m J g^{z m} d_m phi  from the four-point differences of the ghost-side and
+// the valid-side plane.  ExtrapolateFaceAndCopy(phi, phi, FAB box & domain, z, side, 2) has just rewritten the ghost-side
+// plane (order 2 from the column) and, in BOTH planes, the cells beyond the horizontal domain sides (order 2 along
+// the plane); cells across box interfaces are the neighbours' (the residual evaluation that closed the previous order
+// exchanged phi).  One thread per column, both sides.
+__global__ void __launch_bounds__(QTPB) k_vert_horiz_grad(const Geom g, const double* __restrict__ jgz0,
+                                                          const double* __restrict__ jgz1, const double* __restrict__ phi,
+                                                          double* __restrict__ flatLo, double* __restrict__ flatHi,
+                                                          double scale) {
+    const int i = blockIdx.x * QTPB + threadIdx.x;
+    const int j = blockIdx.y;
+    if (i >= g.n[0]) return;
+    const double dxinv0 = scale * 0.25 / g.dx[0];
+    const double dxinv1 = scale * 0.25 / g.dx[1];
+    for (int side = 0; side < 2; ++side) {
+        const int k0 = side ? g.n[2] - 1 : 0, ks = side ? -1 : 1;
+        // plane value at an in-domain column: which = 0 the ghost-side plane (extrapolated), 1 the valid-side plane
+        auto plane = [&](int ii, int jj, int which) {
+            const long long c = g.idx(ii, jj, k0);
+            if (which) return phi[c];
+            return 3.0 * (phi[c] - phi[c + ks * g.sz]) + phi[c + 2 * ks * g.sz];
+        };
+        // the same, one column beyond a horizontal domain side: order 2 along the plane
+        auto at = [&](int ii, int jj, int which) {
+            const int gi = ii + g.g0[0], gj = jj + g.g0[1];
+            if (gi < 0) return 3.0 * (plane(ii + 1, jj, which) - plane(ii + 2, jj, which)) + plane(ii + 3, jj, which);
+            if (gi >= g.gn[0]) return 3.0 * (plane(ii - 1, jj, which) - plane(ii - 2, jj, which)) + plane(ii - 3, jj, which);
+            if (gj < 0) return 3.0 * (plane(ii, jj + 1, which) - plane(ii, jj + 2, which)) + plane(ii, jj + 3, which);
+            if (gj >= g.gn[1]) return 3.0 * (plane(ii, jj - 1, which) - plane(ii, jj - 2, which)) + plane(ii, jj - 3, which);
+            return plane(ii, jj, which);
+        };
+        const long long f = g.idx(i, j, side ? g.n[2] : 0);     // the domain face (the high one sits in the first ghost slot)
+        const double v = jgz0[f] * dxinv0 * (at(i + 1, j, 0) - at(i - 1, j, 0) + at(i + 1, j, 1) - at(i - 1, j, 1)) +
+                         jgz1[f] * dxinv1 * (at(i, j + 1, 0) - at(i, j - 1, 0) + at(i, j + 1, 1) - at(i, j - 1, 1));
+        (side ? flatHi : flatLo)[g.idx(i, j, 0)] = v;
+    }
 }
 
 // dense out(i, j) = 0 + sum_k jg(i, j, k) * scale over (nx + ex) x (ny + ey) faces
@@ -231,7 +338,15 @@ int somar_leptic_create(SomarLevel* L, const SomarLepticParams* prm, SomarLeptic
     if (!L->finalized) { set_error("leptic: the level is not finalized"); return SOMAR_ERR_ARG; }
     const SomarLevelDesc& D = L->desc;
     const int nd = D.dim, vd = nd - 1;
-    if (!D.is_diagonal) { set_error("leptic solver: diagonal metrics only (levelVertHorizGradient / MAPPEDMACGRAD not built)"); return SOMAR_ERR_ARG; }
+    const bool fullMetric = !D.is_diagonal;
+    if (fullMetric && (nd != 3 || D.nranks > 1)) {
+        set_error("leptic solver: a full metric is built for 3-D levels on one rank");
+        return SOMAR_ERR_ARG;
+    }
+    if (fullMetric && (D.n[0] < 3 || D.n[1] < 3 || D.n[2] < 3)) {
+        set_error("leptic solver: a full metric needs 3 cells in every direction (order-2 extrapolated ghosts)");
+        return SOMAR_ERR_ARG;
+    }
     if (D.periodic[vd]) { set_error("leptic solver: the vertical direction is periodic (LevelLepticSolver.cpp:1316)"); return SOMAR_ERR_ARG; }
     if (prm->max_order < 0 || prm->max_order > 14) { set_error("leptic solver: max_order must be in 0..14"); return SOMAR_ERR_ARG; }
     cudaSetDevice(L->device);
@@ -268,8 +383,11 @@ int somar_leptic_create(SomarLevel* L, const SomarLepticParams* prm, SomarLeptic
         Depth& dst = S->vert->depths[0];
         if (src.g.total != dst.g.total) { set_error("leptic: vertical level layout differs"); return fail(SOMAR_ERR_ARG); }
         for (int d = 0; d < nd; ++d)
-            if (cudaMemcpyAsync(dst.jg[d][d], src.jg[d][d], sizeof(double) * src.g.total, cudaMemcpyDeviceToDevice,
-                                S->vert->cx.stream) != cudaSuccess) { set_error("leptic: metric copy failed"); return fail(SOMAR_ERR_CUDA); }
+            for (int e = 0; e < nd; ++e) {
+                if (e != d && !fullMetric) continue;
+                if (cudaMemcpyAsync(dst.jg[d][e], src.jg[d][e], sizeof(double) * src.g.total, cudaMemcpyDeviceToDevice,
+                                    S->vert->cx.stream) != cudaSuccess) { set_error("leptic: metric copy failed"); return fail(SOMAR_ERR_CUDA); }
+            }
         if ((rc = sync(L))) return fail(rc);
         launch_fill(S->vert->cx, dst.g, dst.jinv, 1.0);
         if ((rc = level_finalize(S->vert))) return fail(rc);
@@ -293,7 +411,7 @@ int somar_leptic_create(SomarLevel* L, const SomarLepticParams* prm, SomarLeptic
         dh.dx[2] = 1.0;
         dh.alpha = 0.0;
         dh.beta = 1.0;
-        dh.is_diagonal = 1;
+        dh.is_diagonal = fullMetric ? 0 : 1;   // J g^{ab}, a, b horizontal (LevelGeometryBasics.cpp:545-568)
         for (int s = 0; s < 6; ++s) { dh.bc_type[s] = 0; dh.bc_value[s] = 0.0; }   // EllipticConstNeumBCFluxClass(0,0) (:363-368)
         // flattened boxes of the level, each footprint once (LepticBoxUtils::FlattenTransform; the reference then
         // re-balances them, createHorizontalSolverGrids -- the layout only enters through the multigrid schedule)
@@ -341,8 +459,9 @@ int somar_leptic_create(SomarLevel* L, const SomarLepticParams* prm, SomarLeptic
             }
         }
         // vertically averaged J g^{00}, J g^{11}: scale = 1 / Nz (LevelGeometryBasics.cpp:545-568), on this rank's rows
-        const long long n0 = (long long)(g.n[0] + 1) * g.n[1], n1 = (long long)g.n[0] * (g.n[1] + 1);
-        const long long G0 = (long long)(nxg + 1) * nyg, G1 = (long long)nxg * (nyg + 1), GC = (long long)nxg * nyg;
+        const int nc = fullMetric ? 2 : 1;     // components per face direction, component outermost
+        const long long n0 = (long long)(g.n[0] + 1) * g.n[1] * nc, n1 = (long long)g.n[0] * (g.n[1] + 1) * nc;
+        const long long G0 = (long long)(nxg + 1) * nyg * nc, G1 = (long long)nxg * (nyg + 1) * nc, GC = (long long)nxg * nyg;
         double *dense = nullptr, *glob = nullptr;
         if (cudaMalloc(&dense, sizeof(double) * (n0 + n1)) != cudaSuccess || cudaMalloc(&glob, sizeof(double) * (G0 + G1 + GC)) != cudaSuccess) {
             cudaFree(dense);
@@ -352,8 +471,16 @@ int somar_leptic_create(SomarLevel* L, const SomarLepticParams* prm, SomarLeptic
         cudaStream_t st = S->vert->cx.stream;
         const double scale = 1.0 / (double)g.n[2];
         const Depth& dv = S->vert->depths[0];
-        k_vert_avg_dense<<<plane_grid(g, 1, 0), QTPB, 0, st>>>(g, dense, dv.jg[0][0], 1, 0, scale);
-        k_vert_avg_dense<<<plane_grid(g, 0, 1), QTPB, 0, st>>>(g, dense + n0, dv.jg[1][1], 0, 1, scale);
+        if (fullMetric) {
+            for (int e = 0; e < 2; ++e) {
+                k_vert_avg_dense<<<plane_grid(g, 1, 0), QTPB, 0, st>>>(g, dense + e * (n0 / 2), dv.jg[0][e], 1, 0, scale);
+                k_vert_avg_dense<<<plane_grid(g, 0, 1), QTPB, 0, st>>>(g, dense + n0 + e * (n1 / 2), dv.jg[1][e], 0, 1, scale);
+            }
+            S->vert->cx.launches += 2;
+        } else {
+            k_vert_avg_dense<<<plane_grid(g, 1, 0), QTPB, 0, st>>>(g, dense, dv.jg[0][0], 1, 0, scale);
+            k_vert_avg_dense<<<plane_grid(g, 0, 1), QTPB, 0, st>>>(g, dense + n0, dv.jg[1][1], 0, 1, scale);
+        }
         k_fill_dense<<<64, 256, 0, st>>>(glob + G0 + G1, GC, 1.0);   // "because we are solving L[phi] = J*rhs" (:428-430)
         S->vert->cx.launches += 3;
         rc = SOMAR_OK;
@@ -365,7 +492,7 @@ int somar_leptic_create(SomarLevel* L, const SomarLepticParams* prm, SomarLeptic
         }
         cudaError_t ce = cudaStreamSynchronize(st);
         if (!rc && ce == cudaSuccess) {
-            rc = somar_level_set_metric_device(S->horiz, 1, glob, glob + G0, nullptr, glob + G0 + G1);
+            rc = somar_level_set_metric_device(S->horiz, nc, glob, glob + G0, nullptr, glob + G0 + G1);
             if (!rc) rc = somar_level_finalize(S->horiz);
         }
         cudaFree(dense);
@@ -432,9 +559,14 @@ int somar_leptic_solve(SomarLeptic* S, SomarField* phi, const SomarField* rhs, i
     for (int order = 0; order <= maxOrder; ++order) {
         st->orders = order + 1;
         if (S->doHoriz) {
-            if (order >= 1) {
+            if (order >= 1 && dv.m.diagonal) {
                 // levelVertHorizGradient: zero for a diagonal metric (:1122-1125)
                 if ((rc = flat_zero(S, S->bdryLo)) || (rc = flat_zero(S, S->bdryHi))) return rc;
+            } else if (order >= 1) {
+                // -Grad[phi_{order-1}]^z on the vertical boundary faces (:760-762)
+                k_vert_horiz_grad<<<plane_grid(g), QTPB, 0, vs>>>(g, dv.jg[2][0], dv.jg[2][1], S->vertPhi->p, S->bdryLo->p,
+                                                                  S->bdryHi->p, -1.0);
+                V->cx.launches++;
             }
             if (order >= 1 && useExcess) {                                                 // vertPlus(excess, 1, Hi) (:766)
                 k_flat_axpy<<<plane_grid(g), QTPB, 0, vs>>>(g, S->bdryHi->p, S->excess->p, 1.0);
@@ -455,8 +587,13 @@ int somar_leptic_solve(SomarLeptic* S, SomarField* phi, const SomarField* rhs, i
         if (useHoriz) {
             // flatRhs = computeHorizRHS [- excess / H] (:800-808); "this exchanges vertPhi" (:1006)
             if ((rc = exchange(V, 0, S->vertPhi->p, 1))) return rc;
-            k_horiz_rhs<<<plane_grid(g), QTPB, 0, vs>>>(g, S->flatRhs->p, S->vertPhi->p, dv.jg[0][0], dv.jg[1][1],
-                                                        useExcess ? S->excess->p : nullptr, -1.0 / H, 1.0 / (double)g.n[2]);
+            if (dv.m.diagonal)
+                k_horiz_rhs<<<plane_grid(g), QTPB, 0, vs>>>(g, S->flatRhs->p, S->vertPhi->p, dv.jg[0][0], dv.jg[1][1],
+                                                            useExcess ? S->excess->p : nullptr, -1.0 / H, 1.0 / (double)g.n[2]);
+            else
+                k_horiz_rhs_full<<<plane_grid(g), QTPB, 0, vs>>>(g, dv.m, S->flatRhs->p, S->vertPhi->p,
+                                                                 useExcess ? S->excess->p : nullptr, -1.0 / H,
+                                                                 1.0 / (double)g.n[2]);
             V->cx.launches++;
             // to the horizontal grids (:811-812)
             const Geom& gh = Hz->depths[0].g;
@@ -520,7 +657,7 @@ int somar_leptic_solve(SomarLeptic* S, SomarField* phi, const SomarField* rhs, i
             st->exit_status = (order == 0) ? 4 : 2;
             break;
         }
-        useHoriz = false;                                                                  // LevelGeometry::isDiagonal() (:924-926)
+        if (dv.m.diagonal) useHoriz = false;                                               // LevelGeometry::isDiagonal() (:924-926)
     }
 
     if ((rc = sync(V))) return rc;

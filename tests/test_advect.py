@@ -117,6 +117,44 @@ def test_oracle_fourth_order_faces_and_extremum_preserving_limiter():
 
 
 # ---------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("dim", [2, 3])
+def test_oracle_low_order_predictors(dim):
+    """normalPredOrder 0 (CTU) and 1 (PLM): constants preserved; PLM with fourth-order slopes is second order on a
+    uniform translation, CTU first order; and the reference's quirk -- PLM with useLimiting but WITHOUT fourth-order
+    slopes hands zeroed one-sided differences to the limiter (AdvectUtil.cpp:1116-1128) and so equals CTU bit for bit."""
+    shape = (6 if dim == 3 else 1, 10, 12)
+    W, J, ov, av, _ = _inputs(shape, dim)
+    for order, lim, fourth in itertools.product([0, 1], [False, True], [False, True]):
+        out = ar.predict_scalar(np.full(shape, 2.5), J, ov, av, 0.01, [0.1] * 3, dim, use_limiting=lim, return_flux=False,
+                                normal_pred_order=order, fourth_order_slopes=fourth)
+        for o in out:
+            assert np.abs(o - 2.5).max() <= 1e-14
+    ctu = ar.predict_scalar(W, J, ov, av, 0.01, [0.1] * 3, dim, normal_pred_order=0)
+    plm_lim = ar.predict_scalar(W, J, ov, av, 0.01, [0.1] * 3, dim, normal_pred_order=1, use_limiting=True)
+    plm = ar.predict_scalar(W, J, ov, av, 0.01, [0.1] * 3, dim, normal_pred_order=1)
+    for a, b, c in zip(ctu, plm_lim, plm):
+        assert np.array_equal(a, b)
+        assert not np.array_equal(a, c)
+    u = [0.7, -0.4, 0.3][:dim]
+    errs = {0: [], 1: []}
+    for n in (16, 32, 64):
+        nz = n if dim == 3 else 1
+        dx = [1.0 / n] * 3
+        z, y, x = np.meshgrid((np.arange(nz) + 0.5) / max(nz, 1), (np.arange(n) + 0.5) / n, (np.arange(n) + 0.5) / n,
+                              indexing="ij")
+        f = lambda x, y, z: np.sin(2 * np.pi * x) * np.cos(2 * np.pi * y) * (np.cos(2 * np.pi * z) if dim == 3 else 1.0)
+        Wn = f(x, y, z)
+        vel = [np.full_like(Wn, c) for c in u]
+        dt = 0.4 * dx[0]
+        exact = f(x - 0.5 * dx[0] - u[0] * dt / 2, y - u[1] * dt / 2, (z - u[2] * dt / 2) if dim == 3 else z)
+        for order in (0, 1):
+            out = ar.predict_scalar(Wn, np.ones_like(Wn), vel, vel, dt, dx, dim, return_flux=False, normal_pred_order=order,
+                                    fourth_order_slopes=True)
+            errs[order].append(np.abs(out[0] - exact).max())
+    assert errs[1][1] < errs[1][0] / 3.5 and errs[1][2] < errs[1][1] / 3.5, errs
+    assert errs[0][2] > errs[0][1] / 2.5 and errs[0][2] > 10 * errs[1][2], errs      # CTU: first order only
+
+
 OPTS = list(itertools.product([False, True], [False, True], [False, True], [False, True]))   # lim, upwind, src, flux
 
 
@@ -139,6 +177,16 @@ def test_predict_scalar_parity(dim, n, somar):
         for d in range(dim):
             got = out[d].get()
             assert np.array_equal(got, want[d]), (dim, d, lim, up, with_src, flux, ho, np.abs(got - want[d]).max())
+    # the other two normal predictors: CTU (order 0) and PLM (order 1, with and without fourth-order slopes)
+    for order, lim, fourth, with_src in itertools.product([0, 1], [False, True], [False, True], [False, True]):
+        lev.advect_predict_scalar(out, fW, fov, fav, fJ, dt, source=fS if with_src else None, use_limiting=lim,
+                                  normal_pred_order=order, use_fourth_order_slopes=fourth)
+        want = ar.predict_scalar(W, J, ov, av, dt, pb.spec.dx, dim, source=src if with_src else None, use_limiting=lim,
+                                 normal_pred_order=order, fourth_order_slopes=fourth)
+        for d in range(dim):
+            got = out[d].get()
+            assert np.array_equal(got, want[d]), (dim, d, order, lim, fourth, with_src, np.abs(got - want[d]).max())
+    lev.advect_predict_scalar(out, fW, fov, fav, fJ, dt, source=fS, use_limiting=True, use_high_order_limiter=True)
     # the flux's periodic image is in place: the MAC divergence of the device equals the wrapped numpy divergence
     div = lev.field(0)
     lev.mac_divergence(div, out)
@@ -168,6 +216,6 @@ def test_predict_scalar_rejects_what_is_not_built(somar):
     lev = pb.level(somar)
     f = [lev.field(0) for _ in range(12)]
     with pytest.raises(somar.SomarError):
-        lev.advect_predict_scalar(f[0:3], f[3], f[4:7], f[7:10], f[10], 0.1, normal_pred_order=1)
+        lev.advect_predict_scalar(f[0:3], f[3], f[4:7], f[7:10], f[10], 0.1, normal_pred_order=3)
     with pytest.raises(somar.SomarError):          # output aliases an input
         lev.advect_predict_scalar([f[3], f[1], f[2]], f[3], f[4:7], f[7:10], f[10], 0.1)

@@ -188,10 +188,44 @@ def test_leptic_solve_accumulates_into_phi_and_is_repeatable(oracle_lib, somar):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("parts", [(1, 1, 1), (2, 2, 1), (1, 2, 1)])
+def test_leptic_solve_full_metric_parity(parts, oracle_lib, somar):
+    """terrain-following metric: the boundary data of every order from levelVertHorizGradient (k_vert_horiz_grad), the
+    horizontal right-hand side with MAPPEDMACGRAD's transverse terms seen from every box (k_horiz_rhs_full), a 2-D
+    full-metric horizontal level from the vertically averaged J g^{ab}, a horizontal solve at every order"""
+    pb = Problem(n=(32, 32, 16), map_name="terrain", aniso=64.0, parts=parts)
+    rhs_h = _rhs(pb)
+    # (layouts with 8-cell boxes are left out on purpose: there the 2-D full-metric horizontal multigrid HANGS on both
+    # stacks -- exit status 4 at 1e-4..1e-7 of its initial residual after 5-10 V-cycles, the iteration plateaus at
+    # 1.4e-3 -- and where a stalled solve stops differs between two correct stacks at the 1e-8 level)
+    so = _oracle_solver(oracle_lib, pb)
+    want = so.solve(np.zeros_like(rhs_h), rhs_h, homogeneous=True)
+    assert not so.diag and so.horiz_solves == 5 and not so.krylov_used
+
+    lev = pb.level(somar)
+    ls = somar.LepticSolver(lev, somar.leptic_default_params())
+    j0, j1 = ls.horiz_metric(full=True)
+    assert np.array_equal(j0, so.hjg[0]) and np.array_equal(j1, so.hjg[1])     # createVertAvgFCJgupPtr, all four J g^{ab}
+    phi, rhs = lev.field(0), lev.field(0, rhs_h)
+    st = ls.solve(phi, rhs, homogeneous=True)
+    got = phi.get()
+    assert st["exit_status"] == so.exit_status and st["horiz_solves"] == so.horiz_solves and not st["krylov_used"]
+    assert len(st["res_norms"]) == len(so.res_norms)
+    # the first norm has no multigrid solve in front of it; the others follow horizontal solves stopped on a tolerance
+    assert np.allclose(st["res_norms"][:1], so.res_norms[:1], rtol=1e-12, atol=0), (st["res_norms"], so.res_norms)
+    assert np.allclose(st["res_norms"], so.res_norms, rtol=1e-5, atol=0), (st["res_norms"], so.res_norms)
+    assert np.abs(got - want).max() < 1e-7 * np.abs(want).max()
+    res = lev.field(0)
+    lev.residual(res, phi, rhs, homogeneous=True)
+    r_want = so.orig.residual(want, rhs_h, homogeneous=True)
+    assert np.abs(res.get()).max() <= 1.5 * np.abs(r_want).max() + 1e-12
+
+
+@pytest.mark.gpu
 def test_leptic_create_rejects_out_of_scope_levels(somar):
     for kw, msg in [(dict(n=(16, 16, 8), aniso=16.0, periodic=(1, 0, 0)), "non-periodic horizontal"),
                     (dict(n=(16, 16, 8), aniso=16.0, periodic=(0, 0, 1)), "vertical direction is periodic"),
-                    (dict(n=(16, 12, 16), map_name="terrain", aniso=4.0), "diagonal metrics only")]:
+                    (dict(n=(16, 12, 2), map_name="terrain", aniso=4.0), "3 cells in every direction")]:
         pb = Problem(**kw)
         lev = pb.level(somar)
         with pytest.raises(somar.SomarError, match=msg):
@@ -200,7 +234,7 @@ def test_leptic_create_rejects_out_of_scope_levels(somar):
 
 # ---------------------------------------------------------------------------------------------------------------
 # Pieces of the leptic iteration that need per-box ghost cells (oracle/somar_oracle.cpp Op::lepticHorizRHS /
-# ::lepticVertHorizGradient, written for either metric; the device has the diagonal case only so far).
+# ::lepticVertHorizGradient, written for either metric).
 @pytest.mark.parametrize("parts", [(1, 1, 1), (2, 2, 1)])
 def test_oracle_horiz_rhs_diagonal_equals_the_global_restatement(parts, oracle_lib):
     from oracle import leptic_ref as lr
