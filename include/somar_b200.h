@@ -321,9 +321,9 @@ int somar_leptic_level(SomarLeptic* s, int which, SomarLevel** out);
  * whalf_d (face fields, out): time-centred face states, times adv_vel_d when return_flux (the flux whose
  * somar_mac_divergence gives the advective update, AMRNavierStokesAdvancePPM.cpp:379-620).  w_old, source (may be NULL),
  * old_vel_d (cell-centred components) and cc_j (cell-centred J, LevelGeometry::fill_J) are cell fields, adv_vel_d face
- * fields.  Built for FULLY PERIODIC single-rank levels, the three normal predictors (CTU, PLM, PPM) and both limiter
- * families; anything else returns SOMAR_ERR_ARG (non-periodic sides need the physics BC holders, which are outside this
- * library). */
+ * fields.  Built for FULLY PERIODIC levels on one rank or y-slab ranks (the ghost rows of the INPUT fields are refreshed
+ * in place by the halo exchanges), the three normal predictors (CTU, PLM, PPM) and both limiter families; anything else
+ * returns SOMAR_ERR_ARG (non-periodic sides need the physics BC holders, which are outside this library). */
 typedef struct SomarAdvectParams {
     int normal_pred_order;        /* ProblemContext normalPredOrder{Vel,Scal}: 0 = CTU, 1 = PLM, 2 = PPM */
     int use_limiting;             /* useLimiting{Vel,Scal}: van Leer + PPM limiters */

@@ -311,6 +311,38 @@ private:
     PressureSolver& solver_;
 };
 
+// LevelCCProjector (src/projection/LevelCCProjector.H:38-100): the cell-centred ("approximate") projection of the time
+// step (AMRNavierStokes::doCCProjection, AMRNavierStokesAdvancePPM.cpp:1513-1573).  The velocity components are CELL
+// fields; J is the cell-centred Jacobian field the reference caches (LevelGeometry::getCCJ), or nullptr when the velocity
+// is already a flux (a_velIsFlux = true).  multByJ / CellToEdge / the wall BC of m_divBC / EdgeToCell / divByJ are folded
+// into the two sweeps either side of the solve.
+class CCProjector {
+public:
+    explicit CCProjector(PressureSolver& solver) : solver_(solver) {}
+    // computeDiv (LevelCCProjector.cpp:156-187) [of J u when J is given]
+    void computeDiv(Field& div, Field& ux, Field& uy, Field* uz = nullptr, Field* J = nullptr) {
+        check(somar_cc_divergence(L(), div.handle(), ux.handle(), uy.handle(), uz ? uz->handle() : nullptr,
+                                  J ? J->handle() : nullptr, 0.0), "CCProjector::computeDiv");
+    }
+    // computeGrad (:199-231): cell-centred J g^{dj} d_j phi with the order-2 extrapolated ghosts of gradPiFuncBC
+    void computeGrad(Field& gx, Field& gy, Field* gz, Field& phi) {
+        check(somar_cc_gradient(L(), gx.handle(), gy.handle(), gz ? gz->handle() : nullptr, phi.handle()), "CCProjector::computeGrad");
+    }
+    // levelProject: [u *= J;] rhs = Div[u]/dt; solve; u -= dt Grad[pressure]; [u *= 1/J]
+    SomarSolveStats project(Field& ux, Field& uy, Field* uz, Field& pressure, double dt, Field* J = nullptr,
+                            bool zeroPressure = true, bool forceHomogeneous = false) {
+        SomarSolveStats st{};
+        const int rc = somar_project_cc(L(), ux.handle(), uy.handle(), uz ? uz->handle() : nullptr, J ? J->handle() : nullptr,
+                                        pressure.handle(), dt, zeroPressure, forceHomogeneous, &st);
+        if (rc != SOMAR_OK && rc != SOMAR_ERR_DIVERGED) check(rc, "CCProjector::project");
+        return st;
+    }
+
+private:
+    SomarLevel* L() const { return solver_.level().handle(); }
+    PressureSolver& solver_;
+};
+
 // LevelLepticSolver (src/calculus/LepticSolver/LevelLepticSolver.H:40-347): the LinearSolver<LevelData<FArrayBox>> built
 // on a LepticOperator.  define() takes the level that plays the operator's part (its metric, BCs and boxes are what
 // LepticOperator::getFCJgup/getCCJinv/getBCs/smallestGridSize hand over, LepticOperator.H:33-44); the parameter setters

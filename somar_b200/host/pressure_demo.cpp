@@ -176,7 +176,19 @@ int main(int argc, char** argv) {
         proj.computeDiv(div, ux, uy, &uz);
         const double div1 = op.norm(div, 0);
         std::printf("projection: %d V-cycles, max|div| %.3e -> %.3e\n", ps.iters, div0, div1);
-        const bool ok = rel <= 1e-9 && err <= 1e-7 && div1 <= 1e-8 * div0;
+        // ---- and the cell-centred projection of the time step (LevelCCProjector): the cell-centred gradient of phi* as
+        //      the velocity flux; the projection is approximate (Div_cc Grad_cc is the 2h-wide Laplacian), so the
+        //      cell-centred divergence falls but does not vanish ------------------------------------------------------
+        CCProjector ccProj(solver);
+        Field cx(lev, 0), cy(lev, 0), cz(lev, 0), cpres(lev, 0);
+        ccProj.computeGrad(cx, cy, &cz, dStar);
+        ccProj.computeDiv(div, cx, cy, &cz);
+        const double cdiv0 = op.norm(div, 0);
+        const SomarSolveStats cs = ccProj.project(cx, cy, &cz, cpres, 1.0, nullptr, true, false);
+        ccProj.computeDiv(div, cx, cy, &cz);
+        const double cdiv1 = op.norm(div, 0);
+        std::printf("cc projection: %d V-cycles, max|div_cc| %.3e -> %.3e\n", cs.iters, cdiv0, cdiv1);
+        const bool ok = rel <= 1e-9 && err <= 1e-7 && div1 <= 1e-8 * div0 && cdiv1 < cdiv0;
         std::printf(ok ? "DEMO-OK\n" : "DEMO-FAILED\n");
         return ok ? 0 : 1;
     } catch (const Error& e) {

@@ -41,3 +41,16 @@ def test_n_ranks_match_one_rank_nccl(args, nproc):
         pytest.skip(f"needs {nproc} GPUs")
     rc, out = _launch(nproc, args)
     assert rc == 0 and "MGPU-OK nccl" in out, out[-4000:]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nproc", [2, 4])
+def test_advection_predictor_on_y_slab_ranks(nproc):
+    """predictScalar (PPM / PLM / CTU, both limiter families) on 2 and 4 ranks, bit-exact against the numpy oracle of the
+    whole periodic domain"""
+    import torch
+    if torch.cuda.device_count() < nproc:
+        pytest.skip(f"needs {nproc} GPUs")
+    rc, out = _launch(nproc, ["advect"])
+    assert rc == 0 and "MGPU-OK nccl" in out, out[-4000:]
+
