@@ -44,7 +44,9 @@ inline void gsrb_ortho(FAB& phi, const FAB& rhs, const FAB* Jg, const FAB& Jinv,
                                                       Jg[2](i, j, k, 2) * phi(i, j, k - 1, n));
                             lphi = beta * Jinv(i, j, k) * (JDxx + JDyy + JDzz);
                         } else {
-                            lphi = beta * Jinv(i, j, k) * (JDxx + JDyy);
+                            // GSRBITER2DORTHO (GSRBF.ChF:442-543) associates differently from the 3-D kernel:
+                            // lphi = beta * (JDxx + JDyy) * Jinv  (found by running the Fortran itself, oracle/chf2py.py)
+                            lphi = beta * (JDxx + JDyy) * Jinv(i, j, k);
                         }
                         phi(i, j, k, n) = (rhs(i, j, k, n) - lphi) / (alpha + beta * lapDiag(i, j, k));
                     }
@@ -117,20 +119,27 @@ inline void gsrb_boundary_ortho(FAB& phi, const FAB& rhs, const FAB* Jg, const F
                 for (int i = imin; i <= region.hi[0]; i += 2) {
                     double JDlo[3] = {0, 0, 0}, JDhi[3] = {0, 0, 0};
                     double lapDiag = 0.0;
-                    // order of accumulation follows the Fortran: loX, loY, (loZ), hiX, hiY, (hiZ)
-                    for (int d = 0; d < nd; ++d) {
+                    // order of accumulation follows the Fortran: 3-D loX, loY, loZ, hiX, hiY, hiZ (GSRBF.ChF:1440-1480);
+                    // 2-D loX, hiX, loY, hiY (:1300-1330 -- found by running the Fortran itself, oracle/chf2py.py)
+                    auto lo_term = [&](int d) {
                         const int di = d == 0, dj = d == 1, dk = d == 2;
                         if (st[d][Lo] != BC_Neum) {
                             JDlo[d] = Jg[d](i, j, k, d) * phi(i - di, j - dj, k - dk, n);
                             lapDiag = lapDiag - sc[d] * Jg[d](i, j, k, d);
                         }
-                    }
-                    for (int d = 0; d < nd; ++d) {
+                    };
+                    auto hi_term = [&](int d) {
                         const int di = d == 0, dj = d == 1, dk = d == 2;
                         if (st[d][Hi] != BC_Neum) {
                             JDhi[d] = Jg[d](i + di, j + dj, k + dk, d) * phi(i + di, j + dj, k + dk, n);
                             lapDiag = lapDiag - sc[d] * Jg[d](i + di, j + dj, k + dk, d);
                         }
+                    };
+                    if (nd > 2) {
+                        for (int d = 0; d < nd; ++d) lo_term(d);
+                        for (int d = 0; d < nd; ++d) hi_term(d);
+                    } else {
+                        for (int d = 0; d < nd; ++d) { lo_term(d); hi_term(d); }
                     }
                     lapDiag = lapDiag * Jinv(i, j, k);
                     double s = (JDlo[0] + JDhi[0]) * sc[0] + (JDlo[1] + JDhi[1]) * sc[1];

@@ -493,14 +493,14 @@ void Op::create(LevelData& y, int ghosts) const { y.define(grids, 1, activeDirs 
 // ----------------------------------------------------------------------------------------------
 
 // MAPPEDMACGRADORTHO, normal derivative -- DivCurlGradF.ChF:221-262.
-static void macgrad_ortho(FAB& grad, const FAB& phi, const FAB& Jga, const Box& edgeBox, double dxDir, int dir) {
+void macgrad_ortho(FAB& grad, const FAB& phi, const FAB& Jga, const Box& edgeBox, double dxDir, int dir) {
     const int gi = dir == 0, gj = dir == 1, gk = dir == 2;
     const double dxinv = 1.0 / dxDir;
     ORC_LOOP(edgeBox, i, j, k) grad(i, j, k) = dxinv * Jga(i, j, k, dir) * (phi(i, j, k) - phi(i - gi, j - gj, k - gk));
 }
 
 // MAPPEDMACGRAD, normal derivative (gradDir == edgeDir) -- DivCurlGradF.ChF:87-147.
-static void macgrad_full(FAB& grad, const FAB& phi, const FAB& ex, const FAB& Jga, const Box& edgeBox, const double* dx,
+void macgrad_full(FAB& grad, const FAB& phi, const FAB& ex, const FAB& Jga, const Box& edgeBox, const double* dx,
                          int adir, int nd) {
     const int bdir = (adir + 1) % nd, cdir = (adir + 2) % nd;
     const int ai = adir == 0, aj = adir == 1, ak = adir == 2;

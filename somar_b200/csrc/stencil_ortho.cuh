@@ -177,7 +177,7 @@ __device__ __forceinline__ double gsrb_update_vals(const Geom& g, const GsrbCoef
             const double JDzz = sc2 * (q.ghi[2] * nb[2][1] + q.glo[2] * nb[2][0]);
             lphi = g.beta * ji * (JDxx + JDyy + JDzz);
         } else {
-            lphi = g.beta * ji * (JDxx + JDyy);
+            lphi = g.beta * (JDxx + JDyy) * ji;   // GSRBITER2DORTHO's own association (GSRBF.ChF:442-543), not the 3-D kernel's
         }
         double lap = q.lap;
         if (LAPFLY) {
@@ -191,8 +191,9 @@ __device__ __forceinline__ double gsrb_update_vals(const Geom& g, const GsrbCoef
     double JDlo[3] = {0.0, 0.0, 0.0}, JDhi[3] = {0.0, 0.0, 0.0};
     double lapDiag = 0.0;
     const double sc[3] = {sc0, sc1, sc2};
-#pragma unroll
-    for (int d = 0; d < ND; ++d) {
+    // the diagonal is accumulated in the Fortran's order: 3-D lo x, lo y, lo z, hi x, hi y, hi z (GSRBBOUNDARYITER3DORTHO);
+    // 2-D lo x, hi x, lo y, hi y (GSRBBOUNDARYITER2DORTHO, GSRBF.ChF:1233-1361)
+    auto lo_term = [&](int d) {
         const bool atB = (sm >> (2 * d)) & 1u;
         if (!(atB && g.bc[d][0] == BC_NEUM)) {
             double v = nb[d][0];
@@ -200,15 +201,26 @@ __device__ __forceinline__ double gsrb_update_vals(const Geom& g, const GsrbCoef
             JDlo[d] = q.glo[d] * v;
             lapDiag = lapDiag - sc[d] * q.glo[d];
         }
-    }
-#pragma unroll
-    for (int d = 0; d < ND; ++d) {
+    };
+    auto hi_term = [&](int d) {
         const bool atB = (sm >> (2 * d + 1)) & 1u;
         if (!(atB && g.bc[d][1] == BC_NEUM)) {
             double v = nb[d][1];
             if (atB && g.bc[d][1] == BC_DIRI) v = diri_ghost_val(pc, nb[d][0], 0.0, g.diriOrder);
             JDhi[d] = q.ghi[d] * v;
             lapDiag = lapDiag - sc[d] * q.ghi[d];
+        }
+    };
+    if (ND > 2) {
+#pragma unroll
+        for (int d = 0; d < ND; ++d) lo_term(d);
+#pragma unroll
+        for (int d = 0; d < ND; ++d) hi_term(d);
+    } else {
+#pragma unroll
+        for (int d = 0; d < ND; ++d) {
+            lo_term(d);
+            hi_term(d);
         }
     }
     lapDiag = lapDiag * ji;

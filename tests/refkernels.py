@@ -1,0 +1,452 @@
+"""Kernel-by-kernel comparison harness (used by tests/test_reference_kernels.py and tools/make_reference_goldens.py).
+
+Every case builds seeded inputs on small boxes with non-zero origins, runs ONE kernel of the reference -- its own
+Chombo-Fortran source executed through oracle/chf2py.py -- and the oracle's hand-written restatement of that kernel
+(oracle/kernel_capi.cpp for the C++ ones, oracle/advect_ref.py for the numpy ones), and returns both outputs.  The
+arguments follow the reference's call sites, which are cited case by case."""
+import ctypes as C
+import itertools
+import os
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_SO = os.path.join(ROOT, "oracle", "liboracle.so")
+
+
+class RawFab(C.Structure):
+    _fields_ = [("p", C.c_void_p), ("lo", C.c_int * 3), ("hi", C.c_int * 3), ("nc", C.c_int)]
+
+
+def _lib():
+    if not hasattr(_lib, "h"):
+        _lib.h = C.CDLL(ORACLE_SO)
+    return _lib.h
+
+
+class Arr:
+    """a FAB for both sides: numpy (nc, [nz,] ny, nx) over the box [lo, hi] (D entries)"""
+
+    def __init__(self, lo, hi, nc=1, rng=None, fill=None, positive=False):
+        self.lo, self.hi, self.D = list(lo), list(hi), len(lo)
+        shp = (nc,) + tuple(hi[d] - lo[d] + 1 for d in reversed(range(self.D)))
+        if fill is not None:
+            self.a = np.full(shp, float(fill))
+        elif positive:
+            self.a = rng.uniform(0.5, 1.5, size=shp)
+        else:
+            self.a = rng.uniform(-1.0, 1.0, size=shp)
+
+    def copy(self):
+        o = Arr.__new__(Arr)
+        o.lo, o.hi, o.D, o.a = list(self.lo), list(self.hi), self.D, self.a.copy()
+        return o
+
+    def fab(self, comp0=0):            # for the translated Fortran
+        from oracle.chf_runtime import Fab
+        return Fab(self.a, self.lo, comp0=comp0)
+
+    def raw(self):                     # for the C++ oracle
+        r = RawFab()
+        r.p = self.a.ctypes.data
+        for d in range(3):
+            r.lo[d] = self.lo[d] if d < self.D else 0
+            r.hi[d] = self.hi[d] if d < self.D else 0
+        r.nc = self.a.shape[0]
+        return C.byref(r)
+
+
+def _i3(v, pad=0):
+    v = list(v) + [pad] * (3 - len(v))
+    return (C.c_int * 3)(*v)
+
+
+def _d3(v):
+    v = list(v) + [1.0] * (3 - len(v))
+    return (C.c_double * 3)(*v)
+
+
+def _box(lo, hi):
+    from oracle.chf_runtime import Box
+    return Box(lo, hi)
+
+
+def _vec(v, integer=False):
+    from oracle.chf_runtime import Vec
+    return Vec(v, integer=integer)
+
+
+def _grow(lo, hi, g, dirs=None):
+    D = len(lo)
+    dirs = range(D) if dirs is None else dirs
+    lo, hi = list(lo), list(hi)
+    for d in dirs:
+        lo[d] -= g
+        hi[d] += g
+    return lo, hi
+
+
+def _faces(lo, hi, d):
+    hi = list(hi)
+    hi[d] += 1
+    return list(lo), hi
+
+
+class Setup:
+    """the fields of one box of a level: valid box with non-zero origin, phi / extrap with one ghost layer, face-centred
+    J g^{d.} with SpaceDim components (FluxBox), cell-centred 1/J and lapDiag"""
+
+    def __init__(self, D, seed):
+        rng = np.random.default_rng(seed)
+        self.D = D
+        self.lo = [2, -1, 3][:D]
+        self.hi = [self.lo[d] + [5, 4, 3][d] for d in range(D)]
+        self.dx = [0.5, 0.25, 0.125][:D]
+        glo, ghi = _grow(self.lo, self.hi, 1)
+        self.phi = Arr(glo, ghi, 1, rng)
+        self.ex = Arr(glo, ghi, 1, rng)
+        self.rhs = Arr(self.lo, self.hi, 1, rng)
+        self.jinv = Arr(glo, ghi, 1, rng, positive=True)
+        self.lapdiag = Arr(self.lo, self.hi, 1, rng)
+        self.lapdiag.a -= 3.0                              # away from zero (it is a divisor)
+        self.jg = []
+        for d in range(D):
+            flo, fhi = _faces(*_grow(self.lo, self.hi, 1, [e for e in range(D) if e != d]), d)
+            a = Arr(flo, fhi, D, rng, positive=True)
+            for e in range(D):
+                if e != d:
+                    a.a[e] = 0.3 * (a.a[e] - 1.0)          # cross terms: smaller, either sign
+            self.jg.append(a)
+        self.rng = rng
+
+
+def _jg_raw(s):
+    return [s.jg[d].raw() if d < s.D else None for d in range(3)]
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Each case: name -> function(D, ref_module_or_None) -> (oracle_outputs, reference_outputs_or_None); outputs are dicts of
+# numpy arrays.  Call sites cited are the reference's.
+# ---------------------------------------------------------------------------------------------------------------
+def case_gsrb_ortho(D, ref):
+    """GSRBITER{2,3}DORTHO <- BaseGSRB::fullStencilGSRB, GSRB.cpp:405-445"""
+    out_o, out_r = {}, ({} if ref else None)
+    for (alpha, beta), rb in itertools.product([(0.0, 1.0), (0.3, 0.7)], [0, 1]):
+        s = Setup(D, 11)
+        key = "a%.1f_b%.1f_rb%d" % (alpha, beta, rb)
+        p = s.phi.copy()
+        _lib().orck_gsrb_ortho(p.raw(), s.rhs.raw(), *_jg_raw(s), s.jinv.raw(), s.lapdiag.raw(), _i3(s.lo), _i3(s.hi), _d3(s.dx),
+                               C.c_double(alpha), C.c_double(beta), rb, D)
+        out_o[key] = p.a
+        if ref:
+            q = s.phi.copy()
+            f = getattr(ref, "gsrbiter%ddortho" % D)
+            f(q.fab(), s.rhs.fab(), *[s.jg[d].fab(d) for d in range(D)], s.jinv.fab(), s.lapdiag.fab(), _box(s.lo, s.hi),
+              _vec(s.dx), alpha, beta, rb)
+            out_r[key] = q.a
+    return out_o, out_r
+
+
+def case_gsrb_full(D, ref):
+    """GSRBITER{2,3}D <- BaseGSRB::fullStencilGSRB, GSRB.cpp:447-487"""
+    out_o, out_r = {}, ({} if ref else None)
+    for (alpha, beta), rb in itertools.product([(0.0, 1.0), (0.3, 0.7)], [0, 1]):
+        s = Setup(D, 12)
+        key = "a%.1f_b%.1f_rb%d" % (alpha, beta, rb)
+        p = s.phi.copy()
+        _lib().orck_gsrb_full(p.raw(), s.ex.raw(), s.rhs.raw(), *_jg_raw(s), s.jinv.raw(), s.lapdiag.raw(), _i3(s.lo), _i3(s.hi),
+                              _d3(s.dx), C.c_double(alpha), C.c_double(beta), rb, D)
+        out_o[key] = p.a
+        if ref:
+            q = s.phi.copy()
+            f = getattr(ref, "gsrbiter%dd" % D)
+            f(q.fab(), s.ex.fab(), s.rhs.fab(), *[s.jg[d].fab() for d in range(D)], s.jinv.fab(), s.lapdiag.fab(),
+              _box(s.lo, s.hi), _vec(s.dx), alpha, beta, rb)
+            out_r[key] = q.a
+    return out_o, out_r
+
+
+# BCType codes per side (lo x, hi x, lo y, ...): -1 none (box interface), 0 Neumann, 1 Dirichlet, 2 periodic.  (All-Neumann is
+# left out: every term of the diagonal is dropped and the Fortran divides by zero.)
+STENCILS = {2: [(0, 1, 0, 1), (0, -1, 1, 0), (-1, 0, -1, 1), (2, 2, 0, 1), (1, 1, 1, 1), (-1, -1, -1, -1)],
+            3: [(0, 1, 0, 1, 0, 1), (0, -1, 1, 0, -1, -1), (-1, 0, -1, 1, 0, 1), (2, 2, 0, 1, -1, 0), (1, 1, 1, 1, 1, 1),
+                (-1, -1, -1, -1, -1, -1)]}
+
+
+def _case_gsrb_boundary(D, ref, full):
+    out_o, out_r = {}, ({} if ref else None)
+    for st, rb, (alpha, beta) in itertools.product(STENCILS[D], [0, 1], [(0.0, 1.0), (0.3, 0.7)]):
+        s = Setup(D, 13)
+        key = "st%s_rb%d_a%.1f" % ("".join(str(x + 2) for x in st), rb, alpha)
+        st6 = (C.c_int * 6)(*(list(st) + [0] * (6 - len(st))))
+        p = s.phi.copy()
+        if full:
+            _lib().orck_gsrb_boundary_full(p.raw(), s.ex.raw(), s.rhs.raw(), *_jg_raw(s), s.jinv.raw(), _i3(s.lo), _i3(s.hi),
+                                           _d3(s.dx), C.c_double(alpha), C.c_double(beta), st6, rb, D)
+        else:
+            _lib().orck_gsrb_boundary_ortho(p.raw(), s.rhs.raw(), *_jg_raw(s), s.jinv.raw(), _i3(s.lo), _i3(s.hi), _d3(s.dx),
+                                            C.c_double(alpha), C.c_double(beta), st6, rb, D)
+        out_o[key] = p.a
+        if ref:
+            q = s.phi.copy()
+            if full:
+                getattr(ref, "gsrbboundaryiter%dd" % D)(q.fab(), s.ex.fab(), s.rhs.fab(), *[s.jg[d].fab() for d in range(D)],
+                                                        s.jinv.fab(), _box(s.lo, s.hi), _vec(s.dx), alpha, beta, *st, rb)
+            else:
+                getattr(ref, "gsrbboundaryiter%ddortho" % D)(q.fab(), s.rhs.fab(), *[s.jg[d].fab(d) for d in range(D)],
+                                                             s.jinv.fab(), _box(s.lo, s.hi), _vec(s.dx), alpha, beta, *st, rb)
+            out_r[key] = q.a
+    return out_o, out_r
+
+
+def case_gsrb_boundary_ortho(D, ref):
+    """GSRBBOUNDARYITER{2,3}DORTHO <- BaseGSRB::boundaryGSRB, GSRB.cpp:489-653 (stencil codes = BCType of every side)"""
+    return _case_gsrb_boundary(D, ref, False)
+
+
+def case_gsrb_boundary_full(D, ref):
+    """GSRBBOUNDARYITER{2,3}D <- BaseGSRB::boundaryGSRB, GSRB.cpp:489-653"""
+    return _case_gsrb_boundary(D, ref, True)
+
+
+def case_jacobi(D, ref):
+    """JACOBIITER <- Jacobi::relax, Jacobi.cpp:50-90"""
+    s = Setup(D, 14)
+    p = s.phi.copy()
+    _lib().orck_jacobi(p.raw(), s.rhs.raw(), s.lapdiag.raw(), _i3(s.lo), _i3(s.hi), C.c_double(0.3), C.c_double(0.7))
+    out_r = None
+    if ref:
+        q = s.phi.copy()
+        ref.jacobiiter(q.fab(), s.rhs.fab(), s.lapdiag.fab(), _box(s.lo, s.hi), 0.3, 0.7)
+        out_r = {"phi": q.a}
+    return {"phi": p.a}, out_r
+
+
+def case_lapdiag(D, ref):
+    """FILLMAPPEDLAPDIAG{2,3}D <- MappedAMRPoissonOpFactory::fill_MGfields, MappedAMRPoissonOpFactory.cpp:1199-1230"""
+    s = Setup(D, 15)
+    l = s.lapdiag.copy()
+    _lib().orck_fill_lapdiag(l.raw(), *_jg_raw(s), s.jinv.raw(), _i3(s.lo), _i3(s.hi), _d3(s.dx), D)
+    out_r = None
+    if ref:
+        q = s.lapdiag.copy()
+        getattr(ref, "fillmappedlapdiag%dd" % D)(q.fab(), *[s.jg[d].fab() for d in range(D)], s.jinv.fab(), _box(s.lo, s.hi),
+                                                 _vec(s.dx))
+        out_r = {"lapdiag": q.a}
+    return {"lapdiag": l.a}, out_r
+
+
+def case_diagprecond(D, ref):
+    """DIAGPRECOND <- MappedAMRPoissonOp::preCond, MappedAMRPoissonOp.cpp:684-734"""
+    s = Setup(D, 16)
+    p = s.phi.copy()
+    _lib().orck_diagprecond(p.raw(), s.rhs.raw(), s.lapdiag.raw(), _i3(s.lo), _i3(s.hi), C.c_double(0.3), C.c_double(0.7))
+    out_r = None
+    if ref:
+        q = s.phi.copy()
+        ref.diagprecond(q.fab(), s.rhs.fab(), s.lapdiag.fab(), _box(s.lo, s.hi), 0.3, 0.7)
+        out_r = {"phi": q.a}
+    return {"phi": p.a}, out_r
+
+
+def case_getflux(D, ref):
+    """MAPPEDGETFLUX / MAPPEDGETFLUXORTHO <- MappedAMRPoissonOp::getFluxComplete, MappedAMRPoissonOp.cpp:2070-2160"""
+    out_o, out_r = {}, ({} if ref else None)
+    beta = 0.7
+    for adir in range(D):
+        s = Setup(D, 17 + adir)
+        flo, fhi = _faces(s.lo, s.hi, adir)
+        fo, ff = Arr(flo, fhi, 1, fill=0.0), Arr(flo, fhi, 1, fill=0.0)
+        _lib().orck_getflux_ortho(fo.raw(), s.phi.raw(), s.jg[adir].raw(), adir, _i3(flo), _i3(fhi), C.c_double(beta / s.dx[adir]))
+        # interior faces in the transverse directions only where the cross stencil stays inside phi + 1 ghost
+        _lib().orck_getflux_full(ff.raw(), s.phi.raw(), s.ex.raw(), s.jg[adir].raw(), adir, _i3(flo), _i3(fhi), C.c_double(beta),
+                                 _d3(s.dx), D)
+        out_o["ortho%d" % adir], out_o["full%d" % adir] = fo.a, ff.a
+        if ref:
+            ro, rf = Arr(flo, fhi, 1, fill=0.0), Arr(flo, fhi, 1, fill=0.0)
+            ref.mappedgetfluxortho(ro.fab(), s.phi.fab(), s.jg[adir].fab(adir), _box(flo, fhi), beta / s.dx[adir], adir)
+            ref.mappedgetflux(rf.fab(), s.phi.fab(), s.ex.fab(), s.jg[adir].fab(), _box(flo, fhi), beta, _vec(s.dx), adir)
+            out_r["ortho%d" % adir], out_r["full%d" % adir] = ro.a, rf.a
+    return out_o, out_r
+
+
+def case_divergence(D, ref):
+    """MAPPEDFLUXDIVERGENCE{2,3}D <- MappedAMRPoissonOp::applyOpI (:880-893), Divergence::levelDivergenceMAC (Divergence.cpp:103-123)"""
+    s = Setup(D, 21)
+    fl = [Arr(*_faces(s.lo, s.hi, d), 1, s.rng) for d in range(D)]
+    d_o = Arr(s.lo, s.hi, 1, fill=0.0)
+    _lib().orck_flux_divergence(d_o.raw(), *[fl[d].raw() if d < D else None for d in range(3)], s.jinv.raw(), _i3(s.lo), _i3(s.hi),
+                                _d3(s.dx), D)
+    out_r = None
+    if ref:
+        d_r = Arr(s.lo, s.hi, 1, fill=0.0)
+        getattr(ref, "mappedfluxdivergence%dd" % D)(d_r.fab(), *[f.fab() for f in fl], s.jinv.fab(), _box(s.lo, s.hi), _vec(s.dx))
+        out_r = {"div": d_r.a}
+    return {"div": d_o.a}, out_r
+
+
+def case_macgrad(D, ref):
+    """MAPPEDMACGRAD / MAPPEDMACGRADORTHO, normal derivatives <- Gradient::singleBoxMacGrad, Gradient.cpp:1056-1078"""
+    out_o, out_r = {}, ({} if ref else None)
+    for adir in range(D):
+        s = Setup(D, 23 + adir)
+        flo, fhi = _faces(s.lo, s.hi, adir)
+        go, gf = Arr(flo, fhi, 1, fill=0.0), Arr(flo, fhi, 1, fill=0.0)
+        _lib().orck_macgrad_ortho(go.raw(), s.phi.raw(), s.jg[adir].raw(), _i3(flo), _i3(fhi), C.c_double(s.dx[adir]), adir)
+        _lib().orck_macgrad_full(gf.raw(), s.phi.raw(), s.ex.raw(), s.jg[adir].raw(), _i3(flo), _i3(fhi), _d3(s.dx), adir, D)
+        out_o["ortho%d" % adir], out_o["full%d" % adir] = go.a, gf.a
+        if ref:
+            ro, rf = Arr(flo, fhi, 1, fill=0.0), Arr(flo, fhi, 1, fill=0.0)
+            ref.mappedmacgradortho(ro.fab(), s.phi.fab(), s.ex.fab(), s.jg[adir].fab(), _box(flo, fhi), s.dx[adir], adir, adir)
+            ref.mappedmacgrad(rf.fab(), s.phi.fab(), s.ex.fab(), s.jg[adir].fab(), _box(flo, fhi), _vec(s.dx), adir, adir)
+            out_r["ortho%d" % adir], out_r["full%d" % adir] = ro.a, rf.a
+    return out_o, out_r
+
+
+def _ghost_box(s, d, side):
+    lo, hi = list(s.lo), list(s.hi)
+    if side == 0:
+        lo[d] = hi[d] = s.lo[d] - 1
+    else:
+        lo[d] = hi[d] = s.hi[d] + 1
+    return lo, hi
+
+
+def case_extrapolate(D, ref):
+    """EXTRAPOLATEFACENOEV <- ExtrapolateFaceNoEV, ExtrapolationUtils.cpp:34-62"""
+    out_o, out_r = {}, ({} if ref else None)
+    for d, side, order in itertools.product(range(D), [0, 1], [0, 1, 2, 3, 4]):
+        if order >= [5, 4, 3][d]:
+            continue                                  # the stencil must fit in the box
+        s = Setup(D, 31)
+        glo, ghi = _ghost_box(s, d, side)
+        sign = 1 if side else -1
+        p = s.phi.copy()
+        _lib().orck_extrapolate_face_noev(p.raw(), s.phi.raw(), _i3(glo), _i3(ghi), d, sign, order)
+        key = "d%d_s%d_o%d" % (d, side, order)
+        out_o[key] = p.a
+        if ref:
+            q = s.phi.copy()
+            ref.extrapolatefacenoev(q.fab(), s.phi.fab(), _box(glo, ghi), d, sign, order)
+            out_r[key] = q.a
+    return out_o, out_r
+
+
+def case_bc_ghosts(D, ref):
+    """ELLIPTICCONSTDIRIBCGHOST, ELLIPTICCONSTNEUMBCGHOST[ORTHO] <- setSideDiriBC / setSideNeumBC, EllipticBCUtils.cpp:41-215"""
+    out_o, out_r = {}, ({} if ref else None)
+    for d, side in itertools.product(range(D), [0, 1]):
+        sign = 1 if side else -1
+        for order, bcval in itertools.product([0, 1, 2], [0.0, 0.4]):
+            s = Setup(D, 33)
+            glo, ghi = _ghost_box(s, d, side)
+            p = s.phi.copy()
+            _lib().orck_diri_ghost(p.raw(), _i3(glo), _i3(ghi), C.c_double(bcval), d, sign, order)
+            key = "diri_d%d_s%d_o%d_v%.1f" % (d, side, order, bcval)
+            out_o[key] = p.a
+            if ref:
+                q = s.phi.copy()
+                ref.ellipticconstdiribcghost(q.fab(), _box(glo, ghi), bcval, d, sign, order)
+                out_r[key] = q.a
+        for bcval in (0.0, 0.4):
+            s = Setup(D, 34)
+            glo, ghi = _ghost_box(s, d, side)
+            p, pf = s.phi.copy(), s.phi.copy()
+            _lib().orck_neum_ghost_ortho(p.raw(), s.jg[d].raw(), d, _i3(glo), _i3(ghi), C.c_double(bcval), d, sign, C.c_double(s.dx[d]))
+            # the full-metric ghost reads extrap one cell beyond the ghost box in the transverse directions: shrink it
+            flo, fhi = list(glo), list(ghi)
+            for e in range(D):
+                if e != d:
+                    flo[e] += 1
+                    fhi[e] -= 1
+            _lib().orck_neum_ghost_full(pf.raw(), s.ex.raw(), s.jg[d].raw(), _i3(flo), _i3(fhi), C.c_double(bcval), d, sign,
+                                        _d3(s.dx), D)
+            ko, kf = "neumortho_d%d_s%d_v%.1f" % (d, side, bcval), "neumfull_d%d_s%d_v%.1f" % (d, side, bcval)
+            out_o[ko], out_o[kf] = p.a, pf.a
+            if ref:
+                q, qf = s.phi.copy(), s.phi.copy()
+                ref.ellipticconstneumbcghostortho(q.fab(), s.jg[d].fab(d), _box(glo, ghi), bcval, d, sign, s.dx[d])
+                ref.ellipticconstneumbcghost(qf.fab(), s.ex.fab(), s.jg[d].fab(), _box(flo, fhi), bcval, d, sign, _vec(s.dx))
+                out_r[ko], out_r[kf] = q.a, qf.a
+    return out_o, out_r
+
+
+def case_transfer(D, ref):
+    """MAPPEDAVERAGE2, UNMAPPEDAVERAGEHARMONIC, UNMAPPEDAVERAGEFACE, ConstInterpPS, ConstInterpWithAvgPS <-
+    MappedCoarseAverage.cpp:170-215,447-470, ProlongationStrategy.cpp:49-165"""
+    out_o, out_r = {}, ({} if ref else None)
+    rng = np.random.default_rng(41)
+    ratios = {2: [(2, 2), (1, 2), (2, 1)], 3: [(1, 1, 2), (2, 2, 2), (2, 1, 2)]}[D]
+    for r in ratios:
+        clo = [1, -2, 0][:D]
+        chi = [clo[d] + [2, 3, 1][d] for d in range(D)]
+        flo = [clo[d] * r[d] for d in range(D)]
+        fhi = [(chi[d] + 1) * r[d] - 1 for d in range(D)]
+        fine, jinv = Arr(flo, fhi, 1, rng), Arr(flo, fhi, 1, rng, positive=True)
+        key = "r" + "".join(map(str, r))
+        co, ch = Arr(clo, chi, 1, fill=0.0), Arr(clo, chi, 1, fill=0.0)
+        _lib().orck_mappedaverage2(co.raw(), fine.raw(), jinv.raw(), _i3(clo), _i3(chi), _i3(r, 1))
+        _lib().orck_average_harmonic(ch.raw(), jinv.raw(), _i3(clo), _i3(chi), _i3(r, 1))
+        out_o["avg2_" + key], out_o["harm_" + key] = co.a, ch.a
+        crse = Arr(clo, chi, 1, rng)
+        f1, f2 = fine.copy(), fine.copy()
+        _lib().orck_const_interp(f1.raw(), crse.raw(), _i3(flo), _i3(fhi), _i3(r, 1))
+        vol, tot = C.c_double(0.0), C.c_double(0.0)
+        _lib().orck_const_interp_with_avg(f2.raw(), crse.raw(), _i3(flo), _i3(fhi), _i3(r, 1), jinv.raw(), C.c_double(0.37),
+                                          C.byref(vol), C.byref(tot))
+        out_o["interp_" + key], out_o["interpavg_" + key] = f1.a, f2.a
+        out_o["interpavg_sums_" + key] = np.array([vol.value, tot.value])
+        if ref:
+            bref = _box([0] * D, [r[d] - 1 for d in range(D)])
+            rc, rh = Arr(clo, chi, 1, fill=0.0), Arr(clo, chi, 1, fill=0.0)
+            ref.mappedaverage2(rc.fab(), fine.fab(), jinv.fab(), _box(clo, chi), _vec(r, integer=True), bref)
+            ref.unmappedaverageharmonic(rh.fab(), jinv.fab(), _box(clo, chi), _vec(r, integer=True), bref)
+            out_r["avg2_" + key], out_r["harm_" + key] = rc.a, rh.a
+            # the C++ caller shifts both boxes so that the fine box starts at 0 (ProlongationStrategy.cpp:69-78)
+            g1, g2 = fine.copy(), fine.copy()
+            sh_f = [0] * D
+            sh_fh = [fhi[d] - flo[d] for d in range(D)]
+            from oracle.chf_runtime import Fab
+            shift = lambda arr, lo: Fab(arr.a, lo)
+            ref.constinterpps(shift(g1, sh_f), shift(crse, [0] * D), _box(sh_f, sh_fh), _vec(r, integer=True))
+            vs = _vec([0.0])
+            ss = _vec([0.0])
+            res = ref.constinterpwithavgps(shift(g2, sh_f), shift(crse, [0] * D), _box(sh_f, sh_fh), _vec(r, integer=True),
+                                           shift(jinv, sh_f), 0.37, 0.0, 0.0)
+            out_r["interp_" + key], out_r["interpavg_" + key] = g1.a, g2.a
+            out_r["interpavg_sums_" + key] = np.array(res) if res is not None else None
+        # face average in every direction
+        for d in range(D):
+            cflo, cfhi = _faces(clo, chi, d)
+            fflo = [cflo[e] * r[e] for e in range(D)]
+            ffhi = [(cfhi[e] + 1) * r[e] - 1 if e != d else cfhi[e] * r[e] for e in range(D)]
+            ffine = Arr(fflo, ffhi, 1, rng)
+            cf = Arr(cflo, cfhi, 1, fill=0.0)
+            _lib().orck_average_face(cf.raw(), ffine.raw(), _i3(cflo), _i3(cfhi), d, _i3(r, 1))
+            out_o["face%d_%s" % (d, key)] = cf.a
+            if ref:
+                rf = Arr(cflo, cfhi, 1, fill=0.0)
+                rb_hi = [r[e] - 1 if e != d else 0 for e in range(D)]
+                ref.unmappedaverageface(rf.fab(), ffine.fab(), _box(cflo, cfhi), d, _vec(r, integer=True), _box([0] * D, rb_hi))
+                out_r["face%d_%s" % (d, key)] = rf.a
+    return out_o, out_r
+
+
+CASES = {
+    "gsrb_ortho": case_gsrb_ortho, "gsrb_full": case_gsrb_full, "gsrb_boundary_ortho": case_gsrb_boundary_ortho,
+    "gsrb_boundary_full": case_gsrb_boundary_full, "jacobi": case_jacobi, "lapdiag": case_lapdiag,
+    "diagprecond": case_diagprecond, "getflux": case_getflux, "divergence": case_divergence, "macgrad": case_macgrad,
+    "extrapolate": case_extrapolate, "bc_ghosts": case_bc_ghosts, "transfer": case_transfer,
+}
+
+
+def reference_module(D):
+    """the translated reference kernels for CH_SPACEDIM = D, or None where neither /root/reference nor oracle/_ref exists"""
+    import importlib
+    from oracle import chf2py
+    path = os.path.join(chf2py.OUT, "chf_kernels_%dd.py" % D)
+    if os.path.isdir(chf2py.REF):
+        chf2py.build()
+    if not os.path.exists(path):
+        return None
+    return importlib.import_module("oracle._ref.chf_kernels_%dd" % D)
