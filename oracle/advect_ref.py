@@ -20,8 +20,12 @@ pure stencil on exchanged ghosts), so the restatement works on global arrays wit
 All three normal predictors (normalPredOrder 0 CTU, 1 PLM with or without fourth-order slopes, 2 PPM).
 NOT covered (the device path rejects them too): non-periodic sides (the physics BC holders scalarRiemannBC /
 scalarSlopeBC; the reference itself carries TODO() markers there, AdvectUtil.cpp:713,780,874,905).
-PARITY UNPINNED against reference output (the reference cannot be built here and ships no vectors); pinned by
-tests/test_advect.py to exactness properties of the scheme (constants, uniform translation, conservation).
+PINNED to the reference's own Fortran kernels (SecondSlopeDiffsF, VanLeerLimiterF, ExtPreservingVanLeerLimiterF,
+FourthSlopeDiffsF, PPMFaceValuesF, FourthInterpFaces, PPMLimiterF, GETSECONDDIFF, CheckCubicLimiterF, PPMNormalPredF,
+PLMNormalPredF, RiemannSolver, AvgStates, QuasilinearUpdateF), executed through oracle/chf2py.py in the call order of the
+reference's C++: tests/test_reference_kernels.py (case "advect") demands identical bits for every direction, limiter family
+and predictor in 2-D and 3-D.  The sequencing of predictScalar above the kernels is pinned by tests/test_advect.py to
+exactness properties of the scheme (constants, uniform translation, conservation).
 
 Arrays are (nz, ny, nx) C-ordered (nz = 1 in 2-D); direction d lives on numpy axis 2 - d.  Face f of direction d is
 the LOW face of cell f (periodic: n faces per direction)."""
@@ -35,11 +39,30 @@ def _sh(a, d, o):
     return np.roll(a, -o, axis=2 - d)
 
 
-def van_leer_slopes(W, d, use_limiting):
-    """vanLeerSlopes -> slopes (SecondSlopeDiffsF, centre box) [+ slopeLimiter -> VanLeerLimiterF]"""
+def van_leer_slopes(W, d, use_limiting, ext_preserving=False):
+    """vanLeerSlopes (MappedGodunovUtilities.cpp:49-102) -> slopes (SecondSlopeDiffsF, centre box) [+ slopeLimiter ->
+    VanLeerLimiterF, or -- when the utilities' m_highOrderLimiter is set, which MappedAdvectionUtil::define does with
+    useHighOrderLimiter (AdvectUtil.cpp:104) -- slopeLimiterExtPreserving -> ExtPreservingVanLeerLimiterF,
+    MappedGodunovUtilitiesF.ChF:190-262]"""
     dWR = _sh(W, d, 1) - W
     dWL = W - _sh(W, d, -1)
     dWC = 0.5 * (dWR + dWL)
+    if use_limiting and ext_preserving:
+        dWLL = _sh(dWL, d, -1)
+        dWRR = _sh(dWR, d, 1)
+        dp1 = dWL * dWR
+        dp2 = dWLL * dWRR
+        dpmin = np.minimum(dp1, dp2)
+        dW2L = dWL - dWLL
+        dW2C = (dWR - dWL) * 0.5
+        dW2R = dWRR - dWR
+        sign2 = np.copysign(1.0, dW2C)
+        dW2lim = np.minimum(np.minimum(np.abs(dW2C), np.maximum(sign2 * dW2L, 0.0)), np.maximum(sign2 * dW2R, 0.0))
+        cvl = 5.0 * 0.25
+        dWvl = cvl * 3.0 * 0.5 * dW2lim
+        ext = np.where(sign2 * dWC < 0.0, np.minimum(dWvl, 2.0 * np.abs(dWL)), np.minimum(dWvl, 2.0 * np.abs(dWR)))
+        dWlim = np.where(dpmin < 0.0, ext, 2.0 * np.minimum(np.abs(dWL), np.abs(dWR)))
+        return np.copysign(1.0, dWC) * np.minimum(np.abs(dWC), dWlim)
     if use_limiting:
         lim = np.minimum(2.0 * np.abs(dWL), 2.0 * np.abs(dWR))
         lim = np.minimum(lim, np.abs(dWC))
@@ -146,21 +169,22 @@ def van_leer_limiter(dWc, dWl, dWr):
     return np.where(dWl * dWr < 0.0, 0.0, lim * np.copysign(1.0, dWl))
 
 
-def plm_normal_pred(W, vel_d, d, dtbydx, use_limiting, fourth_order_slopes=False):
+def plm_normal_pred(W, vel_d, d, dtbydx, use_limiting, fourth_order_slopes=False, high_order=False):
     """MappedAdvectionUtil::PLMNormalPred, AdvectUtil.cpp:1066-1152 -> FourthSlopeDiffsF (MappedGodunovUtilitiesF.ChF:
     96-146), oneSidedDifferences / slopeLimiter (MappedGodunovUtilities.cpp:143-171,240-262), PLMNormalPredF (:266-311).
     The second limiter pass is the reference's, quirk included: WITHOUT fourth-order slopes it is handed the zeroed
     a_WMinus / a_WPlus as one-sided differences (AdvectUtil.cpp:1116-1128), so `use_limiting` alone flattens every slope
-    and the predictor degenerates to CTU.  m_util's own m_highOrderLimiter is never set (MappedGodunovUtilities.cpp:15)."""
+    and the predictor degenerates to CTU.  With useHighOrderLimiter the van Leer slopes are limited by the
+    extremum-preserving limiter (the utilities' m_highOrderLimiter, AdvectUtil.cpp:104)."""
     if fourth_order_slopes:
-        dWvL = van_leer_slopes(W, d, use_limiting)
+        dWvL = van_leer_slopes(W, d, use_limiting, high_order)
         dWR = _sh(W, d, 1) - _sh(dWvL, d, 1) * 0.25
         dWL = _sh(W, d, -1) + _sh(dWvL, d, -1) * 0.25
         dW = TWO3RD * (dWR - dWL)
         dWm = W - _sh(W, d, -1)
         dWp = _sh(W, d, 1) - W
     else:
-        dW = van_leer_slopes(W, d, use_limiting)
+        dW = van_leer_slopes(W, d, use_limiting, high_order)
         dWm = np.zeros_like(W)
         dWp = np.zeros_like(W)
     if use_limiting or fourth_order_slopes:
@@ -180,7 +204,7 @@ def normal_pred(W, J, vel_d, d, dtbydx, use_limiting, high_order, order, fourth_
     if order == 0:      # CTUNormalPred, AdvectUtil.cpp:1043-1057: straight copies
         return W.copy(), W.copy()
     if order == 1:
-        return plm_normal_pred(W, vel_d, d, dtbydx, use_limiting, fourth_order_slopes)
+        return plm_normal_pred(W, vel_d, d, dtbydx, use_limiting, fourth_order_slopes, high_order)
     if order == 2:
         return ppm_normal_pred(W, J, vel_d, d, dtbydx, use_limiting, high_order)
     raise ValueError("normal predictor order must be 0 (CTU), 1 (PLM) or 2 (PPM)")

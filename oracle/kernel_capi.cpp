@@ -70,6 +70,16 @@ void orck_gsrb_boundary_full(RawFab* phi, const RawFab* ex, const RawFab* rhs, c
     store(p, phi);
 }
 
+void orck_line_gsrb(RawFab* phi, const RawFab* ex, const RawFab* rhs, const RawFab* jg0, const RawFab* jg1, const RawFab* jg2,
+                    const RawFab* jinv, const int* rlo, const int* rhi, const double* dx, double dzCrse, double alpha, double beta,
+                    int redBlack, const int* st6, int nd, int isDiagonal) {
+    FAB p = load(phi);
+    FAB Jg[3] = {load(jg0), load(jg1), nd > 2 ? load(jg2) : FAB()};
+    const int st[3][2] = {{st6[0], st6[1]}, {st6[2], st6[3]}, {st6[4], st6[5]}};
+    line_gsrb(p, load(ex), load(rhs), Jg, load(jinv), box3(rlo, rhi), dx, dzCrse, alpha, beta, redBlack, st, nd, isDiagonal != 0);
+    store(p, phi);
+}
+
 void orck_jacobi(RawFab* phi, const RawFab* res, const RawFab* lapDiag, const int* rlo, const int* rhi, double alpha, double beta) {
     FAB p = load(phi);
     jacobi_iter(p, load(res), load(lapDiag), box3(rlo, rhi), alpha, beta);

@@ -2,9 +2,10 @@
 //
 // Plain C++ restatement of the Chombo-Fortran kernels on SOMAR's pressure-solve hot path.
 // Each function cites the reference file:line it follows (paths relative to /root/reference).
-// The reference cannot be compiled here (needs Chombo 3.1 + Fortran + MPI + HDF5),
-// and ships no golden vectors: PARITY UNPINNED against reference outputs; pinned instead to the
-// discrete identities in tests/test_oracle_identities.py.
+// The reference cannot be compiled here (needs Chombo 3.1 + Fortran + MPI + HDF5) and ships no golden
+// vectors, but its Fortran kernels can be EXECUTED here: oracle/chf2py.py translates the .ChF sources mechanically and
+// tests/test_reference_kernels.py runs every function of this file, of smoothers.hpp and of line_transfer.hpp next to the
+// reference kernel it restates, on the same seeded arrays -- PINNED, bit for bit (fixtures tests/golden/refkernels_*.npz).
 //
 // "nd" = number of active directions: 3 for a 3-D operator, 2 for a 2-D operator (CH_SPACEDIM==2)
 // or for the horizontal operator of a 3-D run (m_horizontalOp).  2-D boxes are one cell thick in

@@ -10,8 +10,9 @@
 //   orc_leptic_add_extrusion    ADDEXTRUSION                                src/utils/SubspaceF.ChF:66-110
 //   orc_leptic_accum_div        LEPTICACCUMDIV                              LevelLepticSolverF.ChF:291-331
 //   orc_leptic_vertical_excess  LevelLepticSolver::computeVerticalExcess    LevelLepticSolver.cpp:1183-1240
-// PARITY UNPINNED against reference output (the reference cannot be built here and ships no vectors); pinned by
-// tests/test_leptic.py to the exact solution of the tridiagonal systems and to the identities the solver relies on.
+// PINNED to the reference's own Fortran for TRIDIAGPOISSONNN1DFAB, UNMAPPEDVERTINTEGRAL, ADDEXTRUSION and LEPTICACCUMDIV
+// (executed through oracle/chf2py.py; tests/test_reference_kernels.py case "leptic", identical bits); the LAPACK branch
+// (dptsv) is pinned by tests/test_leptic.py to the exact solution of the tridiagonal systems.
 //
 // Arrays are global, x fastest: cell fields (nv, [ny,] nx), J g^{zz} on vertical faces (nv+1, [ny,] nx), flat fields
 // ([ny,] nx).  `nh` = number of columns (nx*ny), `nv` = cells per column; the vertical stride is nh.

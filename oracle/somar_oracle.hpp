@@ -5,8 +5,9 @@
 //   RelaxationMethod + LevelGSRB/LooseGSRB/LineGSRB/Jacobi, FullWeightingPS, (ZeroAvg)ConstInterpPS,
 //   MappedAMRPoissonOpFactory::MGnewOp (semicoarsening schedule + coarse metrics),
 //   MappedMultiGrid::cycle, MappedAMRMultiGrid::solveNoInitResid, and a BiCGStab bottom solver.
-// Each function cites the reference file:line it follows.  PARITY UNPINNED: the reference cannot be
-// built here and ships no golden vectors.
+// Each function cites the reference file:line it follows.  KERNELS PINNED to the reference's own Fortran: oracle/chf2py.py executes the .ChF sources from /root/reference and
+// tests/test_reference_kernels.py demands identical bits (fixtures tests/golden/refkernels_{2,3}d.npz); the C++ DRIVERS above
+// the kernels stay unpinned (the reference cannot be built here and ships no golden vectors).
 #pragma once
 #include "chombo_lite.hpp"
 #include "kernels.hpp"

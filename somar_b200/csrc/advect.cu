@@ -69,6 +69,27 @@ __device__ __forceinline__ double vl_slope(double xm, double x0, double xp) {
     }
     return dWC;
 }
+// vanLeerSlopes with the utilities' m_highOrderLimiter set (MappedAdvectionUtil::define hands it useHighOrderLimiter,
+// AdvectUtil.cpp:104): slopeLimiterExtPreserving -> ExtPreservingVanLeerLimiterF, MappedGodunovUtilitiesF.ChF:190-262
+__device__ __forceinline__ double vl_slope_ext(double xm2, double xm1, double x0, double xp1, double xp2) {
+    const double dWL = x0 - xm1, dWLL = xm1 - xm2, dWR = xp1 - x0, dWRR = xp2 - xp1;
+    const double dWC = 0.5 * (dWR + dWL);
+    const double dp1 = dWL * dWR, dp2 = dWLL * dWRR;
+    double dWlim;
+    if (fmin(dp1, dp2) < 0.0) {
+        const double dW2L = dWL - dWLL;
+        const double dW2C = (dWR - dWL) * 0.5;
+        const double dW2R = dWRR - dWR;
+        const double sign2 = copysign(1.0, dW2C);
+        const double dW2lim = fmin(fmin(fabs(dW2C), fmax(sign2 * dW2L, 0.0)), fmax(sign2 * dW2R, 0.0));
+        const double cvl = 5.0 * 0.25;
+        const double dWvl = cvl * 3.0 * 0.5 * dW2lim;
+        dWlim = (sign2 * dWC < 0.0) ? fmin(dWvl, 2.0 * fabs(dWL)) : fmin(dWvl, 2.0 * fabs(dWR));
+    } else {
+        dWlim = 2.0 * fmin(fabs(dWL), fabs(dWR));
+    }
+    return copysign(1.0, dWC) * fmin(fabs(dWC), dWlim);
+}
 // PPMFaceValuesF (centre box): the face between cells -1 and 0
 template <bool LIM>
 __device__ __forceinline__ double ppm_face(double xm2, double xm1, double x0, double xp1) {
@@ -160,6 +181,7 @@ struct AStates {
     double* wminus[3];
     double* wplus[3];
     double dtbydx[3];
+    int plmExt;             // PLM: the van Leer slopes are limited by the extremum-preserving limiter (useLimiting && useHighOrderLimiter)
 };
 
 // The normal predictor of every direction at one cell.  ORDER 2: PPM (X = m_useHighOrderLimiter); ORDER 1: PLM
@@ -232,15 +254,25 @@ __global__ void __launch_bounds__(ATPB) k_adv_states(const AGeom g, const double
         } else if (ORDER == 1) {
             const double wm1 = W[aoff(g, i, j, k, d, -1)], wp1 = W[aoff(g, i, j, k, d, 1)];
             double dW, dWm = 0.0, dWp = 0.0;
+            const bool ext = LIM && a.plmExt;
             if (X) {   // FourthSlopeDiffsF (MappedGodunovUtilitiesF.ChF:96-146) + one-sided differences for the limiter
                 const double wm2 = W[aoff(g, i, j, k, d, -2)], wp2 = W[aoff(g, i, j, k, d, 2)];
-                const double vlP = vl_slope<LIM>(w, wp1, wp2);
-                const double vlM = vl_slope<LIM>(wm2, wm1, w);
+                double vlP, vlM;
+                if (ext) {
+                    const double wm3 = W[aoff(g, i, j, k, d, -3)], wp3 = W[aoff(g, i, j, k, d, 3)];
+                    vlP = vl_slope_ext(wm1, w, wp1, wp2, wp3);
+                    vlM = vl_slope_ext(wm3, wm2, wm1, w, wp1);
+                } else {
+                    vlP = vl_slope<LIM>(w, wp1, wp2);
+                    vlM = vl_slope<LIM>(wm2, wm1, w);
+                }
                 const double dWR = wp1 - vlP * 0.25;
                 const double dWL = wm1 + vlM * 0.25;
                 dW = (2.0 / 3.0) * (dWR - dWL);
                 dWm = w - wm1;
                 dWp = wp1 - w;
+            } else if (ext) {
+                dW = vl_slope_ext(W[aoff(g, i, j, k, d, -2)], wm1, w, wp1, W[aoff(g, i, j, k, d, 2)]);
             } else {
                 dW = vl_slope<LIM>(wm1, w, wp1);
             }
@@ -390,6 +422,12 @@ int advect_predict_scalar(SomarLevel* L, SomarField* const whalf[3], const Somar
         a.wminus[d] = d < nd ? wm[d] : nullptr;
         a.wplus[d] = d < nd ? wp[d] : nullptr;
         a.dtbydx[d] = dtondx[d];
+    }
+    a.plmExt = (order == 1 && lim && ho) ? 1 : 0;
+    if (multi && a.plmExt && fourth) {
+        set_error("predictScalar: PLM with fourth-order slopes and the extremum-preserving limiter reaches three rows: "
+                  "one rank only");
+        return SOMAR_ERR_ARG;
     }
     const double* src = source ? source->p : nullptr;
 #define ADV_STATES(ORDER_, LIM_, X_) \

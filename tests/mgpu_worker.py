@@ -82,6 +82,7 @@ def advect_main():
     ok = True
     combos = [dict(normal_pred_order=2, use_limiting=l, use_high_order_limiter=h) for l, h in itertools.product([False, True], repeat=2)]
     combos += [dict(normal_pred_order=1, use_limiting=l, use_fourth_order_slopes=f) for l, f in itertools.product([False, True], repeat=2)]
+    combos += [dict(normal_pred_order=1, use_limiting=True, use_high_order_limiter=True)]     # extremum-preserving van Leer slopes
     combos += [dict(normal_pred_order=0)]
     for kw in combos:
         for up, flux in ((True, True), (False, False)):

@@ -450,3 +450,269 @@ def reference_module(D):
     if not os.path.exists(path):
         return None
     return importlib.import_module("oracle._ref.chf_kernels_%dd" % D)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Advection predictor: the numpy oracle (oracle/advect_ref.py, periodic global arrays) against the reference's Fortran
+# kernels called in the order of the reference's C++ (cited), on the same arrays continued periodically by four ghost
+# layers (ADVECT_GROW).  With every direction periodic the lo / hi one-sided boxes of PeriodicLoHiCenter* are empty.
+# ---------------------------------------------------------------------------------------------------------------
+G = 4
+
+
+def _ext(a, D):
+    """(nz, ny, nx) or (ny, nx) periodic array -> Arr over [-G, n + G - 1] in every direction"""
+    b = np.pad(a, [(G, G)] * D, mode="wrap")
+    o = Arr.__new__(Arr)
+    o.D = D
+    o.lo = [-G] * D
+    o.hi = [a.shape[D - 1 - d] + G - 1 for d in range(D)]
+    o.a = np.ascontiguousarray(b[None])
+    return o
+
+
+def _like(x, fill=0.0):
+    o = x.copy()
+    o.a[...] = fill
+    return o
+
+
+def _inner(x, n, D):
+    sl = (0,) + tuple(slice(G, G + n[D - 1 - q]) for q in range(D))
+    return x.a[sl]
+
+
+def _shrunk(x, d, g):
+    lo, hi = list(x.lo), list(x.hi)
+    lo[d] += g
+    hi[d] -= g
+    return lo, hi
+
+
+def _ref_van_leer(ref, W, d, lim, ho):
+    """MappedGodunovUtilities::vanLeerSlopes, MappedGodunovUtilities.cpp:49-102 (periodic: centre box only)"""
+    D = W.D
+    dW, dWm, dWp = _like(W), _like(W), _like(W)
+    empty = _box([0] * D, [-1] * D)
+    c1 = _shrunk(W, d, 1)
+    ref.secondslopediffsf(dW.fab(), dWm.fab(), dWp.fab(), W.fab(), 1, d, empty, 0, empty, 0, _box(*c1))
+    if lim and ho:
+        ref.extpreservingvanleerlimiterf(dW.fab(), dWm.fab(), dWp.fab(), 1, d, _box(*_shrunk(W, d, 2)))
+    elif lim:
+        ref.vanleerlimiterf(dW.fab(), dWm.fab(), dWp.fab(), 1, _box(*c1))
+    return dW, dWm, dWp
+
+
+def _ref_faces(ref, X, d, lim, ho):
+    """one interpolation of MappedAdvectionUtil::PPMFaceValues (AdvectUtil.cpp:1246-1418): face f = low face of cell f"""
+    D = X.D
+    empty = _box([0] * D, [-1] * D)
+    F = _like(X)
+    fl, fh = _shrunk(X, d, 3)
+    if ho:
+        ref.fourthinterpfaces(F.fab(), X.fab(), 1, d, empty, empty, 0, empty, empty, 0, _box(fl, fh))
+    else:
+        dX, _, _ = _ref_van_leer(ref, X, d, lim, False)
+        ref.ppmfacevaluesf(F.fab(), X.fab(), dX.fab(), 1, d, empty, 0, empty, 0, _box(fl, fh))
+    return F
+
+
+def case_advect(D, ref):
+    """SecondSlopeDiffsF, VanLeerLimiterF, ExtPreservingVanLeerLimiterF, FourthSlopeDiffsF, PPMFaceValuesF, FourthInterpFaces,
+    PPMLimiterF, GETSECONDDIFF, CheckCubicLimiterF, PPMNormalPredF, PLMNormalPredF, RiemannSolver, AvgStates,
+    QuasilinearUpdateF <- MappedAdvectionUtil::PPMNormalPred / PLMNormalPred / PPMFaceValues / RiemannSolver /
+    quasilinearUpdate (AdvectUtil.cpp:944-1418) and MappedGodunovUtilities (MappedGodunovUtilities.cpp:49-500)"""
+    from oracle import advect_ref as ar
+    rng = np.random.default_rng(51)
+    n = [9, 8, 7][:D]
+    shape = tuple(reversed(n))
+    z = np.meshgrid(*[np.arange(m) / m for m in shape], indexing="ij")
+    W = np.cos(2 * np.pi * z[-1]) * np.sin(2 * np.pi * z[-2] + 0.3) + 0.35 * rng.uniform(-1, 1, shape)
+    J = 1.0 + 0.2 * rng.uniform(-1, 1, shape)
+    vel = [rng.uniform(-1, 1, shape) for _ in range(D)]
+    adv = [rng.uniform(-1, 1, shape) for _ in range(D)]
+    for a in adv:
+        a[..., ::4] = 0.0
+    dtbydx = 0.37
+    out_o, out_r = {}, ({} if ref else None)
+    W3 = W if D == 3 else W[None]
+    J3 = J if D == 3 else J[None]
+    as3 = lambda a: a if D == 3 else a[None]
+    un3 = lambda a: a if D == 3 else a[0]
+    for d in range(D):
+        for lim, ho in itertools.product([False, True], repeat=2):
+            tag = "d%d_l%d_h%d" % (d, lim, ho)
+            out_o["vl_" + tag] = un3(ar.van_leer_slopes(W3, d, lim, ho))
+            out_o["face_" + tag] = un3(ar.ppm_face_values(W3, J3, d, lim, ho))
+            m, p = ar.ppm_normal_pred(W3, J3, as3(vel[d]), d, dtbydx, lim, ho)
+            out_o["ppm_m_" + tag], out_o["ppm_p_" + tag] = un3(m), un3(p)
+            for fourth in (False, True):
+                m, p = ar.plm_normal_pred(W3, as3(vel[d]), d, dtbydx, lim, fourth, ho)
+                out_o["plm%d_m_%s" % (fourth, tag)], out_o["plm%d_p_%s" % (fourth, tag)] = un3(m), un3(p)
+        wp, wm = rng.uniform(-1, 1, shape), rng.uniform(-1, 1, shape)
+        for up in (True, False):
+            out_o["riemann_d%d_u%d" % (d, up)] = un3(ar.riemann(as3(wp), as3(wm), as3(adv[d]), d, up))
+        out_o["quasi_d%d" % d] = un3(ar.quasilinear_update(as3(wp), as3(vel[d]), -0.21, d))
+        if not ref:
+            continue
+        eW, eJ, eV = _ext(W, D), _ext(J, D), _ext(vel[d], D)
+        eJW = _ext(W * J, D)          # JW.copy(a_W); JW *= ccJ (AdvectUtil.cpp:1338-1341)
+        empty = _box([0] * D, [-1] * D)
+        for lim, ho in itertools.product([False, True], repeat=2):
+            tag = "d%d_l%d_h%d" % (d, lim, ho)
+            dW, _, _ = _ref_van_leer(ref, eW, d, lim, ho)
+            out_r["vl_" + tag] = _inner(dW, n, D)
+            # PPMFaceValues: interpolate J and J W with the same weights, divide (:1253-1417)
+            FJ, FW = _ref_faces(ref, eJ, d, lim, ho), _ref_faces(ref, eJW, d, lim, ho)
+            face = _like(eW)
+            with np.errstate(divide="ignore", invalid="ignore"):
+                face.a[...] = np.where(FJ.a != 0.0, FW.a / np.where(FJ.a != 0.0, FJ.a, 1.0), 0.0)
+            out_r["face_" + tag] = _inner(face, n, D)
+            # PPMNormalPred (:1158-1240): deltas from the two faces of the cell, limiter, predictor, "+= W"
+            dm, dp = _like(eW), _like(eW)
+            sl_hi = [slice(None)] * (D + 1)
+            sl_lo = [slice(None)] * (D + 1)
+            ax = D - d                                   # numpy axis of direction d in (1, [nz,] ny, nx)
+            sl_hi[ax] = slice(1, None)
+            sl_lo[ax] = slice(0, -1)
+            dm.a[...] = (0.0 - eW.a) + face.a
+            dp.a[tuple(sl_lo)] = (0.0 - eW.a[tuple(sl_lo)]) + face.a[tuple(sl_hi)]
+            box = _box(*_shrunk(eW, d, 3))
+            if lim and ho:                               # MappedGodunovUtilities::PPMLimiter, :386-461
+                d2fcf = _like(eW)
+                d2fcf.a[...] = (dm.a + dp.a) * 6.0
+                d2W = _like(eW)
+                ref.getseconddiff(d2W.fab(), eW.fab(), 1, d, empty, 0, empty, 0, _box(*_shrunk(eW, d, 1)))
+                ref.checkcubiclimiterf(dm.fab(), dp.fab(), eW.fab(), d2W.fab(), d2fcf.fab(), 1, d, empty, empty, 0, empty, empty, 0,
+                                       box, 1.25, 0.1, 1.0e-12)
+            elif lim:
+                ref.ppmlimiterf(dm.fab(), dp.fab(), 1, box)
+            ref.ppmnormalpredf(dm.fab(), dp.fab(), eV.fab(), dtbydx, 1, box)
+            out_r["ppm_m_" + tag] = _inner(dm, n, D) + W
+            out_r["ppm_p_" + tag] = _inner(dp, n, D) + W
+            # PLMNormalPred (:1066-1152)
+            for fourth in (False, True):
+                if fourth:
+                    dvl, _, _ = _ref_van_leer(ref, eW, d, lim, ho)
+                    dW4 = _like(eW)
+                    ref.fourthslopediffsf(dW4.fab(), eW.fab(), dvl.fab(), 1, d, empty, 0, empty, 0, box)
+                    _, dWm, dWp = _ref_van_leer(ref, eW, d, False, False)      # oneSidedDifferences (:143-171)
+                    slope = dW4
+                else:
+                    slope, _, _ = _ref_van_leer(ref, eW, d, lim, ho)
+                    dWm, dWp = _like(eW), _like(eW)                            # a_WMinus / a_WPlus .setVal(0.0)
+                if lim or fourth:
+                    ref.vanleerlimiterf(slope.fab(), dWm.fab(), dWp.fab(), 1, box)
+                pm, pp = _like(eW), _like(eW)
+                ref.plmnormalpredf(pm.fab(), pp.fab(), slope.fab(), eV.fab(), dtbydx, 1, box)
+                out_r["plm%d_m_%s" % (fourth, tag)] = _inner(pm, n, D) + W
+                out_r["plm%d_p_%s" % (fourth, tag)] = _inner(pp, n, D) + W
+        # RiemannSolver (:944-998): the left state is the W+ of the cell below the face (shiftHalf)
+        ewp, ewm, eadv = _ext(wp, D), _ext(wm, D), _ext(adv[d], D)
+        from oracle.chf_runtime import Fab
+        lo_shift = list(ewp.lo)
+        lo_shift[d] += 1
+        left = Fab(ewp.a, lo_shift)
+        fbox = _box(*_shrunk(eW, d, 2))
+        for up in (True, False):
+            g = _like(eW)
+            if up:
+                ref.riemannsolver(g.fab(), left, ewm.fab(), eadv.fab(), d, fbox)
+            else:
+                ref.avgstates(g.fab(), left, ewm.fab(), d, fbox)
+            out_r["riemann_d%d_u%d" % (d, up)] = _inner(g, n, D)
+        q = _like(eW)
+        ref.quasilinearupdatef(q.fab(), ewp.fab(), eV.fab(), -0.21, d, fbox)
+        out_r["quasi_d%d" % d] = _inner(q, n, D)
+    return out_o, out_r
+
+
+CASES["advect"] = case_advect
+
+
+def case_leptic(D, ref):
+    """TRIDIAGPOISSONNN1DFAB (src/utils/TridiagUtilsF.ChF:85-164) <- LevelLepticSolver::verticalLineSolver (:1392-1404);
+    UNMAPPEDVERTINTEGRAL, ADDEXTRUSION (src/utils/SubspaceF.ChF) and LEPTICACCUMDIV (LevelLepticSolverF.ChF:291-331) <-
+    LevelLepticSolver::computeHorizRHS / addHorizontalCorrection.  Three-dimensional build only (the vertical is z)."""
+    if D != 3:
+        return {}, ({} if ref else None)
+    from oracle import pyoracle as po
+    from oracle.chf_runtime import Fab
+    rng = np.random.default_rng(61)
+    nx, ny, nv = 5, 4, 7
+    lo = [2, -1, 0]
+    dz = 0.37
+    rhs = rng.uniform(-1, 1, (nv, ny, nx))
+    jgzz = rng.uniform(0.5, 1.5, (nv + 1, ny, nx))
+    out_o, out_r = {}, ({} if ref else None)
+    phi, _, info = po.leptic_vertical_solve(rhs, jgzz, dz, 0, 0)
+    assert info == 0
+    out_o["tridiag_nn"] = phi
+    flat0 = rng.uniform(-1, 1, (ny, nx))
+    out_o["vert_integral"] = po.leptic_vert_integral(flat0, rhs, dz)
+    out_o["add_extrusion"] = po.leptic_add_extrusion(rhs, flat0)
+    fl = [rng.uniform(-1, 1, (ny, nx + 1)), rng.uniform(-1, 1, (ny + 1, nx))]
+    for d in range(2):
+        out_o["accum_div%d" % d] = po.leptic_accum_div(flat0, fl[d], d, -1.0 / 0.21)
+    if ref:
+        hi = [lo[0] + nx - 1, lo[1] + ny - 1, lo[2] + nv - 1]
+        p = np.zeros((1, nv, ny, nx))
+        ref.tridiagpoissonnn1dfab(Fab(p, lo), Fab(np.ascontiguousarray(rhs[None]), lo), Fab(np.ascontiguousarray(jgzz[None]), lo),
+                                  _box(lo, [hi[0], hi[1], lo[2]]), nv, dz, 2)
+        out_r["tridiag_nn"] = p[0]
+        f = flat0[None, None].copy()
+        ref.unmappedvertintegral(Fab(f, [lo[0], lo[1], 0]), Fab(np.ascontiguousarray(rhs[None]), lo), _box(lo, hi), dz)
+        out_r["vert_integral"] = f[0, 0]
+        dst = np.ascontiguousarray(rhs[None].copy())
+        ref.addextrusion(Fab(dst, lo), Fab(flat0[None, None].copy(), [lo[0], lo[1], 0]), _box(lo, hi))
+        out_r["add_extrusion"] = dst[0]
+        for d in range(2):
+            r2 = np.ascontiguousarray(flat0[None, None].copy())
+            ref.lepticaccumdiv(Fab(r2, [lo[0], lo[1], 0]), Fab(np.ascontiguousarray(fl[d][None, None]), [lo[0], lo[1], 0]),
+                               _box([lo[0], lo[1], 0], [hi[0], hi[1], 0]), -1.0 / 0.21, d)
+            out_r["accum_div%d" % d] = r2[0, 0]
+    return out_o, out_r
+
+
+CASES["leptic"] = case_leptic
+
+
+def case_line_gsrb(D, ref):
+    """LineGSRBIter2D (GSRBF.ChF:1529-1729) <- LineGSRB::relax, GSRB.cpp:148-330 (work FABs D, B over [1, Nz], DU over
+    [2, Nz], DL over [1, Nz - 1]; the box is shifted so that the column starts at 0; dgtsv is LAPACK's).  The 3-D kernel
+    (:1730-2042) compares `j` with jmin / jmax, which it never assigns (:1764,1831,1835) -- undefined in Fortran and not
+    executable here -- so only the 2-D kernel can be pinned; the oracle documents its reading of the 3-D one."""
+    if D != 2:
+        return {}, ({} if ref else None)
+    from oracle.chf_runtime import Fab
+    out_o, out_r = {}, ({} if ref else None)
+    for st, rb, full, (alpha, beta) in itertools.product([(0, 1, 0, 0), (-1, -1, 0, 1), (1, 0, 1, 0), (2, 2, 0, 0)], [0, 1],
+                                                         [False, True], [(0.0, 1.0), (0.3, 0.7)]):
+        s = Setup(2, 71)
+        # the caller's shift: the vertical index of the box starts at 0
+        sh = s.lo[1]
+        for a in [s.phi, s.ex, s.rhs, s.jinv, s.lapdiag] + s.jg:
+            a.lo[1] -= sh
+            a.hi[1] -= sh
+        lo, hi = [s.lo[0], 0], [s.hi[0], s.hi[1] - sh]
+        if not full:
+            for d in range(2):
+                s.jg[d].a[1 - d] = 0.0
+        key = "st%s_rb%d_f%d_a%.1f" % ("".join(str(x + 2) for x in st), rb, full, alpha)
+        st6 = (C.c_int * 6)(*(list(st) + [0, 0]))
+        p = s.phi.copy()
+        _lib().orck_line_gsrb(p.raw(), s.ex.raw(), s.rhs.raw(), s.jg[0].raw(), s.jg[1].raw(), None, s.jinv.raw(), _i3(lo), _i3(hi),
+                              _d3(s.dx), C.c_double(2.0 * s.dx[1]), C.c_double(alpha), C.c_double(beta), rb, st6, 2, int(not full))
+        out_o[key] = p.a
+        if ref:
+            q = s.phi.copy()
+            nz = hi[1] + 1
+            Dw, Bw = Fab(np.zeros((1, 1, nz)), [1, 1]), Fab(np.zeros((1, 1, nz)), [1, 1])
+            DUw, DLw = Fab(np.zeros((1, 1, nz - 1)), [2, 1]), Fab(np.zeros((1, 1, nz - 1)), [1, 1])
+            ref.linegsrbiter2d(q.fab(), s.ex.fab(), s.rhs.fab(), s.jg[0].fab(), s.jg[1].fab(), s.jinv.fab(), _box(lo, hi), _vec(s.dx),
+                               2.0 * s.dx[1], alpha, beta, rb, DUw, Dw, DLw, Bw, *st)
+            out_r[key] = q.a
+    return out_o, out_r
+
+
+CASES["line_gsrb"] = case_line_gsrb

@@ -178,14 +178,14 @@ def test_predict_scalar_parity(dim, n, somar):
             got = out[d].get()
             assert np.array_equal(got, want[d]), (dim, d, lim, up, with_src, flux, ho, np.abs(got - want[d]).max())
     # the other two normal predictors: CTU (order 0) and PLM (order 1, with and without fourth-order slopes)
-    for order, lim, fourth, with_src in itertools.product([0, 1], [False, True], [False, True], [False, True]):
+    for order, lim, fourth, with_src, ho in itertools.product([0, 1], [False, True], [False, True], [False, True], [False, True]):
         lev.advect_predict_scalar(out, fW, fov, fav, fJ, dt, source=fS if with_src else None, use_limiting=lim,
-                                  normal_pred_order=order, use_fourth_order_slopes=fourth)
+                                  normal_pred_order=order, use_fourth_order_slopes=fourth, use_high_order_limiter=ho)
         want = ar.predict_scalar(W, J, ov, av, dt, pb.spec.dx, dim, source=src if with_src else None, use_limiting=lim,
-                                 normal_pred_order=order, fourth_order_slopes=fourth)
+                                 normal_pred_order=order, fourth_order_slopes=fourth, high_order=ho)
         for d in range(dim):
             got = out[d].get()
-            assert np.array_equal(got, want[d]), (dim, d, order, lim, fourth, with_src, np.abs(got - want[d]).max())
+            assert np.array_equal(got, want[d]), (dim, d, order, lim, fourth, with_src, ho, np.abs(got - want[d]).max())
     lev.advect_predict_scalar(out, fW, fov, fav, fJ, dt, source=fS, use_limiting=True, use_high_order_limiter=True)
     # the flux's periodic image is in place: the MAC divergence of the device equals the wrapped numpy divergence
     div = lev.field(0)

@@ -27,6 +27,8 @@ def _gold(D):
 @pytest.mark.parametrize("name", list(rk.CASES))
 def test_oracle_kernel_reproduces_reference_fixture(name, D, oracle_lib):
     out_o, _ = rk.CASES[name](D, None)
+    if not out_o:
+        pytest.skip("this kernel exists for the other CH_SPACEDIM only")
     g = _gold(D)
     keys = [k for k in g.files if k.startswith(name + "/")]
     assert len(keys) == len(out_o) and keys, (name, D, len(keys), len(out_o))
@@ -52,7 +54,7 @@ def test_reference_kernels_run_here_and_match(D, oracle_lib):
             assert np.array_equal(a, b), "%s %dD %s: oracle vs reference, max diff %.3e" % (name, D, k, np.abs(a - b).max())
             assert np.array_equal(b, g[name + "/" + k]), "%s %dD %s: the committed fixture is stale" % (name, D, k)
             n += 1
-    assert n > 100
+    assert n > 200
 
 
 def test_translator_covers_the_hot_path_kernels():
@@ -68,5 +70,7 @@ def test_translator_covers_the_hot_path_kernels():
               "mappedgetflux", "mappedgetfluxortho", "fillmappedlapdiag3d", "diagprecond", "mappedfluxdivergence3d",
               "mappedmacgrad", "mappedmacgradortho", "ellipticconstneumbcghost", "ellipticconstdiribcghost",
               "extrapolatefacenoev", "mappedaverage2", "constinterpps", "constinterpwithavgps", "jacobiiter",
-              "ppmfacevaluesf", "ppmlimiterf", "ppmnormalpredf", "checkcubiclimiterf", "riemannsolver", "quasilinearupdatef"]:
+              "ppmfacevaluesf", "ppmlimiterf", "ppmnormalpredf", "checkcubiclimiterf", "riemannsolver", "quasilinearupdatef",
+              "plmnormalpredf", "fourthslopediffsf", "extpreservingvanleerlimiterf", "linegsrbiter2d", "tridiagpoissonnn1dfab",
+              "lepticaccumdiv", "unmappedvertintegral", "addextrusion"]:
         assert k in done, k
