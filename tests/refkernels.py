@@ -716,3 +716,71 @@ def case_line_gsrb(D, ref):
 
 
 CASES["line_gsrb"] = case_line_gsrb
+
+
+def _adj(lo, hi, d, side):
+    lo, hi = list(lo), list(hi)
+    if side == 0:
+        lo[d] = hi[d] = lo[d] - 1
+    else:
+        lo[d] = hi[d] = hi[d] + 1
+    return lo, hi
+
+
+def _isect(a, b):
+    lo = [max(x, y) for x, y in zip(a[0], b[0])]
+    hi = [min(x, y) for x, y in zip(a[1], b[1])]
+    return lo, hi
+
+
+def case_leptic_bdry_gradient(D, ref):
+    """LEPTICVERTHORIZGRAD (LevelLepticSolverF.ChF:74-122) <- LevelLepticSolver::levelVertHorizGradient (:1107-1176), with its
+    in-place ExtrapolateFaceAndCopy (ExtrapolationUtils.cpp:109-163, EXTRAPOLATEFACENOEV) restated box by box in this
+    harness, against the oracle's Op::lepticVertHorizGradient on a single-box terrain-following level"""
+    if D != 3:
+        return {}, ({} if ref else None)
+    from common import Problem
+    from oracle import pyoracle as po
+    from oracle.chf_runtime import Fab
+    pb = Problem(n=(10, 8, 6), map_name="terrain", aniso=4.0)
+    orc = pb.oracle(po)
+    phi = np.random.default_rng(81).uniform(-1, 1, pb.shape)
+    lo_o, hi_o = orc.leptic_vert_horiz_grad(phi, -1.0)
+    out_o, out_r = {"lo": lo_o, "hi": hi_o}, None
+    if ref:
+        nx, ny, nz = pb.n
+        dom = ([0, 0, 0], [nx - 1, ny - 1, nz - 1])
+        fab = ([-1, -1, -1], [nx, ny, nz])
+        out_r = {}
+        for side, name in ((0, "lo"), (1, "hi")):
+            p = np.zeros((1, nz + 2, ny + 2, nx + 2))
+            p[0, 1:-1, 1:-1, 1:-1] = phi
+            P = Fab(p, fab[0])
+            sign = 1 if side else -1
+
+            def noev(box, d, s):                                   # ExtrapolateFaceNoEV, :34-62
+                to = _isect(_adj(box[0], box[1], d, s), fab)
+                if all(a <= b for a, b in zip(*to)):
+                    ref.extrapolatefacenoev(P, P, _box(*to), d, 1 if s else -1, 2)
+            valid = _isect(fab, dom)                               # domValid = phiFAB.box() & domain
+            noev(valid, 2, side)
+            ghost = _isect(_adj(valid[0], valid[1], 2, side), fab)
+            near = ([ghost[0][0], ghost[0][1], ghost[0][2] - sign], [ghost[1][0], ghost[1][1], ghost[1][2] - sign])
+            for edir in (0, 1):
+                for es in (0, 1):
+                    noev(ghost, edir, es)
+                    noev(near, edir, es)
+                for b in (ghost, near):
+                    b[0][edir] -= 1
+                    b[1][edir] += 1
+                ghost, near = _isect(ghost, fab), _isect(near, fab)
+            kf = nz if side else 0
+            bc = np.zeros((1, 1, ny, nx))
+            jgz = np.ascontiguousarray(np.asarray(pb.jgup[2]))       # (3, nz + 1, ny, nx)
+            ref.lepticverthorizgrad(Fab(bc, [0, 0, kf]), P, Fab(jgz, [0, 0, 0]), _box([0, 0, kf], [nx - 1, ny - 1, kf]), sign,
+                                    _vec(pb.spec.dx), -1.0)
+            out_r[name] = bc[0, 0]
+    return out_o, out_r
+
+
+CASES["leptic_bdry_gradient"] = case_leptic_bdry_gradient
