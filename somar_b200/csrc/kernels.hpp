@@ -58,7 +58,7 @@ void launch_line_gsrb(Ctx& cx, const Geom& g, const Metric& m, double* phiOut, c
 // ---- transfers ----
 // coarse = J-weighted average of (rhs - L phi) over the ratio block   (restrictResidual + MAPPEDAVERAGE2)
 void launch_restrict_residual(Ctx& cx, const Geom& gf, const Metric& mf, const Geom& gc, double* crse,
-                              const double* phi, const double* rhs, const int ratio[3]);
+                              const double* phi, const double* rhs, const int ratio[3], double* scratch = nullptr);
 // fine += coarse[i/m]; if sums != nullptr also sums[0] += sum(dV*fine), sums[1] += sum(dV)  (ConstInterp[WithAvg]PS)
 void launch_prolong(Ctx& cx, const Geom& gf, const Metric& mf, const Geom& gc, double* fine, const double* crse,
                     const int ratio[3], double dxProduct, double* sums);

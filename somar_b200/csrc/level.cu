@@ -328,6 +328,13 @@ int op_relax(SomarLevel* L, int depth, SomarField* phi, const SomarField* rhs, i
     Depth& dp = L->depths[depth];
     const int mode = (modeOverride != -100) ? modeOverride : L->prm.relaxMode;
     int rc;
+    if (mode == SOMAR_RELAX_LINE_GSRB && dp.g.bs[dp.g.nd - 1] != dp.g.gn[dp.g.nd - 1]) {
+        // LineGSRB::relax solves one tridiagonal system per BOX column (GSRB.cpp:177-330); a box side inside the domain gets
+        // the low-order closure (coefficient 0, GSRBF.ChF:1590-1604), so vertically split boxes give a different smoother.
+        // The kernels here solve whole columns, which is that smoother only when every box spans the vertical.
+        set_error("relax: LineGSRB needs boxes that span the vertical (per-box line solves on vertically split boxes are not built)");
+        return SOMAR_ERR_LAYOUT;
+    }
     // phiIsZero: the caller skipped "set the correction to zero".  The pipelined smoother then takes every input plane
     // of its first iteration from the level's zero plane (no DRAM read of phi, no fill pass, no halo exchange: every
     // rank's phi is zero); any other smoother gets the fill it would have had.
@@ -447,7 +454,7 @@ int op_restrict(SomarLevel* L, int depth, SomarField* crse, SomarField* phi, con
     Depth& dp = L->depths[depth];
     int rc = exchange(L, depth, phi->p, 1);
     if (rc != SOMAR_OK) return rc;
-    launch_restrict_residual(L->cx, dp.g, dp.m, L->depths[depth + 1].g, crse->p, phi->p, rhs->p, dp.ratio);
+    launch_restrict_residual(L->cx, dp.g, dp.m, L->depths[depth + 1].g, crse->p, phi->p, rhs->p, dp.ratio, dp.tmp);
     return SOMAR_OK;
 }
 

@@ -1,5 +1,8 @@
 // ops_ortho.cu -- diagonal-metric operator kernels: apply / residual, red-black point relaxation, Jacobi,
 // diagonal preconditioner, fused residual+restriction.  HBM-bound fp64 streaming kernels (DESIGN.md "Kernels").
+#include <algorithm>
+#include <cstdlib>
+
 #include "kernels.hpp"
 #include "stencil_ortho.cuh"
 #include "stencil_full.cuh"
@@ -21,9 +24,87 @@ __device__ __forceinline__ bool full_inner_xy(const Geom& g, int i, int j) {
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// Full metric: the cells that touch a side of their box take the general statement (box-relative extrapolated views,
+// ExView), which is an order of magnitude longer than the branch-free one.  In a thread-per-cell mapping the two x-edge
+// cells of a row put it into that row's first and last warp with ONE active lane (ncu on k_gsrb_full,
+// profiles/r2_ncu_k_gsrb_full.txt: 15 of 32 lanes active on average, 2.6 warps per scheduler), so the full-metric kernels
+// run in two launches: the box-interior cells, and the rim cells mapped densely onto lanes -- three slabs, each rim cell
+// in exactly one: blockIdx.z < nzr: the z-rim planes, all (i, j); then the y-rim rows of the other planes, all i; then
+// the x-rim columns of what is left (lanes along j).  The m-th rim index of a direction is side m % 2 of local box m / 2
+// (a rank owns whole boxes); a one-cell-thick box has one.
+// ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ int rim_index(const Geom& g, int d, int m) {
+    return (g.bs[d] > 1) ? (m >> 1) * g.bs[d] + ((m & 1) ? g.bs[d] - 1 : 0) : m;
+}
+__device__ __forceinline__ int rim_count(const Geom& g, int d) { return (g.bs[d] > 1) ? 2 * (g.n[d] / g.bs[d]) : g.n[d]; }
+
+// One block row per rim line: `row` (blockIdx.y + gridDim.y * blockIdx.z) counts the nzr * n1 rows of the z-rim planes, then
+// nyr rows for each plane, then nxr columns for each plane; blockIdx.x tiles the line.
+#ifndef RIM_MINB
+#define RIM_MINB 4
+#endif
+template <int ND>
+__device__ __forceinline__ bool rim_cell(const Geom& g, int nzr, int nyr, int nxr, int& i, int& j, int& k, int pass = -1) {
+    // pass >= 0: only the cells of that colour, two cells of the line per lane step
+    const int lane0 = blockIdx.x * blockDim.x + threadIdx.x;
+    const int gsum = g.g0[0] + g.g0[1] + ((ND > 2) ? g.g0[2] : 0) + pass;
+#define RIM_LANE(a, b) ((pass < 0) ? lane0 : 2 * lane0 + ((gsum + (a) + (b)) & 1))
+    const int planes = (ND > 2) ? g.n[2] : 1;
+    int row = blockIdx.y + gridDim.y * blockIdx.z;
+    if (row < nzr * g.n[1]) {                                    // slab Z
+        k = rim_index(g, 2, row / g.n[1]);
+        j = row % g.n[1];
+        i = RIM_LANE(j, k);
+        return i < g.n[0];
+    }
+    row -= nzr * g.n[1];
+    if (row < planes * nyr) {                                    // slab Y
+        k = row / nyr;
+        j = rim_index(g, 1, row % nyr);
+        i = RIM_LANE(j, k);
+        if (ND > 2 && !box_inner_dir<ND>(g, k, 2)) return false;
+        return i < g.n[0];
+    }
+    row -= planes * nyr;
+    if (row >= planes * nxr) return false;
+    k = row / nxr;                                               // slab X: lanes along j
+    i = rim_index(g, 0, row % nxr);
+    j = RIM_LANE(i, k);
+    if (ND > 2 && !box_inner_dir<ND>(g, k, 2)) return false;
+    return j < g.n[1] && box_inner_dir<ND>(g, j, 1);
+#undef RIM_LANE
+}
+
+// host side: can this rank's part of the depth be split (whole boxes in every direction), and the rim kernel's grid
+static bool rim_split_usable(const Geom& g) {
+    static const bool on = []() { const char* e = getenv("SOMAR_B200_FULL_SPLIT"); return !(e && e[0] == '0'); }();
+    if (!on) return false;
+    for (int d = 0; d < g.nd; ++d)
+        if (g.bs[d] <= 0 || g.n[d] % g.bs[d] != 0 || g.g0[d] % g.bs[d] != 0) return false;
+    return true;
+}
+struct RimGrid {
+    dim3 grid;
+    int nzr, nyr, nxr;
+};
+static RimGrid rim_grid(const Geom& g, bool oneColour = false) {
+    auto cnt = [&](int d) { return (g.bs[d] > 1) ? 2 * (g.n[d] / g.bs[d]) : g.n[d]; };
+    RimGrid r;
+    r.nzr = (g.nd == 3) ? cnt(2) : 0;
+    r.nyr = cnt(1);
+    r.nxr = cnt(0);
+    const int planes = (g.nd == 3) ? g.n[2] : 1;
+    const long long rows = (long long)r.nzr * g.n[1] + (long long)planes * (r.nyr + r.nxr);
+    const int gy = (int)std::min<long long>(rows, 32768);
+    const int line = std::max(g.n[0], g.n[1]);
+    r.grid = dim3(((oneColour ? (line + 1) / 2 : line) + 127) / 128, gy, (unsigned)((rows + gy - 1) / gy));
+    return r;
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // apply / residual: one thread per cell of an (BX x BY) tile, marching KZ planes in z.
 // ---------------------------------------------------------------------------------------------------------
-template <int ND, bool FULL>
+template <int ND, bool FULL, bool SPLIT = false>
 __global__ void __launch_bounds__(BX* BY) k_apply(const Geom g, const Metric m, double* __restrict__ out,
                                                    const double* __restrict__ phi, const double* __restrict__ rhs,
                                                    int mode, bool homog, int kz) {
@@ -38,12 +119,24 @@ __global__ void __launch_bounds__(BX* BY) k_apply(const Geom g, const Metric m, 
         double v;
         if (FULL) {
             if (innerXY && (ND < 3 || box_inner_dir<ND>(g, k, 2))) v = apply_cell_full_inner<ND>(g, m, phi, i, j, k, c, homog);
+            else if (SPLIT) continue;                            // left to k_apply_full_rim
             else v = apply_cell_full<ND>(g, m, phi, i, j, k, c, homog);
         } else {
             v = apply_cell_ortho<ND>(g, m, phi, i, j, k, c, homog);
         }
         out[c] = mode ? (rhs[c] - v) : v;
     }
+}
+
+template <int ND>
+__global__ void __launch_bounds__(128, RIM_MINB) k_apply_full_rim(const Geom g, const Metric m, double* __restrict__ out,
+                                                         const double* __restrict__ phi, const double* __restrict__ rhs,
+                                                         int mode, bool homog, int nzr, int nyr, int nxr) {
+    int i, j, k;
+    if (!rim_cell<ND>(g, nzr, nyr, nxr, i, j, k)) return;
+    const long long c = g.idx(i, j, k);
+    const double v = apply_cell_full_kind<ND>(g, m, phi, i, j, k, c, homog, cell_kind<ND>(g, i, j, k));
+    out[c] = mode ? (rhs[c] - v) : v;
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -171,8 +264,18 @@ void launch_apply(Ctx& cx, const Geom& g, const Metric& m, double* out, const do
         if (g.nd == 3) k_apply<3, false><<<grid, block, 0, cx.stream>>>(g, m, out, phi, rhs, mode, homog, kz);
         else k_apply<2, false><<<grid, block, 0, cx.stream>>>(g, m, out, phi, rhs, mode, homog, kz);
     } else {
-        if (g.nd == 3) k_apply<3, true><<<grid, block, 0, cx.stream>>>(g, m, out, phi, rhs, mode, homog, kz);
-        else k_apply<2, true><<<grid, block, 0, cx.stream>>>(g, m, out, phi, rhs, mode, homog, kz);
+        const bool split = rim_split_usable(g);
+        if (!split) {
+            if (g.nd == 3) k_apply<3, true><<<grid, block, 0, cx.stream>>>(g, m, out, phi, rhs, mode, homog, kz);
+            else k_apply<2, true><<<grid, block, 0, cx.stream>>>(g, m, out, phi, rhs, mode, homog, kz);
+        } else {
+            if (g.nd == 3) k_apply<3, true, true><<<grid, block, 0, cx.stream>>>(g, m, out, phi, rhs, mode, homog, kz);
+            else k_apply<2, true, true><<<grid, block, 0, cx.stream>>>(g, m, out, phi, rhs, mode, homog, kz);
+            const RimGrid r = rim_grid(g);
+            if (g.nd == 3) k_apply_full_rim<3><<<r.grid, 128, 0, cx.stream>>>(g, m, out, phi, rhs, mode, homog, r.nzr, r.nyr, r.nxr);
+            else k_apply_full_rim<2><<<r.grid, 128, 0, cx.stream>>>(g, m, out, phi, rhs, mode, homog, r.nzr, r.nyr, r.nxr);
+            cx.launches++;
+        }
     }
     cx.launches++;
 }
@@ -270,7 +373,11 @@ void launch_gsrb_loose(Ctx& cx, const Geom& g, const Metric& m, double* phi, con
 // A thread owns the x-adjacent PAIR (2t, 2t+1) of a row: exactly one of the two cells is of the pass's colour in any
 // plane, so every lane computes (a thread per cell idles the lanes of the other colour) and the pair leaves as one
 // 16-byte store.  Box-interior cells take the branch-free statement.
-template <int ND>
+// SPLIT: cells that touch a side of their box are left to k_gsrb_full_rim (their old value is copied).  The general
+// statement (box-relative extrapolated views, ExView) is an order of magnitude longer than the branch-free one, and in
+// this kernel's mapping the two x-edge cells of a row put it into two of the row's eight warps with ONE active lane:
+// ncu (profiles/r2_ncu_k_gsrb_full.txt) shows 15 of 32 lanes active on average and 2.6 warps per scheduler.
+template <int ND, bool SPLIT>
 __global__ void __launch_bounds__(BX* BY) k_gsrb_full(const Geom g, const Metric m, double* __restrict__ phiOut,
                                                        const double* __restrict__ phiIn,
                                                        const double* __restrict__ rhs, int pass, int kz) {
@@ -291,9 +398,11 @@ __global__ void __launch_bounds__(BX* BY) k_gsrb_full(const Geom g, const Metric
         double va = phiIn[c], vb = two ? phiIn[c + 1] : 0.0;
         if (i < g.n[0]) {
             const bool inner = (par ? inner1 : inner0) && (ND < 3 || box_inner_dir<ND>(g, k, 2));
-            const double v = inner ? gsrb_cell_full_inner<ND>(g, m, phiIn, rhs, i, j, k, c + par)
-                                   : gsrb_cell_full<ND>(g, m, phiIn, rhs, i, j, k, c + par);
-            if (par) vb = v; else va = v;
+            if (inner || !SPLIT) {
+                const double v = inner ? gsrb_cell_full_inner<ND>(g, m, phiIn, rhs, i, j, k, c + par)
+                                       : gsrb_cell_full<ND>(g, m, phiIn, rhs, i, j, k, c + par);
+                if (par) vb = v; else va = v;
+            }
         }
         if (two && ((c & 1) == 0)) {
             *reinterpret_cast<double2*>(phiOut + c) = make_double2(va, vb);
@@ -304,14 +413,33 @@ __global__ void __launch_bounds__(BX* BY) k_gsrb_full(const Geom g, const Metric
     }
 }
 
+template <int ND>
+__global__ void __launch_bounds__(128, RIM_MINB) k_gsrb_full_rim(const Geom g, const Metric m, double* __restrict__ phiOut,
+                                                        const double* __restrict__ phiIn, const double* __restrict__ rhs,
+                                                        int pass, int nzr, int nyr, int nxr) {
+    int i, j, k;
+    if (!rim_cell<ND>(g, nzr, nyr, nxr, i, j, k, pass)) return;
+    const long long c = g.idx(i, j, k);
+    phiOut[c] = gsrb_cell_full_kind<ND>(g, m, phiIn, rhs, i, j, k, c, cell_kind<ND>(g, i, j, k));
+}
+
 void launch_gsrb_full(Ctx& cx, const Geom& g, const Metric& m, double* phiOut, const double* phiIn,
                       const double* rhs, int pass) {
     const int kz = (g.n[2] >= 64) ? 8 : 1;
     const int half = (g.n[0] + 1) / 2;
     dim3 grid((half + BX - 1) / BX, (g.n[1] + BY - 1) / BY, (g.n[2] + kz - 1) / kz), block(BX, BY);
-    if (g.nd == 3) k_gsrb_full<3><<<grid, block, 0, cx.stream>>>(g, m, phiOut, phiIn, rhs, pass, kz);
-    else k_gsrb_full<2><<<grid, block, 0, cx.stream>>>(g, m, phiOut, phiIn, rhs, pass, kz);
-    cx.launches++;
+    if (!rim_split_usable(g)) {
+        if (g.nd == 3) k_gsrb_full<3, false><<<grid, block, 0, cx.stream>>>(g, m, phiOut, phiIn, rhs, pass, kz);
+        else k_gsrb_full<2, false><<<grid, block, 0, cx.stream>>>(g, m, phiOut, phiIn, rhs, pass, kz);
+        cx.launches++;
+        return;
+    }
+    if (g.nd == 3) k_gsrb_full<3, true><<<grid, block, 0, cx.stream>>>(g, m, phiOut, phiIn, rhs, pass, kz);
+    else k_gsrb_full<2, true><<<grid, block, 0, cx.stream>>>(g, m, phiOut, phiIn, rhs, pass, kz);
+    const RimGrid r = rim_grid(g, true);
+    if (g.nd == 3) k_gsrb_full_rim<3><<<r.grid, 128, 0, cx.stream>>>(g, m, phiOut, phiIn, rhs, pass, r.nzr, r.nyr, r.nxr);
+    else k_gsrb_full_rim<2><<<r.grid, 128, 0, cx.stream>>>(g, m, phiOut, phiIn, rhs, pass, r.nzr, r.nyr, r.nxr);
+    cx.launches += 2;
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -401,8 +529,38 @@ __global__ void __launch_bounds__(BX* BY) k_restrict(const Geom gf, const Metric
     crse[gc.idx(ic, jc, kc)] = s / sj;
 }
 
+// the averaging half alone, of a residual already in HBM (same sums, same order)
+__global__ void __launch_bounds__(BX* BY) k_restrict_avg(const Geom gf, const Metric mf, const Geom gc,
+                                                          double* __restrict__ crse, const double* __restrict__ res,
+                                                          int r0, int r1, int r2) {
+    const int ic = blockIdx.x * BX + threadIdx.x;
+    const int jc = blockIdx.y * BY + threadIdx.y;
+    const int kc = blockIdx.z;
+    if (ic >= gc.n[0] || jc >= gc.n[1]) return;
+    double s = 0.0, sj = 0.0;
+    for (int kk = 0; kk < r2; ++kk)
+        for (int jj = 0; jj < r1; ++jj)
+            for (int ii = 0; ii < r0; ++ii) {
+                const long long c = gf.idx(ic * r0 + ii, jc * r1 + jj, kc * r2 + kk);
+                const double ji = mf.jinv[c];
+                s = s + res[c] / ji;
+                sj = sj + 1.0 / ji;
+            }
+    crse[gc.idx(ic, jc, kc)] = s / sj;
+}
+
 void launch_restrict_residual(Ctx& cx, const Geom& gf, const Metric& mf, const Geom& gc, double* crse,
-                              const double* phi, const double* rhs, const int r[3]) {
+                              const double* phi, const double* rhs, const int r[3], double* scratch) {
+    if (!mf.diagonal && scratch && rim_split_usable(gf)) {
+        // full metric: the residual through the inner / rim pair of launch_apply (the general cells densely packed), then
+        // the average; 16 B per fine cell more traffic, several times less time than one thread per coarse cell running
+        // the general statement for the rim cells of its block
+        launch_apply(cx, gf, mf, scratch, phi, rhs, 1, true);
+        dim3 grid((gc.n[0] + BX - 1) / BX, (gc.n[1] + BY - 1) / BY, gc.n[2]), block(BX, BY);
+        k_restrict_avg<<<grid, block, 0, cx.stream>>>(gf, mf, gc, crse, scratch, r[0], r[1], r[2]);
+        cx.launches++;
+        return;
+    }
     if (mf.diagonal && gf.nd == 3 && r[0] == 1 && r[1] == 1 && r[2] == 2 && (gf.n[2] & 1) == 0) {
         // vertical semicoarsening (the anisotropic case): z-marching kernel
         const int kzm = march_kz(gf);

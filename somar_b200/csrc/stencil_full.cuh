@@ -150,6 +150,178 @@ __device__ __forceinline__ bool box_inner_dir(const Geom& g, int q, int d) {
     return r != 0 && r != g.bs[d] - 1;
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Which accessor a cell needs.  ex_slow's rules, read per direction d of the cell q being updated (every access is within one
+// cell of q):
+//   class 0  q[d] touches no side of its box and is at least two cells from a Neumann DOMAIN side
+//   class 1  touches no side, but sits next to the first layer of (one cell from) a Neumann domain side
+//   class 2  touches only box-box interfaces, and is not within one cell of a Neumann domain side
+//   class 3  touches a domain side (any type), or touches an interface within one cell of a Neumann domain side
+// An access leaves the box only in directions of class 2 / 3; `force` (order-2 extrapolation of every direction left) needs
+// a Neumann side crossed (class 3) or a point in the first layer next to one while another direction is left (class 1 or 3
+// together with a class 2 / 3).  Hence:
+//   CELL_FAST     no class 3, and not (a class 2 together with a class 1): every ex() is phi (interfaces read the halo);
+//   CELL_DIR0..2  exactly one direction of class 3, the others class 0: only that direction can be left, and `force` is
+//                 "the side crossed is Neumann" -- DirView below;
+//   CELL_GENERAL  the rest (edges and corners of the boxes next to the domain boundary): ExView.
+// ---------------------------------------------------------------------------------------------------------
+enum { CELL_FAST = 0, CELL_DIR0 = 1, CELL_DIR1 = 2, CELL_DIR2 = 3, CELL_GENERAL = 4 };
+
+__device__ __forceinline__ int cell_dir_class(const Geom& g, int q, int d) {
+    const int gq = q + g.g0[d];
+    const int r = gq % g.bs[d];
+    const bool touch = (r == 0) || (r == g.bs[d] - 1);
+    const bool nearN = (gq <= 1 && g.bct[d][0] == BC_NEUM) || (gq >= g.gn[d] - 2 && g.bct[d][1] == BC_NEUM);
+    if (!touch) return nearN ? 1 : 0;
+    const bool dom = (gq == 0) || (gq == g.gn[d] - 1);
+    return (dom || nearN) ? 3 : 2;
+}
+
+template <int ND>
+__device__ __forceinline__ int cell_kind(const Geom& g, int i, int j, int k) {
+    const int c0 = cell_dir_class(g, i, 0), c1 = cell_dir_class(g, j, 1), c2 = (ND > 2) ? cell_dir_class(g, k, 2) : 0;
+    const bool any3 = (c0 == 3) | (c1 == 3) | (c2 == 3);
+    const bool any2 = (c0 == 2) | (c1 == 2) | (c2 == 2);
+    const bool any1 = (c0 == 1) | (c1 == 1) | (c2 == 1);
+    if (!any3 && !(any2 && any1)) return CELL_FAST;
+    if (c0 == 3 && c1 == 0 && c2 == 0) return CELL_DIR0;
+    if (c1 == 3 && c0 == 0 && c2 == 0) return CELL_DIR1;
+    if (ND > 2 && c2 == 3 && c0 == 0 && c1 == 0) return CELL_DIR2;
+    return CELL_GENERAL;
+}
+
+// value of an order-`ord` extrapolation from the three values one, two and three steps inside (ExRec's expressions)
+__device__ __forceinline__ double ex_comb(int ord, double s1, double s2, double s3) {
+    const double r1 = 2.0 * s1 - s2, r2 = 3.0 * (s1 - s2) + s3;
+    return (ord == 0) ? s1 : (ord == 1 ? r1 : r2);
+}
+// how many steps inside the K-th value (K = 0, 1, 2) of an order-`ord` extrapolation sits; a value the order does not use
+// repeats the last one it does, so that no address is read that ex_slow would not read
+__device__ __forceinline__ int ex_steps(int ord, int K) { return (ord == 0) ? 0 : ((K < ord) ? K + 1 : ord + 1); }
+
+// The accessors below are written for memory-level parallelism.  ex_slow / ExView reach every value through branches and
+// calls, so the ~50 reads of a cell's statement are issued one behind the other: a thread needs tens of microseconds for its
+// cell, and on a coarse depth (few warps) that latency IS the launch.  Here every read is unconditional -- a direction that is
+// not extrapolated reads offset 0 three times -- and whether a direction CAN be left is decided at compile time from the
+// point's offset from the cell (a constant at every call site of the statements).
+
+// Accessor of a CELL_DIR<D> cell: ex_slow with every direction but D known to stay inside the box.
+template <int ND, int D>
+struct DirView {
+    const double* __restrict__ phi;
+    long long base;      // index of the cell
+    long long sy, sz;
+    int i0, j0, k0;
+    int ordLo, ordHi;    // order of the extrapolation one cell below / above the cell in direction D; 0: phi itself (the
+                         // point is inside the box, or behind a box-box interface: the neighbour's phi)
+    __device__ __forceinline__ DirView(const Geom& g, const double* __restrict__ phi_, int i, int j, int k, long long c, int mode)
+        : phi(phi_), base(c), sy(g.sy), sz(g.sz), i0(i), j0(j), k0(k) {
+        const int q = (D == 0) ? i : (D == 1 ? j : k);
+        const int gq = q + g.g0[D];
+        const int glo = (gq / g.bs[D]) * g.bs[D], ghi = glo + g.bs[D] - 1;
+        const int tLo = (glo == 0) ? g.bct[D][0] : SIDE_INTERNAL, tHi = (ghi == g.gn[D] - 1) ? g.bct[D][1] : SIDE_INTERNAL;
+        ordLo = (gq == glo) ? side_order(tLo, mode) : 0;
+        ordHi = (gq == ghi) ? side_order(tHi, mode) : 0;
+    }
+    __device__ static __forceinline__ int side_order(int t, int mode) {
+        if (t == BC_NEUM) return 2;                                  // force
+        if (t == SIDE_INTERNAL) return 0;
+        if (t == BC_PERIODIC) return (mode == EXMODE_OP) ? 0 : 1;
+        return (mode == EXMODE_OP) ? 2 : 1;
+    }
+    __device__ __forceinline__ double ex(int i, int j, int k) const {
+        const int di = i - i0, dj = j - j0, dk = k - k0;            // constants at the call sites
+        const long long a = base + di + sy * dj + sz * dk;
+        const int dq = (D == 0) ? di : (D == 1 ? dj : dk);
+        if (dq == 0) return phi[a];
+        const int ord = (dq < 0) ? ordLo : ordHi;
+        const long long st = (D == 0) ? 1 : (D == 1 ? sy : sz);
+        const long long in = (dq < 0) ? st : -st;                    // one step back into the box
+        const double s1 = phi[a + ex_steps(ord, 0) * in], s2 = phi[a + ex_steps(ord, 1) * in], s3 = phi[a + ex_steps(ord, 2) * in];
+        return ex_comb(ord, s1, s2, s3);
+    }
+};
+
+// Accessor of a CELL_GENERAL cell.  The 48 ex() reads of a cell's statement visit 18 points only (the 6 face and 12 edge
+// neighbours; 8 in 2-D): each is evaluated once, ex_slow's rules with the nested extrapolation laid out flat -- 3 values for a
+// face neighbour, 9 for an edge neighbour, loaded unconditionally and combined in ExRec's order (lowest direction innermost):
+// the same expressions, the same bits.
+template <int ND>
+struct TabView {
+    // the values as scalars (an array member keeps the whole view, its i0/j0/k0 included, in local memory: the compiler then
+    // cannot fold ex()'s index); slot = (di+1) + 3 (dj+1) + 9 (dk+1)
+    double e1, e3, e4, e5, e7;                                         // dk = -1
+    double e9, e10, e11, e12, e14, e15, e16, e17;                      // dk = 0
+    double e19, e21, e22, e23, e25;                                    // dk = +1
+    int i0, j0, k0;
+    template <int DI, int DJ, int DK>
+    __device__ static __forceinline__ double eval(const Geom& g, const double* __restrict__ phi, const BoxOf& b, int i, int j,
+                                                  int k, long long c, int mode) {
+        constexpr int dd[3] = {DI, DJ, DK};
+        const int p[3] = {i + DI, j + DJ, k + DK};
+        int o[3] = {0, 0, 0}, t[3] = {0, 0, 0}, ord[3] = {0, 0, 0};
+        bool force = false;
+#pragma unroll
+        for (int d = 0; d < ND; ++d) {
+            if (dd[d] < 0 && p[d] < b.lo[d]) { o[d] = -1; t[d] = b.st[d][0]; }
+            if (dd[d] > 0 && p[d] > b.hi[d]) { o[d] = 1; t[d] = b.st[d][1]; }
+            if (o[d] != 0) force = force | (t[d] == BC_NEUM);
+            else force = force | (p[d] == b.lo[d] && b.st[d][0] == BC_NEUM) | (p[d] == b.hi[d] && b.st[d][1] == BC_NEUM);
+        }
+#pragma unroll
+        for (int d = 0; d < ND; ++d) {
+            if (o[d] == 0) ord[d] = 0;
+            else if (force) ord[d] = 2;
+            else if (t[d] == SIDE_INTERNAL) ord[d] = 0;
+            else if (t[d] == BC_PERIODIC) ord[d] = (mode == EXMODE_OP) ? 0 : 1;
+            else ord[d] = (mode == EXMODE_OP) ? 2 : 1;
+        }
+        const long long str[3] = {1, g.sy, g.sz};
+        const double* __restrict__ q = phi + (c + DI + g.sy * DJ + g.sz * DK);
+        constexpr int n0 = DI ? 3 : 1, n1 = DJ ? 3 : 1, n2 = (ND > 2 && DK) ? 3 : 1;
+        long long off[3][3];
+#pragma unroll
+        for (int d = 0; d < 3; ++d)
+#pragma unroll
+            for (int K = 0; K < 3; ++K) off[d][K] = (d < ND && dd[d] != 0) ? -(long long)o[d] * ex_steps(ord[d], K) * str[d] : 0;
+        double vz[3] = {0.0, 0.0, 0.0};
+#pragma unroll
+        for (int cc = 0; cc < n2; ++cc) {
+            double vy[3] = {0.0, 0.0, 0.0};
+#pragma unroll
+            for (int bb = 0; bb < n1; ++bb) {
+                const long long a = off[1][bb] + off[2][cc];
+                vy[bb] = (n0 == 1) ? q[a] : ex_comb(ord[0], q[a + off[0][0]], q[a + off[0][1]], q[a + off[0][2]]);
+            }
+            vz[cc] = (n1 == 1) ? vy[0] : ex_comb(ord[1], vy[0], vy[1], vy[2]);
+        }
+        return (n2 == 1) ? vz[0] : ex_comb(ord[2], vz[0], vz[1], vz[2]);
+    }
+    __device__ __forceinline__ TabView(const Geom& g, const double* __restrict__ phi, int i, int j, int k, long long c, int mode)
+        : i0(i), j0(j), k0(k) {
+        const BoxOf b = box_of<ND>(g, i, j, k);
+#define TAB_SET(slot, di, dj, dk) e##slot = eval<di, dj, dk>(g, phi, b, i, j, k, c, mode)
+        TAB_SET(12, -1, 0, 0); TAB_SET(14, 1, 0, 0); TAB_SET(10, 0, -1, 0); TAB_SET(16, 0, 1, 0);
+        TAB_SET(9, -1, -1, 0); TAB_SET(11, 1, -1, 0); TAB_SET(15, -1, 1, 0); TAB_SET(17, 1, 1, 0);
+        e1 = e3 = e4 = e5 = e7 = e19 = e21 = e22 = e23 = e25 = 0.0;
+        if (ND > 2) {
+            TAB_SET(4, 0, 0, -1); TAB_SET(22, 0, 0, 1);
+            TAB_SET(3, -1, 0, -1); TAB_SET(5, 1, 0, -1); TAB_SET(1, 0, -1, -1); TAB_SET(7, 0, 1, -1);
+            TAB_SET(21, -1, 0, 1); TAB_SET(23, 1, 0, 1); TAB_SET(19, 0, -1, 1); TAB_SET(25, 0, 1, 1);
+        }
+#undef TAB_SET
+    }
+    __device__ __forceinline__ double ex(int i, int j, int k) const {
+        switch ((i - i0 + 1) + 3 * (j - j0 + 1) + 9 * (k - k0 + 1)) {   // a constant wherever the statements call it
+            case 1: return e1; case 3: return e3; case 4: return e4; case 5: return e5; case 7: return e7;
+            case 9: return e9; case 10: return e10; case 11: return e11; case 12: return e12;
+            case 14: return e14; case 15: return e15; case 16: return e16; case 17: return e17;
+            case 19: return e19; case 21: return e21; case 22: return e22; case 23: return e23; case 25: return e25;
+            default: return 0.0;
+        }
+    }
+};
+
 // 4-point transverse difference used by every cross term: around the face between cell A=(a0,a1,a2) and
 // cell B = A - e_n (n = face normal), difference taken in direction t:
 //    ex(A+t) - ex(A-t) + ex(B+t) - ex(B-t)
@@ -223,6 +395,30 @@ __device__ __forceinline__ double apply_cell_full(const Geom& g, const Metric& m
     const ExView<ND> v(g, phi, i, j, k, EXMODE_OP);
     return apply_cell_full_v<ND>(g, m, v, phi, i, j, k, c, homog, side_mask(g, i, j, k));
 }
+// a cell of known kind (cell_kind): the accessor that kind allows
+template <int ND>
+__device__ __forceinline__ double apply_cell_full_kind(const Geom& g, const Metric& m, const double* __restrict__ phi,
+                                                       int i, int j, int k, long long c, bool homog, int kind) {
+    if (kind == CELL_FAST) {
+        const FastView<ND> v{phi + c, i, j, k, g.sy, g.sz};
+        return apply_cell_full_v<ND>(g, m, v, phi, i, j, k, c, homog, 0u);
+    }
+    const unsigned sm = side_mask(g, i, j, k);
+    if (kind == CELL_DIR0) {
+        const DirView<ND, 0> v(g, phi, i, j, k, c, EXMODE_OP);
+        return apply_cell_full_v<ND>(g, m, v, phi, i, j, k, c, homog, sm);
+    }
+    if (kind == CELL_DIR1) {
+        const DirView<ND, 1> v(g, phi, i, j, k, c, EXMODE_OP);
+        return apply_cell_full_v<ND>(g, m, v, phi, i, j, k, c, homog, sm);
+    }
+    if (ND > 2 && kind == CELL_DIR2) {
+        const DirView<ND, (ND > 2 ? 2 : 0)> v(g, phi, i, j, k, c, EXMODE_OP);
+        return apply_cell_full_v<ND>(g, m, v, phi, i, j, k, c, homog, sm);
+    }
+    const TabView<ND> v(g, phi, i, j, k, c, EXMODE_OP);
+    return apply_cell_full_v<ND>(g, m, v, phi, i, j, k, c, homog, sm);
+}
 // box-interior cell: no boundary side, no extrapolated value
 template <int ND>
 __device__ __forceinline__ double apply_cell_full_inner(const Geom& g, const Metric& m, const double* __restrict__ phi,
@@ -282,10 +478,10 @@ __device__ __forceinline__ double gsrb_cell_full_inner(const Geom& g, const Metr
     return gsrb_interior_full<ND>(g, m, v, phi, rhs, i, j, k, c);
 }
 
-template <int ND>
-__device__ __forceinline__ double gsrb_cell_full(const Geom& g, const Metric& m, const double* __restrict__ phi,
-                                                 const double* __restrict__ rhs, int i, int j, int k, long long c) {
-    const ExView<ND> v(g, phi, i, j, k, EXMODE_SMOOTHER);
+template <int ND, class V>
+__device__ __forceinline__ double gsrb_cell_full_v(const Geom& g, const Metric& m, const V& v,
+                                                   const double* __restrict__ phi, const double* __restrict__ rhs, int i,
+                                                   int j, int k, long long c) {
     if (!on_domain_rim<ND>(g, i, j, k)) return gsrb_interior_full<ND>(g, m, v, phi, rhs, i, j, k, c);
     const long long st[3] = {1, g.sy, g.sz};
     const double ji = m.jinv[c];
@@ -325,6 +521,33 @@ __device__ __forceinline__ double gsrb_cell_full(const Geom& g, const Metric& m,
     if (ND > 2) s = s + JD[2][0] + JD[2][1];
     const double lphi = g.beta * ji * s;
     return (rhs[c] - lphi) / (g.alpha + g.beta * lapDiag);
+}
+template <int ND>
+__device__ __forceinline__ double gsrb_cell_full(const Geom& g, const Metric& m, const double* __restrict__ phi,
+                                                 const double* __restrict__ rhs, int i, int j, int k, long long c) {
+    const ExView<ND> v(g, phi, i, j, k, EXMODE_SMOOTHER);
+    return gsrb_cell_full_v<ND>(g, m, v, phi, rhs, i, j, k, c);
+}
+// a cell of known kind (cell_kind)
+template <int ND>
+__device__ __forceinline__ double gsrb_cell_full_kind(const Geom& g, const Metric& m, const double* __restrict__ phi,
+                                                      const double* __restrict__ rhs, int i, int j, int k, long long c,
+                                                      int kind) {
+    if (kind == CELL_FAST) return gsrb_cell_full_inner<ND>(g, m, phi, rhs, i, j, k, c);
+    if (kind == CELL_DIR0) {
+        const DirView<ND, 0> v(g, phi, i, j, k, c, EXMODE_SMOOTHER);
+        return gsrb_cell_full_v<ND>(g, m, v, phi, rhs, i, j, k, c);
+    }
+    if (kind == CELL_DIR1) {
+        const DirView<ND, 1> v(g, phi, i, j, k, c, EXMODE_SMOOTHER);
+        return gsrb_cell_full_v<ND>(g, m, v, phi, rhs, i, j, k, c);
+    }
+    if (ND > 2 && kind == CELL_DIR2) {
+        const DirView<ND, (ND > 2 ? 2 : 0)> v(g, phi, i, j, k, c, EXMODE_SMOOTHER);
+        return gsrb_cell_full_v<ND>(g, m, v, phi, rhs, i, j, k, c);
+    }
+    const TabView<ND> v(g, phi, i, j, k, c, EXMODE_SMOOTHER);
+    return gsrb_cell_full_v<ND>(g, m, v, phi, rhs, i, j, k, c);
 }
 
 }  // namespace somar
