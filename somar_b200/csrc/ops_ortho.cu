@@ -114,12 +114,17 @@ __global__ void __launch_bounds__(BX* BY) k_apply(const Geom g, const Metric m, 
     const int k0 = blockIdx.z * kz;
     const int k1 = min(k0 + kz, g.n[2]);
     const bool innerXY = FULL && full_inner_xy<ND>(g, i, j);
+    // SPLIT: every cell whose accessor is phi itself (CELL_FAST: box-interior cells, and cells on box-box interfaces away from
+    // the domain boundary); the others are left to k_apply_full_rim
+    const unsigned cxy = (FULL && SPLIT) ? (class_bit(cell_dir_class(g, i, 0)) | class_bit(cell_dir_class(g, j, 1))) : 0u;
     for (int k = k0; k < k1; ++k) {
         const long long c = g.idx(i, j, k);
         double v;
         if (FULL) {
-            if (innerXY && (ND < 3 || box_inner_dir<ND>(g, k, 2))) v = apply_cell_full_inner<ND>(g, m, phi, i, j, k, c, homog);
-            else if (SPLIT) continue;                            // left to k_apply_full_rim
+            const bool fast = SPLIT ? classes_fast(cxy | ((ND > 2) ? class_bit(cell_dir_class(g, k, 2)) : 0u))
+                                    : (innerXY && (ND < 3 || box_inner_dir<ND>(g, k, 2)));
+            if (fast) v = apply_cell_full_inner<ND>(g, m, phi, i, j, k, c, homog);
+            else if (SPLIT) continue;
             else v = apply_cell_full<ND>(g, m, phi, i, j, k, c, homog);
         } else {
             v = apply_cell_ortho<ND>(g, m, phi, i, j, k, c, homog);
@@ -135,7 +140,9 @@ __global__ void __launch_bounds__(128, RIM_MINB) k_apply_full_rim(const Geom g, 
     int i, j, k;
     if (!rim_cell<ND>(g, nzr, nyr, nxr, i, j, k)) return;
     const long long c = g.idx(i, j, k);
-    const double v = apply_cell_full_kind<ND>(g, m, phi, i, j, k, c, homog, cell_kind<ND>(g, i, j, k));
+    const int kind = cell_kind<ND>(g, i, j, k);
+    if (kind == CELL_FAST) return;                               // k_apply<ND, true, true> did it
+    const double v = apply_cell_full_kind<ND>(g, m, phi, i, j, k, c, homog, kind);
     out[c] = mode ? (rhs[c] - v) : v;
 }
 
@@ -420,6 +427,8 @@ __global__ void __launch_bounds__(128, RIM_MINB) k_gsrb_full_rim(const Geom g, c
     int i, j, k;
     if (!rim_cell<ND>(g, nzr, nyr, nxr, i, j, k, pass)) return;
     const long long c = g.idx(i, j, k);
+    // (the box-interior test costs k_gsrb_full<ND, true> 80 registers, the CELL_FAST test 100 and 6 % of its rate: the
+    // CELL_FAST cells on box-box interfaces stay here)
     phiOut[c] = gsrb_cell_full_kind<ND>(g, m, phiIn, rhs, i, j, k, c, cell_kind<ND>(g, i, j, k));
 }
 

@@ -177,13 +177,15 @@ __device__ __forceinline__ int cell_dir_class(const Geom& g, int q, int d) {
     return (dom || nearN) ? 3 : 2;
 }
 
+// CELL_FAST from the classes as a bit mask (bit c-1 for a direction of class c): no class 3, and not a 2 with a 1.
+// A z-marching thread keeps the mask of x and y.
+__device__ __forceinline__ unsigned class_bit(int c) { return c ? 1u << (c - 1) : 0u; }
+__device__ __forceinline__ bool classes_fast(unsigned mask) { return mask < 3u; }
+
 template <int ND>
 __device__ __forceinline__ int cell_kind(const Geom& g, int i, int j, int k) {
     const int c0 = cell_dir_class(g, i, 0), c1 = cell_dir_class(g, j, 1), c2 = (ND > 2) ? cell_dir_class(g, k, 2) : 0;
-    const bool any3 = (c0 == 3) | (c1 == 3) | (c2 == 3);
-    const bool any2 = (c0 == 2) | (c1 == 2) | (c2 == 2);
-    const bool any1 = (c0 == 1) | (c1 == 1) | (c2 == 1);
-    if (!any3 && !(any2 && any1)) return CELL_FAST;
+    if (classes_fast(class_bit(c0) | class_bit(c1) | class_bit(c2))) return CELL_FAST;
     if (c0 == 3 && c1 == 0 && c2 == 0) return CELL_DIR0;
     if (c1 == 3 && c0 == 0 && c2 == 0) return CELL_DIR1;
     if (ND > 2 && c2 == 3 && c0 == 0 && c1 == 0) return CELL_DIR2;
@@ -341,19 +343,15 @@ __device__ __forceinline__ double face_flux_full(const Geom& g, const Metric& m,
     constexpr int B = (A + 1) % ND;
     constexpr int C = (A + 2) % ND;
     const long long st = (A == 0) ? 1 : (A == 1 ? g.sy : g.sz);
-    if (atBdry && g.bc[A][S] == BC_NEUM) return (homog ? 0.0 : g.bcval[A][S]) * g.beta;
-    double nb;
-    if (atBdry) {  // Dirichlet ghost
-        const double farV = S ? phi[c - st] : phi[c + st];
-        if (g.bc[A][S] == BC_EXTRAP2) {   // ELLIPTICEXTRAPBCGHOST order 2 (projector gradients only)
-            const double far2 = S ? phi[c - 2 * st] : phi[c + 2 * st];
-            nb = 3.0 * (pc - farV) + far2;
-        } else {
-            nb = diri_ghost_val(pc, farV, homog ? 0.0 : g.bcval[A][S], g.diriOrder);
-        }
-    } else {
-        nb = S ? phi[c + st] : phi[c - st];
-    }
+    // No load sits behind a branch (a thread's reads then go out together, see the accessors above): the neighbour is read
+    // even where it is a ghost cell, and a Neumann face computes its interior expression before discarding it.
+    const bool neum = atBdry && g.bc[A][S] == BC_NEUM;
+    const bool extrap2 = atBdry && g.bc[A][S] == BC_EXTRAP2;   // ELLIPTICEXTRAPBCGHOST order 2 (projector gradients only)
+    const double nearV = S ? phi[c + st] : phi[c - st];
+    const double farV = S ? phi[c - st] : phi[c + st];
+    const double far2 = phi[extrap2 ? (S ? c - 2 * st : c + 2 * st) : c];
+    double nb = nearV;
+    if (atBdry) nb = extrap2 ? 3.0 * (pc - farV) + far2 : diri_ghost_val(pc, farV, homog ? 0.0 : g.bcval[A][S], g.diriOrder);
     const long long f = S ? c + st : c;
     // "cell A" of the face = the cell on its high side
     const int a0 = i + (S && A == 0), a1 = j + (S && A == 1), a2 = k + (S && A == 2);
@@ -365,7 +363,7 @@ __device__ __forceinline__ double face_flux_full(const Geom& g, const Metric& m,
         const double cS = 0.25 * 1.0 / g.dx[C];
         fl += cS * m.jg[A][C][f] * cross4<ND>(v, a0, a1, a2, A, C);
     }
-    return fl * g.beta;
+    return neum ? (homog ? 0.0 : g.bcval[A][S]) * g.beta : fl * g.beta;
 }
 
 // (alpha I + beta L) phi at one cell, full metric (applyOpI, MappedAMRPoissonOp.cpp:772-898).
@@ -495,11 +493,12 @@ __device__ __forceinline__ double gsrb_cell_full_v(const Geom& g, const Metric& 
 #pragma unroll
         for (int s = 0; s < 2; ++s) {
             const bool atB = (sm >> (2 * d + s)) & 1u;
-            if (atB && g.bc[d][s] == BC_NEUM) continue;
-            const long long f = s ? c + st[d] : c;
+            const bool skip = atB && g.bc[d][s] == BC_NEUM;      // the face contributes nothing (no load behind a branch:
+            const long long f = s ? c + st[d] : c;               // its expression is computed and discarded)
             const int a0 = i + (s && d == 0), a1 = j + (s && d == 1), a2 = k + (s && d == 2);
             double nb = s ? phi[c + st[d]] : phi[c - st[d]];
-            if (atB && g.bc[d][s] == BC_DIRI) nb = diri_ghost_val(pc, s ? phi[c - st[d]] : phi[c + st[d]], 0.0, g.diriOrder);
+            const double farV = s ? phi[c - st[d]] : phi[c + st[d]];
+            if (atB && g.bc[d][s] == BC_DIRI) nb = diri_ghost_val(pc, farV, 0.0, g.diriOrder);
             const double sgn = s ? 1.0 : -1.0;
             double val = 0.0;
 #pragma unroll
@@ -512,8 +511,9 @@ __device__ __forceinline__ double gsrb_cell_full_v(const Geom& g, const Metric& 
                     val += sgn * ab * m.jg[d][t][f] * cross4<ND>(v, a0, a1, a2, d, t);
                 }
             }
-            JD[d][s] = val;
-            lapDiag = lapDiag - (1.0 / (g.dx[d] * g.dx[d])) * m.jg[d][d][f];
+            JD[d][s] = skip ? 0.0 : val;
+            const double ld = lapDiag - (1.0 / (g.dx[d] * g.dx[d])) * m.jg[d][d][f];
+            lapDiag = skip ? lapDiag : ld;
         }
     }
     lapDiag = lapDiag * ji;
