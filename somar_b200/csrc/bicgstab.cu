@@ -18,6 +18,7 @@
 #include "level.hpp"
 #include <cmath>
 #include <cstdlib>
+#include <cstring>
 
 namespace somar {
 
@@ -151,10 +152,31 @@ static int bottom_solve_device(SomarLevel* L, SomarField* a_phi, const SomarFiel
     hs->status = loop_top(*hs) ? 0 : 1;
 
     const int CHUNK = 8;
-    while (hs->status == 0) {
-        SOMAR_CUDA(cudaMemcpyAsync(ds, hs, sizeof(BicgState), cudaMemcpyHostToDevice, cx.stream));
-        int todo = hs->imax - hs->i;
-        if (todo > CHUNK) todo = CHUNK;
+    // One iteration is ~40 launches of kernels that run 3-30 us each on the bottom grid: sequenced launch by launch the host
+    // cannot keep the stream fed (0.8 ms per iteration against 0.4 ms of kernel time, profiles/r2_ncu_k_gsrb_full.txt).
+    // The iterations never read the host (every scalar lives in *ds), so a full chunk is captured once as a CUDA graph
+    // and replayed.  The graph holds pointers and by-value geometry: it is rebuilt when anything it captured changes
+    // (the key below).  One rank and full metric only -- the diagonal metric has the resident kernel, several ranks
+    // have NCCL calls in the loop.
+    static const bool graphOn = []() { const char* e = getenv("SOMAR_B200_BOTTOM_GRAPH"); return !(e && e[0] == '0'); }();
+    const Depth& bdp = L->depths[bd];
+    const bool graphable = graphOn && L->desc.nranks == 1 && !bdp.m.diagonal && p.relaxMode == SOMAR_RELAX_LEVEL_GSRB &&
+                           p.precondMode != 2;
+    struct GraphKey {
+        double alpha, beta;
+        const void* ptr[12];
+        int relaxMode, precondMode, nsp, kind, nb, n[3];
+    } key;
+    std::memset(&key, 0, sizeof(key));
+    static_assert(sizeof(GraphKey) <= sizeof(L->bicg_graph_key), "bicg_graph_key too small");
+    if (graphable) {
+        key.alpha = g.alpha; key.beta = g.beta;
+        for (int q = 0; q < 8; ++q) key.ptr[q] = L->bwork[q]->p;
+        key.ptr[8] = bdp.tmp; key.ptr[9] = ds; key.ptr[10] = cx.scratch; key.ptr[11] = bdp.m.jinv;
+        key.relaxMode = p.relaxMode; key.precondMode = p.precondMode; key.nsp = p.num_smooth_precond; key.kind = kind;
+        key.nb = nb; key.n[0] = g.n[0]; key.n[1] = g.n[1]; key.n[2] = g.n[2];
+    }
+    auto iterate = [&](int todo) -> int {
         for (int it = 0; it < todo; ++it) {
             launch_reduce(cx, g, r_tilde->p, r->p, 3, &ds->red[0]);
             if ((rc = allreduce_state(L, &ds->red[0], 1, false))) return rc;
@@ -183,6 +205,35 @@ static int bottom_solve_device(SomarLevel* L, SomarField* a_phi, const SomarFiel
             if ((rc = allreduce_state(L, &ds->red[0], 1, normMax))) return rc;
             k_bicg_c5<<<1, 1, 0, cx.stream>>>(ds);
             cx.launches += 5;
+        }
+        return SOMAR_OK;
+    };
+    while (hs->status == 0) {
+        SOMAR_CUDA(cudaMemcpyAsync(ds, hs, sizeof(BicgState), cudaMemcpyHostToDevice, cx.stream));
+        int todo = hs->imax - hs->i;
+        if (todo > CHUNK) todo = CHUNK;
+        if (graphable && todo == CHUNK) {
+            if (!L->bicg_graph || std::memcmp(&key, L->bicg_graph_key, sizeof(key)) != 0) {
+                if (L->bicg_graph) { cudaGraphExecDestroy(L->bicg_graph); L->bicg_graph = nullptr; }
+                const long long l0 = cx.launches;
+                SOMAR_CUDA(cudaStreamBeginCapture(cx.stream, cudaStreamCaptureModeThreadLocal));
+                rc = iterate(CHUNK);
+                cudaGraph_t graph = nullptr;
+                const cudaError_t ce = cudaStreamEndCapture(cx.stream, &graph);
+                const int captured = (int)(cx.launches - l0);
+                cx.launches = l0;
+                if (rc != SOMAR_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
+                SOMAR_CUDA(ce);
+                const cudaError_t ie = cudaGraphInstantiate(&L->bicg_graph, graph, 0);
+                cudaGraphDestroy(graph);
+                SOMAR_CUDA(ie);
+                L->bicg_graph_launches = captured;
+                std::memcpy(L->bicg_graph_key, &key, sizeof(key));
+            }
+            SOMAR_CUDA(cudaGraphLaunch(L->bicg_graph, cx.stream));
+            cx.launches += L->bicg_graph_launches;
+        } else if ((rc = iterate(todo))) {
+            return rc;
         }
         SOMAR_CUDA(cudaMemcpyAsync(hs, ds, sizeof(BicgState), cudaMemcpyDeviceToHost, cx.stream));
         SOMAR_CUDA(cudaStreamSynchronize(cx.stream));

@@ -157,6 +157,7 @@ int somar_level_destroy(SomarLevel* L) {
     cudaFree(L->cx.scratch); cudaFree(L->cx.tickets); cudaFree(L->d_scal); cudaFreeHost(L->h_scal);
     if (L->d_bicg) cudaFree(L->d_bicg);
     if (L->h_bicg) cudaFreeHost(L->h_bicg);
+    if (L->bicg_graph) cudaGraphExecDestroy(L->bicg_graph);
     gathered_bottom_free(L);
     cudaFree(L->stage);
     cudaEventDestroy(L->ev0); cudaEventDestroy(L->ev1);

@@ -87,6 +87,10 @@ struct SomarLevel {
     int bottom_mode = 3;               // SOMAR_B200_BOTTOM: 0 host-sequenced BiCGStab, 1 scalars on the device,
                                        // 2 one persistent kernel per bottom visit where usable (else 1),
                                        // 3 (default) the on-chip-resident kernel where usable (else as 2)
+    // launch-per-step bottom solver, one rank, full metric: a chunk of BiCGStab iterations as one CUDA graph (bicgstab.cu)
+    cudaGraphExec_t bicg_graph = nullptr;
+    unsigned char bicg_graph_key[160] = {0};
+    int bicg_graph_launches = 0;       // kernel launches one replay stands for
     int bottom_resident_blocks = -1;   // co-resident blocks of k_bicg_resident (-1: not yet queried)
     int bottom_coop_blocks = -1;       // co-resident blocks of the persistent kernel (-1: not yet queried)
     bool bottom_iters_pending = false; // the device-side iteration counter holds uncollected counts
