@@ -21,10 +21,14 @@
 //   * <r_tilde, r> of the next iteration is accumulated by the pass that produces r.
 // The fields are deliberately NOT const/__restrict__: they are written and re-read across grid.sync() by other
 // SMs, so no load may go through the non-coherent path.
-// Usable for: single rank, diagonal metric, point GSRB smoother/preconditioner, no periodic direction.
+// Usable for: single rank, point GSRB smoother/preconditioner, no periodic direction.  The full metric (FULL) runs the
+// pass-per-barrier formulation with the cell statements of stencil_full.cuh dispatched by cell kind; its colour passes are
+// out of place (the cross terms read the pre-pass state of BOTH colours) and ping-pong with the t field, which is free
+// whenever a relaxation runs.
 #pragma once
 #include "cells.cuh"
 #include "stencil_ortho.cuh"
+#include "stencil_full.cuh"
 #include <cooperative_groups.h>
 
 namespace somar {
@@ -289,8 +293,38 @@ __device__ __forceinline__ void bp_tile_relax_apply(const Geom& g, const Metric&
     }
 }
 
+// ---- full metric: one colour pass (out of place) and the operator, one copy of each in the kernel -------------------
+#ifndef BP_MINBLOCKS_FULL
+#define BP_MINBLOCKS_FULL 2
+#endif
 template <int ND>
-__global__ void __launch_bounds__(BP_TPB, BP_MINBLOCKS)
+__device__ __noinline__ void bp_full_colour_pass(const Geom& g, const Metric& m, double* out, const double* in,
+                                                 const double* rhs, int pass, int gwarp, int nwarps, int lane) {
+    BP_FOR_ITEMS(g, 64, {
+        const int par = (g.g0[0] + g.g0[1] + j + ((ND > 2) ? (g.g0[2] + k) : 0) + pass) & 1;
+        const int ia = i0 + 2 * lane;
+        const int i = ia + par;                                  // the lane's cell of this pass's colour
+        if (ia < g.n[0]) {
+            const long long ca = g.idx(ia, j, k);
+            double va = in[ca];
+            double vb = (ia + 1 < g.n[0]) ? in[ca + 1] : 0.0;
+            if (i < g.n[0]) {
+                const double v = gsrb_cell_full_kind<ND>(g, m, in, rhs, i, j, k, ca + par, cell_kind<ND>(g, i, j, k));
+                if (par) vb = v; else va = v;
+            }
+            out[ca] = va;
+            if (ia + 1 < g.n[0]) out[ca + 1] = vb;
+        }
+    })
+}
+template <int ND>
+__device__ __noinline__ void bp_full_apply(const Geom& g, const Metric& m, double* out, const double* in, int gwarp,
+                                           int nwarps, int lane) {
+    BP_FOR_CELLS(g, c, { out[c] = apply_cell_full_kind<ND>(g, m, in, i, j, k, c, true, cell_kind<ND>(g, i, j, k)); })
+}
+
+template <int ND, bool FULL = false>
+__global__ void __launch_bounds__(BP_TPB, FULL ? BP_MINBLOCKS_FULL : BP_MINBLOCKS)
     k_bicg_persistent(const Geom g, const Metric m, const BicgFields f, const BicgArgs a, double* part,
                       int* itersAccum, const int cb, unsigned long long* bar) {
     cg::grid_group grid = cg::this_grid();
@@ -303,10 +337,10 @@ __global__ void __launch_bounds__(BP_TPB, BP_MINBLOCKS)
     };
     __shared__ BicgState s;
     __shared__ double rhoNext;   // <r_tilde, r> formed by the pass that wrote r
-    __shared__ double tile[(ND > 2) ? BP_TILE_CAP : 1];
+    __shared__ double tile[(ND > 2 && !FULL) ? BP_TILE_CAP : 1];
     // fused preconditioner + operator (bp_tile_relax_apply): the diagonally scaled input of preCond(p) is staged in
     // stl's array and that of preCond(s) in pt's array -- each is free at that point of the iteration
-    const bool tiled = (ND > 2) && a.tcx > 0 && a.nprecond > 0;
+    const bool tiled = !FULL && (ND > 2) && a.tcx > 0 && a.nprecond > 0;
     int buf = 0;
     const int tid = threadIdx.x;
     const int lane = tid & 31;
@@ -369,17 +403,28 @@ __global__ void __launch_bounds__(BP_TPB, BP_MINBLOCKS)
         })
     };
     auto relax = [&](double* phi, const double* rhs, int iters) {   // enters and leaves with phi complete
-        for (int it = 0; it < iters; ++it) {
-            colour_pass(phi, rhs, 0);
-            gsync();
-            colour_pass(phi, rhs, 1);
-            gsync();
+        if (FULL) {   // two passes per iteration: the result is back in phi
+            double* src = phi;
+            double* dst = f.t;
+            for (int ps = 0; ps < 2 * iters; ++ps) {
+                bp_full_colour_pass<ND>(g, m, dst, src, rhs, ps & 1, gwarp, nwarps, lane);
+                gsync();
+                double* sw = src; src = dst; dst = sw;
+            }
+        } else {
+            for (int it = 0; it < iters; ++it) {
+                colour_pass(phi, rhs, 0);
+                gsync();
+                colour_pass(phi, rhs, 1);
+                gsync();
+            }
         }
     };
     // r = rhs - L phi, r_tilde = r, e = 0, norm(r), <r, r>      (phi complete on entry)
     auto true_residual = [&]() {
+        if (FULL) bp_full_apply<ND>(g, m, f.r, f.phi, gwarp, nwarps, lane);   // (same cell, same thread below)
         BP_FOR_CELLS(g, c, {
-            const double rv = f.rhs[c] - apply_cell_ortho<ND>(g, m, f.phi, i, j, k, c, true);
+            const double rv = f.rhs[c] - (FULL ? f.r[c] : apply_cell_ortho<ND>(g, m, f.phi, i, j, k, c, true));
             f.r[c] = rv;
             f.rt[c] = rv;
             f.e[c] = 0.0;
@@ -429,9 +474,10 @@ __global__ void __launch_bounds__(BP_TPB, BP_MINBLOCKS)
         }
         {   // v = L p_tilde (spread over the grid), then <r_tilde, v> in the canonical order
             if (tiled) {
-                if (ND > 2) bp_tile_relax_apply(g, m, tile, f.stl, f.pv, f.pt, f.v, a.nprecond, a.tcx, a.tcy);
+                if (!FULL && ND > 2) bp_tile_relax_apply(g, m, tile, f.stl, f.pv, f.pt, f.v, a.nprecond, a.tcx, a.tcy);
             } else {
-                BP_FOR_CELLS(g, c, { f.v[c] = apply_cell_ortho<ND>(g, m, f.pt, i, j, k, c, true); })
+                if (FULL) bp_full_apply<ND>(g, m, f.v, f.pt, gwarp, nwarps, lane);
+                else BP_FOR_CELLS(g, c, { f.v[c] = apply_cell_ortho<ND>(g, m, f.pt, i, j, k, c, true); })
             }
             gsync();
             double acc = 0.0;
@@ -462,9 +508,10 @@ __global__ void __launch_bounds__(BP_TPB, BP_MINBLOCKS)
             if (!tiled) relax(f.stl, f.r, a.nprecond);
             {   // t = L s_tilde (spread over the grid), then <t, r>, <t, t> in the canonical order
                 if (tiled) {
-                    if (ND > 2) bp_tile_relax_apply(g, m, tile, f.pt, f.r, f.stl, f.t, a.nprecond, a.tcx, a.tcy);
+                    if (!FULL && ND > 2) bp_tile_relax_apply(g, m, tile, f.pt, f.r, f.stl, f.t, a.nprecond, a.tcx, a.tcy);
                 } else {
-                    BP_FOR_CELLS(g, c, { f.t[c] = apply_cell_ortho<ND>(g, m, f.stl, i, j, k, c, true); })
+                    if (FULL) bp_full_apply<ND>(g, m, f.t, f.stl, gwarp, nwarps, lane);
+                    else BP_FOR_CELLS(g, c, { f.t[c] = apply_cell_ortho<ND>(g, m, f.stl, i, j, k, c, true); })
                 }
                 gsync();
                 double a0 = 0.0, a1 = 0.0;

@@ -386,12 +386,16 @@ bool bottom_persistent_usable(SomarLevel* L) {
     if (L->bottom_mode < 2) return false;
     const Depth& dp = L->depths[L->ndepths() - 1];
     const Geom& g = dp.g;
-    if (!dp.m.diagonal || L->desc.nranks > 1 || g.nbr[0] >= 0 || g.nbr[1] >= 0) return false;
-    return bottom_persistent_params_ok(L, g);
+    if (L->desc.nranks > 1 || g.nbr[0] >= 0 || g.nbr[1] >= 0) return false;
+    if (!dp.m.diagonal) {   // the FULL instantiation (SOMAR_B200_BOTTOM_FULL_PERSISTENT=0: the launch-per-step graph instead)
+        static const bool on = []() { const char* e = getenv("SOMAR_B200_BOTTOM_FULL_PERSISTENT"); return !(e && e[0] == '0'); }();
+        if (!on) return false;
+    }
+    return bottom_persistent_params_ok(L, g, !dp.m.diagonal);
 }
 
 // solver parameters and size the persistent kernel supports, for a single-rank diagonal-metric geometry g
-bool bottom_persistent_params_ok(SomarLevel* L, const Geom& g) {
+bool bottom_persistent_params_ok(SomarLevel* L, const Geom& g, bool full) {
     const SomarSolverParams& p = L->prm;
     if (g.periodic[0] || g.periodic[1] || (g.nd > 2 && g.periodic[2])) return false;
     if (p.relaxMode != SOMAR_RELAX_LEVEL_GSRB) return false;
@@ -402,7 +406,10 @@ bool bottom_persistent_params_ok(SomarLevel* L, const Geom& g) {
         int dev = 0, coop = 0, perSm = 0;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
-        if (g.nd == 3) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_bicg_persistent<3>, BP_TPB, 0);
+        // (a level has one metric kind, so one cached count per level serves)
+        if (full && g.nd == 3) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_bicg_persistent<3, true>, BP_TPB, 0);
+        else if (full) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_bicg_persistent<2, true>, BP_TPB, 0);
+        else if (g.nd == 3) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_bicg_persistent<3>, BP_TPB, 0);
         else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_bicg_persistent<2>, BP_TPB, 0);
         int cap = coop ? perSm * L->cx.sms : 0;
         L->bottom_coop_blocks = cap > MAX_RED_BLOCKS ? MAX_RED_BLOCKS : cap;
@@ -462,7 +469,7 @@ int launch_bottom_persistent(SomarLevel* L, const Geom& g_, const Metric& m_, do
     a.tcx = a.tcy = 0;
     {
         static const bool tiledOn = []() { const char* e = getenv("SOMAR_B200_BOTTOM_TILED"); return !(e && e[0] == '0'); }();
-        if (tiledOn && g.nd == 3 && a.nprecond > 0) {
+        if (tiledOn && m.diagonal && g.nd == 3 && a.nprecond > 0) {
             const int h = 2 * a.nprecond + 1;
             int cx = 16, cy = 8;
             while ((cx + 2 * h) * (cy + 2 * h) * g.n[2] > BP_TILE_CAP && (cx > 4 || cy > 4)) {
@@ -490,7 +497,8 @@ int launch_bottom_persistent(SomarLevel* L, const Geom& g_, const Metric& m_, do
     if (bar) SOMAR_CUDA(cudaMemsetAsync(bar, 0, sizeof(dv->bar), L->cx.stream));
     void* args[] = {&g, &m, &f, &a, &part, &itersAccum, &cb, &bar};
     const dim3 grid(nb), block(BP_TPB);
-    const void* fn = (g.nd == 3) ? (const void*)k_bicg_persistent<3> : (const void*)k_bicg_persistent<2>;
+    const void* fn = m.diagonal ? ((g.nd == 3) ? (const void*)k_bicg_persistent<3> : (const void*)k_bicg_persistent<2>)
+                                : ((g.nd == 3) ? (const void*)k_bicg_persistent<3, true> : (const void*)k_bicg_persistent<2, true>);
     SOMAR_CUDA(cudaLaunchCooperativeKernel(fn, grid, block, args, 0, L->cx.stream));
     L->cx.launches++;
     L->bottom_iters_pending = true;

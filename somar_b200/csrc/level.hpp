@@ -187,7 +187,7 @@ int bottom_solve(SomarLevel* L, SomarField* e, const SomarField* r, int* iters);
 bool bottom_persistent_usable(SomarLevel* L);
 int bottom_persistent(SomarLevel* L, SomarField* e, const SomarField* r);
 int bottom_collect_iters(SomarLevel* L);
-bool bottom_persistent_params_ok(SomarLevel* L, const Geom& g);
+bool bottom_persistent_params_ok(SomarLevel* L, const Geom& g, bool full = false);
 int launch_bottom_persistent(SomarLevel* L, const Geom& g, const Metric& m, double* phi, double* rhs,
                              double* const work[8]);
 // bicg_resident.cu
