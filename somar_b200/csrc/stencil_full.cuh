@@ -25,6 +25,17 @@
 
 namespace somar {
 
+// every function of this header also compiles for the host: tests/cuda/full_accessors_host.cu runs the accessors and the
+// statements on the CPU (DirView / TabView / FastView against ExView, cell by cell, bit for bit) without a GPU
+#ifndef SOMAR_HD
+#define SOMAR_HD __host__ __device__
+#endif
+#ifdef __CUDA_ARCH__
+#define SOMAR_UNROLL _Pragma("unroll")
+#else
+#define SOMAR_UNROLL   // (the host pass does not know the pragma)
+#endif
+
 enum { EXMODE_SMOOTHER = 0, EXMODE_OP = 1 };
 enum { SIDE_INTERNAL = -3 };
 
@@ -36,11 +47,11 @@ struct BoxOf {
 };
 
 template <int ND>
-__device__ __forceinline__ BoxOf box_of(const Geom& g, int i, int j, int k) {
+SOMAR_HD __forceinline__ BoxOf box_of(const Geom& g, int i, int j, int k) {
     BoxOf b;
     const int q[3] = {i, j, k};
     b.rim = false;
-#pragma unroll
+SOMAR_UNROLL
     for (int d = 0; d < 3; ++d) {
         if (d < ND) {
             const int gq = q[d] + g.g0[d];
@@ -61,7 +72,7 @@ __device__ __forceinline__ BoxOf box_of(const Geom& g, int i, int j, int k) {
 
 template <int D>
 struct ExRec {
-    __device__ static double eval(const Geom& g, const double* __restrict__ phi, int p0, int p1, int p2,
+    SOMAR_HD static double eval(const Geom& g, const double* __restrict__ phi, int p0, int p1, int p2,
                                   const int* o, const int* ord) {
         if (ord[D] == 0) return ExRec<D - 1>::eval(g, phi, p0, p1, p2, o, ord);
         int p[3] = {p0, p1, p2};
@@ -78,7 +89,7 @@ struct ExRec {
 };
 template <>
 struct ExRec<-1> {
-    __device__ static double eval(const Geom& g, const double* __restrict__ phi, int p0, int p1, int p2, const int*,
+    SOMAR_HD static double eval(const Geom& g, const double* __restrict__ phi, int p0, int p1, int p2, const int*,
                                   const int*) {
         return phi[g.idx(p0, p1, p2)];
     }
@@ -86,12 +97,12 @@ struct ExRec<-1> {
 
 // extrap(p) as seen from box b.
 template <int ND>
-__device__ __noinline__ double ex_slow(const Geom& g, const double* __restrict__ phi, const BoxOf& b, int p0, int p1,
+SOMAR_HD __noinline__ double ex_slow(const Geom& g, const double* __restrict__ phi, const BoxOf& b, int p0, int p1,
                                        int p2, int mode) {
     const int p[3] = {p0, p1, p2};
     int o[3] = {0, 0, 0}, ord[3] = {0, 0, 0}, t[3] = {0, 0, 0};
     bool force = false, any = false;
-#pragma unroll
+SOMAR_UNROLL
     for (int d = 0; d < ND; ++d) {
         if (p[d] < b.lo[d]) { o[d] = -1; t[d] = b.st[d][0]; }
         else if (p[d] > b.hi[d]) { o[d] = 1; t[d] = b.st[d][1]; }
@@ -103,7 +114,7 @@ __device__ __noinline__ double ex_slow(const Geom& g, const double* __restrict__
         }
     }
     if (!any) return phi[g.idx(p0, p1, p2)];
-#pragma unroll
+SOMAR_UNROLL
     for (int d = 0; d < ND; ++d) {
         if (o[d] == 0) continue;
         if (force) ord[d] = 2;
@@ -121,9 +132,9 @@ struct ExView {
     const double* __restrict__ phi;
     BoxOf b;
     int mode;
-    __device__ ExView(const Geom& g_, const double* __restrict__ phi_, int i, int j, int k, int mode_)
+    SOMAR_HD ExView(const Geom& g_, const double* __restrict__ phi_, int i, int j, int k, int mode_)
         : g(g_), phi(phi_), b(box_of<ND>(g_, i, j, k)), mode(mode_) {}
-    __device__ __forceinline__ double ex(int i, int j, int k) const {
+    SOMAR_HD __forceinline__ double ex(int i, int j, int k) const {
         if (!b.rim) return phi[g.idx(i, j, k)];
         return ex_slow<ND>(g, phi, b, i, j, k, mode);
     }
@@ -137,7 +148,7 @@ struct FastView {
     const double* __restrict__ p;   // phi + index of the cell (i0, j0, k0)
     int i0, j0, k0;
     long long sy, sz;
-    __device__ __forceinline__ double ex(int i, int j, int k) const {
+    SOMAR_HD __forceinline__ double ex(int i, int j, int k) const {
         return p[(i - i0) + sy * (j - j0) + sz * (k - k0)];
     }
 };
@@ -145,7 +156,7 @@ struct FastView {
 // Is local cell (q0, q1, q2) strictly inside its box of the level's uniform tiling (not touching any box side)?
 // x/y part and z part separately, so that a z-marching thread tests x/y once.
 template <int ND>
-__device__ __forceinline__ bool box_inner_dir(const Geom& g, int q, int d) {
+SOMAR_HD __forceinline__ bool box_inner_dir(const Geom& g, int q, int d) {
     const int r = (q + g.g0[d]) % g.bs[d];
     return r != 0 && r != g.bs[d] - 1;
 }
@@ -167,7 +178,7 @@ __device__ __forceinline__ bool box_inner_dir(const Geom& g, int q, int d) {
 // ---------------------------------------------------------------------------------------------------------
 enum { CELL_FAST = 0, CELL_DIR0 = 1, CELL_DIR1 = 2, CELL_DIR2 = 3, CELL_GENERAL = 4 };
 
-__device__ __forceinline__ int cell_dir_class(const Geom& g, int q, int d) {
+SOMAR_HD __forceinline__ int cell_dir_class(const Geom& g, int q, int d) {
     const int gq = q + g.g0[d];
     const int r = gq % g.bs[d];
     const bool touch = (r == 0) || (r == g.bs[d] - 1);
@@ -179,11 +190,11 @@ __device__ __forceinline__ int cell_dir_class(const Geom& g, int q, int d) {
 
 // CELL_FAST from the classes as a bit mask (bit c-1 for a direction of class c): no class 3, and not a 2 with a 1.
 // A z-marching thread keeps the mask of x and y.
-__device__ __forceinline__ unsigned class_bit(int c) { return c ? 1u << (c - 1) : 0u; }
-__device__ __forceinline__ bool classes_fast(unsigned mask) { return mask < 3u; }
+SOMAR_HD __forceinline__ unsigned class_bit(int c) { return c ? 1u << (c - 1) : 0u; }
+SOMAR_HD __forceinline__ bool classes_fast(unsigned mask) { return mask < 3u; }
 
 template <int ND>
-__device__ __forceinline__ int cell_kind(const Geom& g, int i, int j, int k) {
+SOMAR_HD __forceinline__ int cell_kind(const Geom& g, int i, int j, int k) {
     const int c0 = cell_dir_class(g, i, 0), c1 = cell_dir_class(g, j, 1), c2 = (ND > 2) ? cell_dir_class(g, k, 2) : 0;
     if (classes_fast(class_bit(c0) | class_bit(c1) | class_bit(c2))) return CELL_FAST;
     if (c0 == 3 && c1 == 0 && c2 == 0) return CELL_DIR0;
@@ -193,13 +204,13 @@ __device__ __forceinline__ int cell_kind(const Geom& g, int i, int j, int k) {
 }
 
 // value of an order-`ord` extrapolation from the three values one, two and three steps inside (ExRec's expressions)
-__device__ __forceinline__ double ex_comb(int ord, double s1, double s2, double s3) {
+SOMAR_HD __forceinline__ double ex_comb(int ord, double s1, double s2, double s3) {
     const double r1 = 2.0 * s1 - s2, r2 = 3.0 * (s1 - s2) + s3;
     return (ord == 0) ? s1 : (ord == 1 ? r1 : r2);
 }
 // how many steps inside the K-th value (K = 0, 1, 2) of an order-`ord` extrapolation sits; a value the order does not use
 // repeats the last one it does, so that no address is read that ex_slow would not read
-__device__ __forceinline__ int ex_steps(int ord, int K) { return (ord == 0) ? 0 : ((K < ord) ? K + 1 : ord + 1); }
+SOMAR_HD __forceinline__ int ex_steps(int ord, int K) { return (ord == 0) ? 0 : ((K < ord) ? K + 1 : ord + 1); }
 
 // The accessors below are written for memory-level parallelism.  ex_slow / ExView reach every value through branches and
 // calls, so the ~50 reads of a cell's statement are issued one behind the other: a thread needs tens of microseconds for its
@@ -216,7 +227,7 @@ struct DirView {
     int i0, j0, k0;
     int ordLo, ordHi;    // order of the extrapolation one cell below / above the cell in direction D; 0: phi itself (the
                          // point is inside the box, or behind a box-box interface: the neighbour's phi)
-    __device__ __forceinline__ DirView(const Geom& g, const double* __restrict__ phi_, int i, int j, int k, long long c, int mode)
+    SOMAR_HD __forceinline__ DirView(const Geom& g, const double* __restrict__ phi_, int i, int j, int k, long long c, int mode)
         : phi(phi_), base(c), sy(g.sy), sz(g.sz), i0(i), j0(j), k0(k) {
         const int q = (D == 0) ? i : (D == 1 ? j : k);
         const int gq = q + g.g0[D];
@@ -225,13 +236,13 @@ struct DirView {
         ordLo = (gq == glo) ? side_order(tLo, mode) : 0;
         ordHi = (gq == ghi) ? side_order(tHi, mode) : 0;
     }
-    __device__ static __forceinline__ int side_order(int t, int mode) {
+    SOMAR_HD static __forceinline__ int side_order(int t, int mode) {
         if (t == BC_NEUM) return 2;                                  // force
         if (t == SIDE_INTERNAL) return 0;
         if (t == BC_PERIODIC) return (mode == EXMODE_OP) ? 0 : 1;
         return (mode == EXMODE_OP) ? 2 : 1;
     }
-    __device__ __forceinline__ double ex(int i, int j, int k) const {
+    SOMAR_HD __forceinline__ double ex(int i, int j, int k) const {
         const int di = i - i0, dj = j - j0, dk = k - k0;            // constants at the call sites
         const long long a = base + di + sy * dj + sz * dk;
         const int dq = (D == 0) ? di : (D == 1 ? dj : dk);
@@ -257,20 +268,20 @@ struct TabView {
     double e19, e21, e22, e23, e25;                                    // dk = +1
     int i0, j0, k0;
     template <int DI, int DJ, int DK>
-    __device__ static __forceinline__ double eval(const Geom& g, const double* __restrict__ phi, const BoxOf& b, int i, int j,
+    SOMAR_HD static __forceinline__ double eval(const Geom& g, const double* __restrict__ phi, const BoxOf& b, int i, int j,
                                                   int k, long long c, int mode) {
         constexpr int dd[3] = {DI, DJ, DK};
         const int p[3] = {i + DI, j + DJ, k + DK};
         int o[3] = {0, 0, 0}, t[3] = {0, 0, 0}, ord[3] = {0, 0, 0};
         bool force = false;
-#pragma unroll
+SOMAR_UNROLL
         for (int d = 0; d < ND; ++d) {
             if (dd[d] < 0 && p[d] < b.lo[d]) { o[d] = -1; t[d] = b.st[d][0]; }
             if (dd[d] > 0 && p[d] > b.hi[d]) { o[d] = 1; t[d] = b.st[d][1]; }
             if (o[d] != 0) force = force | (t[d] == BC_NEUM);
             else force = force | (p[d] == b.lo[d] && b.st[d][0] == BC_NEUM) | (p[d] == b.hi[d] && b.st[d][1] == BC_NEUM);
         }
-#pragma unroll
+SOMAR_UNROLL
         for (int d = 0; d < ND; ++d) {
             if (o[d] == 0) ord[d] = 0;
             else if (force) ord[d] = 2;
@@ -282,15 +293,15 @@ struct TabView {
         const double* __restrict__ q = phi + (c + DI + g.sy * DJ + g.sz * DK);
         constexpr int n0 = DI ? 3 : 1, n1 = DJ ? 3 : 1, n2 = (ND > 2 && DK) ? 3 : 1;
         long long off[3][3];
-#pragma unroll
+SOMAR_UNROLL
         for (int d = 0; d < 3; ++d)
-#pragma unroll
+SOMAR_UNROLL
             for (int K = 0; K < 3; ++K) off[d][K] = (d < ND && dd[d] != 0) ? -(long long)o[d] * ex_steps(ord[d], K) * str[d] : 0;
         double vz[3] = {0.0, 0.0, 0.0};
-#pragma unroll
+SOMAR_UNROLL
         for (int cc = 0; cc < n2; ++cc) {
             double vy[3] = {0.0, 0.0, 0.0};
-#pragma unroll
+SOMAR_UNROLL
             for (int bb = 0; bb < n1; ++bb) {
                 const long long a = off[1][bb] + off[2][cc];
                 vy[bb] = (n0 == 1) ? q[a] : ex_comb(ord[0], q[a + off[0][0]], q[a + off[0][1]], q[a + off[0][2]]);
@@ -299,7 +310,7 @@ struct TabView {
         }
         return (n2 == 1) ? vz[0] : ex_comb(ord[2], vz[0], vz[1], vz[2]);
     }
-    __device__ __forceinline__ TabView(const Geom& g, const double* __restrict__ phi, int i, int j, int k, long long c, int mode)
+    SOMAR_HD __forceinline__ TabView(const Geom& g, const double* __restrict__ phi, int i, int j, int k, long long c, int mode)
         : i0(i), j0(j), k0(k) {
         const BoxOf b = box_of<ND>(g, i, j, k);
 #define TAB_SET(slot, di, dj, dk) e##slot = eval<di, dj, dk>(g, phi, b, i, j, k, c, mode)
@@ -313,7 +324,7 @@ struct TabView {
         }
 #undef TAB_SET
     }
-    __device__ __forceinline__ double ex(int i, int j, int k) const {
+    SOMAR_HD __forceinline__ double ex(int i, int j, int k) const {
         switch ((i - i0 + 1) + 3 * (j - j0 + 1) + 9 * (k - k0 + 1)) {   // a constant wherever the statements call it
             case 1: return e1; case 3: return e3; case 4: return e4; case 5: return e5; case 7: return e7;
             case 9: return e9; case 10: return e10; case 11: return e11; case 12: return e12;
@@ -328,7 +339,7 @@ struct TabView {
 // cell B = A - e_n (n = face normal), difference taken in direction t:
 //    ex(A+t) - ex(A-t) + ex(B+t) - ex(B-t)
 template <int ND, class V>
-__device__ __forceinline__ double cross4(const V& v, int a0, int a1, int a2, int n, int t) {
+SOMAR_HD __forceinline__ double cross4(const V& v, int a0, int a1, int a2, int n, int t) {
     const int e0 = (n == 0), e1 = (n == 1), e2 = (n == 2);
     const int t0 = (t == 0), t1 = (t == 1), t2 = (t == 2);
     return v.ex(a0 + t0, a1 + t1, a2 + t2) - v.ex(a0 - t0, a1 - t1, a2 - t2) +
@@ -337,7 +348,7 @@ __device__ __forceinline__ double cross4(const V& v, int a0, int a1, int a2, int
 
 // beta * flux through the low (S=0) / high (S=1) face of cell q=(i,j,k) in direction A (MAPPEDGETFLUX + BCs).
 template <int ND, int A, int S, class V>
-__device__ __forceinline__ double face_flux_full(const Geom& g, const Metric& m, const V& v,
+SOMAR_HD __forceinline__ double face_flux_full(const Geom& g, const Metric& m, const V& v,
                                                  const double* __restrict__ phi, int i, int j, int k, long long c,
                                                  bool atBdry, bool homog, double pc) {
     constexpr int B = (A + 1) % ND;
@@ -368,7 +379,7 @@ __device__ __forceinline__ double face_flux_full(const Geom& g, const Metric& m,
 
 // (alpha I + beta L) phi at one cell, full metric (applyOpI, MappedAMRPoissonOp.cpp:772-898).
 template <int ND, class V>
-__device__ __forceinline__ double apply_cell_full_v(const Geom& g, const Metric& m, const V& v,
+SOMAR_HD __forceinline__ double apply_cell_full_v(const Geom& g, const Metric& m, const V& v,
                                                     const double* __restrict__ phi, int i, int j, int k, long long c,
                                                     bool homog, unsigned sm) {
     const double pc = phi[c];
@@ -388,14 +399,14 @@ __device__ __forceinline__ double apply_cell_full_v(const Geom& g, const Metric&
     return r;
 }
 template <int ND>
-__device__ __forceinline__ double apply_cell_full(const Geom& g, const Metric& m, const double* __restrict__ phi,
+SOMAR_HD __forceinline__ double apply_cell_full(const Geom& g, const Metric& m, const double* __restrict__ phi,
                                                   int i, int j, int k, long long c, bool homog) {
     const ExView<ND> v(g, phi, i, j, k, EXMODE_OP);
     return apply_cell_full_v<ND>(g, m, v, phi, i, j, k, c, homog, side_mask(g, i, j, k));
 }
 // a cell of known kind (cell_kind): the accessor that kind allows
 template <int ND>
-__device__ __forceinline__ double apply_cell_full_kind(const Geom& g, const Metric& m, const double* __restrict__ phi,
+SOMAR_HD __forceinline__ double apply_cell_full_kind(const Geom& g, const Metric& m, const double* __restrict__ phi,
                                                        int i, int j, int k, long long c, bool homog, int kind) {
     if (kind == CELL_FAST) {
         const FastView<ND> v{phi + c, i, j, k, g.sy, g.sz};
@@ -419,7 +430,7 @@ __device__ __forceinline__ double apply_cell_full_kind(const Geom& g, const Metr
 }
 // box-interior cell: no boundary side, no extrapolated value
 template <int ND>
-__device__ __forceinline__ double apply_cell_full_inner(const Geom& g, const Metric& m, const double* __restrict__ phi,
+SOMAR_HD __forceinline__ double apply_cell_full_inner(const Geom& g, const Metric& m, const double* __restrict__ phi,
                                                         int i, int j, int k, long long c, bool homog) {
     const FastView<ND> v{phi + c, i, j, k, g.sy, g.sz};
     return apply_cell_full_v<ND>(g, m, v, phi, i, j, k, c, homog, 0u);
@@ -427,7 +438,7 @@ __device__ __forceinline__ double apply_cell_full_inner(const Geom& g, const Met
 
 // d_a ( J g^{ab} d_b ex ) without the 1/(4 dx_a dx_b) factor: high-face term minus low-face term.
 template <int ND, class V>
-__device__ __forceinline__ double cross_ab(const Metric& m, const V& v, int i, int j, int k, long long c,
+SOMAR_HD __forceinline__ double cross_ab(const Metric& m, const V& v, int i, int j, int k, long long c,
                                            long long sta, int a, int b) {
     const int e0 = (a == 0), e1 = (a == 1), e2 = (a == 2);
     const double up = m.jg[a][b][c + sta] * cross4<ND>(v, i + e0, j + e1, k + e2, a, b);
@@ -439,7 +450,7 @@ __device__ __forceinline__ double cross_ab(const Metric& m, const V& v, int i, i
 // cross terms the frozen snapshot).  GSRBITER{2,3}D / GSRBBOUNDARYITER{2,3}D.
 // interior statement (GSRBITER{2,3}D) on any accessor
 template <int ND, class V>
-__device__ __forceinline__ double gsrb_interior_full(const Geom& g, const Metric& m, const V& v,
+SOMAR_HD __forceinline__ double gsrb_interior_full(const Geom& g, const Metric& m, const V& v,
                                                      const double* __restrict__ phi, const double* __restrict__ rhs,
                                                      int i, int j, int k, long long c) {
     const double ji = m.jinv[c];
@@ -470,14 +481,14 @@ __device__ __forceinline__ double gsrb_interior_full(const Geom& g, const Metric
 }
 // box-interior cell: every ex() is phi
 template <int ND>
-__device__ __forceinline__ double gsrb_cell_full_inner(const Geom& g, const Metric& m, const double* __restrict__ phi,
+SOMAR_HD __forceinline__ double gsrb_cell_full_inner(const Geom& g, const Metric& m, const double* __restrict__ phi,
                                                        const double* __restrict__ rhs, int i, int j, int k, long long c) {
     const FastView<ND> v{phi + c, i, j, k, g.sy, g.sz};
     return gsrb_interior_full<ND>(g, m, v, phi, rhs, i, j, k, c);
 }
 
 template <int ND, class V>
-__device__ __forceinline__ double gsrb_cell_full_v(const Geom& g, const Metric& m, const V& v,
+SOMAR_HD __forceinline__ double gsrb_cell_full_v(const Geom& g, const Metric& m, const V& v,
                                                    const double* __restrict__ phi, const double* __restrict__ rhs, int i,
                                                    int j, int k, long long c) {
     if (!on_domain_rim<ND>(g, i, j, k)) return gsrb_interior_full<ND>(g, m, v, phi, rhs, i, j, k, c);
@@ -488,9 +499,9 @@ __device__ __forceinline__ double gsrb_cell_full_v(const Geom& g, const Metric& 
     const double pc = phi[c];
     double JD[3][2] = {{0.0, 0.0}, {0.0, 0.0}, {0.0, 0.0}};
     double lapDiag = 0.0;
-#pragma unroll
+SOMAR_UNROLL
     for (int d = 0; d < ND; ++d) {
-#pragma unroll
+SOMAR_UNROLL
         for (int s = 0; s < 2; ++s) {
             const bool atB = (sm >> (2 * d + s)) & 1u;
             const bool skip = atB && g.bc[d][s] == BC_NEUM;      // the face contributes nothing (no load behind a branch:
@@ -501,7 +512,7 @@ __device__ __forceinline__ double gsrb_cell_full_v(const Geom& g, const Metric& 
             if (atB && g.bc[d][s] == BC_DIRI) nb = diri_ghost_val(pc, farV, 0.0, g.diriOrder);
             const double sgn = s ? 1.0 : -1.0;
             double val = 0.0;
-#pragma unroll
+SOMAR_UNROLL
             for (int t = 0; t < ND; ++t) {
                 if (t == d) {
                     const double aa = 1.0 / (g.dx[d] * g.dx[d]);
@@ -523,14 +534,14 @@ __device__ __forceinline__ double gsrb_cell_full_v(const Geom& g, const Metric& 
     return (rhs[c] - lphi) / (g.alpha + g.beta * lapDiag);
 }
 template <int ND>
-__device__ __forceinline__ double gsrb_cell_full(const Geom& g, const Metric& m, const double* __restrict__ phi,
+SOMAR_HD __forceinline__ double gsrb_cell_full(const Geom& g, const Metric& m, const double* __restrict__ phi,
                                                  const double* __restrict__ rhs, int i, int j, int k, long long c) {
     const ExView<ND> v(g, phi, i, j, k, EXMODE_SMOOTHER);
     return gsrb_cell_full_v<ND>(g, m, v, phi, rhs, i, j, k, c);
 }
 // a cell of known kind (cell_kind)
 template <int ND>
-__device__ __forceinline__ double gsrb_cell_full_kind(const Geom& g, const Metric& m, const double* __restrict__ phi,
+SOMAR_HD __forceinline__ double gsrb_cell_full_kind(const Geom& g, const Metric& m, const double* __restrict__ phi,
                                                       const double* __restrict__ rhs, int i, int j, int k, long long c,
                                                       int kind) {
     if (kind == CELL_FAST) return gsrb_cell_full_inner<ND>(g, m, phi, rhs, i, j, k, c);

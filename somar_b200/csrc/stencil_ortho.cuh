@@ -13,14 +13,14 @@
 
 namespace somar {
 
-__device__ __forceinline__ double diri_ghost_val(double nearV, double farV, double bcval, int order) {
+__host__ __device__ __forceinline__ double diri_ghost_val(double nearV, double farV, double bcval, int order) {
     if (order == 0) return bcval;
     if (order == 1) return (bcval == 0.0) ? -nearV : 2.0 * bcval - nearV;
     return (bcval == 0.0) ? (1.0 / 3.0) * farV - 2.0 * nearV : (8.0 * bcval - 6.0 * nearV + farV) / 3.0;
 }
 
 // Which physical-boundary sides does local cell (i,j,k) touch?  bit (2*d+s).
-__device__ __forceinline__ unsigned side_mask(const Geom& g, int i, int j, int k) {
+__host__ __device__ __forceinline__ unsigned side_mask(const Geom& g, int i, int j, int k) {
     unsigned m = 0;
     if (i == 0 && g.bc[0][0] != BC_NONE) m |= 1u;
     if (i == g.n[0] - 1 && g.bc[0][1] != BC_NONE) m |= 2u;
@@ -119,7 +119,7 @@ __device__ __forceinline__ double apply_vals_ortho3(const Geom& g, unsigned sm, 
 // Is the cell on the rim of the DOMAIN (any active direction, periodic or not)?  Such cells are relaxed by the
 // boundary kernels of the reference (BaseGSRB::boundaryGSRB, GSRB.cpp:489-653; domInterior = grow(domain,-1)).
 template <int ND>
-__device__ __forceinline__ bool on_domain_rim(const Geom& g, int i, int j, int k) {
+__host__ __device__ __forceinline__ bool on_domain_rim(const Geom& g, int i, int j, int k) {
     const int gi = i + g.g0[0], gk = k + g.g0[2];
     int gj = j + g.g0[1];
     // a ghost row beyond a periodic y side is the image of a row at the other end of the domain (the fused smoother
