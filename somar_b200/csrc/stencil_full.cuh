@@ -25,16 +25,8 @@
 
 namespace somar {
 
-// every function of this header also compiles for the host: tests/cuda/full_accessors_host.cu runs the accessors and the
-// statements on the CPU (DirView / TabView / FastView against ExView, cell by cell, bit for bit) without a GPU
-#ifndef SOMAR_HD
-#define SOMAR_HD __host__ __device__
-#endif
-#ifdef __CUDA_ARCH__
-#define SOMAR_UNROLL _Pragma("unroll")
-#else
-#define SOMAR_UNROLL   // (the host pass does not know the pragma)
-#endif
+// every function of this header also compiles for the host (SOMAR_HD, stencil_ortho.cuh): tests/cuda/full_accessors_host.cu
+// runs the accessors and the statements on the CPU (DirView / TabView / FastView against ExView, cell by cell, bit for bit)
 
 enum { EXMODE_SMOOTHER = 0, EXMODE_OP = 1 };
 enum { SIDE_INTERNAL = -3 };

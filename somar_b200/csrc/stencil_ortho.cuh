@@ -13,14 +13,26 @@
 
 namespace somar {
 
-__host__ __device__ __forceinline__ double diri_ghost_val(double nearV, double farV, double bcval, int order) {
+// every function of this header also compiles for the host (tests/cuda/*_host.cu run the statements on the CPU)
+#ifndef SOMAR_HD
+#define SOMAR_HD __host__ __device__
+#endif
+#ifndef SOMAR_UNROLL
+#ifdef __CUDA_ARCH__
+#define SOMAR_UNROLL _Pragma("unroll")
+#else
+#define SOMAR_UNROLL   // (the host pass does not know the pragma)
+#endif
+#endif
+
+SOMAR_HD __forceinline__ double diri_ghost_val(double nearV, double farV, double bcval, int order) {
     if (order == 0) return bcval;
     if (order == 1) return (bcval == 0.0) ? -nearV : 2.0 * bcval - nearV;
     return (bcval == 0.0) ? (1.0 / 3.0) * farV - 2.0 * nearV : (8.0 * bcval - 6.0 * nearV + farV) / 3.0;
 }
 
 // Which physical-boundary sides does local cell (i,j,k) touch?  bit (2*d+s).
-__host__ __device__ __forceinline__ unsigned side_mask(const Geom& g, int i, int j, int k) {
+SOMAR_HD __forceinline__ unsigned side_mask(const Geom& g, int i, int j, int k) {
     unsigned m = 0;
     if (i == 0 && g.bc[0][0] != BC_NONE) m |= 1u;
     if (i == g.n[0] - 1 && g.bc[0][1] != BC_NONE) m |= 2u;
@@ -36,7 +48,7 @@ __host__ __device__ __forceinline__ unsigned side_mask(const Geom& g, int i, int
 // beta * flux through the low (S=0) / high (S=1) face of the cell at address c in direction with stride st.
 // pc = phi(c); the neighbour / ghost is resolved here.
 template <int S>
-__device__ __forceinline__ double face_flux_ortho(const Geom& g, const double* __restrict__ phi,
+SOMAR_HD __forceinline__ double face_flux_ortho(const Geom& g, const double* __restrict__ phi,
                                                   const double* __restrict__ jgd, long long c, long long st, int d,
                                                   bool atBdry, bool homog, double pc) {
     const double beta_dx = g.rdx[d];
@@ -62,7 +74,7 @@ __device__ __forceinline__ double face_flux_ortho(const Geom& g, const double* _
 
 // (alpha I + beta L) phi at one cell, diagonal metric.
 template <int ND>
-__device__ __forceinline__ double apply_cell_ortho(const Geom& g, const Metric& m, const double* __restrict__ phi,
+SOMAR_HD __forceinline__ double apply_cell_ortho(const Geom& g, const Metric& m, const double* __restrict__ phi,
                                                    int i, int j, int k, long long c, bool homog) {
     const unsigned sm = side_mask(g, i, j, k);
     const double pc = phi[c];
@@ -86,7 +98,7 @@ __device__ __forceinline__ double apply_cell_ortho(const Geom& g, const Metric& 
 // across the face, farV = phi across the opposite face (Dirichlet ghosts), jgf = J g^{dd} on the face.  Statement
 // for statement the arithmetic of face_flux_ortho / apply_cell_ortho.
 template <int S>
-__device__ __forceinline__ double face_flux_vals(const Geom& g, int d, bool atBdry, bool homog, double pc, double nbv,
+SOMAR_HD __forceinline__ double face_flux_vals(const Geom& g, int d, bool atBdry, bool homog, double pc, double nbv,
                                                  double farV, double jgf) {
     const double beta_dx = g.rdx[d];
     double nb = nbv;
@@ -99,7 +111,7 @@ __device__ __forceinline__ double face_flux_vals(const Geom& g, int d, bool atBd
     return (jgf * beta_dx * diff) * g.beta;
 }
 
-__device__ __forceinline__ double apply_vals_ortho3(const Geom& g, unsigned sm, bool homog, double pc,
+SOMAR_HD __forceinline__ double apply_vals_ortho3(const Geom& g, unsigned sm, bool homog, double pc,
                                                     const double (&nb)[3][2], const double (&glo)[3],
                                                     const double (&ghi)[3], double ji) {
     const double f0l = face_flux_vals<0>(g, 0, sm & 1u, homog, pc, nb[0][0], nb[0][1], glo[0]);
@@ -119,7 +131,7 @@ __device__ __forceinline__ double apply_vals_ortho3(const Geom& g, unsigned sm, 
 // Is the cell on the rim of the DOMAIN (any active direction, periodic or not)?  Such cells are relaxed by the
 // boundary kernels of the reference (BaseGSRB::boundaryGSRB, GSRB.cpp:489-653; domInterior = grow(domain,-1)).
 template <int ND>
-__host__ __device__ __forceinline__ bool on_domain_rim(const Geom& g, int i, int j, int k) {
+SOMAR_HD __forceinline__ bool on_domain_rim(const Geom& g, int i, int j, int k) {
     const int gi = i + g.g0[0], gk = k + g.g0[2];
     int gj = j + g.g0[1];
     // a ghost row beyond a periodic y side is the image of a row at the other end of the domain (the fused smoother
@@ -137,7 +149,7 @@ struct GsrbCoef {
 };
 
 template <int ND>
-__device__ __forceinline__ GsrbCoef gsrb_load_coef(const Geom& g, const Metric& m, const double* __restrict__ rhs,
+SOMAR_HD __forceinline__ GsrbCoef gsrb_load_coef(const Geom& g, const Metric& m, const double* __restrict__ rhs,
                                                    long long c) {
     GsrbCoef q;
     q.glo[0] = m.jg[0][0][c];
@@ -160,7 +172,7 @@ __device__ __forceinline__ GsrbCoef gsrb_load_coef(const Geom& g, const Metric& 
 // LAPFLY: do not read q.lap; form lapDiag from the six face coefficients and 1/J the update holds anyway, with the
 // statements of FILLMAPPEDLAPDIAG (k_lapdiag) -- the same bits, one array less to stream (8 of 64 B/cell).
 template <int ND, bool LAPFLY = false>
-__device__ __forceinline__ double gsrb_update_vals(const Geom& g, const GsrbCoef& q, int i, int j, int k, double pc,
+SOMAR_HD __forceinline__ double gsrb_update_vals(const Geom& g, const GsrbCoef& q, int i, int j, int k, double pc,
                                                    const double (&nb)[3][2], bool knownInterior = false,
                                                    bool forceRim = false) {
     const double sc0 = g.rdx2[0];
@@ -212,12 +224,12 @@ __device__ __forceinline__ double gsrb_update_vals(const Geom& g, const GsrbCoef
         }
     };
     if (ND > 2) {
-#pragma unroll
+SOMAR_UNROLL
         for (int d = 0; d < ND; ++d) lo_term(d);
-#pragma unroll
+SOMAR_UNROLL
         for (int d = 0; d < ND; ++d) hi_term(d);
     } else {
-#pragma unroll
+SOMAR_UNROLL
         for (int d = 0; d < ND; ++d) {
             lo_term(d);
             hi_term(d);
@@ -232,7 +244,7 @@ __device__ __forceinline__ double gsrb_update_vals(const Geom& g, const GsrbCoef
 
 // Same, reading everything from global memory (in-place colour pass).
 template <int ND>
-__device__ __forceinline__ double gsrb_cell_ortho(const Geom& g, const Metric& m, const double* __restrict__ phi,
+SOMAR_HD __forceinline__ double gsrb_cell_ortho(const Geom& g, const Metric& m, const double* __restrict__ phi,
                                                   const double* __restrict__ rhs, int i, int j, int k, long long c) {
     double nb[3][2];
     nb[0][0] = phi[c - 1];

@@ -1,7 +1,8 @@
-// tests/cuda/full_statements_host.cu -- TEST INFRASTRUCTURE.  The product's full-metric cell statements
+// tests/cuda/statements_host.cu -- TEST INFRASTRUCTURE.  The product's full-metric cell statements
 // (somar_b200/csrc/stencil_full.cuh, __host__ __device__) compiled for the HOST behind a small C ABI, so that
-// tests/test_full_statements_host.py can compare them with the CPU oracle without a GPU: the operator and one red-black
-// colour pass on a one-rank level, dense arrays in, dense arrays out.  `accessor` 0 runs the statements through ExView
+// tests/test_statements_host.py can compare them with the CPU oracle without a GPU: the operator and the red-black
+// smoother on a one-rank level, dense arrays in, dense arrays out (also the diagonal-metric statements of
+// stencil_ortho.cuh: fh_apply_ortho / fh_relax_ortho).  `accessor` 0 runs the statements through ExView
 // (ex_slow), 1 through the accessor cell_kind selects (what the rim kernels and the persistent bottom kernel run).
 // Built by the test:  nvcc -shared -Xcompiler -fPIC -O1 -std=c++17 -fmad=false -I somar_b200/csrc ...
 #include <cstring>
@@ -128,9 +129,72 @@ void gsrb_pass(const HostLevel& L, std::vector<double>& phi, const std::vector<d
             }
     phi.swap(out);
 }
+
+// diagonal metric: apply_cell_ortho, and gsrb_cell_ortho IN PLACE (a cell only reads the other colour)
+template <int ND>
+void apply_all_ortho(const HostLevel& L, const std::vector<double>& phi, double* outDense, bool homog) {
+    const Geom& g = L.g;
+    for (int k = 0; k < g.n[2]; ++k)
+        for (int j = 0; j < g.n[1]; ++j)
+            for (int i = 0; i < g.n[0]; ++i)
+                outDense[((long long)k * g.n[1] + j) * g.n[0] + i] = apply_cell_ortho<ND>(g, L.m, phi.data(), i, j, k, g.idx(i, j, k), homog);
+}
+template <int ND>
+void gsrb_pass_ortho(const HostLevel& L, std::vector<double>& phi, const std::vector<double>& rhs, int pass) {
+    const Geom& g = L.g;
+    for (int k = 0; k < g.n[2]; ++k)
+        for (int j = 0; j < g.n[1]; ++j)
+            for (int i = 0; i < g.n[0]; ++i) {
+                if (((i + j + ((ND > 2) ? k : 0) + pass) & 1) != 0) continue;
+                const long long c = g.idx(i, j, k);
+                phi[c] = gsrb_cell_ortho<ND>(g, L.m, phi.data(), rhs.data(), i, j, k, c);
+            }
+}
 }  // namespace
 
 extern "C" {
+
+// the same two for a diagonal metric: jg holds nd arrays (J g^{dd} on the faces of direction d)
+int fh_apply_ortho(int nd, const int* n, const int* bs, const int* bc_type, const double* bc_value, const int* periodic,
+                   const double* dx, double alpha, double beta, const double* const* jg, const double* jinv,
+                   const double* lap, const double* phi, double* out, int homog) {
+    HostLevel L;
+    std::vector<const double*> full(nd * nd, nullptr);
+    for (int d = 0; d < nd; ++d)
+        for (int e = 0; e < nd; ++e) full[d * nd + e] = jg[d];   // (off-diagonal slots are not read)
+    build(L, nd, n, bs, bc_type, bc_value, periodic, dx, alpha, beta, full.data(), jinv, lap);
+    L.m.diagonal = 1;
+    std::vector<double> p;
+    scatter(L.g, phi, p);
+    periodic_fill(L.g, p);
+    if (nd == 3) apply_all_ortho<3>(L, p, out, homog != 0);
+    else apply_all_ortho<2>(L, p, out, homog != 0);
+    return 0;
+}
+int fh_relax_ortho(int nd, const int* n, const int* bs, const int* bc_type, const double* bc_value, const int* periodic,
+                   const double* dx, double alpha, double beta, const double* const* jg, const double* jinv,
+                   const double* lap, double* phi, const double* rhs, int iters) {
+    HostLevel L;
+    std::vector<const double*> full(nd * nd, nullptr);
+    for (int d = 0; d < nd; ++d)
+        for (int e = 0; e < nd; ++e) full[d * nd + e] = jg[d];
+    build(L, nd, n, bs, bc_type, bc_value, periodic, dx, alpha, beta, full.data(), jinv, lap);
+    L.m.diagonal = 1;
+    std::vector<double> p, r;
+    scatter(L.g, phi, p);
+    scatter(L.g, rhs, r);
+    for (int it = 0; it < iters; ++it)
+        for (int pass = 0; pass < 2; ++pass) {
+            periodic_fill(L.g, p);
+            if (nd == 3) gsrb_pass_ortho<3>(L, p, r, pass);
+            else gsrb_pass_ortho<2>(L, p, r, pass);
+        }
+    const Geom& g = L.g;
+    for (int k = 0; k < g.n[2]; ++k)
+        for (int j = 0; j < g.n[1]; ++j)
+            for (int i = 0; i < g.n[0]; ++i) phi[((long long)k * g.n[1] + j) * g.n[0] + i] = p[g.idx(i, j, k)];
+    return 0;
+}
 
 // out = (alpha + beta L) phi, applyOpI with its exchange (here: the periodic ghost fill; boxes share one array)
 int fh_apply(int nd, const int* n, const int* bs, const int* bc_type, const double* bc_value, const int* periodic,

@@ -1,5 +1,6 @@
-"""CPU parity of the product's full-metric cell statements.  somar_b200/csrc/stencil_full.cuh is __host__ __device__;
-tests/cuda/full_statements_host.cu compiles it for the host behind a small C ABI.  Here the operator (applyOpI) and the
+"""CPU parity of the product's cell statements.  somar_b200/csrc/stencil_full.cuh and stencil_ortho.cuh are
+__host__ __device__; tests/cuda/statements_host.cu compiles them for the host behind a small C ABI (the SASS of the
+library is identical with and without the host qualifiers).  Here the operator (applyOpI) and the
 red-black smoother (LevelGSRB) run through those statements on the CPU, over multi-box levels, and are compared with the
 oracle on the same seeded inputs -- the `-m gpu` parity tests do this with the kernels; this one needs no GPU and covers
 what the kernels are made of (the accessors ExView and the kind-dispatched FastView / DirView / TabView, the interior and
@@ -43,7 +44,7 @@ def fh(tmp_path_factory):
     so = tmp_path_factory.mktemp("fullhost") / "libfullhost.so"
     cmd = [_nvcc(), "-shared", "-Xcompiler", "-fPIC", "-O1", "-std=c++17", "-fmad=false", "-gencode",
            "arch=compute_100a,code=sm_100a", "-I", os.path.join(ROOT, "somar_b200", "csrc"), "-o", str(so),
-           os.path.join(ROOT, "tests", "cuda", "full_statements_host.cu")]
+           os.path.join(ROOT, "tests", "cuda", "statements_host.cu")]
     b = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert b.returncode == 0, b.stdout + b.stderr
     return C.CDLL(str(so))
@@ -96,3 +97,47 @@ def test_host_statements_relax_matches_oracle(name, oracle_lib, fh):
     assert np.array_equal(got[0], got[1]), "kind-dispatched accessors differ from ExView"
     assert rel_err(got[1], want) <= 10 * TOL, rel_err(got[1], want)   # (two sweeps, as tests/test_gpu_parity.py)
     assert (got[1] != want).mean() < 0.02, (got[1] != want).sum()       # ... and bit-exact in all but a few edge cells
+
+
+# ---- diagonal metric: the statements of stencil_ortho.cuh (bit-exact, as the kernels are) -----------------------------
+DIAG_CASES = {
+    "stretched3d": dict(n=(16, 12, 8), map_name="stretched", aniso=4.0),
+    "stretched3d_boxes": dict(n=(16, 16, 8), map_name="stretched", aniso=4.0, parts=(2, 2, 2)),
+    "periodic_y": dict(n=(16, 8, 8), map_name="stretched", aniso=2.0, periodic=(0, 1, 0)),
+    "periodic_xy": dict(n=(8, 8, 8), map_name="cartesian", aniso=1.0, periodic=(1, 1, 0)),
+    "dirichlet_top": dict(n=(8, 8, 8), map_name="stretched", aniso=4.0, bc_type=[0, 0, 0, 0, 0, 1],
+                          bc_value=[0, 0, 0, 0, 0, 0.5]),
+    "helmholtz": dict(n=(8, 8, 8), map_name="stretched", aniso=4.0, alpha=1.0, beta=-0.05),
+    "stretched2d": dict(n=(32, 16, 1), dim=2, map_name="stretched", aniso=4.0),
+}
+
+
+def _args_diag(pb, orc):
+    nd = pb.dim
+    bs = [pb.boxes[0][1][d] - pb.boxes[0][0][d] + 1 for d in range(3)]
+    bct = list(pb.bc_type) if pb.bc_type is not None else [0] * 6
+    bcv = [float(x) for x in (pb.bc_value if pb.bc_value is not None else [0.0] * 6)]
+    _, jinv, lap = orc.metric(0)
+    keep = [np.ascontiguousarray(pb.jgup[d], dtype=np.float64) for d in range(nd)]
+    keep += [np.ascontiguousarray(jinv, dtype=np.float64), np.ascontiguousarray(lap, dtype=np.float64)]
+    jgp = (C.POINTER(C.c_double) * nd)(*[a.ctypes.data_as(C.POINTER(C.c_double)) for a in keep[:nd]])
+    dp = lambda a: a.ctypes.data_as(C.POINTER(C.c_double))
+    head = (C.c_int(nd), (C.c_int * 3)(*pb.n), (C.c_int * 3)(*bs), (C.c_int * 6)(*bct), (C.c_double * 6)(*bcv),
+            (C.c_int * 3)(*pb.periodic), (C.c_double * 3)(*[float(x) for x in pb.spec.dx]), C.c_double(pb.alpha),
+            C.c_double(pb.beta), jgp, dp(keep[-2]), dp(keep[-1]))
+    return head, keep, dp
+
+
+@pytest.mark.parametrize("name", list(DIAG_CASES))
+def test_host_statements_diagonal_metric_bit_exact(name, oracle_lib, fh):
+    pb = Problem(**DIAG_CASES[name])
+    orc = pb.oracle(oracle_lib, relaxMode=1)
+    head, keep, dp = _args_diag(pb, orc)
+    phi, rhs = np.ascontiguousarray(pb.rand(orc.shape(0))), np.ascontiguousarray(pb.rand(orc.shape(0)))
+    for homog in (True, False):
+        got = np.zeros_like(phi)
+        assert fh.fh_apply_ortho(*head, dp(phi), dp(got), C.c_int(int(homog))) == 0
+        assert np.array_equal(got, orc.apply_op(phi, depth=0, homogeneous=homog)), (name, homog)
+    got = phi.copy()
+    assert fh.fh_relax_ortho(*head, dp(got), dp(rhs), C.c_int(2)) == 0
+    assert np.array_equal(got, orc.relax(phi, rhs, iters=2, depth=0)), name
