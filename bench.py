@@ -217,7 +217,7 @@ KERNEL_DESC = {"k_gsrb_ortho": "k_gsrb_ortho<3> (depth-0 red/black colour pass, 
                "k_gsrb_fused": "k_gsrb_fused (depth-0 red+black iteration in one sweep)",
                "k_gsrb_async": "k_gsrb_async (depth-0 red+black iteration in one sweep, producer/consumer pipeline)",
                "k_gsrb_tma": "k_gsrb_tma (depth-0 red+black iteration in one sweep, rings fed by TMA tensor-map loads)",
-               "k_gsrb_full": "k_gsrb_full<3> (depth-0 colour pass, full metric)",
+               "k_gsrb_full": "k_gsrb_full<3,true> + k_gsrb_full_rim<3> (depth-0 colour pass, full metric: box-interior cells, then the packed rim cells)",
                "k_gsrb_full_march": "k_gsrb_full_march (depth-0 red+black iteration in one sweep, full metric)",
                "k_line_gsrb": "k_line_gsrb<3> (depth-0 vertical-line colour pass)",
                "k_line_pass_c": "k_line_pass_c (depth-0 vertical-line colour pass, colour-split layout)",
