@@ -212,18 +212,17 @@ def byte_model(schedule, diagonal, relax, pre, post):
     return total
 
 
-KERNEL_BYTES = {"k_gsrb_ortho": 48, "k_gsrb_fused": 96, "k_gsrb_async": 96, "k_gsrb_tma": 96, "k_gsrb_full": 104, "k_gsrb_full_march": 208}
+KERNEL_BYTES = {"k_gsrb_ortho": 48, "k_gsrb_fused": 96, "k_gsrb_async": 96, "k_gsrb_tma": 96, "k_gsrb_full": 104}
 KERNEL_DESC = {"k_gsrb_ortho": "k_gsrb_ortho<3> (depth-0 red/black colour pass, 2 launches per iteration)",
                "k_gsrb_fused": "k_gsrb_fused (depth-0 red+black iteration in one sweep)",
                "k_gsrb_async": "k_gsrb_async (depth-0 red+black iteration in one sweep, producer/consumer pipeline)",
                "k_gsrb_tma": "k_gsrb_tma (depth-0 red+black iteration in one sweep, rings fed by TMA tensor-map loads)",
                "k_gsrb_full": "k_gsrb_full<3,true> + k_gsrb_full_rim<3> (depth-0 colour pass, full metric: box-interior cells, then the packed rim cells)",
-               "k_gsrb_full_march": "k_gsrb_full_march (depth-0 red+black iteration in one sweep, full metric)",
                "k_line_gsrb": "k_line_gsrb<3> (depth-0 vertical-line colour pass)",
                "k_line_pass_c": "k_line_pass_c (depth-0 vertical-line colour pass, colour-split layout)",
                "k_line_pair": "k_line_pair (depth-0 vertical-line red+black iteration in one launch)"}
 KERNEL_SOURCE = {"k_gsrb_ortho": "ops_ortho.cu", "k_gsrb_fused": "gsrb_fused.cu", "k_gsrb_async": "gsrb_async.cu", "k_gsrb_tma": "gsrb_tma.cu",
-                 "k_gsrb_full": "ops_ortho.cu", "k_gsrb_full_march": "gsrb_full_march.cu", "k_line_gsrb": "line.cu", "k_line_pass_c": "line_compact.cu",
+                 "k_gsrb_full": "ops_ortho.cu", "k_line_gsrb": "line.cu", "k_line_pass_c": "line_compact.cu",
                  "k_line_pair": "line.cu"}
 
 
