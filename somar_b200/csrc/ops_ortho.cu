@@ -29,9 +29,9 @@ __device__ __forceinline__ bool full_inner_xy(const Geom& g, int i, int j) {
 // cells of a row put it into that row's first and last warp with ONE active lane (ncu on k_gsrb_full,
 // profiles/r2_ncu_k_gsrb_full.txt: 15 of 32 lanes active on average, 2.6 warps per scheduler), so the full-metric kernels
 // run in two launches: the box-interior cells, and the rim cells mapped densely onto lanes -- three slabs, each rim cell
-// in exactly one: blockIdx.z < nzr: the z-rim planes, all (i, j); then the y-rim rows of the other planes, all i; then
-// the x-rim columns of what is left (lanes along j).  The m-th rim index of a direction is side m % 2 of local box m / 2
-// (a rank owns whole boxes); a one-cell-thick box has one.
+// in exactly one: the z-rim planes, all (i, j); then the y-rim rows of the other planes, all i; then the x-rim columns of
+// what is left (lanes along j).  The m-th rim index of a direction is side m % 2 of local box m / 2 (a rank owns whole
+// boxes); a one-cell-thick box has one.  Each rim cell is then dispatched by kind (cell_kind, stencil_full.cuh).
 // ---------------------------------------------------------------------------------------------------------
 __device__ __forceinline__ int rim_index(const Geom& g, int d, int m) {
     return (g.bs[d] > 1) ? (m >> 1) * g.bs[d] + ((m & 1) ? g.bs[d] - 1 : 0) : m;
