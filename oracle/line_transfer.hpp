@@ -74,7 +74,9 @@ inline int dgtsv(int n, double* dl, double* d, double* du, double* b) {
 // DIVERGENCE FROM THE REFERENCE (SURVEY.md hard part 5): the 3-D Fortran tests the x-side Neumann
 // condition against the parity-shifted `imin` (GSRBF.ChF:1795,1821) and the y-side against `jmin`/`jmax`
 // which are never assigned (:1764,1831,1835).  The evident intent -- the box bounds, as the 2-D
-// version does (:1607,1611) -- is what is restated here.
+// version does (:1607,1611) -- is what is restated here.  Wherever the 3-D Fortran is well defined and agrees with
+// that intent (non-Neumann y sides; with a Neumann x side, the rows whose colour starts on the box's first cell) this
+// function reproduces it bit for bit: tests/refkernels.py case line_gsrb, 48 3-D arrays.
 inline void line_gsrb(FAB& phi, const FAB& ex, const FAB& rhs, const FAB* Jg, const FAB& Jinv, const Box& region,
                       const double* dx, double dzCrse, double alpha, double beta, int redBlack, const int st[3][2],
                       int nd, bool isDiagonal) {

@@ -679,11 +679,16 @@ CASES["leptic"] = case_leptic
 
 def case_line_gsrb(D, ref):
     """LineGSRBIter2D (GSRBF.ChF:1529-1729) <- LineGSRB::relax, GSRB.cpp:148-330 (work FABs D, B over [1, Nz], DU over
-    [2, Nz], DL over [1, Nz - 1]; the box is shifted so that the column starts at 0; dgtsv is LAPACK's).  The 3-D kernel
-    (:1730-2042) compares `j` with jmin / jmax, which it never assigns (:1764,1831,1835) -- undefined in Fortran and not
-    executable here -- so only the 2-D kernel can be pinned; the oracle documents its reading of the 3-D one."""
-    if D != 2:
-        return {}, ({} if ref else None)
+    [2, Nz], DL over [1, Nz - 1]; the box is shifted so that the column starts at 0; dgtsv is LAPACK's).
+    LineGSRBIter3D (:1730-2042) compares `j` with jmin / jmax, which it never assigns (:1764,1831,1835): undefined in
+    Fortran.  The tests sit in `(loYBCType .ne. BCType_Neum) .or. (j .ne. jmin)`, so with non-Neumann y sides the kernel's
+    result does not depend on them and it IS pinned here (every vertical side type, both colours, diagonal and full
+    metric).  Its x test compares `i` with the parity-shifted imin (:1795,1821) -- the first cell of the colour, not the
+    first cell of the box -- so with a Neumann x side the rows whose colour starts one cell in are treated differently from
+    the 2-D kernel; on the other rows it agrees with the box bound, and those rows are pinned too (the others are blanked
+    on both sides).  The oracle restates the box bounds (its header says so)."""
+    if D == 3:
+        return _case_line_gsrb_3d(ref)
     from oracle.chf_runtime import Fab
     out_o, out_r = {}, ({} if ref else None)
     for st, rb, full, (alpha, beta) in itertools.product([(0, 1, 0, 0), (-1, -1, 0, 1), (1, 0, 1, 0), (2, 2, 0, 0)], [0, 1],
@@ -712,6 +717,51 @@ def case_line_gsrb(D, ref):
             ref.linegsrbiter2d(q.fab(), s.ex.fab(), s.rhs.fab(), s.jg[0].fab(), s.jg[1].fab(), s.jinv.fab(), _box(lo, hi), _vec(s.dx),
                                2.0 * s.dx[1], alpha, beta, rb, DUw, Dw, DLw, Bw, *st)
             out_r[key] = q.a
+    return out_o, out_r
+
+
+def _case_line_gsrb_3d(ref):
+    from oracle.chf_runtime import Fab
+    out_o, out_r = {}, ({} if ref else None)
+    # (loX, hiX, loY, hiY, loZ, hiZ); 0 Neumann, 1 Dirichlet, 3 coarse-fine, -1 / 2 anything else
+    sts = [(1, 1, 1, -1, 0, 1), (-1, 2, 1, 1, 1, 0), (1, -1, 2, 1, 3, 3), (2, 1, -1, -1, -1, 0), (0, 0, 1, 1, 0, 0),
+           (0, 1, -1, 1, 1, 3)]
+    for st, rb, full, (alpha, beta) in itertools.product(sts, [0, 1], [False, True], [(0.0, 1.0), (0.3, 0.7)]):
+        s = Setup(3, 73)
+        sh = s.lo[2]
+        for a in [s.phi, s.ex, s.rhs, s.jinv, s.lapdiag] + s.jg:
+            a.lo[2] -= sh
+            a.hi[2] -= sh
+        lo, hi = [s.lo[0], s.lo[1], 0], [s.hi[0], s.hi[1], s.hi[2] - sh]
+        if not full:
+            for d in range(3):
+                for e in range(3):
+                    if e != d:
+                        s.jg[d].a[e] = 0.0
+        key = "st%s_rb%d_f%d_a%.1f" % ("".join(str(x + 2) for x in st), rb, full, alpha)
+        # rows the reference's x test reads as intended: all of them without a Neumann x side, else those whose colour
+        # starts on the first cell of the box
+        rows = [j for j in range(lo[1], hi[1] + 1) if (st[0] != 0) or ((lo[0] + j + rb) % 2 == 0)]
+
+        def keep(arr):                                            # arr: (1, nz + 2, ny + 2, nx + 2) with one ghost layer
+            out = np.zeros_like(arr)
+            for j in rows:
+                out[:, :, j - (lo[1] - 1), :] = arr[:, :, j - (lo[1] - 1), :]
+            return out
+        st6 = (C.c_int * 6)(*st)
+        p = s.phi.copy()
+        _lib().orck_line_gsrb(p.raw(), s.ex.raw(), s.rhs.raw(), s.jg[0].raw(), s.jg[1].raw(), s.jg[2].raw(), s.jinv.raw(),
+                              _i3(lo), _i3(hi), _d3(s.dx), C.c_double(2.0 * s.dx[2]), C.c_double(alpha), C.c_double(beta), rb,
+                              st6, 3, int(not full))
+        out_o[key] = keep(p.a)
+        if ref:
+            q = s.phi.copy()
+            nz = hi[2] + 1
+            Dw, Bw = Fab(np.zeros((1, 1, 1, nz)), [1, 1, 1]), Fab(np.zeros((1, 1, 1, nz)), [1, 1, 1])
+            DUw, DLw = Fab(np.zeros((1, 1, 1, nz - 1)), [2, 1, 1]), Fab(np.zeros((1, 1, 1, nz - 1)), [1, 1, 1])
+            ref.linegsrbiter3d(q.fab(), s.ex.fab(), s.rhs.fab(), s.jg[0].fab(), s.jg[1].fab(), s.jg[2].fab(), s.jinv.fab(),
+                               _box(lo, hi), _vec(s.dx), 2.0 * s.dx[2], alpha, beta, rb, DUw, Dw, DLw, Bw, *st)
+            out_r[key] = keep(q.a)
     return out_o, out_r
 
 
